@@ -1,0 +1,613 @@
+"""CPU oracle for the femo_alpha Reissner-Mindlin shell hot path (NumPy/SciPy, fp64).
+
+TEST INFRASTRUCTURE ONLY.  Nothing in ``femo_alpha_b200/`` may import this
+module; only ``tests/``, ``__graft_entry__.smoke()`` and the ``cpu_baseline`` /
+``--impl reference`` legs of ``bench.py`` use it, and only as the checker.
+
+PARITY UNPINNED: the reference's arithmetic for this path lives in un-vendored
+third-party packages (fenics-ufl 2022.2.0, fenics-ffcx 0.5.0, fenics-basix
+0.5.0, fenics-dolfinx 0.5.1, petsc 3.17.3, mumps 5.2.1 -- pins at
+/root/reference/environment.yml:13-19,49-50,56-57), none of which can be
+imported here, and the reference's own tests (tests/test_pytest.py) hold no
+golden vector for it.  This file restates the *published* algorithm (UFL forms
+written out in the reference + dolfinx assembly/BC semantics) and is anchored
+on the weak pins the reference does hold: the Euler-Bernoulli tip deflection
+printed by examples/advanced_examples/simple_shell_opt/ex_simple_shell_opt.py:100-105
+and FD-vs-adjoint `check_totals`.
+
+What is restated (file:line relative to /root/reference/femo_alpha):
+  * kinematics   rm_shell/linear_shell_fenicsx/kinematics.py:12-106
+  * CLT          rm_shell/linear_shell_fenicsx/linear_shell_model.py:136-157
+  * strains      .../linear_shell_model.py:199-258
+  * energies     .../linear_shell_model.py:260-306
+  * residual     .../linear_shell_model.py:308-333 (incl. penalty BC)
+  * spaces/outs  rm_shell/rm_shell_pde.py:25-47,50-58,64-110
+  * BCs          rm_shell/rm_shell_model.py:83-98,168-180
+  * solve/adj    fea/utils_dolfinx.py:208-221,438-468,514-531,
+                 fea/fea_dolfinx.py:189-203, csdl_alpha_opt/state_operation.py:86-131,174-220
+
+Third-party semantics reproduced from their documentation (not from source in
+the tree): UFL manifold pull-back grad f = (df/dX) K with K = (J^T J)^-1 J^T;
+CellNormal = J[:,0] x J[:,1] / |.|; CellDiameter = max vertex distance; dolfinx
+quadrilateral reference cell [0,1]^2 with tensor vertex order; Gauss-Legendre
+tensor rule with m = (degree+2)//2 points; assemble_matrix(bcs) zeroes rows and
+columns and puts 1 on the diagonal.
+
+DOF numbering (ours; the reference's is dolfinx-internal and opaque to callers,
+SURVEY B12): 3x3 "block nodes": vertex v -> u-block 2v, theta-block 2v+1; edge e
+-> 2*nn+e; cell centre c -> 2*nn+ne+c.  dof = 3*block + component.
+"""
+from __future__ import annotations
+
+import numpy as np
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+SHEAR_K = 0.833          # linear_shell_model.py:149 ("from Nastran", not 5/6)
+BETA_PENALTY = 1.0e15    # linear_shell_model.py:324
+REG_ALPHA1 = 1.0e-2      # rm_shell_pde.py:67
+
+# ----------------------------------------------------------------------------
+# reference element tables (dolfinx quadrilateral: tensor vertex order)
+# local Q2 nodes: v0 v1 v2 v3 | e0(v0v1) e1(v0v2) e2(v1v3) e3(v2v3) | centre
+# ----------------------------------------------------------------------------
+Q2_IJ = np.array([(0, 0), (2, 0), (0, 2), (2, 2), (1, 0), (0, 1), (2, 1), (1, 2), (1, 1)])
+LOCAL_EDGES = np.array([(0, 1), (0, 2), (1, 3), (2, 3)])
+# Q2 local node ids on each local edge: (first vertex, mid, second vertex)
+EDGE_Q2 = np.array([(0, 4, 1), (0, 5, 2), (1, 6, 3), (2, 7, 3)])
+VTK_TO_TENSOR = np.array([0, 1, 3, 2])   # dolfinx io.cells.perm_vtk for quads
+
+
+def gauss01(m):
+    x, w = np.polynomial.legendre.leggauss(m)
+    return 0.5 * (x + 1.0), 0.5 * w
+
+
+def lag2(x):
+    """1-D quadratic Lagrange on nodes {0, 1/2, 1}: values and derivatives."""
+    v = np.array([2.0 * (x - 0.5) * (x - 1.0), 4.0 * x * (1.0 - x), 2.0 * x * (x - 0.5)])
+    d = np.array([4.0 * x - 3.0, 4.0 - 8.0 * x, 4.0 * x - 1.0])
+    return v, d
+
+
+def basis_q1(X0, X1):
+    N = np.array([(1 - X0) * (1 - X1), X0 * (1 - X1), (1 - X0) * X1, X0 * X1])
+    dN = np.array([[-(1 - X1), -(1 - X0)], [(1 - X1), -X0], [-X1, (1 - X0)], [X1, X0]])
+    return N, dN
+
+
+def basis_q2(X0, X1):
+    v0, d0 = lag2(X0)
+    v1, d1 = lag2(X1)
+    phi = np.array([v0[i] * v1[j] for i, j in Q2_IJ])
+    dphi = np.array([[d0[i] * v1[j], v0[i] * d1[j]] for i, j in Q2_IJ])
+    return phi, dphi
+
+
+def skew(v):
+    """[v]x so that skew(v) @ a = v x a; v has shape (...,3)."""
+    z = np.zeros_like(v[..., 0])
+    return np.stack([np.stack([z, -v[..., 2], v[..., 1]], -1),
+                     np.stack([v[..., 2], z, -v[..., 0]], -1),
+                     np.stack([-v[..., 1], v[..., 0], z], -1)], -2)
+
+
+# ----------------------------------------------------------------------------
+# topology / dofmap
+# ----------------------------------------------------------------------------
+class ShellTopology:
+    """Q2xQ1 block-node numbering of a quad surface mesh (possibly non-manifold).
+
+    `quads` are in VTK/meshio cyclic vertex order, the order
+    fea/utils_dolfinx.py:653-668 (reconstructFEAMesh) hands to dolfinx.
+    """
+
+    def __init__(self, nodes, quads):
+        self.x = np.ascontiguousarray(nodes, dtype=np.float64)
+        quads = np.asarray(quads).astype(np.int64)
+        self.nn = self.x.shape[0]
+        self.nc = quads.shape[0]
+        self.cv = quads[:, VTK_TO_TENSOR]                      # tensor-ordered vertices
+        ev = np.sort(self.cv[:, LOCAL_EDGES], axis=2).reshape(-1, 2)
+        key = ev[:, 0] * self.nn + ev[:, 1]
+        ukey, inv = np.unique(key, return_inverse=True)
+        self.ne = ukey.size
+        self.edges = np.stack([ukey // self.nn, ukey % self.nn], 1)
+        self.ce = inv.reshape(self.nc, 4)                      # cell -> global edge ids
+        nn, ne, nc = self.nn, self.ne, self.nc
+        self.nb = 2 * nn + ne + nc
+        self.ndof = 3 * self.nb
+        cb = np.empty((nc, 13), dtype=np.int64)
+        cb[:, 0:4] = 2 * self.cv
+        cb[:, 4:8] = 2 * nn + self.ce
+        cb[:, 8] = 2 * nn + ne + np.arange(nc)
+        cb[:, 9:13] = 2 * self.cv + 1
+        self.cell_blocks = cb
+        self.cell_dofs = (3 * cb[:, :, None] + np.arange(3)[None, None, :]).reshape(nc, 39)
+        self.edge_ncells = np.bincount(self.ce.ravel(), minlength=ne)
+
+    def block_coords(self):
+        """Coordinates of every block node (dof coordinates of W.sub(0)/W.sub(1))."""
+        xc = np.empty((self.nb, 3))
+        xc[0:2 * self.nn:2] = self.x
+        xc[1:2 * self.nn:2] = self.x
+        xc[2 * self.nn:2 * self.nn + self.ne] = 0.5 * (self.x[self.edges[:, 0]] + self.x[self.edges[:, 1]])
+        xc[2 * self.nn + self.ne:] = self.x[self.cv].mean(axis=1)
+        return xc
+
+    def cell_diameter(self):
+        xv = self.x[self.cv]
+        d = np.linalg.norm(xv[:, :, None, :] - xv[:, None, :, :], axis=-1)
+        return d.reshape(self.nc, -1).max(axis=1)
+
+    # strong BC: locate_dofs_geometrical on W.sub(0), W.sub(1) (rm_shell_model.py:168-180)
+    def strong_bc_dofs(self, bc_func):
+        xc = self.block_coords()
+        on = np.asarray(bc_func(xc.T)).astype(bool)
+        blocks = np.nonzero(on)[0]
+        return np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel())
+
+    # penalty BC: facets whose vertices all satisfy bc_func (utils_dolfinx.py:555-565)
+    def penalty_edges(self, bc_func):
+        on = np.asarray(bc_func(self.x.T)).astype(bool)
+        sel = on[self.edges[:, 0]] & on[self.edges[:, 1]]
+        return np.nonzero(sel)[0]
+
+
+def plate_mesh(nx, ny, lx, ly, z_func=None):
+    """Structured quads on [0,lx]x[0,ly]; VTK cyclic connectivity (createRectangleMesh analogue)."""
+    xs = np.linspace(0.0, lx, nx + 1)
+    ys = np.linspace(0.0, ly, ny + 1)
+    X, Y = np.meshgrid(xs, ys, indexing="ij")
+    Z = np.zeros_like(X) if z_func is None else z_func(X, Y)
+    nodes = np.stack([X.ravel(), Y.ravel(), Z.ravel()], 1)
+    idx = np.arange((nx + 1) * (ny + 1)).reshape(nx + 1, ny + 1)
+    quads = np.stack([idx[:-1, :-1].ravel(), idx[1:, :-1].ravel(),
+                      idx[1:, 1:].ravel(), idx[:-1, 1:].ravel()], 1)
+    return nodes, quads
+
+
+# ----------------------------------------------------------------------------
+# per-quadrature-point geometry + strain operator
+# ----------------------------------------------------------------------------
+class QPData:
+    pass
+
+
+def qp_geometry(xv, uh, X0, X1):
+    """Geometry at one reference point for all cells.  xv, uh: (nc,4,3) tensor order."""
+    g = QPData()
+    N1, dN1 = basis_q1(X0, X1)
+    phi2, dphi2 = basis_q2(X0, X1)
+    g.N1, g.dN1, g.phi2, g.dphi2 = N1, dN1, phi2, dphi2
+    Jm = np.einsum("cvi,va->cia", xv, dN1)                       # dx/dX (3x2)
+    Gm = np.einsum("cia,cib->cab", Jm, Jm)
+    g.detJ = np.sqrt(np.linalg.det(Gm))                          # surface measure
+    Kinv = np.einsum("cab,cib->cai", np.linalg.inv(Gm), Jm)      # pseudo-inverse (2x3)
+    a0, a1 = Jm[:, :, 0], Jm[:, :, 1]
+    n = np.cross(a0, a1)
+    nl = np.linalg.norm(n, axis=1)
+    g.E2 = n / nl[:, None]                                       # kinematics.py:65 CellNormal
+    g.E0 = a0 / np.linalg.norm(a0, axis=1)[:, None]              # kinematics.py:66-67
+    g.E1 = np.cross(g.E2, g.E0)                                  # kinematics.py:68
+    g.T = np.stack([g.E0, g.E1], 1)                              # kinematics.py:72-82
+    # X-dependence of the normal on bilinear quads (UFL differentiates CellNormal
+    # on non-affine cells; zero on planar cells)
+    c = xv[:, 0] - xv[:, 1] - xv[:, 2] + xv[:, 3]                # d2x/dX0dX1
+    dn = np.stack([np.cross(a0, c), np.cross(c, a1)], 1)         # (nc,2,3)
+    g.dE2 = (dn - g.E2[:, None, :] * np.einsum("cai,ci->ca", dn, g.E2)[:, :, None]) / nl[:, None, None]
+    gradu_hat = np.einsum("cia,caj->cij", np.einsum("cvi,va->cia", uh, dN1), Kinv)
+    F = np.eye(3)[None] + gradu_hat                              # kinematics.py:34-44
+    g.Ju = np.linalg.det(F)                                      # kinematics.py:24-32
+    g.Finv = np.linalg.inv(F)
+    g.Kx = np.einsum("cai,cij->caj", Kinv, g.Finv)               # gradx(f) = (df/dX) Kx
+    g.Kinv = Kinv
+    g.a0, g.a1 = a0, a1
+    return g
+
+
+def strain_operator(g):
+    """B (nc,9,39): rows [eps00, eps11, 2eps01, kap00, kap11, 2kap01, gam0, gam1, drill].
+
+    Built by pushing the 39 unit DOF vectors through the reference's strain
+    definitions (linear_shell_model.py:220-258,288-289) literally.
+    """
+    nc = g.Kx.shape[0]
+    U = np.zeros((3, 39)); dU = np.zeros((3, 2, 39))
+    Th = np.zeros((3, 39)); dTh = np.zeros((3, 2, 39))
+    for a in range(9):
+        for i in range(3):
+            U[i, 3 * a + i] = g.phi2[a]
+            dU[i, :, 3 * a + i] = g.dphi2[a]
+    for b in range(4):
+        for i in range(3):
+            Th[i, 27 + 3 * b + i] = g.N1[b]
+            dTh[i, :, 27 + 3 * b + i] = g.dN1[b]
+    gradx_u = np.einsum("iap,caj->cijp", dU, g.Kx)               # model:220
+    t_gu = np.einsum("cki,cijp,clj->cklp", g.T, gradx_u, g.T)    # model:222 / kin:84-91
+    S2 = skew(g.E2)                                              # cross(E2, .)
+    beta = np.einsum("cij,jp->cip", S2, Th)
+    dbeta = np.stack([np.einsum("cij,jp->cip", skew(g.dE2[:, a]), Th)
+                      + np.einsum("cij,jp->cip", S2, dTh[:, a, :]) for a in range(2)], 2)  # (nc,3,2,39)
+    gradx_b = np.einsum("ciap,caj->cijp", dbeta, g.Kx)
+    kap = np.einsum("cki,cijp,clj->cklp", g.T, gradx_b, g.T)
+    kap = 0.5 * (kap + kap.transpose(0, 2, 1, 3))                # model:241-243
+    eps = 0.5 * (t_gu + t_gu.transpose(0, 2, 1, 3))              # model:232-239 (offset = 0)
+    gam = np.einsum("ckj,cjp->ckp", g.T, -beta + np.einsum("ci,cijp->cjp", g.E2, gradx_u))  # model:245-258
+    drill = 0.5 * (t_gu[:, 0, 1] - t_gu[:, 1, 0]) + np.einsum("ip,ci->cp", Th, g.E2)       # model:288-289
+    B = np.stack([eps[:, 0, 0], eps[:, 1, 1], 2 * eps[:, 0, 1],
+                  kap[:, 0, 0], kap[:, 1, 1], 2 * kap[:, 0, 1],
+                  gam[:, 0], gam[:, 1], drill], 1)
+    assert B.shape == (nc, 9, 39)
+    return B
+
+
+def clt_matrix(h, E, nu, hE, Ju, mode="value"):
+    """Block-diagonal constitutive matrix D (nc,9,9) or its partial wrt h / E / nu.
+
+    model:136-157 (A = hC, B = 0, D = h^3/12 C, A_s = k G h I), drilling
+    alpha = E h^3 / h_E^2 (model:284-296); shear and drilling carry J(uhat),
+    membrane and bending do not.
+    """
+    nc = h.shape[0]
+
+    def Cmat(E, nu):
+        c = E / (1 - nu * nu)
+        C = np.zeros((nc, 3, 3))
+        C[:, 0, 0] = c; C[:, 1, 1] = c; C[:, 0, 1] = c * nu; C[:, 1, 0] = c * nu
+        C[:, 2, 2] = c * 0.5 * (1 - nu)
+        return C
+
+    D = np.zeros((nc, 9, 9))
+    if mode == "value":
+        C = Cmat(E, nu); G = E / 2 / (1 + nu)
+        D[:, 0:3, 0:3] = h[:, None, None] * C
+        D[:, 3:6, 3:6] = (h ** 3 / 12)[:, None, None] * C
+        D[:, 6, 6] = D[:, 7, 7] = SHEAR_K * G * h * Ju
+        D[:, 8, 8] = E * h ** 3 / hE ** 2 * Ju
+    elif mode == "dh":
+        C = Cmat(E, nu); G = E / 2 / (1 + nu)
+        D[:, 0:3, 0:3] = C
+        D[:, 3:6, 3:6] = (h ** 2 / 4)[:, None, None] * C
+        D[:, 6, 6] = D[:, 7, 7] = SHEAR_K * G * Ju
+        D[:, 8, 8] = 3 * E * h ** 2 / hE ** 2 * Ju
+    elif mode == "dE":
+        C = Cmat(np.ones_like(E), nu); G = 1.0 / 2 / (1 + nu)
+        D[:, 0:3, 0:3] = h[:, None, None] * C
+        D[:, 3:6, 3:6] = (h ** 3 / 12)[:, None, None] * C
+        D[:, 6, 6] = D[:, 7, 7] = SHEAR_K * G * h * Ju
+        D[:, 8, 8] = h ** 3 / hE ** 2 * Ju
+    elif mode == "dnu":
+        c = E / (1 - nu * nu)
+        dc = 2 * E * nu / (1 - nu * nu) ** 2
+        dC = np.zeros((nc, 3, 3))
+        dC[:, 0, 0] = dc; dC[:, 1, 1] = dc
+        dC[:, 0, 1] = dC[:, 1, 0] = dc * nu + c
+        dC[:, 2, 2] = dc * 0.5 * (1 - nu) - 0.5 * c
+        dG = -E / 2 / (1 + nu) ** 2
+        D[:, 0:3, 0:3] = h[:, None, None] * dC
+        D[:, 3:6, 3:6] = (h ** 3 / 12)[:, None, None] * dC
+        D[:, 6, 6] = D[:, 7, 7] = SHEAR_K * dG * h * Ju
+    else:
+        raise ValueError(mode)
+    return D
+
+
+class RMShellOracle:
+    """Assembled RM-shell problem on the CPU (the checker for the CUDA path)."""
+
+    def __init__(self, nodes, quads, element_wise_material=False, elementwise_pressure=False,
+                 quadrature_degree=6):
+        self.topo = ShellTopology(nodes, quads)
+        self.ewm = bool(element_wise_material)
+        self.ewp = bool(elementwise_pressure)
+        self.m = (quadrature_degree + 2) // 2
+        gx, gw = gauss01(self.m)
+        self.qp = [(gx[i], gx[j], gw[i] * gw[j]) for i in range(self.m) for j in range(self.m)]
+        t = self.topo
+        self.n_mat = t.nc if self.ewm else t.nn
+        self.n_f = 3 * (t.nc if self.ewp else t.nn)
+        self.hE = t.cell_diameter()
+        # inputs (rm_shell_model.py:209-214 initial values)
+        self.h = np.full(self.n_mat, 1e-3)
+        self.E = np.ones(self.n_mat)
+        self.nu = np.ones(self.n_mat) * 0.3
+        self.rho = np.ones(self.n_mat)
+        self.f = np.ones(self.n_f)
+        self.uhat = np.zeros(3 * t.nn)
+        self.bc_dofs = np.zeros(0, dtype=np.int64)
+        self.pen_edges = np.zeros(0, dtype=np.int64)
+
+    # ---- inputs -------------------------------------------------------
+    def set_inputs(self, thickness=None, E=None, nu=None, density=None, F_solid=None, uhat=None):
+        def put(dst, v):
+            v = np.asarray(v, dtype=np.float64).ravel()
+            dst[:] = v if v.size > 1 else v[0]          # utils_dolfinx.py:319-330 `update`
+        if thickness is not None: put(self.h, thickness)
+        if E is not None: put(self.E, E)
+        if nu is not None: put(self.nu, nu)
+        if density is not None: put(self.rho, density)
+        if F_solid is not None: put(self.f, F_solid)
+        if uhat is not None: put(self.uhat, uhat)
+
+    def set_strong_bc(self, bc_func):
+        self.bc_dofs = self.topo.strong_bc_dofs(bc_func)
+
+    def set_penalty_bc(self, bc_func):
+        self.pen_edges = self.topo.penalty_edges(bc_func)
+
+    # ---- coefficient evaluation at a quadrature point ------------------
+    def _mat_at(self, arr, N1):
+        t = self.topo
+        return arr.copy() if self.ewm else arr[t.cv] @ N1
+
+    def _f_at(self, N1):
+        t = self.topo
+        f3 = self.f.reshape(-1, 3)
+        return f3.copy() if self.ewp else np.einsum("cvi,v->ci", f3[t.cv], N1)
+
+    # ---- element loops -------------------------------------------------
+    def element_matrices(self, mode="value"):
+        """K_e (nc,39,39) [mode='value'] or sum_q (dD/dp)-weighted B^T D' B without the nodal weight."""
+        t = self.topo
+        xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+        Ke = np.zeros((t.nc, 39, 39))
+        for X0, X1, w in self.qp:
+            g = qp_geometry(xv, uh, X0, X1)
+            B = strain_operator(g)
+            D = clt_matrix(self._mat_at(self.h, g.N1), self._mat_at(self.E, g.N1),
+                           self._mat_at(self.nu, g.N1), self.hE, g.Ju, mode)
+            Ke += np.einsum("c,csp,cst,ctq->cpq", w * g.detJ, B, D, B)
+        return Ke
+
+    def element_loads(self):
+        t = self.topo
+        xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+        Fe = np.zeros((t.nc, 39))
+        for X0, X1, w in self.qp:
+            g = qp_geometry(xv, uh, X0, X1)
+            fq = self._f_at(g.N1)
+            Fe[:, :27] += (w * g.detJ * g.Ju)[:, None] * np.einsum("a,ci->cai", g.phi2, fq).reshape(t.nc, 27)
+        return Fe
+
+    def element_param_action(self, wvec, mode):
+        """(dR_e/dp_b) for nodal (or cell) parameter p in {h,E,nu}: (nc,39,nb) with nb=4 (CG1) or 1 (DG0)."""
+        t = self.topo
+        xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+        we = wvec[t.cell_dofs]
+        nb = 1 if self.ewm else 4
+        out = np.zeros((t.nc, 39, nb))
+        for X0, X1, w in self.qp:
+            g = qp_geometry(xv, uh, X0, X1)
+            B = strain_operator(g)
+            D = clt_matrix(self._mat_at(self.h, g.N1), self._mat_at(self.E, g.N1),
+                           self._mat_at(self.nu, g.N1), self.hE, g.Ju, mode)
+            r = np.einsum("c,csp,cst,ctq,cq->cp", w * g.detJ, B, D, B, we)
+            wt = np.ones(1) if self.ewm else g.N1
+            out += r[:, :, None] * wt[None, None, :]
+        return out
+
+    # ---- penalty BC (linear_shell_model.py:323-333) --------------------
+    def penalty_matrix(self):
+        t = self.topo
+        n = t.ndof
+        if self.pen_edges.size == 0:
+            return sp.csr_matrix((n, n))
+        gx, gw = gauss01(3)                       # degree-4 facet measure (utils_dolfinx.py:556)
+        sel = np.zeros(t.ne, dtype=bool); sel[self.pen_edges] = True
+        rows, cols, vals = [], [], []
+        uh3 = self.uhat.reshape(-1, 3)
+        # reference coordinates along each local edge, parameter s in [0,1]
+        def edge_point(le, s):
+            return [(s, 0.0), (0.0, s), (1.0, s), (s, 1.0)][le]
+        for le in range(4):
+            cells = np.nonzero(sel[t.ce[:, le]])[0]
+            if cells.size == 0:
+                continue
+            # ds: exterior facets once; dS: '+' and '-' sides, each with own h_E.  Edges
+            # shared by >2 cells (unspecified in dolfinx): every adjacent cell contributes.
+            xv = t.x[t.cv[cells]]; uh = uh3[t.cv[cells]]
+            va, vb = LOCAL_EDGES[le]
+            tvec = xv[:, vb] - xv[:, va]
+            L = np.linalg.norm(tvec, axis=1)
+            Me = np.zeros((cells.size, 5, 5))     # trace nodes: q2(va), q2(mid), q2(vb), q1(va), q1(vb)
+            for s, ws in zip(gx, gw):
+                X0, X1 = edge_point(le, s)
+                g = qp_geometry(xv, uh, X0, X1)
+                Nf = np.cross(tvec / L[:, None], g.E2)          # in-surface facet normal (sign irrelevant)
+                nanson = g.Ju[:, None] * np.einsum("cji,cj->ci", g.Finv, Nf)
+                sc = np.linalg.norm(nanson, axis=1)
+                l2, _ = lag2(s)
+                tr = np.array([l2[0], l2[1], l2[2], 1 - s, s])
+                # Q2/Q1 traces never couple (u-u and theta-theta only: inner(w, dw))
+                M = np.outer(tr, tr); M[:3, 3:] = 0; M[3:, :3] = 0
+                Me += (ws * L * sc * BETA_PENALTY / self.hE[cells])[:, None, None] * M[None]
+            q2 = EDGE_Q2[le]
+            blocks = np.stack([t.cell_blocks[cells, q2[0]], t.cell_blocks[cells, q2[1]],
+                               t.cell_blocks[cells, q2[2]], t.cell_blocks[cells, 9 + va],
+                               t.cell_blocks[cells, 9 + vb]], 1)
+            for i in range(5):
+                for j in range(5):
+                    for cpt in range(3):
+                        rows.append(3 * blocks[:, i] + cpt); cols.append(3 * blocks[:, j] + cpt)
+                        vals.append(Me[:, i, j])
+        P = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(n, n))
+        P = P.tocsr(); P.eliminate_zeros()
+        return P
+
+    # ---- global assembly -------------------------------------------------
+    def _scatter_matrix(self, Ke):
+        t = self.topo
+        rows = np.repeat(t.cell_dofs, 39, axis=1).ravel()
+        cols = np.tile(t.cell_dofs, (1, 39)).ravel()
+        K = sp.coo_matrix((Ke.ravel(), (rows, cols)), shape=(t.ndof, t.ndof)).tocsr()
+        K.sum_duplicates()
+        return K
+
+    def assemble_dRdu(self, with_penalty=True):
+        """assembleMatrix(dR_du) without BCs (state_operation.py:289)."""
+        K = self._scatter_matrix(self.element_matrices())
+        if with_penalty and self.pen_edges.size:
+            K = (K + self.penalty_matrix()).tocsr()
+        return K
+
+    def assemble_load(self):
+        t = self.topo
+        F = np.zeros(t.ndof)
+        np.add.at(F, t.cell_dofs.ravel(), self.element_loads().ravel())
+        return F
+
+    def assemble_residual(self, w):
+        """assembleVector(R) (utils_dolfinx.py:194-198): R = dPi/dw + penalty - load."""
+        return self.assemble_dRdu() @ w - self.assemble_load()
+
+    def apply_bc_matrix(self, K):
+        """dolfinx assemble_matrix(a, bcs): zero BC rows+cols, 1 on the diagonal (utils_dolfinx.py:208-221)."""
+        if self.bc_dofs.size == 0:
+            return K.tocsr()
+        n = K.shape[0]
+        keep = np.ones(n); keep[self.bc_dofs] = 0.0
+        Dk = sp.diags(keep)
+        A = Dk @ K @ Dk + sp.diags(1.0 - keep)
+        return A.tocsr()
+
+    def solve_state(self):
+        """fea.solve (fea_dolfinx.py:159-170): Newton on a linear problem == one linear solve."""
+        K = self.assemble_dRdu()
+        F = self.assemble_load()
+        A = self.apply_bc_matrix(K)
+        b = F.copy(); b[self.bc_dofs] = 0.0       # homogeneous Dirichlet values
+        self.A = A
+        self.lu = spla.splu(A.tocsc())
+        self.w = self.lu.solve(b)
+        return self.w
+
+    def solve_adjoint(self, rhs):
+        """apply_inverse_jacobian('rev') (state_operation.py:206-218): A symmetric; BC entries zeroed."""
+        lam = self.lu.solve(np.asarray(rhs, dtype=np.float64))
+        lam[self.bc_dofs] = 0.0
+        return lam
+
+    # ---- partials of the residual (state_operation.py:282-286) -----------
+    def assemble_dRdparam(self, w, mode):
+        t = self.topo
+        act = self.element_param_action(w, mode)            # (nc,39,nb)
+        nbp = act.shape[2]
+        pcols = (np.arange(t.nc)[:, None] if self.ewm else t.cv)
+        rows = np.repeat(t.cell_dofs, nbp, axis=1).ravel()
+        cols = np.tile(pcols, (1, 39)).ravel()
+        M = sp.coo_matrix((act.ravel(), (rows, cols)), shape=(t.ndof, self.n_mat)).tocsr()
+        return M
+
+    def assemble_dRdf(self):
+        """dR/dF_solid = -int J phi2_a phi_f (constant rectangular matrix)."""
+        t = self.topo
+        xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+        nbp = 1 if self.ewp else 4
+        Me = np.zeros((t.nc, 9, nbp))
+        for X0, X1, w in self.qp:
+            g = qp_geometry(xv, uh, X0, X1)
+            wt = np.ones(1) if self.ewp else g.N1
+            Me -= (w * g.detJ * g.Ju)[:, None, None] * np.outer(g.phi2, wt)[None]
+        pn = (np.arange(t.nc)[:, None] if self.ewp else t.cv)
+        rows, cols, vals = [], [], []
+        for i in range(3):
+            rows.append(np.repeat(3 * t.cell_blocks[:, :9] + i, nbp, axis=1).ravel())
+            cols.append(np.tile(3 * pn + i, (1, 9)).ravel())
+            vals.append(Me.ravel())
+        return sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))),
+                             shape=(t.ndof, self.n_f)).tocsr()
+
+    # ---- outputs (rm_shell_pde.py:64-110) -----------------------------------
+    def _mass_uu_action(self, w):
+        """(int phi_a phi_b J detJ) u, on the u-blocks only."""
+        t = self.topo
+        xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+        Me = np.zeros((t.nc, 9, 9))
+        for X0, X1, wq in self.qp:
+            g = qp_geometry(xv, uh, X0, X1)
+            Me += (wq * g.detJ * g.Ju)[:, None, None] * np.outer(g.phi2, g.phi2)[None]
+        ue = w[t.cell_dofs[:, :27]].reshape(t.nc, 9, 3)
+        re = np.einsum("cab,cbi->cai", Me, ue)
+        out = np.zeros(t.ndof)
+        np.add.at(out, t.cell_dofs[:, :27].ravel(), re.ravel())
+        return out
+
+    def _reg(self):
+        """regularization (rm_shell_pde.py:64-83): 'L2' for DG0 thickness, 'H1' for CG1; returns (value, d/dh)."""
+        t = self.topo
+        xv = t.x[t.cv]
+        zero = np.zeros_like(xv)
+        val = 0.0; grad = np.zeros(self.n_mat)
+        for X0, X1, wq in self.qp:
+            g = qp_geometry(xv, zero, X0, X1)
+            if self.ewm:
+                val += 0.5 * REG_ALPHA1 * np.sum(wq * g.detJ * self.h ** 2)
+                grad += REG_ALPHA1 * wq * g.detJ * self.h
+            else:
+                gN = np.einsum("va,cai->cvi", g.dN1, g.Kinv)          # grad of CG1 basis (no uhat: plain grad)
+                gh = np.einsum("cvi,cv->ci", gN, self.h[t.cv])
+                val += 0.5 * REG_ALPHA1 * np.sum(wq * g.detJ * np.einsum("ci,ci->c", gh, gh))
+                np.add.at(grad, t.cv.ravel(),
+                          (REG_ALPHA1 * (wq * g.detJ)[:, None] * np.einsum("cvi,ci->cv", gN, gh)).ravel())
+        return val, grad
+
+    def compliance(self, w):
+        return float(w @ self._mass_uu_action(w)) + self._reg()[0]        # pde:85-89 (int u.u J dx + reg)
+
+    def dcompliance_du(self, w):
+        return 2.0 * self._mass_uu_action(w)
+
+    def dcompliance_dh(self):
+        return self._reg()[1]
+
+    def _param_weight_integrals(self, coef_at):
+        """int coef * phi_b J dx per material node (or cell)."""
+        t = self.topo
+        xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+        out = np.zeros(self.n_mat); tot = 0.0
+        for X0, X1, wq in self.qp:
+            g = qp_geometry(xv, uh, X0, X1)
+            c = coef_at(g.N1) * wq * g.detJ * g.Ju
+            if self.ewm:
+                out += c
+            else:
+                np.add.at(out, t.cv.ravel(), (c[:, None] * g.N1[None, :]).ravel())
+        return out
+
+    def mass(self):
+        t = self.topo
+        xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+        tot = 0.0
+        for X0, X1, wq in self.qp:
+            g = qp_geometry(xv, uh, X0, X1)
+            tot += np.sum(self._mat_at(self.rho, g.N1) * self._mat_at(self.h, g.N1) * wq * g.detJ * g.Ju)
+        return float(tot)                                                  # pde:101-102
+
+    def dmass_dh(self):
+        return self._param_weight_integrals(lambda N1: self._mat_at(self.rho, N1))
+
+    def dmass_drho(self):
+        return self._param_weight_integrals(lambda N1: self._mat_at(self.h, N1))
+
+    def elastic_energy(self, w):
+        K = self._scatter_matrix(self.element_matrices())                  # no penalty (pde:107-110)
+        return 0.5 * float(w @ (K @ w))
+
+    def delastic_energy_du(self, w):
+        return self._scatter_matrix(self.element_matrices()) @ w
+
+    def delastic_energy_dparam(self, w, mode):
+        return 0.5 * (self.assemble_dRdparam(w, mode).T @ w)
+
+    def disp_extracted(self, w):
+        """u_mid at mesh vertices, external node order (rm_shell_model.py:505-527)."""
+        t = self.topo
+        return w.reshape(-1, 3)[0:2 * t.nn:2].copy()
+
+    # ---- total derivative via adjoint ------------------------
+    def total_dcompliance_dh(self):
+        w = self.w
+        lam = self.solve_adjoint(self.dcompliance_du(w))
+        dRdh = self.assemble_dRdparam(w, "dh")
+        return self.dcompliance_dh() - dRdh.T @ lam
