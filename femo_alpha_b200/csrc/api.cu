@@ -1,0 +1,528 @@
+// extern "C" surface of libfemo_b200.so (see include/femo_b200.h) + context management.
+#include <cmath>
+#include <cstring>
+#include "femo_internal.cuh"
+
+static thread_local std::string g_err;
+void femo_set_error(const std::string& s) { g_err = s; }
+int femo_fail(const std::string& s) { g_err = s; return 1; }
+
+int check_launch(femo_ctx* c, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return femo_fail(std::string(what) + ": " + cudaGetErrorString(e));
+  (void)c;
+  return 0;
+}
+
+namespace {
+
+struct DevGuard {
+  int prev = 0;
+  explicit DevGuard(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); }
+  ~DevGuard() { cudaSetDevice(prev); }
+};
+
+void gauss01(int m, double* x, double* w) {
+  // Gauss-Legendre on [0,1] by Newton iteration on P_m
+  for (int i = 0; i < m; ++i) {
+    double z = cos(M_PI * (i + 0.75) / (m + 0.5)), pp = 1;
+    for (int it = 0; it < 100; ++it) {
+      double p1 = 1, p2 = 0;
+      for (int j = 0; j < m; ++j) { double p3 = p2; p2 = p1; p1 = ((2.0 * j + 1.0) * z * p2 - j * p3) / (j + 1.0); }
+      pp = m * (z * p1 - p2) / (z * z - 1.0);
+      double dz = p1 / pp;
+      z -= dz;
+      if (fabs(dz) < 1e-16) break;
+    }
+    x[m - 1 - i] = 0.5 * (z + 1.0);
+    w[m - 1 - i] = 1.0 / ((1.0 - z * z) * pp * pp);
+  }
+}
+
+void lag2(double x, double* v, double* d) {
+  v[0] = 2.0 * (x - 0.5) * (x - 1.0); v[1] = 4.0 * x * (1.0 - x); v[2] = 2.0 * x * (x - 0.5);
+  d[0] = 4.0 * x - 3.0; d[1] = 4.0 - 8.0 * x; d[2] = 4.0 * x - 1.0;
+}
+
+void build_tables(Tables& T, int m) {
+  static const int IJ[9][2] = {{0, 0}, {2, 0}, {0, 2}, {2, 2}, {1, 0}, {0, 1}, {2, 1}, {1, 2}, {1, 1}};
+  memset(&T, 0, sizeof(T));
+  T.m = m; T.nq = m * m;
+  double gx[FEMO_MAX_Q1D], gw[FEMO_MAX_Q1D];
+  gauss01(m, gx, gw);
+  for (int i = 0; i < m; ++i)
+    for (int j = 0; j < m; ++j) {
+      int q = i * m + j;
+      double X0 = gx[i], X1 = gx[j];
+      T.X0[q] = X0; T.X1[q] = X1; T.W[q] = gw[i] * gw[j];
+      double v0[3], d0[3], v1[3], d1[3];
+      lag2(X0, v0, d0); lag2(X1, v1, d1);
+      for (int a = 0; a < 9; ++a) {
+        T.phi2[q][a] = v0[IJ[a][0]] * v1[IJ[a][1]];
+        T.dphi2[q][a][0] = d0[IJ[a][0]] * v1[IJ[a][1]];
+        T.dphi2[q][a][1] = v0[IJ[a][0]] * d1[IJ[a][1]];
+      }
+      double N[4] = {(1 - X0) * (1 - X1), X0 * (1 - X1), (1 - X0) * X1, X0 * X1};
+      double dN[4][2] = {{-(1 - X1), -(1 - X0)}, {(1 - X1), -X0}, {-X1, (1 - X0)}, {X1, X0}};
+      for (int v = 0; v < 4; ++v) { T.n1[q][v] = N[v]; T.dn1[q][v][0] = dN[v][0]; T.dn1[q][v][1] = dN[v][1]; }
+    }
+}
+
+__global__ void k_fill(double* p, int64_t n, double v) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+__global__ void k_mask_clear(double* mask, const int32_t* dofs, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) mask[dofs[i]] = 0.0;
+}
+__global__ void k_mul(const double* a, const double* m, int64_t n, double* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = a[i] * m[i];
+}
+__global__ void k_axpby(double a, const double* x, double b, const double* y, int64_t n, double* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = a * x[i] + b * y[i];
+}
+__global__ void k_block_coords(const double* xyz, const int32_t* edges, const int32_t* cv, int64_t nn, int64_t ne,
+                               int64_t nc, double* out) {
+  int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int64_t nq2 = nn + ne + nc;
+  if (I >= nq2 + nn) return;
+  V3 p;
+  if (I < nn) p = ldv3(xyz + 3 * I);
+  else if (I < nn + ne) {
+    int64_t e = I - nn;
+    p = 0.5 * (ldv3(xyz + 3 * (int64_t)edges[2 * e]) + ldv3(xyz + 3 * (int64_t)edges[2 * e + 1]));
+  } else if (I < nq2) {
+    int64_t c = I - nn - ne;
+    p = 0.25 * (ldv3(xyz + 3 * (int64_t)cv[4 * c]) + ldv3(xyz + 3 * (int64_t)cv[4 * c + 1]) +
+                ldv3(xyz + 3 * (int64_t)cv[4 * c + 2]) + ldv3(xyz + 3 * (int64_t)cv[4 * c + 3]));
+  } else p = ldv3(xyz + 3 * (I - nq2));
+  out[3 * I] = p.x; out[3 * I + 1] = p.y; out[3 * I + 2] = p.z;
+}
+__global__ void k_bsr_apply_bc(const int32_t* rowptr, const int32_t* colidx, const double* mask, int64_t nb, double* vals) {
+  int64_t row = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (row >= nb) return;
+  for (int32_t k = rowptr[row]; k < rowptr[row + 1]; ++k) {
+    int64_t col = colidx[k];
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) {
+        double mi = mask[3 * row + i], mj = mask[3 * col + j];
+        double v = mi * mj * vals[(int64_t)k * 9 + 3 * i + j];
+        if (row == col && i == j) v += 1.0 - mi;
+        vals[(int64_t)k * 9 + 3 * i + j] = v;
+      }
+  }
+}
+
+int fill(femo_ctx* c, double* p, int64_t n, double v) {
+  k_fill<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(p, n, v);
+  c->launches += 1;
+  return check_launch(c, "k_fill");
+}
+
+double** input_slot(femo_ctx* c, int which, int64_t* n) {
+  switch (which) {
+    case FEMO_THICKNESS: *n = c->n_mat; return &c->h;
+    case FEMO_E: *n = c->n_mat; return &c->E;
+    case FEMO_NU: *n = c->n_mat; return &c->nu;
+    case FEMO_DENSITY: *n = c->n_mat; return &c->rho;
+    case FEMO_F_SOLID: *n = c->n_f; return &c->f;
+    case FEMO_UHAT: *n = 3 * c->nn; return &c->uhat;
+  }
+  return nullptr;
+}
+
+// copy a caller vector (host or device) into a device buffer / back
+int copy_in(femo_ctx* c, double* dst, const double* src, int64_t n, int on_device) {
+  CUDA_TRY(cudaMemcpyAsync(dst, src, sizeof(double) * n, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+int copy_out(femo_ctx* c, double* dst, const double* src, int64_t n, int on_device) {
+  CUDA_TRY(cudaMemcpyAsync(dst, src, sizeof(double) * n, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+#define NEED_SETUP(c, name) \
+  if (!(c) || !(c)->setup_done) return femo_fail(std::string(name) + ": context not set up (femo_mesh_set + femo_shell_setup)")
+
+}  // namespace
+
+extern "C" {
+
+const char* femo_last_error(void) { return g_err.c_str(); }
+int femo_version(void) { return 100; }
+
+int femo_ctx_create(int device, femo_ctx** out) {
+  if (!out) return femo_fail("femo_ctx_create: null output pointer");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return femo_fail(std::string("femo_ctx_create: no CUDA device available (") + cudaGetErrorString(e) +
+                     "); libfemo_b200 has no CPU fallback");
+  if (device < 0 || device >= ndev) return femo_fail("femo_ctx_create: bad device index");
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return femo_fail("femo_ctx_create: libfemo_b200 is built for sm_100a (Blackwell) only");
+  femo_ctx* c = new femo_ctx();
+  c->device = device;
+  DevGuard g(device);
+  CUDA_TRY(cudaEventCreate(&c->ev0));
+  CUDA_TRY(cudaEventCreate(&c->ev1));
+  *out = c;
+  return 0;
+}
+
+int femo_ctx_destroy(femo_ctx* c) {
+  if (!c) return 0;
+  DevGuard g(c->device);
+  cudaStreamSynchronize(c->stream);
+  void* ptrs[] = {c->xyz, c->cv, c->ce, c->edges, c->cell_blocks, c->hE, c->tab, c->h, c->E, c->nu, c->rho, c->f, c->uhat,
+                  c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
+                  c->nc_adj, c->rec, c->bcmask, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
+                  c->pen_val, c->pen_dest_col, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
+                  c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  delete c;
+  return 0;
+}
+
+int femo_set_stream(femo_ctx* c, void* s) {
+  if (!c) return femo_fail("null context");
+  c->stream = (cudaStream_t)s;
+  return 0;
+}
+
+int femo_mesh_set(femo_ctx* c, int64_t n_nodes, const double* xyz, int64_t n_cells, int npc, const int32_t* conn) {
+  if (!c) return femo_fail("null context");
+  if (npc == 3) return femo_fail("femo_mesh_set: triangles (P2xP1) are not implemented; quadrilaterals only");
+  if (npc != 4) return femo_fail("femo_mesh_set: nodes_per_cell must be 4");
+  if (n_nodes <= 0 || n_cells <= 0 || !xyz || !conn) return femo_fail("femo_mesh_set: empty mesh");
+  DevGuard g(c->device);
+  c->nn = n_nodes; c->nc = n_cells; c->setup_done = false; c->jac_valid = false;
+  TRY(dev_alloc(&c->xyz, (size_t)n_nodes * 3));
+  CUDA_TRY(cudaMemcpy(c->xyz, xyz, sizeof(double) * n_nodes * 3, cudaMemcpyHostToDevice));
+  return topo_build(c, conn);
+}
+
+int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
+  if (!c || c->nc == 0) return femo_fail("femo_shell_setup: set the mesh first");
+  DevGuard g(c->device);
+  femo_shell_opts d = {0, 0, 6, 0};
+  if (o) d = *o;
+  int deg = d.quadrature_degree > 0 ? d.quadrature_degree : 6;
+  int m = (deg + 2) / 2;
+  if (m < 1 || m > FEMO_MAX_Q1D) return femo_fail("femo_shell_setup: quadrature_degree must be in [1, 9]");
+  c->ewm = d.element_wise_material ? 1 : 0;
+  c->ewp = d.elementwise_pressure ? 1 : 0;
+  c->m1d = m; c->nq = m * m;
+  build_tables(c->htab, m);
+  TRY(dev_alloc(&c->tab, 1));
+  CUDA_TRY(cudaMemcpy(c->tab, &c->htab, sizeof(Tables), cudaMemcpyHostToDevice));
+  TRY(pattern_build(c));
+  c->n_mat = c->ewm ? c->nc : c->nn;
+  c->n_f = 3 * (c->ewp ? c->nc : c->nn);
+  TRY(dev_alloc(&c->h, c->n_mat)); TRY(dev_alloc(&c->E, c->n_mat)); TRY(dev_alloc(&c->nu, c->n_mat));
+  TRY(dev_alloc(&c->rho, c->n_mat)); TRY(dev_alloc(&c->f, c->n_f)); TRY(dev_alloc(&c->uhat, 3 * c->nn));
+  // initial values of fea.add_input (rm_shell_model.py:209-214); nu=1 there is singular, use 0.3
+  TRY(fill(c, c->h, c->n_mat, 1e-3)); TRY(fill(c, c->E, c->n_mat, 1.0)); TRY(fill(c, c->nu, c->n_mat, 0.3));
+  TRY(fill(c, c->rho, c->n_mat, 1.0)); TRY(fill(c, c->f, c->n_f, 1.0)); TRY(fill(c, c->uhat, 3 * c->nn, 0.0));
+  c->uhat_zero = 1;
+  c->rec_nqf = c->all_planar ? REC_NQF_PLANAR : REC_NQF_WARPED;
+  c->rec_stride = REC_HEADER + c->nq * c->rec_nqf;
+  TRY(dev_alloc(&c->rec, (size_t)c->nc * c->rec_stride));
+  const int64_t n = c->ndof;
+  TRY(dev_alloc(&c->bcmask, n)); TRY(fill(c, c->bcmask, n, 1.0));
+  c->n_bc = 0;
+  double** vecs[] = {&c->w, &c->b, &c->r, &c->z, &c->p, &c->Ap, &c->tmp, &c->tmp2};
+  for (double** v : vecs) { TRY(dev_alloc(v, n)); CUDA_TRY(cudaMemsetAsync(*v, 0, sizeof(double) * n, c->stream)); }
+  TRY(dev_alloc(&c->dinv6, (size_t)c->nn * 36)); TRY(dev_alloc(&c->dinv3, (size_t)(c->ne + c->nc) * 9));
+  TRY(dev_alloc(&c->red, 8 * 1184)); TRY(dev_alloc(&c->scal, 16));
+  TRY(dev_alloc(&c->cellbuf, (size_t)c->nc * 39));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  c->setup_done = true; c->jac_valid = false; c->prec_valid = false;
+  return 0;
+}
+
+int femo_get_sizes(femo_ctx* c, femo_sizes* s) {
+  if (!c || !s) return femo_fail("null argument");
+  s->n_nodes = c->nn; s->n_edges = c->ne; s->n_cells = c->nc; s->n_blocks = c->nb; s->n_dof = c->ndof;
+  s->nnz_blocks = c->nnzb; s->n_contrib = c->ncontrib; s->n_material = c->n_mat; s->n_force = c->n_f;
+  s->n_qp = c->nq; s->all_planar = c->all_planar;
+  return 0;
+}
+
+int femo_get_block_coords(femo_ctx* c, double* out) {
+  if (!c || c->nb == 0) return femo_fail("femo_get_block_coords: set the mesh first");
+  DevGuard g(c->device);
+  double* d = nullptr;
+  TRY(dev_alloc(&d, (size_t)c->nb * 3));
+  k_block_coords<<<(unsigned)cdiv(c->nb, 256), 256, 0, c->stream>>>(c->xyz, c->edges, c->cv, c->nn, c->ne, c->nc, d);
+  TRY(check_launch(c, "k_block_coords"));
+  c->launches += 1;
+  int r = copy_out(c, out, d, c->nb * 3, 0);
+  dev_free(&d);
+  return r;
+}
+
+int femo_get_cell_blocks(femo_ctx* c, int32_t* out) {
+  if (!c || !c->cell_blocks) return femo_fail("femo_get_cell_blocks: set the mesh first");
+  DevGuard g(c->device);
+  CUDA_TRY(cudaMemcpy(out, c->cell_blocks, sizeof(int32_t) * c->nc * 13, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int femo_set_strong_bc(femo_ctx* c, int64_t n, const int32_t* dofs) {
+  NEED_SETUP(c, "femo_set_strong_bc");
+  DevGuard g(c->device);
+  TRY(fill(c, c->bcmask, c->ndof, 1.0));
+  c->n_bc = n;
+  if (n > 0) {
+    for (int64_t i = 0; i < n; ++i)
+      if (dofs[i] < 0 || dofs[i] >= c->ndof) return femo_fail("femo_set_strong_bc: dof index out of range");
+    int32_t* d = nullptr;
+    TRY(dev_alloc(&d, (size_t)n));
+    CUDA_TRY(cudaMemcpyAsync(d, dofs, sizeof(int32_t) * n, cudaMemcpyHostToDevice, c->stream));
+    k_mask_clear<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(c->bcmask, d, n);
+    TRY(check_launch(c, "k_mask_clear"));
+    c->launches += 1;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    dev_free(&d);
+  }
+  c->prec_valid = false;
+  return 0;
+}
+
+int femo_set_penalty_bc(femo_ctx* c, int64_t n_nodes, const uint8_t* von) {
+  NEED_SETUP(c, "femo_set_penalty_bc");
+  if (n_nodes != c->nn) return femo_fail("femo_set_penalty_bc: vertex mask must have n_nodes entries");
+  DevGuard g(c->device);
+  return penalty_build(c, von);
+}
+
+int femo_set_input(femo_ctx* c, int which, const double* data, int64_t n, int on_device) {
+  NEED_SETUP(c, "femo_set_input");
+  DevGuard g(c->device);
+  int64_t want = 0;
+  double** slot = input_slot(c, which, &want);
+  if (!slot) return femo_fail("femo_set_input: unknown input id");
+  if (n == 1) {  // utils_dolfinx.update: len(v_values) == 1 -> v.vector.set(value)
+    double v;
+    if (on_device) CUDA_TRY(cudaMemcpy(&v, data, sizeof(double), cudaMemcpyDeviceToHost)); else v = data[0];
+    TRY(fill(c, *slot, want, v));
+    if (which == FEMO_UHAT) c->uhat_zero = (v == 0.0);
+  } else {
+    if (n != want) return femo_fail("femo_set_input: size mismatch (got " + std::to_string(n) + ", expected " + std::to_string(want) + ")");
+    TRY(copy_in(c, *slot, data, n, on_device));
+    if (which == FEMO_UHAT) {
+      double nrm = 0;
+      TRY(dev_dot(c, c->uhat, c->uhat, n, &nrm));
+      c->uhat_zero = (nrm == 0.0);
+    }
+  }
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  if (which != FEMO_DENSITY && which != FEMO_F_SOLID) { c->jac_valid = false; c->prec_valid = false; }
+  return 0;
+}
+
+int femo_get_input(femo_ctx* c, int which, double* out, int64_t n, int on_device) {
+  NEED_SETUP(c, "femo_get_input");
+  DevGuard g(c->device);
+  int64_t want = 0;
+  double** slot = input_slot(c, which, &want);
+  if (!slot || n != want) return femo_fail("femo_get_input: bad input id or size");
+  return copy_out(c, out, *slot, n, on_device);
+}
+
+int femo_set_state(femo_ctx* c, const double* w, int on_device) {
+  NEED_SETUP(c, "femo_set_state");
+  DevGuard g(c->device);
+  TRY(copy_in(c, c->w, w, c->ndof, on_device));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+int femo_get_state(femo_ctx* c, double* w, int on_device) {
+  NEED_SETUP(c, "femo_get_state");
+  DevGuard g(c->device);
+  return copy_out(c, w, c->w, c->ndof, on_device);
+}
+
+int femo_assemble_jacobian(femo_ctx* c) {
+  NEED_SETUP(c, "femo_assemble_jacobian");
+  DevGuard g(c->device);
+  return assemble_jacobian(c);
+}
+
+int femo_assemble_load(femo_ctx* c, double* F, int on_device) {
+  NEED_SETUP(c, "femo_assemble_load");
+  DevGuard g(c->device);
+  TRY(assemble_load(c, c->tmp));
+  return copy_out(c, F, c->tmp, c->ndof, on_device);
+}
+
+int femo_assemble_residual(femo_ctx* c, const double* w, double* R, int on_device) {
+  NEED_SETUP(c, "femo_assemble_residual");
+  DevGuard g(c->device);
+  if (!c->jac_valid) TRY(assemble_jacobian(c));
+  const double* wd = c->w;
+  if (w) { TRY(copy_in(c, c->tmp2, w, c->ndof, on_device)); wd = c->tmp2; }
+  TRY(bsr_spmv(c, wd, c->tmp, 0));
+  TRY(assemble_load(c, c->b));
+  k_axpby<<<(unsigned)cdiv(c->ndof, 256), 256, 0, c->stream>>>(1.0, c->tmp, -1.0, c->b, c->ndof, c->tmp);
+  TRY(check_launch(c, "k_axpby"));
+  c->launches += 1;
+  return copy_out(c, R, c->tmp, c->ndof, on_device);
+}
+
+int femo_jacobian_apply(femo_ctx* c, const double* x, double* y, int with_bc, int on_device) {
+  NEED_SETUP(c, "femo_jacobian_apply");
+  DevGuard g(c->device);
+  if (!c->jac_valid) TRY(assemble_jacobian(c));
+  TRY(copy_in(c, c->tmp2, x, c->ndof, on_device));
+  TRY(bsr_spmv(c, c->tmp2, c->tmp, with_bc));
+  return copy_out(c, y, c->tmp, c->ndof, on_device);
+}
+
+int femo_get_bsr(femo_ctx* c, int32_t* rowptr, int32_t* colidx, double* vals, int with_bc) {
+  NEED_SETUP(c, "femo_get_bsr");
+  DevGuard g(c->device);
+  if (rowptr) CUDA_TRY(cudaMemcpy(rowptr, c->rowptr, sizeof(int32_t) * (c->nb + 1), cudaMemcpyDeviceToHost));
+  if (colidx) CUDA_TRY(cudaMemcpy(colidx, c->colidx, sizeof(int32_t) * c->nnzb, cudaMemcpyDeviceToHost));
+  if (vals) {
+    if (!c->jac_valid) TRY(assemble_jacobian(c));
+    if (!with_bc) CUDA_TRY(cudaMemcpy(vals, c->vals, sizeof(double) * c->nnzb * 9, cudaMemcpyDeviceToHost));
+    else {
+      double* t = nullptr;
+      TRY(dev_alloc(&t, (size_t)c->nnzb * 9));
+      CUDA_TRY(cudaMemcpyAsync(t, c->vals, sizeof(double) * c->nnzb * 9, cudaMemcpyDeviceToDevice, c->stream));
+      k_bsr_apply_bc<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colidx, c->bcmask, c->nb, t);
+      TRY(check_launch(c, "k_bsr_apply_bc"));
+      c->launches += 1;
+      int r = copy_out(c, vals, t, c->nnzb * 9, 0);
+      dev_free(&t);
+      return r;
+    }
+  }
+  return 0;
+}
+
+int femo_solve_state(femo_ctx* c, double rtol, int max_it, int* iters, double* relres) {
+  NEED_SETUP(c, "femo_solve_state");
+  DevGuard g(c->device);
+  if (!c->jac_valid) TRY(assemble_jacobian(c));
+  TRY(assemble_load(c, c->b));
+  // homogeneous Dirichlet values (ubc = 0, rm_shell_model.py:174-176)
+  k_mul<<<(unsigned)cdiv(c->ndof, 256), 256, 0, c->stream>>>(c->b, c->bcmask, c->ndof, c->b);
+  k_mul<<<(unsigned)cdiv(c->ndof, 256), 256, 0, c->stream>>>(c->w, c->bcmask, c->ndof, c->w);
+  TRY(check_launch(c, "k_mul"));
+  c->launches += 2;
+  int it = 0; double rr = 0;
+  TRY(pcg_solve(c, c->b, c->w, rtol, max_it, &it, &rr, false));
+  if (iters) *iters = it;
+  if (relres) *relres = rr;
+  return 0;
+}
+
+static int solve_generic(femo_ctx* c, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
+                         int on_device, bool zero_bc) {
+  if (!c->jac_valid) TRY(assemble_jacobian(c));
+  TRY(copy_in(c, c->b, rhs, c->ndof, on_device));
+  CUDA_TRY(cudaMemsetAsync(c->tmp2, 0, sizeof(double) * c->ndof, c->stream));
+  int it = 0; double rr = 0;
+  TRY(pcg_solve(c, c->b, c->tmp2, rtol, max_it, &it, &rr, false));
+  if (zero_bc) {  // state_operation.py:217-218
+    k_mul<<<(unsigned)cdiv(c->ndof, 256), 256, 0, c->stream>>>(c->tmp2, c->bcmask, c->ndof, c->tmp2);
+    TRY(check_launch(c, "k_mul"));
+    c->launches += 1;
+  }
+  if (iters) *iters = it;
+  if (relres) *relres = rr;
+  return copy_out(c, sol, c->tmp2, c->ndof, on_device);
+}
+
+int femo_solve_adjoint(femo_ctx* c, const double* rhs, double* lam, double rtol, int max_it, int* iters, double* relres,
+                       int on_device) {
+  NEED_SETUP(c, "femo_solve_adjoint");
+  DevGuard g(c->device);
+  return solve_generic(c, rhs, lam, rtol, max_it, iters, relres, on_device, true);
+}
+
+int femo_solve_forward(femo_ctx* c, const double* rhs, double* du, double rtol, int max_it, int* iters, double* relres,
+                       int on_device) {
+  NEED_SETUP(c, "femo_solve_forward");
+  DevGuard g(c->device);
+  return solve_generic(c, rhs, du, rtol, max_it, iters, relres, on_device, false);
+}
+
+int femo_dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out, int on_device) {
+  NEED_SETUP(c, "femo_dRdf_T_apply");
+  DevGuard g(c->device);
+  int64_t n = 0;
+  if (!input_slot(c, arg, &n)) return femo_fail("femo_dRdf_T_apply: unknown argument");
+  TRY(copy_in(c, c->tmp2, lam, c->ndof, on_device));
+  TRY(dRdf_T_apply(c, arg, c->tmp2, c->tmp));
+  return copy_out(c, out, c->tmp, n, on_device);
+}
+
+int femo_dRdf_apply(femo_ctx* c, int arg, const double* df, double* out, int on_device) {
+  NEED_SETUP(c, "femo_dRdf_apply");
+  DevGuard g(c->device);
+  int64_t n = 0;
+  if (!input_slot(c, arg, &n)) return femo_fail("femo_dRdf_apply: unknown argument");
+  TRY(copy_in(c, c->tmp2, df, n, on_device));
+  TRY(dRdf_apply(c, arg, c->tmp2, c->tmp));
+  return copy_out(c, out, c->tmp, c->ndof, on_device);
+}
+
+int femo_output(femo_ctx* c, int which, double* value) {
+  NEED_SETUP(c, "femo_output");
+  DevGuard g(c->device);
+  return out_scalar(c, which, value);
+}
+
+int femo_output_grad(femo_ctx* c, int which, int arg, double* gout, int on_device) {
+  NEED_SETUP(c, "femo_output_grad");
+  DevGuard g(c->device);
+  int64_t n = c->ndof;
+  if (arg != FEMO_ARG_STATE && !input_slot(c, arg, &n)) return femo_fail("femo_output_grad: unknown argument");
+  TRY(out_grad(c, which, arg, c->tmp));
+  return copy_out(c, gout, c->tmp, n, on_device);
+}
+
+int femo_launch_count(femo_ctx* c, int64_t* n) {
+  if (!c || !n) return femo_fail("null argument");
+  *n = c->launches;
+  return 0;
+}
+
+int femo_last_timings(femo_ctx* c, double* ms4) {
+  if (!c || !ms4) return femo_fail("null argument");
+  ms4[0] = c->t_rec; ms4[1] = c->t_asm; ms4[2] = c->t_solve; ms4[3] = c->t_iter;
+  return 0;
+}
+
+int femo_pcg_fixed(femo_ctx* c, int n_iter, double* ms_total) {
+  NEED_SETUP(c, "femo_pcg_fixed");
+  DevGuard g(c->device);
+  if (!c->jac_valid) TRY(assemble_jacobian(c));
+  TRY(assemble_load(c, c->b));
+  k_mul<<<(unsigned)cdiv(c->ndof, 256), 256, 0, c->stream>>>(c->b, c->bcmask, c->ndof, c->b);
+  c->launches += 1;
+  CUDA_TRY(cudaMemsetAsync(c->tmp2, 0, sizeof(double) * c->ndof, c->stream));
+  int it = 0; double rr = 0;
+  TRY(pcg_solve(c, c->b, c->tmp2, 0.0, n_iter, &it, &rr, true));
+  if (ms_total) *ms_total = c->t_solve;
+  return 0;
+}
+
+int femo_measure_peaks(femo_ctx* c, double* tf, double* gbs) {
+  if (!c) return femo_fail("null context");
+  DevGuard g(c->device);
+  return measure_peaks(c, tf, gbs);
+}
+
+}  // extern "C"

@@ -1,0 +1,397 @@
+// Deterministic assembly of the RM-shell tangent Jacobian dR/du into BSR(3x3).
+//
+// Replaces assembleMatrix(dR_du) / NonlinearProblem.J (femo_alpha/fea/utils_dolfinx.py:200-221,
+// csdl_alpha_opt/state_operation.py:289-294), i.e. FFCx element kernels + dolfinx
+// MatSetValuesLocal, for the forms of rm_shell/linear_shell_fenicsx/linear_shell_model.py:220-333.
+//
+// Two kernels:
+//   k_cell_records   one thread per (cell, quadrature point): geometry + CLT coefficients
+//   k_gather<PLANAR> one thread per element-block CONTRIBUTION, in destination order (the
+//                    precomputed cell->nnz permutation); contributions to the same BSR block
+//                    are summed in a fixed order through shared memory, each block of the
+//                    matrix is written exactly once -> bitwise reproducible, no atomics.
+#include "femo_internal.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+__global__ void k_cell_records(const double* __restrict__ xyz, const int32_t* __restrict__ cv,
+                               const double* __restrict__ uhat, const double* __restrict__ h,
+                               const double* __restrict__ E, const double* __restrict__ nu,
+                               const double* __restrict__ hE, const Tables* __restrict__ tab, int64_t nc, int nq,
+                               int ewm, int nqf, int stride, double* __restrict__ rec) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= nc * nq) return;
+  int64_t cell = i / nq; int q = (int)(i - cell * nq);
+  V3 xv[4], uh[4];
+  int32_t vid[4];
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    vid[v] = cv[cell * 4 + v];
+    xv[v] = ldv3(xyz + 3 * (int64_t)vid[v]);
+    if (uhat) uh[v] = ldv3(uhat + 3 * (int64_t)vid[v]);
+  }
+  QpGeom g;
+  qp_geometry(xv, uhat ? uh : nullptr, tab->X0[q], tab->X1[q], g);
+  double hq, Eq, nuq;
+  if (ewm) { hq = h[cell]; Eq = E[cell]; nuq = nu[cell]; }
+  else {
+    hq = Eq = nuq = 0;
+#pragma unroll
+    for (int v = 0; v < 4; ++v) { double N = tab->n1[q][v]; hq += N * h[vid[v]]; Eq += N * E[vid[v]]; nuq += N * nu[vid[v]]; }
+  }
+  Coefs cf = clt_coefs(hq, Eq, nuq, hE[cell], g.Ju, 0);
+  double wd = tab->W[q] * g.detJ;
+  double* r = rec + cell * stride + REC_HEADER + q * nqf;
+  V3 E0 = g.E0, E1 = g.E1;
+  if (nqf == REC_NQF_PLANAR) {
+    // planar cell: any in-plane orthonormal frame gives the same energy (isotropic CLT), so one
+    // constant frame per cell (taken at the cell centre) is used at every quadrature point.
+    QpGeom gc;
+    qp_geometry(xv, nullptr, 0.5, 0.5, gc);
+    E0 = gc.E0; E1 = gc.E1;
+    if (q == 0) {
+      double* hd = rec + cell * stride;
+      hd[0] = gc.E0.x; hd[1] = gc.E0.y; hd[2] = gc.E0.z;
+      hd[3] = gc.E1.x; hd[4] = gc.E1.y; hd[5] = gc.E1.z;
+      hd[6] = gc.E2.x; hd[7] = gc.E2.y; hd[8] = gc.E2.z;
+    }
+  }
+  r[REC_K00] = dot(g.Kx0, E0); r[REC_K01] = dot(g.Kx0, E1);
+  r[REC_K10] = dot(g.Kx1, E0); r[REC_K11] = dot(g.Kx1, E1);
+  r[REC_CM11] = wd * cf.cm11; r[REC_CM12] = wd * cf.cm12; r[REC_CM33] = wd * cf.cm33;
+  r[REC_HB] = hq * hq / 12.0;
+  r[REC_CS] = wd * cf.cs; r[REC_CD] = wd * cf.cd;
+  if (nqf == REC_NQF_WARPED) {
+    double* e = r + REC_E0;
+    e[0] = g.E0.x; e[1] = g.E0.y; e[2] = g.E0.z; e[3] = g.E1.x; e[4] = g.E1.y; e[5] = g.E1.z;
+    e[6] = g.E2.x; e[7] = g.E2.y; e[8] = g.E2.z;
+    double k00 = r[REC_K00], k01 = r[REC_K01], k10 = r[REC_K10], k11 = r[REC_K11];
+    V3 g0 = k00 * g.dE2_0 + k10 * g.dE2_1, g1 = k01 * g.dE2_0 + k11 * g.dE2_1;
+    double* gg = r + REC_G0;
+    gg[0] = g0.x; gg[1] = g0.y; gg[2] = g0.z; gg[3] = g1.x; gg[4] = g1.y; gg[5] = g1.z;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+struct SmemTab {
+  double dphi2[FEMO_MAX_NQ][9][2];
+  double n1[FEMO_MAX_NQ][4];
+  double dn1[FEMO_MAX_NQ][4][2];
+};
+
+// 3x3 block (a,b) of one element matrix, planar cell: local-frame accumulation, one rotation
+__device__ __forceinline__ void block_planar(const double* __restrict__ rc, const SmemTab& T, int nq, int a, int b,
+                                             double* K) {
+  const V3 E0 = ldv3(rc), E1 = ldv3(rc + 3), E2 = ldv3(rc + 6);
+  const double* r = rc + REC_HEADER;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) K[i] = 0.0;
+  if (a < 9 && b < 9) {
+    double m00 = 0, m01 = 0, m10 = 0, m11 = 0, s = 0;
+    for (int q = 0; q < nq; ++q, r += REC_NQF_PLANAR) {
+      double k00 = r[REC_K00], k01 = r[REC_K01], k10 = r[REC_K10], k11 = r[REC_K11];
+      double da0 = T.dphi2[q][a][0] * k00 + T.dphi2[q][a][1] * k10, da1 = T.dphi2[q][a][0] * k01 + T.dphi2[q][a][1] * k11;
+      double db0 = T.dphi2[q][b][0] * k00 + T.dphi2[q][b][1] * k10, db1 = T.dphi2[q][b][0] * k01 + T.dphi2[q][b][1] * k11;
+      double P00 = da0 * db0, P01 = da0 * db1, P10 = da1 * db0, P11 = da1 * db1;
+      double cm11 = r[REC_CM11], cm12 = r[REC_CM12], cm33 = r[REC_CM33], cd4 = 0.25 * r[REC_CD], cs = r[REC_CS];
+      m00 += cm11 * P00 + (cm33 + cd4) * P11;
+      m01 += cm12 * P01 + (cm33 - cd4) * P10;
+      m10 += cm12 * P10 + (cm33 - cd4) * P01;
+      m11 += cm11 * P11 + (cm33 + cd4) * P00;
+      s += cs * (P00 + P11);
+    }
+    outer_acc(K, m00 * E0 + m10 * E1, E0);
+    outer_acc(K, m01 * E0 + m11 * E1, E1);
+    outer_acc(K, s * E2, E2);
+  } else if (a >= 9 && b >= 9) {
+    int ta = a - 9, tb = b - 9;
+    double t00 = 0, t01 = 0, t10 = 0, t11 = 0, t22 = 0;
+    for (int q = 0; q < nq; ++q, r += REC_NQF_PLANAR) {
+      double k00 = r[REC_K00], k01 = r[REC_K01], k10 = r[REC_K10], k11 = r[REC_K11];
+      double da0 = T.dn1[q][ta][0] * k00 + T.dn1[q][ta][1] * k10, da1 = T.dn1[q][ta][0] * k01 + T.dn1[q][ta][1] * k11;
+      double db0 = T.dn1[q][tb][0] * k00 + T.dn1[q][tb][1] * k10, db1 = T.dn1[q][tb][0] * k01 + T.dn1[q][tb][1] * k11;
+      double NN = T.n1[q][ta] * T.n1[q][tb];
+      double hb = r[REC_HB];
+      double cb11 = hb * r[REC_CM11], cb12 = hb * r[REC_CM12], cb33 = hb * r[REC_CM33], cs = r[REC_CS];
+      double P00 = da0 * db0, P01 = da0 * db1, P10 = da1 * db0, P11 = da1 * db1;
+      t00 += cb11 * P11 + cb33 * P00 + cs * NN;
+      t11 += cb11 * P00 + cb33 * P11 + cs * NN;
+      t01 -= cb12 * P10 + cb33 * P01;
+      t10 -= cb12 * P01 + cb33 * P10;
+      t22 += r[REC_CD] * NN;
+    }
+    outer_acc(K, t00 * E0 + t10 * E1, E0);
+    outer_acc(K, t01 * E0 + t11 * E1, E1);
+    outer_acc(K, t22 * E2, E2);
+  } else {
+    // displacement node ua, rotation node tb; the (theta,u) block is the transpose
+    bool tr = (a >= 9);
+    int ua = tr ? b : a, tb = (tr ? a : b) - 9;
+    double A0 = 0, A1 = 0, D0 = 0, D1 = 0;
+    for (int q = 0; q < nq; ++q, r += REC_NQF_PLANAR) {
+      double k00 = r[REC_K00], k01 = r[REC_K01], k10 = r[REC_K10], k11 = r[REC_K11];
+      double da0 = T.dphi2[q][ua][0] * k00 + T.dphi2[q][ua][1] * k10, da1 = T.dphi2[q][ua][0] * k01 + T.dphi2[q][ua][1] * k11;
+      double N = T.n1[q][tb];
+      double cs = r[REC_CS] * N, cd = r[REC_CD] * N;
+      A0 += cs * da0; A1 += cs * da1; D0 += cd * da0; D1 += cd * da1;
+    }
+    // K[u_i, th_j] = A0 E2 E1^T - A1 E2 E0^T + 0.5 D1 E0 E2^T - 0.5 D0 E1 E2^T
+    double Kl[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    outer_acc(Kl, E2, A0 * E1 - A1 * E0);
+    outer_acc(Kl, 0.5 * (D1 * E0 - D0 * E1), E2);
+    if (!tr) {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) K[i] = Kl[i];
+    } else {
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) K[3 * i + j] = Kl[3 * j + i];
+    }
+  }
+}
+
+// general (warped / per-point frame) version
+__device__ __forceinline__ void block_general(const double* __restrict__ rc, const SmemTab& T, int nq, int a, int b,
+                                              double* K) {
+  const double* r = rc + REC_HEADER;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) K[i] = 0.0;
+  for (int q = 0; q < nq; ++q, r += REC_NQF_WARPED) {
+    double k00 = r[REC_K00], k01 = r[REC_K01], k10 = r[REC_K10], k11 = r[REC_K11];
+    V3 E0 = ldv3(r + REC_E0), E1 = ldv3(r + REC_E0 + 3), E2 = ldv3(r + REC_E0 + 6);
+    double cm11 = r[REC_CM11], cm12 = r[REC_CM12], cm33 = r[REC_CM33], hb = r[REC_HB], cs = r[REC_CS], cd = r[REC_CD];
+    if (a < 9 && b < 9) {
+      double da0 = T.dphi2[q][a][0] * k00 + T.dphi2[q][a][1] * k10, da1 = T.dphi2[q][a][0] * k01 + T.dphi2[q][a][1] * k11;
+      double db0 = T.dphi2[q][b][0] * k00 + T.dphi2[q][b][1] * k10, db1 = T.dphi2[q][b][0] * k01 + T.dphi2[q][b][1] * k11;
+      URows A = u_rows(da0, da1, E0, E1, E2), B = u_rows(db0, db1, E0, E1, E2);
+      outer_acc(K, A.e0, cm11 * B.e0 + cm12 * B.e1);
+      outer_acc(K, A.e1, cm12 * B.e0 + cm11 * B.e1);
+      outer_acc(K, A.e2, cm33 * B.e2);
+      outer_acc(K, A.g0, cs * B.g0);
+      outer_acc(K, A.g1, cs * B.g1);
+      outer_acc(K, A.dr, cd * B.dr);
+    } else if (a >= 9 && b >= 9) {
+      int ta = a - 9, tb = b - 9;
+      V3 g0 = ldv3(r + REC_G0), g1 = ldv3(r + REC_G0 + 3);
+      double da0 = T.dn1[q][ta][0] * k00 + T.dn1[q][ta][1] * k10, da1 = T.dn1[q][ta][0] * k01 + T.dn1[q][ta][1] * k11;
+      double db0 = T.dn1[q][tb][0] * k00 + T.dn1[q][tb][1] * k10, db1 = T.dn1[q][tb][0] * k01 + T.dn1[q][tb][1] * k11;
+      TRows A = t_rows(T.n1[q][ta], da0, da1, E0, E1, E2, g0, g1), B = t_rows(T.n1[q][tb], db0, db1, E0, E1, E2, g0, g1);
+      double cb11 = hb * cm11, cb12 = hb * cm12, cb33 = hb * cm33;
+      outer_acc(K, A.k0, cb11 * B.k0 + cb12 * B.k1);
+      outer_acc(K, A.k1, cb12 * B.k0 + cb11 * B.k1);
+      outer_acc(K, A.k2, cb33 * B.k2);
+      outer_acc(K, A.g0, cs * B.g0);
+      outer_acc(K, A.g1, cs * B.g1);
+      outer_acc(K, A.dr, cd * B.dr);
+    } else {
+      bool tr = (a >= 9);
+      int ua = tr ? b : a, tb = (tr ? a : b) - 9;
+      V3 g0 = ldv3(r + REC_G0), g1 = ldv3(r + REC_G0 + 3);
+      double da0 = T.dphi2[q][ua][0] * k00 + T.dphi2[q][ua][1] * k10, da1 = T.dphi2[q][ua][0] * k01 + T.dphi2[q][ua][1] * k11;
+      double db0 = T.dn1[q][tb][0] * k00 + T.dn1[q][tb][1] * k10, db1 = T.dn1[q][tb][0] * k01 + T.dn1[q][tb][1] * k11;
+      URows A = u_rows(da0, da1, E0, E1, E2);
+      TRows B = t_rows(T.n1[q][tb], db0, db1, E0, E1, E2, g0, g1);
+      if (!tr) {
+        outer_acc(K, A.g0, cs * B.g0); outer_acc(K, A.g1, cs * B.g1); outer_acc(K, A.dr, cd * B.dr);
+      } else {
+        outer_acc(K, cs * B.g0, A.g0); outer_acc(K, cs * B.g1, A.g1); outer_acc(K, cd * B.dr, A.dr);
+      }
+    }
+  }
+}
+
+#define GATHER_THREADS 256
+
+template <bool PLANAR>
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ cdest, const int32_t* __restrict__ cptr,
+         const double* __restrict__ rec, int stride, const Tables* __restrict__ tab, int nq, int64_t ncontrib,
+         double* __restrict__ vals) {
+  __shared__ SmemTab T;
+  __shared__ double sK[GATHER_THREADS][9];
+  {
+    double* d = (double*)&T;
+    const double* s0 = &tab->dphi2[0][0][0];
+    for (int i = threadIdx.x; i < FEMO_MAX_NQ * 18; i += blockDim.x) d[i] = s0[i];
+    double* d1 = &T.n1[0][0]; const double* s1 = &tab->n1[0][0];
+    for (int i = threadIdx.x; i < FEMO_MAX_NQ * 4; i += blockDim.x) d1[i] = s1[i];
+    double* d2 = &T.dn1[0][0][0]; const double* s2 = &tab->dn1[0][0][0];
+    for (int i = threadIdx.x; i < FEMO_MAX_NQ * 8; i += blockDim.x) d2[i] = s2[i];
+  }
+  __syncthreads();
+  const int64_t i = blockIdx.x * (int64_t)GATHER_THREADS + threadIdx.x;
+  double K[9];
+  int32_t dest = -1;
+  if (i < ncontrib) {
+    int32_t e = centry[i];
+    dest = cdest[i];
+    int32_t cell = e / 169; int pair = e - cell * 169;
+    int a = pair / 13, b = pair - a * 13;
+    const double* rc = rec + (int64_t)cell * stride;
+    if (PLANAR) block_planar(rc, T, nq, a, b, K); else block_general(rc, T, nq, a, b, K);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) sK[threadIdx.x][k] = K[k];
+  }
+  __syncthreads();
+  if (i >= ncontrib) return;
+  const int32_t first = cptr[dest];
+  if ((int64_t)first != i) return;               // not the head of its segment
+  const int32_t len = cptr[dest + 1] - first;
+  for (int j = 1; j < len; ++j) {                 // fixed (cell-ascending) summation order
+    int t = threadIdx.x + j;
+    if (t < GATHER_THREADS) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) K[k] += sK[t][k];
+    } else {                                      // segment spills into the next CTA: recompute
+      int32_t e = centry[i + j];
+      int32_t cell = e / 169; int pair = e - cell * 169;
+      int a = pair / 13, b = pair - a * 13;
+      double K2[9];
+      const double* rc = rec + (int64_t)cell * stride;
+      if (PLANAR) block_planar(rc, T, nq, a, b, K2); else block_general(rc, T, nq, a, b, K2);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) K[k] += K2[k];
+    }
+  }
+  double* o = vals + (int64_t)dest * 9;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) o[k] = K[k];
+}
+
+// ------------------------------------------------------------------------------------------
+// penalty BC: 5x5 trace matrix per (edge, cell), nodes (q2 va, q2 mid, q2 vb, q1 va, q1 vb)
+__global__ void k_penalty_me(const double* __restrict__ xyz, const int32_t* __restrict__ cv,
+                             const double* __restrict__ uhat, const double* __restrict__ hE,
+                             const int32_t* __restrict__ pen_cell, int64_t n_pen, double* __restrict__ me) {
+  int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= n_pen) return;
+  int32_t pc = pen_cell[p];
+  int64_t cell = pc >> 2; int le = pc & 3;
+  const int LE[4][2] = {{0, 1}, {0, 2}, {1, 3}, {2, 3}};
+  V3 xv[4], uh[4];
+  for (int v = 0; v < 4; ++v) {
+    int32_t id = cv[cell * 4 + v];
+    xv[v] = ldv3(xyz + 3 * (int64_t)id);
+    if (uhat) uh[v] = ldv3(uhat + 3 * (int64_t)id);
+  }
+  V3 t = xv[LE[le][1]] - xv[LE[le][0]];
+  double L = sqrt(dot(t, t));
+  t = (1.0 / L) * t;
+  const double gx[3] = {0.5 - 0.5 * 0.7745966692414834, 0.5, 0.5 + 0.5 * 0.7745966692414834};
+  const double gw[3] = {5.0 / 18.0, 8.0 / 18.0, 5.0 / 18.0};   // degree-4 facet rule (utils_dolfinx.py:556)
+  double M[25];
+  for (int i = 0; i < 25; ++i) M[i] = 0;
+  for (int k = 0; k < 3; ++k) {
+    double s = gx[k];
+    double X0 = (le == 0 || le == 3) ? s : (le == 2 ? 1.0 : 0.0);
+    double X1 = (le == 1 || le == 2) ? s : (le == 3 ? 1.0 : 0.0);
+    QpGeom g;
+    qp_geometry(xv, uhat ? uh : nullptr, X0, X1, g);
+    V3 Nf = cross(t, g.E2);
+    // Nanson: J F^-T N
+    const double* Fi = g.Finv;
+    V3 nn = v3(Fi[0] * Nf.x + Fi[3] * Nf.y + Fi[6] * Nf.z, Fi[1] * Nf.x + Fi[4] * Nf.y + Fi[7] * Nf.z,
+               Fi[2] * Nf.x + Fi[5] * Nf.y + Fi[8] * Nf.z);
+    double sc = g.Ju * sqrt(dot(nn, nn));
+    double tr[5] = {2.0 * (s - 0.5) * (s - 1.0), 4.0 * s * (1.0 - s), 2.0 * s * (s - 0.5), 1.0 - s, s};
+    double wgt = gw[k] * L * sc * FEMO_BETA / hE[cell];
+    for (int i = 0; i < 5; ++i)
+      for (int j = 0; j < 5; ++j)
+        if ((i < 3) == (j < 3)) M[i * 5 + j] += wgt * tr[i] * tr[j];
+  }
+  for (int i = 0; i < 25; ++i) me[p * 25 + i] = M[i];
+}
+
+__global__ void k_penalty_add(const int32_t* __restrict__ dest_pos, const int32_t* __restrict__ dest_ptr,
+                              const int32_t* __restrict__ src, const double* __restrict__ me, int64_t n_dest,
+                              double* __restrict__ pen_val, double* __restrict__ vals) {
+  int64_t d = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (d >= n_dest) return;
+  double v = 0;
+  for (int32_t k = dest_ptr[d]; k < dest_ptr[d + 1]; ++k) v += me[src[k]];
+  pen_val[d] = v;
+  double* o = vals + (int64_t)dest_pos[d] * 9;
+  o[0] += v; o[4] += v; o[8] += v;
+}
+
+// ------------------------------------------------------------------------------------------
+// load vector: F_I = sum_{cells containing Q2 node I} sum_q w detJ J phi2_a f(q)   (model:320)
+__global__ void k_load(const double* __restrict__ xyz, const int32_t* __restrict__ cv,
+                       const double* __restrict__ uhat, const double* __restrict__ f,
+                       const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
+                       const Tables* __restrict__ tab, int nq, int ewp, int64_t nq2, double* __restrict__ F) {
+  int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= nq2) return;
+  V3 acc = v3(0, 0, 0);
+  for (int32_t k = nc_ptr[I]; k < nc_ptr[I + 1]; ++k) {
+    int32_t e = nc_adj[k];
+    int64_t cell = e / 13; int a = e - (int32_t)cell * 13;
+    V3 xv[4], uh[4], fv[4];
+    for (int v = 0; v < 4; ++v) {
+      int32_t id = cv[cell * 4 + v];
+      xv[v] = ldv3(xyz + 3 * (int64_t)id);
+      if (uhat) uh[v] = ldv3(uhat + 3 * (int64_t)id);
+      if (!ewp) fv[v] = ldv3(f + 3 * (int64_t)id);
+    }
+    V3 fc = ewp ? ldv3(f + 3 * cell) : v3(0, 0, 0);
+    for (int q = 0; q < nq; ++q) {
+      QpGeom g;
+      qp_geometry(xv, uhat ? uh : nullptr, tab->X0[q], tab->X1[q], g);
+      V3 fq = fc;
+      if (!ewp) fq = tab->n1[q][0] * fv[0] + tab->n1[q][1] * fv[1] + tab->n1[q][2] * fv[2] + tab->n1[q][3] * fv[3];
+      acc = acc + (tab->W[q] * g.detJ * g.Ju * tab->phi2[q][a]) * fq;
+    }
+  }
+  F[3 * I] = acc.x; F[3 * I + 1] = acc.y; F[3 * I + 2] = acc.z;
+}
+
+}  // namespace
+
+int assemble_jacobian(femo_ctx* c) {
+  if (!c->setup_done) return femo_fail("femo_assemble_jacobian: call femo_shell_setup first");
+  const double* uh = c->uhat_zero ? nullptr : c->uhat;
+  cudaEventRecord(c->ev0, c->stream);
+  k_cell_records<<<(unsigned)cdiv(c->nc * c->nq, 128), 128, 0, c->stream>>>(
+      c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->nc, c->nq, c->ewm, c->rec_nqf, c->rec_stride, c->rec);
+  TRY(check_launch(c, "k_cell_records"));
+  cudaEventRecord(c->ev1, c->stream);
+  unsigned grid = (unsigned)cdiv(c->ncontrib, GATHER_THREADS);
+  if (c->all_planar)
+    k_gather<true><<<grid, GATHER_THREADS, 0, c->stream>>>(c->centry, c->cdest, c->cptr, c->rec, c->rec_stride, c->tab,
+                                                           c->nq, c->ncontrib, c->vals);
+  else
+    k_gather<false><<<grid, GATHER_THREADS, 0, c->stream>>>(c->centry, c->cdest, c->cptr, c->rec, c->rec_stride, c->tab,
+                                                            c->nq, c->ncontrib, c->vals);
+  TRY(check_launch(c, "k_gather"));
+  cudaEvent_t ev2; cudaEventCreate(&ev2);
+  cudaEventRecord(ev2, c->stream);
+  c->launches += 2;
+  if (c->n_pen > 0) {
+    k_penalty_me<<<(unsigned)cdiv(c->n_pen, 128), 128, 0, c->stream>>>(c->xyz, c->cv, uh, c->hE, c->pen_cell, c->n_pen, c->pen_me);
+    TRY(check_launch(c, "k_penalty_me"));
+    k_penalty_add<<<(unsigned)cdiv(c->n_pen_dest, 128), 128, 0, c->stream>>>(c->pen_dest_pos, c->pen_dest_ptr, c->pen_src,
+                                                                          c->pen_me, c->n_pen_dest, c->pen_val, c->vals);
+    TRY(check_launch(c, "k_penalty_add"));
+    c->launches += 2;
+  }
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->t_rec = ms;
+  cudaEventElapsedTime(&ms, c->ev1, ev2); c->t_asm = ms;
+  cudaEventDestroy(ev2);
+  c->jac_valid = true;
+  c->prec_valid = false;
+  return 0;
+}
+
+int assemble_load(femo_ctx* c, double* F) {
+  const double* uh = c->uhat_zero ? nullptr : c->uhat;
+  CUDA_TRY(cudaMemsetAsync(F, 0, sizeof(double) * c->ndof, c->stream));
+  k_load<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(c->xyz, c->cv, uh, c->f, c->nc_ptr, c->nc_adj, c->tab, c->nq,
+                                                            c->ewp, c->nq2, F);
+  TRY(check_launch(c, "k_load"));
+  c->launches += 1;
+  return 0;
+}

@@ -1,0 +1,404 @@
+// Scalar outputs, their partials, and the matrix-free partials of the residual.
+//
+// Replaces OutputOperation.compute / compute_derivatives (femo_alpha/csdl_alpha_opt/
+// output_operation.py:51-69) for the forms compliance / mass / elastic_energy
+// (rm_shell/rm_shell_pde.py:64-110), and assembleMatrix(dR_df) + MatMult[Transpose]
+// (csdl_alpha_opt/state_operation.py:163-184,282-286; fea/utils_dolfinx.py:275-306).
+//
+// Pattern: one warp per cell, one lane per quadrature point -> per-cell element vector in
+// `cellbuf` (lane reduction by shuffles, fixed order), then a per-node gather that sums the
+// adjacent cells in ascending cell order.  No atomics: results are bitwise reproducible.
+#include "femo_internal.cuh"
+
+namespace {
+
+enum CellOp {
+  OP_PARAM_T = 0,    // nodal/cell param gradient: sum_q N_v g(q), g = s(lam)^T D' s(w) w detJ   -> 4 (or 1)
+  OP_PARAM_FWD = 1,  // sum_q dp(q) B^T D' s(w) w detJ                                           -> 39
+  OP_F_T = 2,        // -(sum_q wJ N_v(q) lam_u(q))                                              -> 12 (or 3)
+  OP_F_FWD = 3,      // -(sum_q wJ phi_a(q) df(q))                                               -> 27
+  OP_MASS_U = 4,     // sum_q wJ phi_a(q) u(q)                                                   -> 27
+  OP_UU = 5,         // sum_q wJ u.u                                                             -> 1
+  OP_MASS = 6,       // sum_q wJ rho h                                                           -> 1
+  OP_REG = 7,        // regulariser value                                                        -> 1
+  OP_REG_GRAD = 8,   // regulariser gradient                                                     -> 4 (or 1)
+  OP_DMASS_DH = 9,   // sum_q wJ rho N_v                                                         -> 4 (or 1)
+  OP_DMASS_DRHO = 10 // sum_q wJ h N_v                                                           -> 4 (or 1)
+};
+
+struct CellArgs {
+  const double* xyz; const int32_t* cv; const int32_t* cb; const double* uhat;
+  const double *h, *E, *nu, *rho, *f, *hE;
+  const Tables* tab;
+  int64_t nc; int nq, ewm, ewp;
+  const double* vec_w;    // state-like vector (ndof)
+  const double* vec_l;    // adjoint-like vector (ndof) or parameter perturbation
+  int mode;               // coefficient derivative mode 1:h 2:E 3:nu
+  double* out; int out_stride;
+};
+
+__device__ __forceinline__ double lane_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// strains [e0,e1,e2,k0,k1,k2,g0,g1,dr] of element vector `we` (39, shared) at one point
+__device__ __forceinline__ void strains_at(const QpGeom& g, const Tables* tab, int q, const double* we, double* s) {
+  const double k00 = dot(g.Kx0, g.E0), k01 = dot(g.Kx0, g.E1), k10 = dot(g.Kx1, g.E0), k11 = dot(g.Kx1, g.E1);
+  const V3 gq0 = k00 * g.dE2_0 + k10 * g.dE2_1, gq1 = k01 * g.dE2_0 + k11 * g.dE2_1;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) s[i] = 0.0;
+  for (int a = 0; a < 9; ++a) {
+    double d0 = tab->dphi2[q][a][0] * k00 + tab->dphi2[q][a][1] * k10, d1 = tab->dphi2[q][a][0] * k01 + tab->dphi2[q][a][1] * k11;
+    URows R = u_rows(d0, d1, g.E0, g.E1, g.E2);
+    V3 u = ldv3(we + 3 * a);
+    s[0] += dot(R.e0, u); s[1] += dot(R.e1, u); s[2] += dot(R.e2, u);
+    s[6] += dot(R.g0, u); s[7] += dot(R.g1, u); s[8] += dot(R.dr, u);
+  }
+  for (int b = 0; b < 4; ++b) {
+    double d0 = tab->dn1[q][b][0] * k00 + tab->dn1[q][b][1] * k10, d1 = tab->dn1[q][b][0] * k01 + tab->dn1[q][b][1] * k11;
+    TRows R = t_rows(tab->n1[q][b], d0, d1, g.E0, g.E1, g.E2, gq0, gq1);
+    V3 t = ldv3(we + 27 + 3 * b);
+    s[3] += dot(R.k0, t); s[4] += dot(R.k1, t); s[5] += dot(R.k2, t);
+    s[6] += dot(R.g0, t); s[7] += dot(R.g1, t); s[8] += dot(R.dr, t);
+  }
+}
+
+// sig = D s
+__device__ __forceinline__ void apply_D(const Coefs& c, const double* s, double* sig) {
+  sig[0] = c.cm11 * s[0] + c.cm12 * s[1]; sig[1] = c.cm12 * s[0] + c.cm11 * s[1]; sig[2] = c.cm33 * s[2];
+  sig[3] = c.cb11 * s[3] + c.cb12 * s[4]; sig[4] = c.cb12 * s[3] + c.cb11 * s[4]; sig[5] = c.cb33 * s[5];
+  sig[6] = c.cs * s[6]; sig[7] = c.cs * s[7]; sig[8] = c.cd * s[8];
+}
+
+template <int OP>
+__global__ void __launch_bounds__(128) k_cell_op(CellArgs A) {
+  __shared__ double s_w[4][40], s_l[4][40];
+  const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t cell = blockIdx.x * 4LL + wid;
+  if (cell >= A.nc) return;
+  const Tables* tab = A.tab;
+  int32_t vid[4];
+  V3 xv[4], uh[4];
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    vid[v] = A.cv[cell * 4 + v];
+    xv[v] = ldv3(A.xyz + 3 * (int64_t)vid[v]);
+    if (A.uhat) uh[v] = ldv3(A.uhat + 3 * (int64_t)vid[v]);
+  }
+  constexpr bool need_w = (OP == OP_PARAM_T || OP == OP_PARAM_FWD || OP == OP_MASS_U || OP == OP_UU);
+  constexpr bool need_l = (OP == OP_PARAM_T || OP == OP_F_T);
+  if (need_w || need_l) {
+    for (int i = lane; i < 39; i += 32) {
+      int64_t d = 3 * (int64_t)A.cb[cell * 13 + i / 3] + (i % 3);
+      if (need_w) s_w[wid][i] = A.vec_w[d];
+      if (need_l) s_l[wid][i] = A.vec_l[d];
+    }
+    __syncwarp();
+  }
+  const bool active = lane < A.nq;
+  const int q = active ? lane : 0;
+  QpGeom g;
+  qp_geometry(xv, (A.uhat && OP != OP_REG && OP != OP_REG_GRAD) ? uh : nullptr, tab->X0[q], tab->X1[q], g);
+  const double wd = active ? tab->W[q] * g.detJ : 0.0;
+  const double wJ = wd * g.Ju;
+  double hq = 0, Eq = 0, nuq = 0, rhoq = 0;
+  if (A.ewm) { hq = A.h[cell]; Eq = A.E[cell]; nuq = A.nu[cell]; rhoq = A.rho[cell]; }
+  else {
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      double N = tab->n1[q][v];
+      hq += N * A.h[vid[v]]; Eq += N * A.E[vid[v]]; nuq += N * A.nu[vid[v]]; rhoq += N * A.rho[vid[v]];
+    }
+  }
+  double* out = A.out + cell * A.out_stride;
+
+  if (OP == OP_PARAM_T || OP == OP_PARAM_FWD) {
+    Coefs cf = clt_coefs(hq, Eq, nuq, A.hE[cell], g.Ju, A.mode);
+    double s[9], sig[9];
+    strains_at(g, tab, q, s_w[wid], s);
+    apply_D(cf, s, sig);
+    if (OP == OP_PARAM_T) {
+      double sl[9];
+      strains_at(g, tab, q, s_l[wid], sl);
+      double gq = 0;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) gq += sl[i] * sig[i];
+      gq *= wd;
+      if (A.ewm) { double t = lane_sum(gq); if (lane == 0) out[0] = t; }
+      else
+        for (int v = 0; v < 4; ++v) { double t = lane_sum(gq * tab->n1[q][v]); if (lane == 0) out[v] = t; }
+    } else {
+      // perturbation of the parameter at this point
+      double dp;
+      if (A.ewm) dp = A.vec_l[cell];
+      else { dp = 0; for (int v = 0; v < 4; ++v) dp += tab->n1[q][v] * A.vec_l[vid[v]]; }
+      double sc = wd * dp;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) sig[i] *= sc;
+      const double k00 = dot(g.Kx0, g.E0), k01 = dot(g.Kx0, g.E1), k10 = dot(g.Kx1, g.E0), k11 = dot(g.Kx1, g.E1);
+      const V3 gq0 = k00 * g.dE2_0 + k10 * g.dE2_1, gq1 = k01 * g.dE2_0 + k11 * g.dE2_1;
+      for (int a = 0; a < 9; ++a) {
+        double d0 = tab->dphi2[q][a][0] * k00 + tab->dphi2[q][a][1] * k10, d1 = tab->dphi2[q][a][0] * k01 + tab->dphi2[q][a][1] * k11;
+        URows R = u_rows(d0, d1, g.E0, g.E1, g.E2);
+        V3 r = sig[0] * R.e0 + sig[1] * R.e1 + sig[2] * R.e2 + sig[6] * R.g0 + sig[7] * R.g1 + sig[8] * R.dr;
+        double rx = lane_sum(r.x), ry = lane_sum(r.y), rz = lane_sum(r.z);
+        if (lane == 0) { out[3 * a] = rx; out[3 * a + 1] = ry; out[3 * a + 2] = rz; }
+      }
+      for (int b = 0; b < 4; ++b) {
+        double d0 = tab->dn1[q][b][0] * k00 + tab->dn1[q][b][1] * k10, d1 = tab->dn1[q][b][0] * k01 + tab->dn1[q][b][1] * k11;
+        TRows R = t_rows(tab->n1[q][b], d0, d1, g.E0, g.E1, g.E2, gq0, gq1);
+        V3 r = sig[3] * R.k0 + sig[4] * R.k1 + sig[5] * R.k2 + sig[6] * R.g0 + sig[7] * R.g1 + sig[8] * R.dr;
+        double rx = lane_sum(r.x), ry = lane_sum(r.y), rz = lane_sum(r.z);
+        if (lane == 0) { out[27 + 3 * b] = rx; out[27 + 3 * b + 1] = ry; out[27 + 3 * b + 2] = rz; }
+      }
+    }
+  } else if (OP == OP_F_T) {
+    V3 lu = v3(0, 0, 0);
+    for (int a = 0; a < 9; ++a) lu = lu + tab->phi2[q][a] * ldv3(s_l[wid] + 3 * a);
+    if (A.ewp) {
+      double x = lane_sum(-wJ * lu.x), y = lane_sum(-wJ * lu.y), z = lane_sum(-wJ * lu.z);
+      if (lane == 0) { out[0] = x; out[1] = y; out[2] = z; }
+    } else
+      for (int v = 0; v < 4; ++v) {
+        double sN = -wJ * tab->n1[q][v];
+        double x = lane_sum(sN * lu.x), y = lane_sum(sN * lu.y), z = lane_sum(sN * lu.z);
+        if (lane == 0) { out[3 * v] = x; out[3 * v + 1] = y; out[3 * v + 2] = z; }
+      }
+  } else if (OP == OP_F_FWD || OP == OP_MASS_U) {
+    V3 fq = v3(0, 0, 0);
+    if (OP == OP_F_FWD) {
+      if (A.ewp) fq = ldv3(A.vec_l + 3 * cell);
+      else for (int v = 0; v < 4; ++v) fq = fq + tab->n1[q][v] * ldv3(A.vec_l + 3 * (int64_t)vid[v]);
+      fq = (-1.0) * fq;
+    } else {
+      for (int a = 0; a < 9; ++a) fq = fq + tab->phi2[q][a] * ldv3(s_w[wid] + 3 * a);
+    }
+    for (int a = 0; a < 9; ++a) {
+      double sN = wJ * tab->phi2[q][a];
+      double x = lane_sum(sN * fq.x), y = lane_sum(sN * fq.y), z = lane_sum(sN * fq.z);
+      if (lane == 0) { out[3 * a] = x; out[3 * a + 1] = y; out[3 * a + 2] = z; }
+    }
+  } else if (OP == OP_UU) {
+    V3 u = v3(0, 0, 0);
+    for (int a = 0; a < 9; ++a) u = u + tab->phi2[q][a] * ldv3(s_w[wid] + 3 * a);
+    double t = lane_sum(wJ * dot(u, u));
+    if (lane == 0) out[0] = t;
+  } else if (OP == OP_MASS) {
+    double t = lane_sum(wJ * rhoq * hq);
+    if (lane == 0) out[0] = t;
+  } else if (OP == OP_DMASS_DH || OP == OP_DMASS_DRHO) {
+    double cq = wJ * (OP == OP_DMASS_DH ? rhoq : hq);
+    if (A.ewm) { double t = lane_sum(cq); if (lane == 0) out[0] = t; }
+    else
+      for (int v = 0; v < 4; ++v) { double t = lane_sum(cq * tab->n1[q][v]); if (lane == 0) out[v] = t; }
+  } else if (OP == OP_REG || OP == OP_REG_GRAD) {
+    // rm_shell_pde.py:64-83: 'L2' (DG0 thickness) 0.5 a1 h^2 dx ; 'H1' (CG1) 0.5 a1 |grad h|^2 dx
+    if (A.ewm) {
+      double t = lane_sum(OP == OP_REG ? 0.5 * FEMO_REG_ALPHA1 * wd * hq * hq : FEMO_REG_ALPHA1 * wd * hq);
+      if (lane == 0) out[0] = t;
+    } else {
+      V3 gN[4], gh = v3(0, 0, 0);
+      for (int v = 0; v < 4; ++v) {
+        gN[v] = tab->dn1[q][v][0] * g.Ki0 + tab->dn1[q][v][1] * g.Ki1;
+        gh = gh + A.h[vid[v]] * gN[v];
+      }
+      if (OP == OP_REG) {
+        double t = lane_sum(0.5 * FEMO_REG_ALPHA1 * wd * dot(gh, gh));
+        if (lane == 0) out[0] = t;
+      } else
+        for (int v = 0; v < 4; ++v) { double t = lane_sum(FEMO_REG_ALPHA1 * wd * dot(gN[v], gh)); if (lane == 0) out[v] = t; }
+    }
+  }
+}
+
+// out[block I, 0..2] = sum over adjacent cells (ascending) of cellbuf[cell*stride + off(a)]
+__global__ void k_node_gather(const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
+                              const double* __restrict__ cellbuf, int stride, int64_t first_block, int64_t nblocks,
+                              int local_shift, int ncomp, double* __restrict__ out) {
+  int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= nblocks) return;
+  int64_t I = first_block + t;
+  double a0 = 0, a1 = 0, a2 = 0;
+  for (int32_t k = nc_ptr[I]; k < nc_ptr[I + 1]; ++k) {
+    int32_t e = nc_adj[k];
+    int64_t cell = e / 13; int a = e - (int32_t)cell * 13 - local_shift;
+    const double* s = cellbuf + cell * stride + a * ncomp;
+    a0 += s[0];
+    if (ncomp == 3) { a1 += s[1]; a2 += s[2]; }
+  }
+  if (ncomp == 3) { out[3 * t] = a0; out[3 * t + 1] = a1; out[3 * t + 2] = a2; }
+  else out[t] = a0;
+}
+
+__global__ void k_copy_strided(const double* __restrict__ src, int stride, int64_t n, double* __restrict__ dst) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[i * stride];
+}
+__global__ void k_copy_cell3(const double* __restrict__ src, int stride, int64_t n, double* __restrict__ dst) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) { dst[3 * i] = src[i * stride]; dst[3 * i + 1] = src[i * stride + 1]; dst[3 * i + 2] = src[i * stride + 2]; }
+}
+__global__ void k_scale(double* x, int64_t n, double s) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) x[i] *= s;
+}
+// deterministic sum of cellbuf[cell*stride] over all cells: fixed grid, fixed order
+__global__ void __launch_bounds__(256) k_sum_cells(const double* __restrict__ buf, int stride, int64_t n, double* __restrict__ part) {
+  __shared__ double s[8];
+  double v = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x) v += buf[i * stride];
+  v = lane_sum(v);
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) { double t = 0; for (int i = 0; i < 8; ++i) t += s[i]; part[blockIdx.x] = t; }
+}
+__global__ void k_sum_final(const double* __restrict__ part, int n, double* out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) { double t = 0; for (int i = 0; i < n; ++i) t += part[i]; *out = t; }
+}
+
+CellArgs base_args(femo_ctx* c) {
+  CellArgs A;
+  A.xyz = c->xyz; A.cv = c->cv; A.cb = c->cell_blocks; A.uhat = c->uhat_zero ? nullptr : c->uhat;
+  A.h = c->h; A.E = c->E; A.nu = c->nu; A.rho = c->rho; A.f = c->f; A.hE = c->hE; A.tab = c->tab;
+  A.nc = c->nc; A.nq = c->nq; A.ewm = c->ewm; A.ewp = c->ewp;
+  A.vec_w = c->w; A.vec_l = nullptr; A.mode = 0; A.out = c->cellbuf; A.out_stride = 39;
+  return A;
+}
+
+template <int OP>
+int run_cell_op(femo_ctx* c, const CellArgs& A) {
+  k_cell_op<OP><<<(unsigned)cdiv(c->nc, 4), 128, 0, c->stream>>>(A);
+  TRY(check_launch(c, "k_cell_op"));
+  c->launches += 1;
+  return 0;
+}
+
+int sum_cells(femo_ctx* c, double* val) {
+  const int NB = 296;
+  double* part = c->red + 6 * 1184;
+  k_sum_cells<<<NB, 256, 0, c->stream>>>(c->cellbuf, 39, c->nc, part);
+  k_sum_final<<<1, 32, 0, c->stream>>>(part, NB, c->scal + 9);
+  TRY(check_launch(c, "k_sum_cells"));
+  c->launches += 2;
+  CUDA_TRY(cudaMemcpyAsync(val, c->scal + 9, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// material-parameter shaped result: vertex gather (CG1) or per-cell copy (DG0)
+int gather_material(femo_ctx* c, double* out) {
+  if (c->ewm) k_copy_strided<<<(unsigned)cdiv(c->nc, 256), 256, 0, c->stream>>>(c->cellbuf, 39, c->nc, out);
+  else k_node_gather<<<(unsigned)cdiv(c->nn, 256), 256, 0, c->stream>>>(c->nc_ptr, c->nc_adj, c->cellbuf, 39, c->nq2, c->nn, 9, 1, out);
+  TRY(check_launch(c, "gather_material"));
+  c->launches += 1;
+  return 0;
+}
+
+int gather_dofs(femo_ctx* c, double* out, bool with_theta) {
+  k_node_gather<<<(unsigned)cdiv(c->nq2, 256), 256, 0, c->stream>>>(c->nc_ptr, c->nc_adj, c->cellbuf, 39, 0, c->nq2, 0, 3, out);
+  if (with_theta)
+    k_node_gather<<<(unsigned)cdiv(c->nn, 256), 256, 0, c->stream>>>(c->nc_ptr, c->nc_adj, c->cellbuf, 39, c->nq2, c->nn, 0, 3,
+                                                                    out + 3 * c->nq2);
+  else CUDA_TRY(cudaMemsetAsync(out + 3 * c->nq2, 0, sizeof(double) * 3 * c->nn, c->stream));
+  TRY(check_launch(c, "gather_dofs"));
+  c->launches += with_theta ? 2 : 1;
+  return 0;
+}
+
+int mode_of(int arg) { return arg == FEMO_THICKNESS ? 1 : arg == FEMO_E ? 2 : arg == FEMO_NU ? 3 : -1; }
+
+}  // namespace
+
+int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out) {
+  CellArgs A = base_args(c);
+  A.vec_l = lam;
+  if (arg == FEMO_F_SOLID) {
+    TRY(run_cell_op<OP_F_T>(c, A));
+    if (c->ewp) k_copy_cell3<<<(unsigned)cdiv(c->nc, 256), 256, 0, c->stream>>>(c->cellbuf, 39, c->nc, out);
+    else k_node_gather<<<(unsigned)cdiv(c->nn, 256), 256, 0, c->stream>>>(c->nc_ptr, c->nc_adj, c->cellbuf, 39, c->nq2, c->nn, 9, 3, out);
+    TRY(check_launch(c, "dRdF^T"));
+    c->launches += 1;
+    return 0;
+  }
+  A.mode = mode_of(arg);
+  if (A.mode < 0) return femo_fail("femo_dRdf_T_apply: argument not supported (thickness, F_solid, E, nu)");
+  TRY(run_cell_op<OP_PARAM_T>(c, A));
+  return gather_material(c, out);
+}
+
+int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out) {
+  CellArgs A = base_args(c);
+  A.vec_l = df;
+  if (arg == FEMO_F_SOLID) {
+    TRY(run_cell_op<OP_F_FWD>(c, A));
+    return gather_dofs(c, out, false);
+  }
+  A.mode = mode_of(arg);
+  if (A.mode < 0) return femo_fail("femo_dRdf_apply: argument not supported (thickness, F_solid, E, nu)");
+  TRY(run_cell_op<OP_PARAM_FWD>(c, A));
+  return gather_dofs(c, out, true);
+}
+
+int out_scalar(femo_ctx* c, int which, double* val) {
+  CellArgs A = base_args(c);
+  if (which == FEMO_COMPLIANCE) {
+    double uu = 0, reg = 0;
+    TRY(run_cell_op<OP_UU>(c, A)); TRY(sum_cells(c, &uu));
+    TRY(run_cell_op<OP_REG>(c, A)); TRY(sum_cells(c, &reg));
+    *val = uu + reg;
+    return 0;
+  }
+  if (which == FEMO_MASS) { TRY(run_cell_op<OP_MASS>(c, A)); return sum_cells(c, val); }
+  if (which == FEMO_ELASTIC_ENERGY) {
+    if (!c->jac_valid) TRY(assemble_jacobian(c));
+    TRY(bsr_spmv(c, c->w, c->tmp, 0));
+    TRY(penalty_apply(c, c->w, c->tmp, -1.0));
+    double d = 0;
+    TRY(dev_dot(c, c->w, c->tmp, c->ndof, &d));
+    *val = 0.5 * d;
+    return 0;
+  }
+  return femo_fail("femo_output: output not implemented");
+}
+
+int out_grad(femo_ctx* c, int which, int arg, double* g) {
+  CellArgs A = base_args(c);
+  const int64_t n_arg = (arg == FEMO_ARG_STATE) ? c->ndof : (arg == FEMO_F_SOLID) ? c->n_f : (arg == FEMO_UHAT) ? 3 * c->nn : c->n_mat;
+  if (arg == FEMO_UHAT) return femo_fail("derivatives w.r.t. uhat (shape) are not implemented");
+  if (which == FEMO_COMPLIANCE) {
+    if (arg == FEMO_ARG_STATE) {
+      TRY(run_cell_op<OP_MASS_U>(c, A));
+      TRY(gather_dofs(c, g, false));
+      k_scale<<<(unsigned)cdiv(c->ndof, 256), 256, 0, c->stream>>>(g, c->ndof, 2.0);
+      c->launches += 1;
+      return check_launch(c, "k_scale");
+    }
+    if (arg == FEMO_THICKNESS) { TRY(run_cell_op<OP_REG_GRAD>(c, A)); return gather_material(c, g); }
+    CUDA_TRY(cudaMemsetAsync(g, 0, sizeof(double) * n_arg, c->stream));
+    return 0;
+  }
+  if (which == FEMO_MASS) {
+    if (arg == FEMO_THICKNESS) { TRY(run_cell_op<OP_DMASS_DH>(c, A)); return gather_material(c, g); }
+    if (arg == FEMO_DENSITY) { TRY(run_cell_op<OP_DMASS_DRHO>(c, A)); return gather_material(c, g); }
+    CUDA_TRY(cudaMemsetAsync(g, 0, sizeof(double) * n_arg, c->stream));
+    return 0;
+  }
+  if (which == FEMO_ELASTIC_ENERGY) {
+    if (arg == FEMO_ARG_STATE) {
+      if (!c->jac_valid) TRY(assemble_jacobian(c));
+      TRY(bsr_spmv(c, c->w, g, 0));
+      return penalty_apply(c, c->w, g, -1.0);
+    }
+    if (arg == FEMO_THICKNESS || arg == FEMO_E || arg == FEMO_NU) {
+      TRY(dRdf_T_apply(c, arg, c->w, g));
+      k_scale<<<(unsigned)cdiv(c->n_mat, 256), 256, 0, c->stream>>>(g, c->n_mat, 0.5);
+      c->launches += 1;
+      return check_launch(c, "k_scale");
+    }
+    CUDA_TRY(cudaMemsetAsync(g, 0, sizeof(double) * n_arg, c->stream));
+    return 0;
+  }
+  return femo_fail("femo_output_grad: output not implemented");
+}

@@ -1,0 +1,430 @@
+// BSR(3x3) SpMV, block-Jacobi preconditioner and PCG for the state and adjoint solves.
+//
+// Replaces PETSc KSP preonly+LU(MUMPS) (femo_alpha/fea/utils_dolfinx.py:438-468,514-531;
+// fea/fea_dolfinx.py:173-203) and MatMult (utils_dolfinx.py:275-306).  A = dR/du with the
+// dolfinx BC convention (rows+cols of clamped dofs zeroed, unit diagonal) is applied on the
+// fly through `bcmask`, so only one matrix is stored.
+//
+// All reductions are two-stage with fixed grids and fixed summation order -> bitwise
+// reproducible iterations (no floating-point atomics anywhere).
+#include "femo_internal.cuh"
+
+#define RED_BLOCKS 1184          /* 148 SMs x 8 */
+#define RED_THREADS 256
+
+namespace {
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// deterministic CTA reduction of up to 3 values; result valid in thread 0
+__device__ __forceinline__ void block_sum3(double& a, double& b, double& c) {
+  __shared__ double sa[32], sb[32], sc[32];
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+  if (lane == 0) { sa[wid] = a; sb[wid] = b; sc[wid] = c; }
+  __syncthreads();
+  if (wid == 0) {
+    int nw = (blockDim.x + 31) >> 5;
+    a = lane < nw ? sa[lane] : 0.0; b = lane < nw ? sb[lane] : 0.0; c = lane < nw ? sc[lane] : 0.0;
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+  }
+  __syncthreads();
+}
+
+// every CTA sums the same partial array in the same order -> identical scalar everywhere
+__device__ __forceinline__ double sum_partials(const double* __restrict__ part, int n) {
+  __shared__ double s[32];
+  __shared__ double result;
+  double v = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) v += part[i];
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  v = warp_sum(v);
+  if (lane == 0) s[wid] = v;
+  __syncthreads();
+  if (wid == 0) {
+    int nw = (blockDim.x + 31) >> 5;
+    v = lane < nw ? s[lane] : 0.0;
+    v = warp_sum(v);
+    if (lane == 0) result = v;
+  }
+  __syncthreads();
+  double r = result;
+  __syncthreads();
+  return r;
+}
+
+// y = K x (with_bc = 0) or y = A x (with_bc = 1).  LANES lanes cooperate on one block row.
+// Optionally accumulates the partial dot x.y per CTA (deterministic) into dot_part[blockIdx.x].
+template <int LANES>
+__global__ void __launch_bounds__(256)
+k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const double* __restrict__ vals,
+       const double* __restrict__ x, const double* __restrict__ mask, int64_t nb, double* __restrict__ y,
+       double* __restrict__ dot_part) {
+  const int lane = threadIdx.x % LANES;
+  const int64_t grp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / LANES;
+  const int64_t ngrp = (gridDim.x * (int64_t)blockDim.x) / LANES;
+  double dacc = 0.0;
+  for (int64_t row = grp; row < nb; row += ngrp) {
+    const int32_t s = rowptr[row], e = rowptr[row + 1];
+    double y0 = 0, y1 = 0, y2 = 0;
+    for (int32_t k = s + lane; k < e; k += LANES) {
+      const int64_t col = colidx[k];
+      const double* a = vals + (int64_t)k * 9;
+      double x0 = x[3 * col], x1 = x[3 * col + 1], x2 = x[3 * col + 2];
+      if (mask) { x0 *= mask[3 * col]; x1 *= mask[3 * col + 1]; x2 *= mask[3 * col + 2]; }
+      y0 += a[0] * x0 + a[1] * x1 + a[2] * x2;
+      y1 += a[3] * x0 + a[4] * x1 + a[5] * x2;
+      y2 += a[6] * x0 + a[7] * x1 + a[8] * x2;
+    }
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) {
+      y0 += __shfl_down_sync(0xffffffffu, y0, o, LANES);
+      y1 += __shfl_down_sync(0xffffffffu, y1, o, LANES);
+      y2 += __shfl_down_sync(0xffffffffu, y2, o, LANES);
+    }
+    if (lane == 0) {
+      double xr0 = x[3 * row], xr1 = x[3 * row + 1], xr2 = x[3 * row + 2];
+      if (mask) {
+        double m0 = mask[3 * row], m1 = mask[3 * row + 1], m2 = mask[3 * row + 2];
+        y0 = m0 * y0 + (1.0 - m0) * xr0; y1 = m1 * y1 + (1.0 - m1) * xr1; y2 = m2 * y2 + (1.0 - m2) * xr2;
+      }
+      y[3 * row] = y0; y[3 * row + 1] = y1; y[3 * row + 2] = y2;
+      dacc += xr0 * y0 + xr1 * y1 + xr2 * y2;
+    }
+  }
+  if (dot_part) {
+    double b = 0, c2 = 0;
+    block_sum3(dacc, b, c2);
+    if (threadIdx.x == 0) dot_part[blockIdx.x] = dacc;
+  }
+}
+
+// y[row] += sign * sum_d pen_val[d] * x[col(d)]  (penalty part of dR/du, identity 3x3 blocks)
+__global__ void k_penalty_apply(const int32_t* __restrict__ prow, const int32_t* __restrict__ prow_ptr,
+                                const int32_t* __restrict__ dcol, const double* __restrict__ pval, int64_t nrows,
+                                const double* __restrict__ x, double sign, double* __restrict__ y) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= nrows) return;
+  double a0 = 0, a1 = 0, a2 = 0;
+  for (int32_t d = prow_ptr[i]; d < prow_ptr[i + 1]; ++d) {
+    int64_t cidx = dcol[d]; double v = pval[d];
+    a0 += v * x[3 * cidx]; a1 += v * x[3 * cidx + 1]; a2 += v * x[3 * cidx + 2];
+  }
+  int64_t r = prow[i];
+  y[3 * r] += sign * a0; y[3 * r + 1] += sign * a1; y[3 * r + 2] += sign * a2;
+}
+
+// in-place Gauss-Jordan inverse of an SPD n x n matrix (n = 3 or 6), no pivoting needed
+template <int N>
+__device__ __forceinline__ void spd_inverse(double* A) {
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    double ip = 1.0 / A[k * N + k];
+    A[k * N + k] = 1.0;
+#pragma unroll
+    for (int j = 0; j < N; ++j) A[k * N + j] *= ip;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      if (i == k) continue;
+      double f = A[i * N + k];
+      A[i * N + k] = 0.0;
+#pragma unroll
+      for (int j = 0; j < N; ++j) A[i * N + j] -= f * A[k * N + j];
+    }
+  }
+}
+
+// block-Jacobi set-up: 6x6 (u_v, theta_v) at vertices, 3x3 at edge / centre nodes, of A (with BCs)
+__global__ void k_precond_setup(const double* __restrict__ vals, const int32_t* __restrict__ diag_pos,
+                                const int32_t* __restrict__ ut_pos, const int32_t* __restrict__ tu_pos,
+                                const double* __restrict__ mask, int64_t nn, int64_t nq2,
+                                double* __restrict__ dinv6, double* __restrict__ dinv3) {
+  int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= nq2) return;
+  if (I < nn) {
+    double A[36];
+    const double* uu = vals + (int64_t)diag_pos[I] * 9;
+    const double* tt = vals + (int64_t)diag_pos[nq2 + I] * 9;
+    const double* ut = vals + (int64_t)ut_pos[I] * 9;
+    const double* tu = vals + (int64_t)tu_pos[I] * 9;
+    double m[6];
+    for (int i = 0; i < 3; ++i) { m[i] = mask[3 * I + i]; m[3 + i] = mask[3 * (nq2 + I) + i]; }
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) {
+        A[i * 6 + j] = uu[3 * i + j]; A[i * 6 + 3 + j] = ut[3 * i + j];
+        A[(3 + i) * 6 + j] = tu[3 * i + j]; A[(3 + i) * 6 + 3 + j] = tt[3 * i + j];
+      }
+    for (int i = 0; i < 6; ++i)
+      for (int j = 0; j < 6; ++j) A[i * 6 + j] = m[i] * m[j] * A[i * 6 + j] + ((i == j) ? (1.0 - m[i]) : 0.0);
+    spd_inverse<6>(A);
+    for (int i = 0; i < 36; ++i) dinv6[I * 36 + i] = A[i];
+  } else {
+    double A[9];
+    const double* uu = vals + (int64_t)diag_pos[I] * 9;
+    double m[3] = {mask[3 * I], mask[3 * I + 1], mask[3 * I + 2]};
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) A[3 * i + j] = m[i] * m[j] * uu[3 * i + j] + ((i == j) ? (1.0 - m[i]) : 0.0);
+    spd_inverse<3>(A);
+    for (int i = 0; i < 9; ++i) dinv3[(I - nn) * 9 + i] = A[i];
+  }
+}
+
+// z = M^-1 r for the node owned by this thread
+__device__ __forceinline__ void precond_node(int64_t I, int64_t nn, int64_t nq2, const double* __restrict__ dinv6,
+                                             const double* __restrict__ dinv3, const double* rl, double* zl) {
+  if (I < nn) {
+    const double* D = dinv6 + I * 36;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      double s = 0;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) s += D[i * 6 + j] * rl[j];
+      zl[i] = s;
+    }
+  } else {
+    const double* D = dinv3 + (I - nn) * 9;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) zl[i] = D[3 * i] * rl[0] + D[3 * i + 1] * rl[1] + D[3 * i + 2] * rl[2];
+  }
+}
+
+// PCG initialisation: r = b - Ax (Ax given), z = M^-1 r, p = z; partials of r.z, r.r, b.b
+__global__ void __launch_bounds__(RED_THREADS)
+k_pcg_init(const double* __restrict__ b, const double* __restrict__ Ax, const double* __restrict__ dinv6,
+           const double* __restrict__ dinv3, int64_t nn, int64_t nq2, double* __restrict__ r, double* __restrict__ z,
+           double* __restrict__ p, double* __restrict__ part_rz, double* __restrict__ part_rr,
+           double* __restrict__ part_bb) {
+  double rz = 0, rr = 0, bb = 0;
+  for (int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; I < nq2; I += gridDim.x * (int64_t)blockDim.x) {
+    int nd = I < nn ? 6 : 3;
+    double rl[6], zl[6];
+    for (int i = 0; i < nd; ++i) {
+      int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+      double bv = b[d];
+      rl[i] = bv - Ax[d];
+      bb += bv * bv;
+    }
+    precond_node(I, nn, nq2, dinv6, dinv3, rl, zl);
+    for (int i = 0; i < nd; ++i) {
+      int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+      r[d] = rl[i]; z[d] = zl[i]; p[d] = zl[i];
+      rz += rl[i] * zl[i]; rr += rl[i] * rl[i];
+    }
+  }
+  block_sum3(rz, rr, bb);
+  if (threadIdx.x == 0) { part_rz[blockIdx.x] = rz; part_rr[blockIdx.x] = rr; part_bb[blockIdx.x] = bb; }
+}
+
+// alpha = rz_old / pAp; x += alpha p; r -= alpha Ap; z = M^-1 r; partials of r.z and r.r
+__global__ void __launch_bounds__(RED_THREADS)
+k_pcg_update(const double* __restrict__ part_pAp, int n_pAp, const double* __restrict__ part_rz_old,
+             const double* __restrict__ p, const double* __restrict__ Ap, const double* __restrict__ dinv6,
+             const double* __restrict__ dinv3, int64_t nn, int64_t nq2, double* __restrict__ x,
+             double* __restrict__ r, double* __restrict__ z, double* __restrict__ part_rz_new,
+             double* __restrict__ part_rr) {
+  const double pAp = sum_partials(part_pAp, n_pAp);
+  const double rz_old = sum_partials(part_rz_old, RED_BLOCKS);
+  const double alpha = (pAp != 0.0) ? rz_old / pAp : 0.0;
+  double rz = 0, rr = 0, dummy = 0;
+  for (int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; I < nq2; I += gridDim.x * (int64_t)blockDim.x) {
+    int nd = I < nn ? 6 : 3;
+    double rl[6], zl[6];
+    for (int i = 0; i < nd; ++i) {
+      int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+      x[d] += alpha * p[d];
+      rl[i] = r[d] - alpha * Ap[d];
+    }
+    precond_node(I, nn, nq2, dinv6, dinv3, rl, zl);
+    for (int i = 0; i < nd; ++i) {
+      int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+      r[d] = rl[i]; z[d] = zl[i];
+      rz += rl[i] * zl[i]; rr += rl[i] * rl[i];
+    }
+  }
+  block_sum3(rz, rr, dummy);
+  if (threadIdx.x == 0) { part_rz_new[blockIdx.x] = rz; part_rr[blockIdx.x] = rr; }
+}
+
+// beta = rz_new / rz_old; p = z + beta p; CTA 0 publishes r.r
+__global__ void __launch_bounds__(RED_THREADS)
+k_pcg_dir(const double* __restrict__ part_rz_new, const double* __restrict__ part_rz_old,
+          const double* __restrict__ part_rr, const double* __restrict__ z, int64_t n, double* __restrict__ p,
+          double* __restrict__ rr_out) {
+  const double rzn = sum_partials(part_rz_new, RED_BLOCKS);
+  const double rzo = sum_partials(part_rz_old, RED_BLOCKS);
+  const double beta = (rzo != 0.0) ? rzn / rzo : 0.0;
+  if (blockIdx.x == 0) {
+    double rr = sum_partials(part_rr, RED_BLOCKS);
+    if (threadIdx.x == 0) *rr_out = rr;
+  }
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x)
+    p[i] = z[i] + beta * p[i];
+}
+
+__global__ void __launch_bounds__(RED_THREADS)
+k_dot(const double* __restrict__ a, const double* __restrict__ b, int64_t n, double* __restrict__ part) {
+  double s = 0, u = 0, v = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x) s += a[i] * b[i];
+  block_sum3(s, u, v);
+  if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+__global__ void k_sum_partials(const double* __restrict__ part, int n, double* __restrict__ out) {
+  double v = sum_partials(part, n);
+  if (threadIdx.x == 0) *out = v;
+}
+
+// ---- roofline denominators -------------------------------------------------------------
+__global__ void k_fma_peak(double* out, int iters) {
+  double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 0.999999, c = 1e-6;
+  for (int i = 0; i < iters; ++i) {
+    a0 = a0 * m + c; a1 = a1 * m + c; a2 = a2 * m + c; a3 = a3 * m + c;
+    a4 = a4 * m + c; a5 = a5 * m + c; a6 = a6 * m + c; a7 = a7 * m + c;
+  }
+  out[blockIdx.x * (int64_t)blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+__global__ void k_copy(const double4* __restrict__ a, double4* __restrict__ b, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x) b[i] = a[i];
+}
+
+}  // namespace
+
+#define SPMV_BLOCKS (148 * 8)
+
+int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc) {
+  if (!c->jac_valid) return femo_fail("Jacobian not assembled");
+  k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, x, with_bc ? c->bcmask : nullptr, c->nb, y,
+                                                 nullptr);
+  TRY(check_launch(c, "k_spmv"));
+  c->launches += 1;
+  return 0;
+}
+
+int penalty_apply(femo_ctx* c, const double* x, double* y, double sign) {
+  if (c->n_pen_rows == 0) return 0;
+  k_penalty_apply<<<(unsigned)cdiv(c->n_pen_rows, 128), 128, 0, c->stream>>>(c->pen_row, c->pen_row_ptr, c->pen_dest_col,
+                                                                           c->pen_val, c->n_pen_rows, x, sign, y);
+  TRY(check_launch(c, "k_penalty_apply"));
+  c->launches += 1;
+  return 0;
+}
+
+int precond_setup(femo_ctx* c) {
+  if (!c->jac_valid) return femo_fail("Jacobian not assembled");
+  k_precond_setup<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(c->vals, c->diag_pos, c->ut_pos, c->tu_pos, c->bcmask,
+                                                                     c->nn, c->nq2, c->dinv6, c->dinv3);
+  TRY(check_launch(c, "k_precond_setup"));
+  c->launches += 1;
+  c->prec_valid = true;
+  return 0;
+}
+
+int dev_dot(femo_ctx* c, const double* a, const double* b, int64_t n, double* out) {
+  double* part = c->red + 6 * RED_BLOCKS;
+  k_dot<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(a, b, n, part);
+  k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(part, RED_BLOCKS, c->scal + 8);
+  TRY(check_launch(c, "k_dot"));
+  c->launches += 2;
+  CUDA_TRY(cudaMemcpyAsync(out, c->scal + 8, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// red layout: [0]=pAp partials (SPMV_BLOCKS) | [1],[2] = rz ping-pong | [3] = rr | [4] = bb | [5] spare | [6] dot
+int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, int* iters, double* relres,
+              bool fixed_iters) {
+  if (!c->jac_valid) return femo_fail("pcg: Jacobian not assembled");
+  if (!c->prec_valid) TRY(precond_setup(c));
+  double* P_pAp = c->red;
+  double* P_rz[2] = {c->red + 1 * SPMV_BLOCKS, c->red + 2 * SPMV_BLOCKS};
+  double* P_rr = c->red + 3 * SPMV_BLOCKS;
+  double* P_bb = c->red + 4 * SPMV_BLOCKS;
+  const int64_t n = c->ndof;
+  cudaEventRecord(c->ev0, c->stream);
+  // r0 = b - A x0
+  k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, x, c->bcmask, c->nb, c->Ap, nullptr);
+  k_pcg_init<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(b, c->Ap, c->dinv6, c->dinv3, c->nn, c->nq2, c->r, c->z, c->p,
+                                                        P_rz[0], P_rr, P_bb);
+  k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_bb, RED_BLOCKS, c->scal + 0);
+  k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_rr, RED_BLOCKS, c->scal + 1);
+  TRY(check_launch(c, "pcg init"));
+  c->launches += 4;
+  double hs[2];
+  CUDA_TRY(cudaMemcpyAsync(hs, c->scal, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  const double bb = hs[0];
+  double rr = hs[1];
+  const double bnorm = sqrt(bb);
+  int it = 0;
+  double rel = bnorm > 0 ? sqrt(rr) / bnorm : 0.0;
+  if (bnorm == 0.0 && !fixed_iters) {
+    CUDA_TRY(cudaMemsetAsync(x, 0, sizeof(double) * n, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    *iters = 0; *relres = 0.0; c->t_solve = 0; c->t_iter = 0;
+    return 0;
+  }
+  const int check_every = 25;
+  bool done = (!fixed_iters && rel <= rtol);
+  while (!done && it < max_it) {
+    int nloop = std::min(check_every, max_it - it);
+    for (int k = 0; k < nloop; ++k, ++it) {
+      int cur = it & 1, nxt = cur ^ 1;
+      k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->p, c->bcmask, c->nb, c->Ap, P_pAp);
+      k_pcg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_pAp, SPMV_BLOCKS, P_rz[cur], c->p, c->Ap, c->dinv6,
+                                                              c->dinv3, c->nn, c->nq2, x, c->r, c->z, P_rz[nxt], P_rr);
+      k_pcg_dir<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_rz[nxt], P_rz[cur], P_rr, c->z, n, c->p, c->scal + 1);
+    }
+    c->launches += 3 * (int64_t)nloop;
+    TRY(check_launch(c, "pcg iteration"));
+    CUDA_TRY(cudaMemcpyAsync(&rr, c->scal + 1, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    rel = sqrt(rr) / bnorm;
+    if (!(rel == rel)) return femo_fail("pcg: NaN residual (matrix not SPD?)");
+    if (!fixed_iters && rel <= rtol) done = true;
+  }
+  cudaEventRecord(c->ev1, c->stream);
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  c->t_solve = ms; c->t_iter = it > 0 ? ms / it : 0.0;
+  *iters = it; *relres = rel;
+  return 0;
+}
+
+int measure_peaks(femo_ctx* c, double* tf, double* gbs) {
+  // fp64 FMA chain: 8 independent chains/thread, 1024 threads x 148*4 CTAs
+  const int iters = 1 << 14, blocks = 148 * 8, threads = 512;
+  double* out = nullptr;
+  TRY(dev_alloc(&out, (size_t)blocks * threads));
+  k_fma_peak<<<blocks, threads, 0, c->stream>>>(out, 64);
+  cudaEventRecord(c->ev0, c->stream);
+  k_fma_peak<<<blocks, threads, 0, c->stream>>>(out, iters);
+  cudaEventRecord(c->ev1, c->stream);
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  *tf = 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) / 1e12;
+  dev_free(&out);
+  const int64_t nbytes = (int64_t)1 << 30;
+  double4 *a = nullptr, *b = nullptr;
+  TRY(dev_alloc(&a, nbytes / 32)); TRY(dev_alloc(&b, nbytes / 32));
+  CUDA_TRY(cudaMemsetAsync(a, 0, nbytes, c->stream));
+  k_copy<<<148 * 16, 256, 0, c->stream>>>(a, b, nbytes / 32);
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(c->ev0, c->stream);
+    k_copy<<<148 * 16, 256, 0, c->stream>>>(a, b, nbytes / 32);
+    cudaEventRecord(c->ev1, c->stream);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    best = ms < best ? ms : best;
+  }
+  *gbs = 2.0 * nbytes / (best * 1e-3) / 1e9;
+  dev_free(&a); dev_free(&b);
+  c->launches += 8;
+  return 0;
+}

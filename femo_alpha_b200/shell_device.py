@@ -1,0 +1,216 @@
+"""Thin Python handle on one libfemo_b200 context (one RM-shell problem resident on one B200).
+
+All arithmetic happens in the CUDA library; this class only marshals NumPy
+arrays (or torch CUDA tensors) across the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+
+class ShellDevice:
+    def __init__(self, nodes, quads, element_wise_material=False, elementwise_pressure=False,
+                 quadrature_degree=6, device=0):
+        self.lib = L.load()
+        self._ctx = C.c_void_p()
+        L.check(self.lib.femo_ctx_create(int(device), C.byref(self._ctx)))
+        xyz = np.ascontiguousarray(nodes, dtype=np.float64)
+        conn = np.ascontiguousarray(quads, dtype=np.int32)
+        if xyz.ndim != 2 or xyz.shape[1] != 3:
+            raise ValueError("nodes must have shape (n_nodes, 3)")
+        if conn.ndim != 2:
+            raise ValueError("connectivity must have shape (n_cells, nodes_per_cell)")
+        L.check(self.lib.femo_mesh_set(self._ctx, xyz.shape[0], L.ptr(xyz), conn.shape[0], conn.shape[1], L.ptr(conn)))
+        opts = L.ShellOpts(int(bool(element_wise_material)), int(bool(elementwise_pressure)), int(quadrature_degree), 0)
+        L.check(self.lib.femo_shell_setup(self._ctx, C.byref(opts)))
+        s = L.Sizes()
+        L.check(self.lib.femo_get_sizes(self._ctx, C.byref(s)))
+        self.sizes = s
+        self.nn, self.ne, self.nc = s.n_nodes, s.n_edges, s.n_cells
+        self.nb, self.ndof, self.nnzb = s.n_blocks, s.n_dof, s.nnz_blocks
+        self.nq2 = self.nn + self.ne + self.nc
+        self.n_mat, self.n_f = s.n_material, s.n_force
+        self.last_solve = dict(iters=0, relres=0.0)
+
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            self.lib.femo_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- helpers --------------------------------------------------------
+    def _arg_size(self, arg):
+        return {L.THICKNESS: self.n_mat, L.E: self.n_mat, L.NU: self.n_mat, L.DENSITY: self.n_mat,
+                L.F_SOLID: self.n_f, L.UHAT: 3 * self.nn, L.ARG_STATE: self.ndof}[arg]
+
+    @staticmethod
+    def _arg_id(arg):
+        if isinstance(arg, str):
+            if arg in ("disp_solid", "state"):
+                return L.ARG_STATE
+            return L.INPUT_IDS[arg]
+        return int(arg)
+
+    def set_stream(self, stream_ptr):
+        L.check(self.lib.femo_set_stream(self._ctx, C.c_void_p(stream_ptr)))
+
+    # ---- mesh-derived data -------------------------------------------------
+    def block_coords(self):
+        out = np.empty((self.nb, 3))
+        L.check(self.lib.femo_get_block_coords(self._ctx, L.ptr(out)))
+        return out
+
+    def cell_blocks(self):
+        out = np.empty((self.nc, 13), dtype=np.int32)
+        L.check(self.lib.femo_get_cell_blocks(self._ctx, L.ptr(out)))
+        return out
+
+    # ---- boundary conditions --------------------------------------------------
+    def set_strong_bc(self, dofs):
+        d = np.ascontiguousarray(dofs, dtype=np.int32)
+        L.check(self.lib.femo_set_strong_bc(self._ctx, d.size, L.ptr(d)))
+
+    def set_penalty_bc(self, vertex_on):
+        v = np.ascontiguousarray(vertex_on, dtype=np.uint8)
+        L.check(self.lib.femo_set_penalty_bc(self._ctx, v.size, L.ptr(v)))
+
+    # ---- inputs / state ----------------------------------------------------------
+    def set_input(self, name, values):
+        which = self._arg_id(name)
+        if isinstance(values, np.ndarray) or not hasattr(values, "data_ptr"):
+            values = np.ascontiguousarray(np.asarray(values, dtype=np.float64).ravel())
+            n = values.size
+        else:
+            n = values.numel()
+        L.check(self.lib.femo_set_input(self._ctx, which, L.ptr(values), n, L.on_device(values)))
+
+    def get_input(self, name):
+        which = self._arg_id(name)
+        out = np.empty(self._arg_size(which))
+        L.check(self.lib.femo_get_input(self._ctx, which, L.ptr(out), out.size, 0))
+        return out
+
+    def set_state(self, w):
+        w = np.ascontiguousarray(w, dtype=np.float64) if isinstance(w, np.ndarray) else w
+        L.check(self.lib.femo_set_state(self._ctx, L.ptr(w), L.on_device(w)))
+
+    def get_state(self, out=None):
+        if out is None:
+            out = np.empty(self.ndof)
+        L.check(self.lib.femo_get_state(self._ctx, L.ptr(out), L.on_device(out)))
+        return out
+
+    # ---- assembly --------------------------------------------------------------------
+    def assemble_jacobian(self):
+        L.check(self.lib.femo_assemble_jacobian(self._ctx))
+
+    def assemble_residual(self, w=None, out=None):
+        if out is None:
+            out = np.empty(self.ndof)
+        if w is not None and isinstance(w, np.ndarray):
+            w = np.ascontiguousarray(w, dtype=np.float64)
+        L.check(self.lib.femo_assemble_residual(self._ctx, L.ptr(w), L.ptr(out), L.on_device(out)))
+        return out
+
+    def assemble_load(self):
+        out = np.empty(self.ndof)
+        L.check(self.lib.femo_assemble_load(self._ctx, L.ptr(out), 0))
+        return out
+
+    def jacobian_apply(self, x, with_bc=False):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.empty(self.ndof)
+        L.check(self.lib.femo_jacobian_apply(self._ctx, L.ptr(x), L.ptr(y), int(with_bc), 0))
+        return y
+
+    def get_bsr(self, with_bc=False, values=True):
+        rowptr = np.empty(self.nb + 1, dtype=np.int32)
+        colidx = np.empty(self.nnzb, dtype=np.int32)
+        vals = np.empty((self.nnzb, 3, 3)) if values else None
+        L.check(self.lib.femo_get_bsr(self._ctx, L.ptr(rowptr), L.ptr(colidx), L.ptr(vals), int(with_bc)))
+        return rowptr, colidx, vals
+
+    def get_csr(self, with_bc=False):
+        """dR/du as scipy CSR (diagnostics / tests; the reference's getValuesCSR analogue)."""
+        import scipy.sparse as sp
+        rowptr, colidx, vals = self.get_bsr(with_bc)
+        return sp.bsr_matrix((vals, colidx, rowptr), shape=(self.ndof, self.ndof)).tocsr()
+
+    # ---- solves -------------------------------------------------------------------------
+    def solve_state(self, rtol=1e-12, max_it=200000):
+        it = C.c_int(0); rr = C.c_double(0.0)
+        L.check(self.lib.femo_solve_state(self._ctx, float(rtol), int(max_it), C.byref(it), C.byref(rr)))
+        self.last_solve = dict(iters=it.value, relres=rr.value)
+        return it.value, rr.value
+
+    def _solve(self, fn, rhs, rtol, max_it):
+        rhs = np.ascontiguousarray(rhs, dtype=np.float64)
+        out = np.empty(self.ndof)
+        it = C.c_int(0); rr = C.c_double(0.0)
+        L.check(fn(self._ctx, L.ptr(rhs), L.ptr(out), float(rtol), int(max_it), C.byref(it), C.byref(rr), 0))
+        self.last_solve = dict(iters=it.value, relres=rr.value)
+        return out
+
+    def solve_adjoint(self, rhs, rtol=1e-12, max_it=200000):
+        return self._solve(self.lib.femo_solve_adjoint, rhs, rtol, max_it)
+
+    def solve_forward(self, rhs, rtol=1e-12, max_it=200000):
+        return self._solve(self.lib.femo_solve_forward, rhs, rtol, max_it)
+
+    # ---- partials ---------------------------------------------------------------------------
+    def dRdf_T_apply(self, arg, lam):
+        a = self._arg_id(arg)
+        lam = np.ascontiguousarray(lam, dtype=np.float64)
+        out = np.empty(self._arg_size(a))
+        L.check(self.lib.femo_dRdf_T_apply(self._ctx, a, L.ptr(lam), L.ptr(out), 0))
+        return out
+
+    def dRdf_apply(self, arg, df):
+        a = self._arg_id(arg)
+        df = np.ascontiguousarray(df, dtype=np.float64)
+        out = np.empty(self.ndof)
+        L.check(self.lib.femo_dRdf_apply(self._ctx, a, L.ptr(df), L.ptr(out), 0))
+        return out
+
+    # ---- outputs ---------------------------------------------------------------------------------
+    def output(self, name):
+        v = C.c_double(0.0)
+        L.check(self.lib.femo_output(self._ctx, L.OUTPUT_IDS[name] if isinstance(name, str) else int(name), C.byref(v)))
+        return v.value
+
+    def output_grad(self, name, arg):
+        a = self._arg_id(arg)
+        out = np.empty(self._arg_size(a))
+        L.check(self.lib.femo_output_grad(self._ctx, L.OUTPUT_IDS[name] if isinstance(name, str) else int(name), a,
+                                          L.ptr(out), 0))
+        return out
+
+    # ---- instrumentation ------------------------------------------------------------------------------
+    def launch_count(self):
+        n = C.c_int64(0)
+        L.check(self.lib.femo_launch_count(self._ctx, C.byref(n)))
+        return n.value
+
+    def last_timings(self):
+        t = (C.c_double * 4)()
+        L.check(self.lib.femo_last_timings(self._ctx, t))
+        return dict(records_ms=t[0], gather_ms=t[1], solve_ms=t[2], iter_ms=t[3])
+
+    def pcg_fixed(self, n_iter):
+        ms = C.c_double(0.0)
+        L.check(self.lib.femo_pcg_fixed(self._ctx, int(n_iter), C.byref(ms)))
+        return ms.value
+
+    def measure_peaks(self):
+        tf = C.c_double(0.0); gb = C.c_double(0.0)
+        L.check(self.lib.femo_measure_peaks(self._ctx, C.byref(tf), C.byref(gb)))
+        return tf.value, gb.value

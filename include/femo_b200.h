@@ -1,0 +1,155 @@
+/* femo_b200.h -- C ABI of libfemo_b200.so: the B200 (sm_100a) replacement for the
+ * dolfinx/PETSc/MUMPS calls behind femo_alpha's Reissner-Mindlin shell hot path.
+ *
+ * Every entry point returns 0 on success; on failure it returns non-zero and
+ * femo_last_error() describes why.  Plain pointers and sizes only.  Pointers
+ * flagged `on_device` may be CUDA device pointers (e.g. torch tensor
+ * data_ptr()); otherwise they are host pointers borrowed for the call.  All
+ * calls are synchronous with respect to the context's stream unless stated.
+ *
+ * The "replaces" notes cite /root/reference/femo_alpha/... (file:line).
+ *
+ * DOF numbering: 3x3 "block nodes".  Q2 displacement nodes first -- vertices
+ * [0,nn), edge mid-points [nn,nn+ne), cell centres [nn+ne,nq2) -- then the Q1
+ * rotation nodes nq2+v.  dof = 3*block + component.  (The reference's order is
+ * dolfinx-internal and opaque to its callers.)
+ */
+#ifndef FEMO_B200_H
+#define FEMO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct femo_ctx femo_ctx;
+
+/* inputs of the RM shell FEA: rm_shell/rm_shell_model.py:209-214 (fea.add_input) */
+enum femo_input {
+  FEMO_THICKNESS = 0, FEMO_F_SOLID = 1, FEMO_E = 2, FEMO_NU = 3, FEMO_DENSITY = 4, FEMO_UHAT = 5
+};
+/* scalar outputs: rm_shell/rm_shell_model.py:219-230 (fea.add_output) */
+enum femo_output_id {
+  FEMO_COMPLIANCE = 0, FEMO_MASS = 1, FEMO_ELASTIC_ENERGY = 2, FEMO_PNORM_STRESS = 3
+};
+/* pseudo-argument for femo_output_grad: derivative w.r.t. the state 'disp_solid' */
+#define FEMO_ARG_STATE 100
+
+typedef struct femo_shell_opts {
+  int32_t element_wise_material;   /* VT = DG0 instead of CG1     rm_shell_pde.py:36-40 */
+  int32_t elementwise_pressure;    /* VF = [DG0]^3 instead of CG1 rm_shell_pde.py:41-44 */
+  int32_t quadrature_degree;       /* Gauss-Legendre tensor rule, m=(deg+2)/2 points/dir; 0 -> 6 (4x4) */
+  int32_t reserved;
+} femo_shell_opts;
+
+typedef struct femo_sizes {
+  int64_t n_nodes, n_edges, n_cells;   /* nn, ne, nc */
+  int64_t n_blocks, n_dof;             /* nb = nq2+nn, n = 3 nb */
+  int64_t nnz_blocks;                  /* BSR 3x3 blocks of dR/du */
+  int64_t n_contrib;                   /* element-block contributions (169 per quad) */
+  int64_t n_material, n_force;         /* sizes of thickness/E/nu/density and of F_solid */
+  int32_t n_qp, all_planar;
+} femo_sizes;
+
+const char* femo_last_error(void);
+int femo_version(void);
+
+/* ---- context / mesh ------------------------------------------------------- */
+int femo_ctx_create(int device, femo_ctx** out);
+int femo_ctx_destroy(femo_ctx* ctx);
+/* run all kernels of this context on `cuda_stream` (a cudaStream_t); NULL = default stream */
+int femo_set_stream(femo_ctx* ctx, void* cuda_stream);
+
+/* replaces reconstructFEAMesh / readFEAMesh (fea/utils_dolfinx.py:34-50,653-668):
+ * xyz (n_nodes,3) row-major; conn (n_cells, nodes_per_cell) int32 in VTK/meshio cyclic
+ * order; nodes_per_cell must be 4 (quadrilaterals). */
+int femo_mesh_set(femo_ctx* ctx, int64_t n_nodes, const double* xyz,
+                  int64_t n_cells, int nodes_per_cell, const int32_t* conn);
+
+/* replaces RMShellPDE.__init__ + ShellElement (rm_shell_pde.py:25-47,
+ * linear_shell_model.py:26-106): builds edges, the Q2xQ1 block dofmap, the BSR pattern of
+ * dR/du and the cell->nnz contribution permutation used by the deterministic assembly. */
+int femo_shell_setup(femo_ctx* ctx, const femo_shell_opts* opts);
+int femo_get_sizes(femo_ctx* ctx, femo_sizes* out);
+/* coordinates of all n_blocks block nodes (dof coordinates of W.sub(0) / W.sub(1)),
+ * host buffer (n_blocks,3); used to evaluate shell_bc_func (rm_shell_model.py:168-180) */
+int femo_get_block_coords(femo_ctx* ctx, double* xyz_out);
+/* cell -> 13 block ids [9 Q2 (4 vertices, 4 edges, centre), 4 Q1], host (n_cells,13) */
+int femo_get_cell_blocks(femo_ctx* ctx, int32_t* out);
+
+/* ---- boundary conditions ---------------------------------------------------- */
+/* strong Dirichlet (PENALTY_BC=False, rm_shell_model.py:168-180): list of clamped dofs */
+int femo_set_strong_bc(femo_ctx* ctx, int64_t n, const int32_t* dofs);
+/* penalty Dirichlet (PENALTY_BC=True, rm_shell_model.py:83-98, linear_shell_model.py:323-333):
+ * vertex_on[v] != 0 where shell_bc_func holds; every mesh edge with both vertices on gets
+ * beta/h_E * int (w - g).dw ds from each adjacent cell. */
+int femo_set_penalty_bc(femo_ctx* ctx, int64_t n_nodes, const uint8_t* vertex_on);
+
+/* ---- inputs / state --------------------------------------------------------- */
+/* replaces utils_dolfinx.update (fea/utils_dolfinx.py:319-330): n == 1 broadcasts */
+int femo_set_input(femo_ctx* ctx, int which, const double* data, int64_t n, int on_device);
+int femo_get_input(femo_ctx* ctx, int which, double* out, int64_t n, int on_device);
+int femo_set_state(femo_ctx* ctx, const double* w, int on_device);
+int femo_get_state(femo_ctx* ctx, double* w, int on_device);
+
+/* ---- assembly ------------------------------------------------------------------ */
+/* replaces assembleMatrix(dR_du) / assembleSystem / NonlinearProblem.J
+ * (fea/utils_dolfinx.py:200-221; csdl_alpha_opt/state_operation.py:289-294): recomputes the
+ * BSR values of dR/du (incl. penalty terms) from the current inputs; BCs are applied on the
+ * fly by the operator (rows+cols masked, unit diagonal). */
+int femo_assemble_jacobian(femo_ctx* ctx);
+/* replaces assembleVector(residual_form) (fea/utils_dolfinx.py:194-198):
+ * R = dR/du * w - load(F_solid); w = NULL uses the stored state. */
+int femo_assemble_residual(femo_ctx* ctx, const double* w, double* R, int on_device);
+/* load vector int f . du J dx only */
+int femo_assemble_load(femo_ctx* ctx, double* F, int on_device);
+/* y = dR/du x (no BCs) / y = A x (with BCs); replaces computeMatVecProductFwd (utils_dolfinx.py:275-283) */
+int femo_jacobian_apply(femo_ctx* ctx, const double* x, double* y, int with_bc, int on_device);
+/* diagnostic/test: copy the BSR structure+values to host.  rowptr (nb+1) int32, colidx (nnzb) int32,
+ * vals (nnzb,3,3) fp64; any pointer may be NULL.  with_bc applies the dolfinx BC convention. */
+int femo_get_bsr(femo_ctx* ctx, int32_t* rowptr, int32_t* colidx, double* vals, int with_bc);
+
+/* ---- solves ---------------------------------------------------------------------- */
+/* replaces FEA.solve -> solveNonlinear -> NewtonSolver (fea/fea_dolfinx.py:159-170,
+ * fea/utils_dolfinx.py:338-352,438-468): assembles dR/du and the load, then PCG (block-Jacobi,
+ * 6x6 vertex / 3x3 edge+centre blocks) on A w = b, warm-started from the stored state. */
+int femo_solve_state(femo_ctx* ctx, double rtol, int max_it, int* iters, double* relres);
+/* replaces FEA.solveLinearBwd + BC zeroing (fea/fea_dolfinx.py:189-203,
+ * csdl_alpha_opt/state_operation.py:206-218): A lam = rhs (A symmetric), lam[bc] = 0. */
+int femo_solve_adjoint(femo_ctx* ctx, const double* rhs, double* lam, double rtol, int max_it,
+                       int* iters, double* relres, int on_device);
+/* replaces FEA.solveLinearFwd (fea/fea_dolfinx.py:173-187): A du = rhs */
+int femo_solve_forward(femo_ctx* ctx, const double* rhs, double* du, double rtol, int max_it,
+                       int* iters, double* relres, int on_device);
+
+/* ---- partials of the residual (matrix-free) ---------------------------------------- */
+/* out = (dR/d arg)^T lam ; replaces assembleMatrix(dR_df) + computeMatVecProductBwd
+ * (state_operation.py:183-184,282-286; utils_dolfinx.py:294-306).  arg in {THICKNESS,F_SOLID,E,NU} */
+int femo_dRdf_T_apply(femo_ctx* ctx, int arg, const double* lam, double* out, int on_device);
+/* out = (dR/d arg) df ; replaces computeMatVecProductFwd on dRdf (state_operation.py:163-171) */
+int femo_dRdf_apply(femo_ctx* ctx, int arg, const double* df, double* out, int on_device);
+
+/* ---- outputs ------------------------------------------------------------------------- */
+/* replaces OutputOperation.compute -> assemble_scalar (output_operation.py:51-56) */
+int femo_output(femo_ctx* ctx, int which, double* value);
+/* replaces OutputOperation.compute_derivatives (output_operation.py:58-69):
+ * g = d output / d arg, arg = femo_input or FEMO_ARG_STATE */
+int femo_output_grad(femo_ctx* ctx, int which, int arg, double* g, int on_device);
+
+/* ---- instrumentation ---------------------------------------------------------------- */
+/* number of kernels this context has launched so far */
+int femo_launch_count(femo_ctx* ctx, int64_t* n);
+/* device time (ms, CUDA events on the context's stream) of the last call of each phase:
+ * [0] cell records, [1] BSR gather-assembly, [2] last PCG solve, [3] per-PCG-iteration mean */
+int femo_last_timings(femo_ctx* ctx, double* ms4);
+/* run `n_iter` PCG iterations on A x = b without convergence test (bench / roofline use) */
+int femo_pcg_fixed(femo_ctx* ctx, int n_iter, double* ms_total);
+/* micro-benchmarks for the roofline denominators: fp64 FMA throughput (TFLOP/s) and a device
+ * copy (GB/s) measured on this GPU */
+int femo_measure_peaks(femo_ctx* ctx, double* fp64_tflops, double* copy_gbs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

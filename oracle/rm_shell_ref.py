@@ -34,8 +34,9 @@ tensor rule with m = (degree+2)//2 points; assemble_matrix(bcs) zeroes rows and
 columns and puts 1 on the diagonal.
 
 DOF numbering (ours; the reference's is dolfinx-internal and opaque to callers,
-SURVEY B12): 3x3 "block nodes": vertex v -> u-block 2v, theta-block 2v+1; edge e
--> 2*nn+e; cell centre c -> 2*nn+ne+c.  dof = 3*block + component.
+SURVEY B12): 3x3 "block nodes": Q2 displacement nodes first (vertices [0,nn),
+edges nn+e, cell centres nn+ne+c; nq2 = nn+ne+nc), then Q1 rotation nodes
+nq2+v.  dof = 3*block + component.  Same numbering as include/femo_b200.h.
 """
 from __future__ import annotations
 
@@ -115,13 +116,14 @@ class ShellTopology:
         self.edges = np.stack([ukey // self.nn, ukey % self.nn], 1)
         self.ce = inv.reshape(self.nc, 4)                      # cell -> global edge ids
         nn, ne, nc = self.nn, self.ne, self.nc
-        self.nb = 2 * nn + ne + nc
+        self.nq2 = nn + ne + nc
+        self.nb = self.nq2 + nn
         self.ndof = 3 * self.nb
         cb = np.empty((nc, 13), dtype=np.int64)
-        cb[:, 0:4] = 2 * self.cv
-        cb[:, 4:8] = 2 * nn + self.ce
-        cb[:, 8] = 2 * nn + ne + np.arange(nc)
-        cb[:, 9:13] = 2 * self.cv + 1
+        cb[:, 0:4] = self.cv
+        cb[:, 4:8] = nn + self.ce
+        cb[:, 8] = nn + ne + np.arange(nc)
+        cb[:, 9:13] = self.nq2 + self.cv
         self.cell_blocks = cb
         self.cell_dofs = (3 * cb[:, :, None] + np.arange(3)[None, None, :]).reshape(nc, 39)
         self.edge_ncells = np.bincount(self.ce.ravel(), minlength=ne)
@@ -129,10 +131,10 @@ class ShellTopology:
     def block_coords(self):
         """Coordinates of every block node (dof coordinates of W.sub(0)/W.sub(1))."""
         xc = np.empty((self.nb, 3))
-        xc[0:2 * self.nn:2] = self.x
-        xc[1:2 * self.nn:2] = self.x
-        xc[2 * self.nn:2 * self.nn + self.ne] = 0.5 * (self.x[self.edges[:, 0]] + self.x[self.edges[:, 1]])
-        xc[2 * self.nn + self.ne:] = self.x[self.cv].mean(axis=1)
+        xc[:self.nn] = self.x
+        xc[self.nn:self.nn + self.ne] = 0.5 * (self.x[self.edges[:, 0]] + self.x[self.edges[:, 1]])
+        xc[self.nn + self.ne:self.nq2] = self.x[self.cv].mean(axis=1)
+        xc[self.nq2:] = self.x
         return xc
 
     def cell_diameter(self):
@@ -603,7 +605,7 @@ class RMShellOracle:
     def disp_extracted(self, w):
         """u_mid at mesh vertices, external node order (rm_shell_model.py:505-527)."""
         t = self.topo
-        return w.reshape(-1, 3)[0:2 * t.nn:2].copy()
+        return w.reshape(-1, 3)[:t.nn].copy()
 
     # ---- total derivative via adjoint (SURVEY 3.3) ------------------------
     def total_dcompliance_dh(self):

@@ -1,0 +1,132 @@
+"""GPU parity: the CUDA path through the C ABI against the CPU oracle (same seeded inputs).
+
+Tolerances (BASELINE.json north_star): assembled matrix and vector relative error <= 1e-12;
+displacement, compliance, adjoint thickness gradient <= 1e-8.
+"""
+import numpy as np
+import pytest
+
+from tests.problems import PROBLEMS, make_problem, oracle_for, device_for
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.fixture(scope="module", params=PROBLEMS)
+def pair(request, built_lib):
+    p = make_problem(request.param)
+    return p, oracle_for(p), device_for(p)
+
+
+def test_sizes_and_pattern(pair):
+    p, o, d = pair
+    t = o.topo
+    assert (d.nn, d.ne, d.nc, d.ndof) == (t.nn, t.ne, t.nc, t.ndof)
+    assert np.array_equal(d.cell_blocks(), t.cell_blocks)
+    assert np.allclose(d.block_coords(), t.block_coords(), rtol=0, atol=1e-14)
+    K = o.assemble_dRdu().tobsr((3, 3))
+    K.sort_indices()
+    rowptr, colidx, _ = d.get_bsr(values=False)
+    assert np.array_equal(rowptr, K.indptr) and np.array_equal(colidx, K.indices)
+
+
+def test_jacobian_matrix(pair):
+    p, o, d = pair
+    K = o.assemble_dRdu().tocsr()
+    Kd = d.get_csr()
+    assert rel(Kd.toarray(), K.toarray()) <= 1e-12
+    A = o.apply_bc_matrix(K)
+    Ad = d.get_csr(with_bc=True)
+    assert rel(Ad.toarray(), A.toarray()) <= 1e-12
+
+
+def test_assembly_bitwise_deterministic(pair):
+    p, o, d = pair
+    d.assemble_jacobian()
+    v1 = d.get_bsr()[2].copy()
+    d.set_input("thickness", p["thickness"])      # invalidates, forces a re-assembly
+    d.assemble_jacobian()
+    v2 = d.get_bsr()[2]
+    assert np.array_equal(v1, v2)
+
+
+def test_load_and_residual(pair):
+    p, o, d = pair
+    F = o.assemble_load()
+    assert rel(d.assemble_load(), F) <= 1e-12
+    rng = np.random.default_rng(3)
+    w = rng.standard_normal(o.topo.ndof)
+    R = o.assemble_residual(w)
+    assert rel(d.assemble_residual(w), R) <= 1e-12
+    assert rel(d.jacobian_apply(w), o.assemble_dRdu() @ w) <= 1e-12
+
+
+def test_state_adjoint_and_gradient(pair):
+    p, o, d = pair
+    w = o.solve_state()
+    it, rr = d.solve_state(rtol=1e-13, max_it=100000)
+    wd = d.get_state()
+    assert rr <= 1e-12
+    assert rel(wd, w) <= 1e-8
+    o.w = w
+    # outputs on the oracle state (isolates the functional kernels from solver error)
+    d.set_state(w)
+    for name, ref in (("compliance", o.compliance(w)), ("mass", o.mass())):
+        assert abs(d.output(name) - ref) <= 1e-11 * abs(ref), name
+    # 0.5 w^T K w cancels ~7 digits (|K||w| >> |F|) in the oracle and on the device alike
+    assert abs(d.output("elastic_energy") - o.elastic_energy(w)) <= 1e-7 * abs(o.elastic_energy(w))
+    assert rel(d.output_grad("compliance", "disp_solid"), o.dcompliance_du(w)) <= 1e-12
+    assert rel(d.output_grad("compliance", "thickness"), o.dcompliance_dh()) <= 1e-11
+    assert rel(d.output_grad("mass", "thickness"), o.dmass_dh()) <= 1e-12
+    assert rel(d.output_grad("mass", "density"), o.dmass_drho()) <= 1e-12
+    assert rel(d.output_grad("elastic_energy", "disp_solid"), o.delastic_energy_du(w)) <= 1e-9
+    assert rel(d.output_grad("elastic_energy", "thickness"), o.delastic_energy_dparam(w, "dh")) <= 1e-9
+    # partials of the residual
+    rng = np.random.default_rng(5)
+    lam = rng.standard_normal(o.topo.ndof)
+    for arg, mode in (("thickness", "dh"), ("E", "dE"), ("nu", "dnu")):
+        M = o.assemble_dRdparam(w, mode)
+        assert rel(d.dRdf_T_apply(arg, lam), M.T @ lam) <= 1e-11, arg
+        dp = rng.standard_normal(M.shape[1])
+        assert rel(d.dRdf_apply(arg, dp), M @ dp) <= 1e-11, arg
+    Mf = o.assemble_dRdf()
+    assert rel(d.dRdf_T_apply("F_solid", lam), Mf.T @ lam) <= 1e-12
+    df = rng.standard_normal(Mf.shape[1])
+    assert rel(d.dRdf_apply("F_solid", df), Mf @ df) <= 1e-12
+    # adjoint solve + total thickness gradient of the compliance
+    rhs = o.dcompliance_du(w)
+    lam_o = o.solve_adjoint(rhs)
+    lam_d = d.solve_adjoint(rhs, rtol=1e-13, max_it=100000)
+    assert rel(lam_d, lam_o) <= 1e-8
+    g_o = o.total_dcompliance_dh()
+    g_d = d.output_grad("compliance", "thickness") - d.dRdf_T_apply("thickness", lam_d)
+    assert rel(g_d, g_o) <= 1e-8
+
+
+@pytest.mark.parametrize("name", ["plate_4x20", "warped"])
+def test_penalty_bc(name, built_lib):
+    p = make_problem(name)
+    o, d = oracle_for(p, penalty=True), device_for(p, penalty=True)
+    K = o.assemble_dRdu().tocsr()
+    assert rel(d.get_csr().toarray(), K.toarray()) <= 1e-12
+    w = o.solve_state()
+    it, rr = d.solve_state(rtol=1e-13, max_it=200000)
+    free = np.ones(o.topo.ndof, bool)
+    assert rel(d.get_state(), w) <= 1e-7          # beta = 1e15: the direct solve itself carries ~1e-10
+    d.set_state(w)
+    assert abs(d.output("elastic_energy") - o.elastic_energy(w)) <= 1e-9 * abs(o.elastic_energy(w))
+
+
+def test_quadrature_degree_and_errors(built_lib):
+    p = make_problem("plate_dg0")
+    o, d = oracle_for(p, quadrature_degree=4), device_for(p, quadrature_degree=4)
+    assert d.sizes.n_qp == 9
+    assert rel(d.get_csr().toarray(), o.assemble_dRdu().toarray()) <= 1e-12
+    with pytest.raises(RuntimeError):
+        d.set_input("thickness", np.ones(3))
+    from femo_alpha_b200.shell_device import ShellDevice
+    with pytest.raises(RuntimeError):
+        ShellDevice(p["nodes"], p["quads"][:, :3])
