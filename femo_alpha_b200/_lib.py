@@ -63,6 +63,11 @@ SIGNATURES = {
     "femo_dRdf_apply": [_P, C.c_int, _P, _P, C.c_int],
     "femo_output": [_P, C.c_int, _D],
     "femo_output_grad": [_P, C.c_int, C.c_int, _P, C.c_int],
+    "femo_set_stress_params": [_P, C.c_double, C.c_double],
+    "femo_set_cell_tags": [_P, C.c_int64, _P],
+    "femo_pnorm_stress": [_P, C.c_int, _D],
+    "femo_pnorm_stress_grad": [_P, C.c_int, C.c_int, _P, C.c_int],
+    "femo_stress_field": [_P, C.c_int, _P, C.c_int],
     "femo_launch_count": [_P, C.POINTER(C.c_int64)],
     "femo_last_timings": [_P, _D],
     "femo_pcg_fixed": [_P, C.c_int, _D],

@@ -182,7 +182,7 @@ int femo_ctx_destroy(femo_ctx* c) {
   void* ptrs[] = {c->xyz, c->cv, c->ce, c->edges, c->cell_blocks, c->hE, c->tab, c->h, c->E, c->nu, c->rho, c->f, c->uhat,
                   c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
                   c->nc_adj, c->rec, c->bcmask, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
-                  c->pen_val, c->pen_dest_col, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
+                  c->pen_val, c->pen_dest_col, c->tab4, c->cell_tags, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
                   c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->ev0) cudaEventDestroy(c->ev0);
@@ -223,6 +223,12 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   build_tables(c->htab, m);
   TRY(dev_alloc(&c->tab, 1));
   CUDA_TRY(cudaMemcpy(c->tab, &c->htab, sizeof(Tables), cudaMemcpyHostToDevice));
+  Tables t4;
+  build_tables(t4, 3);
+  TRY(dev_alloc(&c->tab4, 1));
+  CUDA_TRY(cudaMemcpy(c->tab4, &t4, sizeof(Tables), cudaMemcpyHostToDevice));
+  c->nq4 = 9;
+  c->area_cache.clear();
   TRY(pattern_build(c));
   c->n_mat = c->ewm ? c->nc : c->nn;
   c->n_f = 3 * (c->ewp ? c->nc : c->nn);
@@ -491,6 +497,49 @@ int femo_output_grad(femo_ctx* c, int which, int arg, double* gout, int on_devic
   if (arg != FEMO_ARG_STATE && !input_slot(c, arg, &n)) return femo_fail("femo_output_grad: unknown argument");
   TRY(out_grad(c, which, arg, c->tmp));
   return copy_out(c, gout, c->tmp, n, on_device);
+}
+
+int femo_set_stress_params(femo_ctx* c, double m, double rho) {
+  if (!c) return femo_fail("null context");
+  c->stress_m = m; c->stress_rho = rho;
+  return 0;
+}
+
+int femo_set_cell_tags(femo_ctx* c, int64_t n, const int32_t* tags) {
+  NEED_SETUP(c, "femo_set_cell_tags");
+  if (n != c->nc) return femo_fail("femo_set_cell_tags: need one tag per cell");
+  DevGuard g(c->device);
+  TRY(dev_alloc(&c->cell_tags, (size_t)n));
+  CUDA_TRY(cudaMemcpy(c->cell_tags, tags, sizeof(int32_t) * n, cudaMemcpyHostToDevice));
+  c->area_cache.clear();
+  return 0;
+}
+
+int femo_pnorm_stress(femo_ctx* c, int tag, double* value) {
+  NEED_SETUP(c, "femo_pnorm_stress");
+  DevGuard g(c->device);
+  return pnorm_value(c, tag, value);
+}
+
+int femo_pnorm_stress_grad(femo_ctx* c, int tag, int arg, double* gout, int on_device) {
+  NEED_SETUP(c, "femo_pnorm_stress_grad");
+  DevGuard g(c->device);
+  int64_t n = c->ndof;
+  if (arg != FEMO_ARG_STATE && !input_slot(c, arg, &n)) return femo_fail("femo_pnorm_stress_grad: unknown argument");
+  TRY(pnorm_grad(c, tag, arg, c->tmp));
+  return copy_out(c, gout, c->tmp, n, on_device);
+}
+
+int femo_stress_field(femo_ctx* c, int surface, double* out, int on_device) {
+  NEED_SETUP(c, "femo_stress_field");
+  if (surface < 0 || surface > 2) return femo_fail("femo_stress_field: surface must be 0 (Top), 1 (Mid) or 2 (Bot)");
+  DevGuard g(c->device);
+  double* t = nullptr;
+  TRY(dev_alloc(&t, (size_t)c->nc * 4));
+  int r = stress_field(c, surface, t);
+  if (r == 0) r = copy_out(c, out, t, c->nc * 4, on_device);
+  dev_free(&t);
+  return r;
 }
 
 int femo_launch_count(femo_ctx* c, int64_t* n) {

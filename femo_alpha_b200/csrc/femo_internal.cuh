@@ -7,6 +7,7 @@
 #include <stdint.h>
 #include <string>
 #include <vector>
+#include <map>
 #include "../../include/femo_b200.h"
 
 #define FEMO_MAX_Q1D 5
@@ -76,6 +77,11 @@ struct femo_ctx {
   // options
   int ewm = 0, ewp = 0, m1d = 4, nq = 16;
   Tables* tab = nullptr;        // device
+  Tables* tab4 = nullptr;       // device: degree-4 rule (3x3) of the stress measure
+  int nq4 = 9;
+  double stress_m = 1e-6, stress_rho = 100.0;
+  int32_t* cell_tags = nullptr; // nc (optional sub-domain ids)
+  std::map<int, double> area_cache;
   Tables htab;                  // host copy
   // inputs (device)
   int64_t n_mat = 0, n_f = 0;
@@ -159,6 +165,9 @@ int out_grad(femo_ctx* c, int which, int arg, double* g_dev);             // out
 int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out);   // outputs.cu
 int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out);      // outputs.cu
 int measure_peaks(femo_ctx* c, double* tf, double* gbs);                  // solver.cu
+int pnorm_value(femo_ctx* c, int tag, double* val);                       // outputs.cu
+int pnorm_grad(femo_ctx* c, int tag, int arg, double* g);                 // outputs.cu
+int stress_field(femo_ctx* c, int surface, double* out);                  // outputs.cu
 
 // ---- device maths --------------------------------------------------------------
 #ifdef __CUDACC__

@@ -65,11 +65,16 @@ k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, c
        const double* __restrict__ x, const double* __restrict__ mask, int64_t nb, double* __restrict__ y,
        double* __restrict__ dot_part) {
   const int lane = threadIdx.x % LANES;
-  const int64_t grp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / LANES;
-  const int64_t ngrp = (gridDim.x * (int64_t)blockDim.x) / LANES;
+  constexpr int GPW = 32 / LANES;                       // row groups per warp
+  const int sub = (threadIdx.x & 31) / LANES;
+  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarp = (gridDim.x * (int64_t)blockDim.x) >> 5;
   double dacc = 0.0;
-  for (int64_t row = grp; row < nb; row += ngrp) {
-    const int32_t s = rowptr[row], e = rowptr[row + 1];
+  // warp-uniform trip count: every lane takes part in the full-mask shuffles below
+  for (int64_t rb = warp * GPW; rb < nb; rb += nwarp * GPW) {
+    const int64_t row = rb + sub;
+    const bool valid = row < nb;
+    const int32_t s = valid ? rowptr[row] : 0, e = valid ? rowptr[row + 1] : 0;
     double y0 = 0, y1 = 0, y2 = 0;
     for (int32_t k = s + lane; k < e; k += LANES) {
       const int64_t col = colidx[k];
@@ -86,7 +91,7 @@ k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, c
       y1 += __shfl_down_sync(0xffffffffu, y1, o, LANES);
       y2 += __shfl_down_sync(0xffffffffu, y2, o, LANES);
     }
-    if (lane == 0) {
+    if (lane == 0 && valid) {
       double xr0 = x[3 * row], xr1 = x[3 * row + 1], xr2 = x[3 * row + 2];
       if (mask) {
         double m0 = mask[3 * row], m1 = mask[3 * row + 1], m2 = mask[3 * row + 2];

@@ -194,6 +194,76 @@ class ShellDevice:
                                           L.ptr(out), 0))
         return out
 
+    # ---- stress functionals ----------------------------------------------------------------------
+    def set_stress_params(self, m, rho):
+        L.check(self.lib.femo_set_stress_params(self._ctx, float(m), float(rho)))
+
+    def set_cell_tags(self, tags):
+        t = np.ascontiguousarray(tags, dtype=np.int32)
+        L.check(self.lib.femo_set_cell_tags(self._ctx, t.size, L.ptr(t)))
+
+    def pnorm_stress(self, tag=-1):
+        v = C.c_double(0.0)
+        L.check(self.lib.femo_pnorm_stress(self._ctx, int(tag), C.byref(v)))
+        return v.value
+
+    def pnorm_stress_grad(self, arg, tag=-1):
+        a = self._arg_id(arg)
+        out = np.empty(self._arg_size(a))
+        L.check(self.lib.femo_pnorm_stress_grad(self._ctx, int(tag), a, L.ptr(out), 0))
+        return out
+
+    def stress_field(self, surface="Top"):
+        out = np.empty(4 * self.nc)
+        L.check(self.lib.femo_stress_field(self._ctx, {"Top": 0, "Mid": 1, "Bot": 2}[surface], L.ptr(out), 0))
+        return out
+
+    # ---- small host-side pre-processing maps (not on the hot path) -------------------------------
+    def _cell_vertices(self):
+        return self.cell_blocks()[:, 9:13] - self.nq2          # tensor-ordered vertex ids
+
+    def _q1_cell_mass(self):
+        """int N_i N_j dx per cell, 2x2 Gauss (exact for the bilinear measure on planar cells)."""
+        cv = self._cell_vertices()
+        x = self.block_coords()[:self.nn][cv]                   # (nc,4,3)
+        g = 0.5 + np.array([-1.0, 1.0]) * 0.5 / np.sqrt(3.0)
+        M = np.zeros((self.nc, 4, 4)); area = np.zeros(self.nc); b = np.zeros((self.nc, 4))
+        for X0 in g:
+            for X1 in g:
+                N = np.array([(1 - X0) * (1 - X1), X0 * (1 - X1), (1 - X0) * X1, X0 * X1])
+                dN = np.array([[-(1 - X1), -(1 - X0)], [(1 - X1), -X0], [-X1, (1 - X0)], [X1, X0]])
+                J = np.einsum("cvi,va->cia", x, dN)
+                dJ = np.linalg.norm(np.cross(J[:, :, 0], J[:, :, 1]), axis=1) * 0.25
+                M += dJ[:, None, None] * np.outer(N, N)[None]
+                b += dJ[:, None] * N[None]
+                area += dJ
+        return cv, M, b, area
+
+    def support_sizes(self):
+        """assemble_vector(v*dx) of the scalar load space (rm_shell_pde.py:46-47)."""
+        cv, M, b, area = self._q1_cell_mass()
+        if self.n_f == 3 * self.nc:
+            return area
+        out = np.zeros(self.nn)
+        np.add.at(out, cv.ravel(), b.ravel())
+        return out
+
+    def load_mass_matrix(self):
+        """int Pv.w dx on the vector load space as SciPy CSR (rm_shell_pde.py:194-209)."""
+        import scipy.sparse as sp
+        cv, M, b, area = self._q1_cell_mass()
+        if self.n_f == 3 * self.nc:
+            return sp.diags(np.repeat(area, 3)).tocsr()
+        rows, cols, vals = [], [], []
+        for i in range(3):
+            rows.append(np.repeat(3 * cv + i, 4, axis=1).ravel())
+            cols.append(np.tile(3 * cv + i, (1, 4)).ravel())
+            vals.append(M.ravel())
+        A = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))),
+                          shape=(3 * self.nn, 3 * self.nn)).tocsr()
+        A.eliminate_zeros()
+        return A
+
     # ---- instrumentation ------------------------------------------------------------------------------
     def launch_count(self):
         n = C.c_int64(0)

@@ -137,6 +137,20 @@ int femo_output(femo_ctx* ctx, int which, double* value);
  * g = d output / d arg, arg = femo_input or FEMO_ARG_STATE */
 int femo_output_grad(femo_ctx* ctx, int which, int arg, double* g, int on_device);
 
+/* ---- stress functionals -------------------------------------------------- */
+/* p-norm parameters m, rho of RMShellModel (rm_shell_model.py:63): pnorm = 1/Area int (m sigma_vm)^rho J dx */
+int femo_set_stress_params(femo_ctx* ctx, double m, double rho);
+/* per-cell sub-domain ids (rm_shell_model.py:101-133 mesh_tags); host int32[n_cells], -1 = untagged */
+int femo_set_cell_tags(femo_ctx* ctx, int64_t n_cells, const int32_t* tags);
+/* replaces assemble_scalar(pnorm_stress_form) (rm_shell_pde.py:112-128), degree-4 measure, von Mises
+ * stress on the top surface xi2 = h/2 (linear_shell_model.py:393-467); tag < 0 = whole surface,
+ * otherwise the sub-domain `tag` with its own area normalisation */
+int femo_pnorm_stress(femo_ctx* ctx, int tag, double* value);
+int femo_pnorm_stress_grad(femo_ctx* ctx, int tag, int arg, double* g, int on_device);
+/* replaces FEA.projectFieldOutput -> project(von_Mises, DG1) (fea/utils_dolfinx.py:568-602):
+ * cell-wise L2 projection, out (n_cells,4) in tensor vertex order; surface 0 Top, 1 Mid, 2 Bot */
+int femo_stress_field(femo_ctx* ctx, int surface, double* out, int on_device);
+
 /* ---- instrumentation ---------------------------------------------------------------- */
 /* number of kernels this context has launched so far */
 int femo_launch_count(femo_ctx* ctx, int64_t* n);

@@ -613,3 +613,92 @@ class RMShellOracle:
         lam = self.solve_adjoint(self.dcompliance_du(w))
         dRdh = self.assemble_dRdparam(w, "dh")
         return self.dcompliance_dh() - dRdh.T @ lam
+
+
+# ----------------------------------------------------------------------------
+# stress functionals: von Mises on the top surface, p-norm, DG1 projection
+# linear_shell_model.py:350-467, rm_shell_pde.py:112-166, rm_shell_model.py:200-253
+# ----------------------------------------------------------------------------
+def _von_mises_at(g, we, hv, Ev, nuv, ewm, xi_sign=1.0):
+    """sigma_vm at one reference point for all cells; inputs may be complex (complex-step derivatives).
+
+    we (nc,39); hv/Ev/nuv: (nc,4) nodal (CG1) or (nc,) (DG0).  Literal restatement:
+    u(xi2) = u_mid - xi2 cross(E2, theta) (model:393-398), eps = sym(T gradx(u(xi2)) T^T) (model:401-419),
+    sigma = D eps (model:438), vm (model:461-462) with xi2 = h/2 INSIDE the gradient.
+    """
+    nc = we.shape[0]
+    ue = we[:, :27].reshape(nc, 9, 3); te = we[:, 27:].reshape(nc, 4, 3)
+    if ewm:
+        hq, Eq, nuq = hv, Ev, nuv
+        dxi = np.zeros((nc, 2), dtype=we.dtype)
+    else:
+        hq, Eq, nuq = hv @ g.N1, Ev @ g.N1, nuv @ g.N1
+        dxi = 0.5 * xi_sign * (hv @ g.dN1)                             # d(xi2)/dX
+    xi = 0.5 * xi_sign * hq
+    theta = np.einsum("cbi,b->ci", te, g.N1)
+    dtheta = np.einsum("cbi,ba->cia", te, g.dN1)
+    beta = np.cross(g.E2, theta)
+    dbeta = np.stack([np.cross(g.dE2[:, a], theta) + np.cross(g.E2, dtheta[:, :, a]) for a in range(2)], 2)
+    du = np.einsum("cai,ab->cib", ue, g.dphi2)                         # d u_mid / dX  (nc,3,2)
+    # d/dX of u(xi2) = u_mid - xi2 beta
+    dU = du - xi[:, None, None] * dbeta - beta[:, :, None] * dxi[:, None, :]
+    G = np.einsum("cia,caj->cij", dU, g.Kx)                            # gradx(u(xi2))
+    gl = np.einsum("cki,cij,clj->ckl", g.T, G, g.T)
+    e = np.stack([gl[:, 0, 0], gl[:, 1, 1], gl[:, 0, 1] + gl[:, 1, 0]], 1)
+    c0 = Eq / (1.0 - nuq * nuq)
+    s0 = c0 * (e[:, 0] + nuq * e[:, 1]); s1 = c0 * (nuq * e[:, 0] + e[:, 1]); s2 = c0 * 0.5 * (1.0 - nuq) * e[:, 2]
+    return np.sqrt(s0 * s0 - s0 * s1 + s1 * s1 + 3.0 * s2 * s2)
+
+
+def _oracle_pnorm(self, w, h=None, E=None, nu=None, m=1e-6, rho=100, cells=None):
+    """1/Area int (m vm)^rho J dx with the degree-4 rule (3x3 Gauss); Area frozen at uhat = 0."""
+    t = self.topo
+    h = self.h if h is None else h; E = self.E if E is None else E; nu = self.nu if nu is None else nu
+    xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+    we = w[t.cell_dofs]
+    pick = (lambda a: a) if self.ewm else (lambda a: a[t.cv])
+    gx, gw = gauss01(3)
+    tot = 0.0; area = 0.0
+    mask = np.ones(t.nc) if cells is None else np.isin(np.arange(t.nc), cells).astype(float)
+    for i in range(3):
+        for j in range(3):
+            g = qp_geometry(xv, uh, gx[i], gx[j])
+            vm = _von_mises_at(g, we, pick(h), pick(E), pick(nu), self.ewm)
+            tot = tot + np.sum(mask * gw[i] * gw[j] * g.detJ * g.Ju * (m * vm) ** rho)
+    for X0, X1, wq in self.qp:                                         # area form: bare dx, uhat = 0 (pde:124-127)
+        g0 = qp_geometry(xv, np.zeros_like(xv), X0, X1)
+        area += np.sum(mask * wq * g0.detJ)
+    return tot / area
+
+
+def _oracle_pnorm_grad(self, w, wrt, m=1e-6, rho=100, cells=None):
+    """Complex-step gradient (exact to round-off) w.r.t. 'w' | 'thickness' | 'E' | 'nu'."""
+    base = dict(w=w, thickness=self.h, E=self.E, nu=self.nu)[wrt]
+    out = np.zeros(base.size)
+    for k in range(base.size):
+        p = base.astype(complex); p[k] += 1e-30j
+        kw = dict(w=w.astype(complex), h=self.h.astype(complex), E=self.E.astype(complex), nu=self.nu.astype(complex))
+        kw[dict(w="w", thickness="h", E="E", nu="nu")[wrt]] = p
+        out[k] = np.imag(_oracle_pnorm(self, kw["w"], kw["h"], kw["E"], kw["nu"], m, rho, cells)) / 1e-30
+    return out
+
+
+def _oracle_stress_field(self, w, surface="Top"):
+    """Cell-wise L2 projection of vm onto DG1 (utils_dolfinx.py:568-602, plain dx): (nc,4)."""
+    t = self.topo
+    xv = t.x[t.cv]; uh = self.uhat.reshape(-1, 3)[t.cv]
+    we = w[t.cell_dofs]
+    pick = (lambda a: a) if self.ewm else (lambda a: a[t.cv])
+    sign = dict(Top=1.0, Mid=0.0, Bot=-1.0)[surface]
+    M = np.zeros((t.nc, 4, 4)); b = np.zeros((t.nc, 4))
+    for X0, X1, wq in self.qp:
+        g = qp_geometry(xv, uh, X0, X1)
+        vm = _von_mises_at(g, we, pick(self.h), pick(self.E), pick(self.nu), self.ewm, sign)
+        M += (wq * g.detJ)[:, None, None] * np.outer(g.N1, g.N1)[None]
+        b += (wq * g.detJ * vm)[:, None] * g.N1[None, :]
+    return np.linalg.solve(M, b[:, :, None])[:, :, 0]
+
+
+RMShellOracle.pnorm_stress = _oracle_pnorm
+RMShellOracle.pnorm_stress_grad = _oracle_pnorm_grad
+RMShellOracle.stress_field = _oracle_stress_field
