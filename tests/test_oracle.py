@@ -1,0 +1,132 @@
+"""CPU tests of the oracle (no GPU): physics invariants, the independent literal
+energy evaluation, FD-vs-adjoint, the reference's weak pin (Euler-Bernoulli deflection,
+ex_simple_shell_opt.py:100-105) and the committed golden fixtures."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle.rm_shell_ref import RMShellOracle, plate_mesh
+from oracle.energy_check import cell_stiffness_by_polarisation
+from tests.problems import PROBLEMS, make_problem, oracle_for
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_sizes_match_survey_appendix_c():
+    for (nx, ny), (ndof, nnz) in {(10, 2): (414, 24444), (20, 4): (1422, 93132), (40, 8): (5238, 363348)}.items():
+        nodes, quads = plate_mesh(nx, ny, 10.0, 2.0)
+        o = RMShellOracle(nodes, quads)
+        o.set_inputs(thickness=0.1, E=1e8, nu=0.3)
+        assert o.topo.ndof == ndof
+        if nx <= 20:
+            assert o.assemble_dRdu().nnz == nnz
+
+
+@pytest.mark.parametrize("name", ["skew_planar", "warped"])
+def test_symmetry_and_rigid_body_modes(name):
+    """Six zero-energy rigid modes on planar cells.  On warped bilinear cells the reference's bending
+    measure sym(T grad(E2 x theta) T^T) differentiates the varying normal, so rigid ROTATIONS are
+    not exactly energy-free there (a property of the formulation, reproduced by the literal energy
+    check) -- only translations are tested on the warped mesh."""
+    p = make_problem(name)
+    o = oracle_for(p)
+    o.uhat[:] = 0.0                       # rigid motions are zero-energy w.r.t. the undeformed surface
+    K = o.assemble_dRdu()
+    assert abs(K - K.T).max() <= 1e-14 * abs(K).max()
+    t = o.topo
+    xc = t.block_coords()
+    isu = np.arange(t.nb) < t.nq2
+    scale = np.abs(K.diagonal()).max()
+    for m in range(6 if name == "skew_planar" else 3):
+        r = np.zeros((t.nb, 3))
+        if m < 3:
+            r[isu, m] = 1.0
+        else:
+            om = np.zeros(3); om[m - 3] = 1.0
+            r[isu] = np.cross(om, xc[isu]); r[~isu] = om
+        assert np.abs(K @ r.ravel()).max() <= 1e-12 * scale, m
+
+
+def test_element_matrix_against_literal_energy():
+    rng = np.random.default_rng(1)
+    nodes = np.array([[0, 0, 0], [1.2, 0.1, 0.05], [1.1, 0.9, 0.3], [-0.1, 1.0, -0.1]], float)
+    quads = np.array([[0, 1, 2, 3]])
+    hv = np.array([0.1, 0.12, 0.09, 0.11]); Ev = np.array([1e3, 1.1e3, 0.9e3, 1e3]); nv = np.array([0.3, 0.25, 0.33, 0.28])
+    uh = 0.05 * rng.standard_normal((4, 3))
+    o = RMShellOracle(nodes, quads)
+    o.set_inputs(thickness=hv, E=Ev, nu=nv, uhat=uh.ravel())
+    Ke = o.element_matrices()[0]
+    cv = o.topo.cv[0]
+    Kp = cell_stiffness_by_polarisation(nodes[cv], uh[cv], hv[cv], Ev[cv], nv[cv])
+    assert np.abs(Ke - Kp).max() <= 1e-12 * np.abs(Ke).max()
+
+
+def test_vertex_order_invariance():
+    """Energy is even in the normal and isotropic in-plane: K does not depend on the cell's vertex order."""
+    p = make_problem("skew_planar")
+    o1 = oracle_for(p)
+    p2 = dict(p); p2["quads"] = p["quads"][:, [1, 2, 3, 0]]
+    o2 = oracle_for(p2)
+    p3 = dict(p); p3["quads"] = p["quads"][:, [3, 2, 1, 0]]     # flipped normal
+    o3 = oracle_for(p3)
+    K1 = o1.assemble_dRdu().toarray()
+    assert np.abs(o2.assemble_dRdu().toarray() - K1).max() <= 1e-11 * np.abs(K1).max()
+    assert np.abs(o3.assemble_dRdu().toarray() - K1).max() <= 1e-11 * np.abs(K1).max()
+
+
+def test_euler_bernoulli_pin_and_mass():
+    p = make_problem("plate_4x20")
+    o = oracle_for(p)
+    w = o.solve_state()
+    tip = np.abs(o.disp_extracted(w)).max()
+    EB = 5.0 * 2.0 * 10.0 ** 4 / (8 * 1e8 * (2.0 * 0.1 ** 3 / 12))        # = 0.75
+    assert abs(EB - 0.75) < 1e-12
+    assert 0.9 * EB < tip < EB
+    assert abs(o.mass() - 20.0) < 1e-10                                     # rho h width length
+    assert abs(o.elastic_energy(w) - 0.5 * w @ o.assemble_load()) <= 1e-6 * o.elastic_energy(w)
+    R = o.assemble_residual(np.zeros_like(w))
+    assert np.allclose(R, -o.assemble_load())                               # R(0) = -F
+
+
+@pytest.mark.parametrize("ewm", [False, True])
+def test_adjoint_gradient_against_fd(ewm):
+    rng = np.random.default_rng(3)
+    nodes, quads = plate_mesh(5, 3, 3.0, 1.0, z_func=lambda X, Y: 0.1 * np.sin(X) * Y)
+    o = RMShellOracle(nodes, quads, element_wise_material=ewm)
+    h0 = 0.1 * (1 + 0.3 * rng.random(o.n_mat))
+    o.set_inputs(thickness=h0, E=1e6, nu=0.3, density=2.0, F_solid=np.tile([0, 0, 5.0], o.topo.nn))
+    o.set_strong_bc(lambda x: np.less(x[0], 1e-12))
+    o.solve_state()
+    g = o.total_dcompliance_dh()
+    d = rng.standard_normal(o.n_mat); eps = 1e-6
+    vals = []
+    for s in (+1, -1):
+        o.set_inputs(thickness=h0 + s * eps * d)
+        vals.append(o.compliance(o.solve_state()))
+    fd = (vals[0] - vals[1]) / (2 * eps)
+    assert abs(fd - g @ d) <= 1e-5 * abs(fd)
+
+
+def test_penalty_equals_strong_bc():
+    p = make_problem("plate_4x20")
+    ws = oracle_for(p, penalty=False).solve_state()
+    wp = oracle_for(p, penalty=True).solve_state()
+    assert np.abs(ws - wp).max() <= 1e-8 * np.abs(ws).max()
+
+
+@pytest.mark.parametrize("name", PROBLEMS)
+def test_golden_fixtures(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    o = oracle_for(make_problem(name))
+    K = o.assemble_dRdu()
+    assert (o.topo.ndof, K.nnz) == (int(g["ndof"]), int(g["nnz"]))
+    assert np.abs(K @ g["probe"] - g["K_probe"]).max() <= 1e-12 * np.abs(g["K_probe"]).max()
+    assert np.abs(K.diagonal() - g["K_diag"]).max() <= 1e-12 * np.abs(g["K_diag"]).max()
+    assert np.abs(o.assemble_load() - g["load"]).max() <= 1e-13 * np.abs(g["load"]).max()
+    w = o.solve_state(); o.w = w
+    assert np.abs(w - g["w"]).max() <= 1e-8 * np.abs(g["w"]).max()
+    assert abs(o.compliance(w) - float(g["compliance"])) <= 1e-8 * float(g["compliance"])
+    assert abs(o.mass() - float(g["mass"])) <= 1e-12 * float(g["mass"])
+    assert np.abs(o.total_dcompliance_dh() - g["dCdh_total"]).max() <= 1e-7 * np.abs(g["dCdh_total"]).max()
+    assert abs(o.pnorm_stress(w, m=1e-4, rho=6.0) - float(g["pnorm"])) <= 1e-7 * float(g["pnorm"])
