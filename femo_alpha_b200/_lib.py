@@ -72,6 +72,7 @@ SIGNATURES = {
     "femo_last_timings": [_P, _D],
     "femo_pcg_fixed": [_P, C.c_int, _D],
     "femo_measure_peaks": [_P, _D, _D],
+    "femo_last_dmma_tflops": [_P, _D],
 }
 
 _lib = None

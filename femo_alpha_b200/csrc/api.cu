@@ -183,7 +183,8 @@ int femo_ctx_destroy(femo_ctx* c) {
                   c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
                   c->nc_adj, c->rec, c->bcmask, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
                   c->pen_val, c->pen_dest_col, c->tab4, c->cell_tags, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
-                  c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf};
+                  c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf, c->it_pack, c->it_dest, c->chunk_ptr, c->halo_ptr,
+                  c->halo_cells, c->tpos};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
@@ -230,6 +231,7 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   c->nq4 = 9;
   c->area_cache.clear();
   TRY(pattern_build(c));
+  if (c->all_planar) TRY(asm_plan_build(c));
   c->n_mat = c->ewm ? c->nc : c->nn;
   c->n_f = 3 * (c->ewp ? c->nc : c->nn);
   TRY(dev_alloc(&c->h, c->n_mat)); TRY(dev_alloc(&c->E, c->n_mat)); TRY(dev_alloc(&c->nu, c->n_mat));
@@ -551,6 +553,12 @@ int femo_launch_count(femo_ctx* c, int64_t* n) {
 int femo_last_timings(femo_ctx* c, double* ms4) {
   if (!c || !ms4) return femo_fail("null argument");
   ms4[0] = c->t_rec; ms4[1] = c->t_asm; ms4[2] = c->t_solve; ms4[3] = c->t_iter;
+  return 0;
+}
+
+int femo_last_dmma_tflops(femo_ctx* c, double* tf) {
+  if (!c || !tf) return femo_fail("null argument");
+  *tf = c->dmma_tf;
   return 0;
 }
 

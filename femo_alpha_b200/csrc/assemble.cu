@@ -260,6 +260,243 @@ k_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ cdest, 
   for (int k = 0; k < 9; ++k) o[k] = K[k];
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Chunked symmetric assembly for planar cells.
+//   one CTA per chunk of C consecutive cells; destinations with row <= col owned by the chunk
+//   stage : expand the quadrature records of own + halo cells into shared memory
+//           (physical shape-function gradients in the cell frame + weighted CLT coefficients)
+//   round : 256 contributions -> 3x3 blocks (type-uniform warps) -> shared exchange buffer ->
+//           segment heads add their followers in list order -> 9 lanes per block write the block
+//           and its transpose (72 contiguous bytes each)
+#define ASM_THREADS 256
+#define TBL_Q 36                      /* doubles per quadrature point in the staged table */
+#define TW_CM11 26
+#define TW_C3P 28
+#define TW_CS 30
+#define TW_CB11 32
+#define SK_STRIDE (ASM_THREADS + 1)
+
+struct AsmRef {                        // reference tables staged once per CTA
+  double dphi2[FEMO_MAX_NQ][9][2];
+  double dn1[FEMO_MAX_NQ][4][2];
+  double n1[FEMO_MAX_NQ][4];
+};
+
+template <int NQ>
+__device__ __forceinline__ void asm_block(const double* __restrict__ tb, const double* __restrict__ fr,
+                                          const AsmRef& R, int nq_rt, int a, int b, int type, double* K) {
+  const int nq = NQ > 0 ? NQ : nq_rt;
+  const V3 E0 = ldv3(fr), E1 = ldv3(fr + 3), E2 = ldv3(fr + 6);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) K[i] = 0.0;
+  if (type == 0) {
+    double m00 = 0, m01 = 0, m10 = 0, m11 = 0, s = 0;
+    const double* pa = tb + 2 * a; const double* pb = tb + 2 * b;
+#pragma unroll
+    for (int q = 0; q < nq; ++q) {
+      const double2 da = *reinterpret_cast<const double2*>(pa + q * TBL_Q);
+      const double2 db = *reinterpret_cast<const double2*>(pb + q * TBL_Q);
+      const double2 w0 = *reinterpret_cast<const double2*>(tb + q * TBL_Q + TW_CM11);   // cm11, cm12
+      const double2 w1 = *reinterpret_cast<const double2*>(tb + q * TBL_Q + TW_C3P);    // cm33+cd/4, cm33-cd/4
+      const double cs = tb[q * TBL_Q + TW_CS];
+      const double P00 = da.x * db.x, P01 = da.x * db.y, P10 = da.y * db.x, P11 = da.y * db.y;
+      m00 += w0.x * P00 + w1.x * P11;
+      m01 += w0.y * P01 + w1.y * P10;
+      m10 += w0.y * P10 + w1.y * P01;
+      m11 += w0.x * P11 + w1.x * P00;
+      s += cs * (P00 + P11);
+    }
+    outer_acc(K, m00 * E0 + m10 * E1, E0);
+    outer_acc(K, m01 * E0 + m11 * E1, E1);
+    outer_acc(K, s * E2, E2);
+  } else if (type == 1) {
+    const int ta = a - 9, tbn = b - 9;
+    double t00 = 0, t01 = 0, t10 = 0, t11 = 0, t22 = 0;
+    const double* pa = tb + 18 + 2 * ta; const double* pb = tb + 18 + 2 * tbn;
+#pragma unroll
+    for (int q = 0; q < nq; ++q) {
+      const double2 da = *reinterpret_cast<const double2*>(pa + q * TBL_Q);
+      const double2 db = *reinterpret_cast<const double2*>(pb + q * TBL_Q);
+      const double2 wsd = *reinterpret_cast<const double2*>(tb + q * TBL_Q + TW_CS);     // cs, cd
+      const double2 wb = *reinterpret_cast<const double2*>(tb + q * TBL_Q + TW_CB11);    // cb11, cb12
+      const double cb33 = tb[q * TBL_Q + TW_CB11 + 2];
+      const double NN = R.n1[q][ta] * R.n1[q][tbn];
+      const double P00 = da.x * db.x, P01 = da.x * db.y, P10 = da.y * db.x, P11 = da.y * db.y;
+      const double csn = wsd.x * NN;
+      t00 += wb.x * P11 + cb33 * P00 + csn;
+      t11 += wb.x * P00 + cb33 * P11 + csn;
+      t01 -= wb.y * P10 + cb33 * P01;
+      t10 -= wb.y * P01 + cb33 * P10;
+      t22 += wsd.y * NN;
+    }
+    outer_acc(K, t00 * E0 + t10 * E1, E0);
+    outer_acc(K, t01 * E0 + t11 * E1, E1);
+    outer_acc(K, t22 * E2, E2);
+  } else {
+    // row = displacement node a, column = rotation node b (row < col always holds for this type)
+    const int tbn = b - 9;
+    double A0 = 0, A1 = 0, D0 = 0, D1 = 0;
+    const double* pa = tb + 2 * a;
+#pragma unroll
+    for (int q = 0; q < nq; ++q) {
+      const double2 da = *reinterpret_cast<const double2*>(pa + q * TBL_Q);
+      const double2 wsd = *reinterpret_cast<const double2*>(tb + q * TBL_Q + TW_CS);
+      const double N = R.n1[q][tbn];
+      const double cs = wsd.x * N, cd = wsd.y * N;
+      A0 += cs * da.x; A1 += cs * da.y; D0 += cd * da.x; D1 += cd * da.y;
+    }
+    outer_acc(K, E2, A0 * E1 - A1 * E0);
+    outer_acc(K, 0.5 * (D1 * E0 - D0 * E1), E2);
+  }
+}
+
+template <int NQ>
+__global__ void __launch_bounds__(ASM_THREADS)
+k_asm_planar(const uint32_t* __restrict__ it_pack, const int32_t* __restrict__ it_dest,
+             const int32_t* __restrict__ chunk_ptr, const int32_t* __restrict__ halo_ptr,
+             const int32_t* __restrict__ halo_cells, const int32_t* __restrict__ tpos,
+             const double* __restrict__ rec, int rec_stride, const Tables* __restrict__ tab, int nq_rt, int C,
+             int64_t nc, int tbl_stride, double* __restrict__ vals) {
+  extern __shared__ __align__(16) double smem[];
+  const int nq = NQ > 0 ? NQ : nq_rt;
+  AsmRef& R = *reinterpret_cast<AsmRef*>(smem);
+  double* sK = smem + sizeof(AsmRef) / sizeof(double);                 // 9 x SK_STRIDE
+  int* sHeadTid = reinterpret_cast<int*>(sK + 9 * SK_STRIDE + 1);      // ASM_THREADS (keeps 16-byte alignment)
+  int* sHeadPos = sHeadTid + ASM_THREADS;
+  int* sHeadTp = sHeadPos + ASM_THREADS;
+  int* sWarpCnt = sHeadTp + ASM_THREADS;                               // 8 (+ next_base at [8])
+  double* sFrame = reinterpret_cast<double*>(sWarpCnt + 16);           // nslots x 9   (max 255 slots)
+  const int64_t chunk = blockIdx.x;
+  const int h0 = halo_ptr[chunk], nhalo = halo_ptr[chunk + 1] - h0;
+  const int nslots = C + nhalo;
+  double* sTbl = sFrame + ((nslots * 9 + 1) & ~1);                     // nslots x tbl_stride, 16-byte aligned
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  {
+    double* d = &R.dphi2[0][0][0]; const double* s0 = &tab->dphi2[0][0][0];
+    for (int i = tid; i < FEMO_MAX_NQ * 18; i += ASM_THREADS) d[i] = s0[i];
+    double* d1 = &R.dn1[0][0][0]; const double* s1 = &tab->dn1[0][0][0];
+    for (int i = tid; i < FEMO_MAX_NQ * 8; i += ASM_THREADS) d1[i] = s1[i];
+    double* d2 = &R.n1[0][0]; const double* s2 = &tab->n1[0][0];
+    for (int i = tid; i < FEMO_MAX_NQ * 4; i += ASM_THREADS) d2[i] = s2[i];
+  }
+  __syncthreads();
+  // ---- stage own + halo cells ------------------------------------------------------------
+  for (int s = wid; s < nslots; s += ASM_THREADS / 32) {
+    int64_t cell = s < C ? chunk * C + s : (int64_t)halo_cells[h0 + s - C];
+    if (cell >= nc) continue;                                         // tail chunk
+    const double* rc = rec + cell * rec_stride;
+    if (lane < 9) sFrame[s * 9 + lane] = rc[lane];
+    double* T = sTbl + (int64_t)s * tbl_stride;
+    for (int idx = lane; idx < 2 * nq; idx += 32) {
+      const int q = idx % nq, half = idx / nq;
+      const double* r = rc + REC_HEADER + q * REC_NQF_PLANAR;
+      const double k00 = r[REC_K00], k01 = r[REC_K01], k10 = r[REC_K10], k11 = r[REC_K11];
+      double* o = T + q * TBL_Q;
+      if (half == 0) {
+#pragma unroll
+        for (int a = 0; a < 9; ++a) {
+          const double g0 = R.dphi2[q][a][0], g1 = R.dphi2[q][a][1];
+          o[2 * a] = g0 * k00 + g1 * k10; o[2 * a + 1] = g0 * k01 + g1 * k11;
+        }
+      } else {
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          const double g0 = R.dn1[q][a][0], g1 = R.dn1[q][a][1];
+          o[18 + 2 * a] = g0 * k00 + g1 * k10; o[18 + 2 * a + 1] = g0 * k01 + g1 * k11;
+        }
+        const double cm11 = r[REC_CM11], cm12 = r[REC_CM12], cm33 = r[REC_CM33], hb = r[REC_HB], cs = r[REC_CS],
+                     cd = r[REC_CD];
+        o[TW_CM11] = cm11; o[TW_CM11 + 1] = cm12;
+        o[TW_C3P] = cm33 + 0.25 * cd; o[TW_C3P + 1] = cm33 - 0.25 * cd;
+        o[TW_CS] = cs; o[TW_CS + 1] = cd;
+        o[TW_CB11] = hb * cm11; o[TW_CB11 + 1] = hb * cm12; o[TW_CB11 + 2] = hb * cm33;
+      }
+    }
+  }
+  __syncthreads();
+  // ---- rounds of ASM_THREADS contributions ---------------------------------------------------
+  const int end = chunk_ptr[chunk + 1];
+  int base = chunk_ptr[chunk];
+  while (base < end) {
+    const int j = base + tid;
+    double K[9];
+    uint32_t pk = 0;
+    if (j < end) {
+      pk = it_pack[j];
+      const int slot = pk & 0xff, pair = (pk >> 8) & 0xff;
+      const int a = pair / 13, b = pair - a * 13;
+      const int type = (a < 9 && b < 9) ? 0 : ((a >= 9) ? 1 : 2);
+      asm_block<NQ>(sTbl + (int64_t)slot * tbl_stride, sFrame + slot * 9, R, nq, a, b, type, K);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) sK[k * SK_STRIDE + tid] = K[k];
+    }
+    if (tid == 0) sWarpCnt[8] = base + ASM_THREADS;
+    __syncthreads();
+    const bool head = (pk >> 16) & 1u;
+    const int len = (int)(pk >> 17);
+    bool emit = false;
+    if (head) {
+      if (tid + len <= ASM_THREADS) {
+        for (int f = 1; f < len; ++f) {                               // fixed (cell-ascending) order
+#pragma unroll
+          for (int k = 0; k < 9; ++k) K[k] += sK[k * SK_STRIDE + tid + f];
+        }
+        emit = true;
+      } else {
+        sWarpCnt[8] = base + tid;                                     // segment continues past this round: redo it next round
+      }
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, emit);
+    if (lane == 0) sWarpCnt[wid] = __popc(bal);
+    __syncthreads();
+    if (emit) {
+      int off = __popc(bal & ((1u << lane) - 1u));
+      for (int w = 0; w < wid; ++w) off += sWarpCnt[w];
+      const int d = it_dest[j];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) sK[k * SK_STRIDE + tid] = K[k];
+      sHeadTid[off] = tid; sHeadPos[off] = d; sHeadTp[off] = tpos[d];
+    }
+    int nheads = 0;
+#pragma unroll
+    for (int w = 0; w < ASM_THREADS / 32; ++w) nheads += sWarpCnt[w];
+    const int next_base = sWarpCnt[8];
+    __syncthreads();
+    for (int idx = tid; idx < nheads * 9; idx += ASM_THREADS) {
+      const int h = idx / 9, k = idx - 9 * h;
+      const double v = sK[k * SK_STRIDE + sHeadTid[h]];
+      vals[(int64_t)sHeadPos[h] * 9 + k] = v;
+      const int tp = sHeadTp[h];
+      if (tp >= 0) vals[(int64_t)tp * 9 + (k % 3) * 3 + k / 3] = v;
+    }
+    __syncthreads();
+    base = next_base;
+  }
+}
+
+size_t asm_smem_bytes(int max_slots, int tbl_stride) {
+  size_t b = sizeof(AsmRef) + sizeof(double) * (9 * SK_STRIDE + 1) + sizeof(int) * (3 * ASM_THREADS + 16);
+  b += sizeof(double) * (size_t)((max_slots * 9 + 1) & ~1);
+  b += sizeof(double) * (size_t)max_slots * tbl_stride;
+  return b;
+}
+
+template <int NQ>
+int launch_asm_planar(femo_ctx* c) {
+  const int tbl_stride = TBL_Q * c->nq + 2;
+  const size_t smem = asm_smem_bytes(c->plan_max_slots, tbl_stride);
+  static size_t configured[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (configured[c->device & 7] < smem) {
+    CUDA_TRY(cudaFuncSetAttribute(k_asm_planar<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[c->device & 7] = smem;
+  }
+  k_asm_planar<NQ><<<(unsigned)c->nchunks, ASM_THREADS, smem, c->stream>>>(
+      c->it_pack, c->it_dest, c->chunk_ptr, c->halo_ptr, c->halo_cells, c->tpos, c->rec, c->rec_stride, c->tab, c->nq,
+      c->plan_C, c->nc, tbl_stride, c->vals);
+  return check_launch(c, "k_asm_planar");
+}
+
 // ------------------------------------------------------------------------------------------
 // penalty BC: 5x5 trace matrix per (edge, cell), nodes (q2 va, q2 mid, q2 vb, q1 va, q1 vb)
 __global__ void k_penalty_me(const double* __restrict__ xyz, const int32_t* __restrict__ cv,
@@ -358,7 +595,15 @@ int assemble_jacobian(femo_ctx* c) {
   TRY(check_launch(c, "k_cell_records"));
   cudaEventRecord(c->ev1, c->stream);
   unsigned grid = (unsigned)cdiv(c->ncontrib, GATHER_THREADS);
-  if (c->all_planar)
+  const int tbl_stride = TBL_Q * c->nq + 2;
+  if (c->all_planar && c->plan_ok && asm_smem_bytes(c->plan_max_slots, tbl_stride) <= 220 * 1024) {
+    switch (c->nq) {
+      case 16: TRY(launch_asm_planar<16>(c)); break;
+      case 9: TRY(launch_asm_planar<9>(c)); break;
+      case 4: TRY(launch_asm_planar<4>(c)); break;
+      default: TRY(launch_asm_planar<0>(c)); break;
+    }
+  } else if (c->all_planar)
     k_gather<true><<<grid, GATHER_THREADS, 0, c->stream>>>(c->centry, c->cdest, c->cptr, c->rec, c->rec_stride, c->tab,
                                                            c->nq, c->ncontrib, c->vals);
   else

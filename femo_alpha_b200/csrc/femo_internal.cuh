@@ -95,6 +95,17 @@ struct femo_ctx {
   int32_t *cdest = nullptr;     // contribution -> destination BSR block
   int32_t *cptr = nullptr;      // destination -> first contribution (nnzb+1)
   int32_t *diag_pos = nullptr;  // nb
+  // chunked symmetric assembly plan (planar meshes): see asm_plan_build in topology.cu
+  bool plan_ok = false;
+  int plan_C = 8;               // own cells per chunk (one CTA per chunk)
+  int plan_max_slots = 0;       // max over chunks of own + halo cells
+  int64_t n_items = 0, nchunks = 0, n_halo = 0;
+  uint32_t *it_pack = nullptr;  // n_items: slot | pair<<8 | head<<16 | seglen<<17
+  int32_t *it_dest = nullptr;   // n_items: destination BSR block (row <= col)
+  int32_t *chunk_ptr = nullptr; // nchunks+1 -> items
+  int32_t *halo_ptr = nullptr;  // nchunks+1 -> halo_cells
+  int32_t *halo_cells = nullptr;
+  int32_t *tpos = nullptr;      // nnzb: position of the transposed block, -1 on the diagonal
   int32_t *ut_pos = nullptr, *tu_pos = nullptr;   // nn: positions of (v, nq2+v) and (nq2+v, v)
   // block node -> (cell, local index) adjacency, cell-ascending
   int32_t *nc_ptr = nullptr;    // nb+1
@@ -128,6 +139,7 @@ struct femo_ctx {
   double *cellbuf = nullptr;    // nc*39 element vectors
   bool jac_valid = false, prec_valid = false;
   double t_rec = 0, t_asm = 0, t_solve = 0, t_iter = 0;
+  double dmma_tf = 0;           // last measured fp64 mma.sync rate (TFLOP/s)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
@@ -152,6 +164,7 @@ int check_launch(femo_ctx* c, const char* what);
 int topo_build(femo_ctx* c, const int32_t* conn_vtk_host);                // topology.cu
 int pattern_build(femo_ctx* c);                                           // topology.cu
 int penalty_build(femo_ctx* c, const uint8_t* vertex_on_host);            // topology.cu
+int asm_plan_build(femo_ctx* c);                                          // topology.cu
 int assemble_jacobian(femo_ctx* c);                                       // assemble.cu
 int assemble_load(femo_ctx* c, double* F_dev);                            // assemble.cu
 int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc);       // solver.cu

@@ -293,6 +293,18 @@ __global__ void k_fma_peak(double* out, int iters) {
   }
   out[blockIdx.x * (int64_t)blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
+// fp64 tensor-core peak: 4 independent mma.sync m8n8k4 f64 chains per warp (512 flop per mma)
+__global__ void k_dmma_peak(double* out, int iters) {
+  double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+  double c0[2] = {0, 0}, c1[2] = {0, 0}, c2[2] = {0, 0}, c3[2] = {0, 0};
+  for (int i = 0; i < iters; ++i) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0[0]), "+d"(c0[1]) : "d"(a), "d"(b));
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c1[0]), "+d"(c1[1]) : "d"(a), "d"(b));
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c2[0]), "+d"(c2[1]) : "d"(a), "d"(b));
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c3[0]), "+d"(c3[1]) : "d"(a), "d"(b));
+  }
+  out[blockIdx.x * (int64_t)blockDim.x + threadIdx.x] = c0[0] + c0[1] + c1[0] + c1[1] + c2[0] + c2[1] + c3[0] + c3[1];
+}
 __global__ void k_copy(const double4* __restrict__ a, double4* __restrict__ b, int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x) b[i] = a[i];
 }
@@ -413,6 +425,15 @@ int measure_peaks(femo_ctx* c, double* tf, double* gbs) {
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
   *tf = 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) / 1e12;
+  if (c->dmma_tf >= 0) {   // also measure the fp64 tensor-core (DMMA) rate
+    k_dmma_peak<<<blocks, threads, 0, c->stream>>>(out, 64);
+    cudaEventRecord(c->ev0, c->stream);
+    k_dmma_peak<<<blocks, threads, 0, c->stream>>>(out, 1 << 12);
+    cudaEventRecord(c->ev1, c->stream);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->dmma_tf = 4.0 * 512.0 * (1 << 12) * (double)blocks * (threads / 32) / (ms * 1e-3) / 1e12;
+  }
   dev_free(&out);
   const int64_t nbytes = (int64_t)1 << 30;
   double4 *a = nullptr, *b = nullptr;

@@ -7,6 +7,7 @@
 #include <cub/cub.cuh>
 #include <algorithm>
 #include <map>
+#include <cstdlib>
 #include "femo_internal.cuh"
 
 namespace {
@@ -128,6 +129,110 @@ __global__ void k_find_pos(const int32_t* rowptr, const int32_t* colidx, const i
     if (v < cidx) lo = mid + 1; else hi = mid - 1;
   }
   pos[i] = res;
+}
+
+// ---- chunked symmetric assembly plan -------------------------------------------------------
+__device__ __forceinline__ int pair_type(int a, int b) { return (a < 9 && b < 9) ? 0 : ((a >= 9 && b >= 9) ? 1 : 2); }
+
+// flag contributions whose destination lies in the upper block triangle (row <= col)
+__global__ void k_plan_flag(const int32_t* centry, const int32_t* cb, int64_t n, uint8_t* flag) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int32_t e = centry[i];
+  int32_t cell = e / 169; int pair = e - cell * 169;
+  int a = pair / 13, b = pair - a * 13;
+  flag[i] = cb[(int64_t)cell * 13 + a] <= cb[(int64_t)cell * 13 + b] ? 1 : 0;
+}
+
+// sort key = (owner chunk << 2) | type; owner chunk = chunk of the first (lowest) contributing cell
+__global__ void k_plan_keys(const int32_t* sel, const int32_t* centry, const int32_t* cdest, const int32_t* cptr,
+                            int64_t n, int C, uint32_t* key) {
+  int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  int32_t i = sel[j];
+  int32_t e = centry[i];
+  int pair = e % 169;
+  int32_t ocell = centry[cptr[cdest[i]]] / 169;
+  key[j] = ((uint32_t)(ocell / C) << 2) | (uint32_t)pair_type(pair / 13, pair % 13);
+}
+
+__global__ void k_plan_halo_keys(const int32_t* src, const uint32_t* key, const int32_t* centry, int64_t n, int C,
+                                 uint64_t* hkey, uint8_t* hflag) {
+  int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  int32_t cell = centry[src[j]] / 169;
+  uint32_t k = key[j] >> 2;
+  bool halo = (uint32_t)(cell / C) != k;
+  hkey[j] = ((uint64_t)k << 32) | (uint32_t)cell;
+  hflag[j] = halo ? 1 : 0;
+}
+
+__global__ void k_plan_unique64(const uint64_t* in, int64_t n, uint8_t* flag) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  flag[i] = (i == 0 || in[i] != in[i - 1]) ? 1 : 0;
+}
+
+// ptr[k] = first index whose (key >> shift) >= k, k = 0..nk
+template <typename K>
+__global__ void k_plan_lower_bound(const K* keys, int64_t n, int shift, int64_t nk, int32_t* ptr) {
+  int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k > nk) return;
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if ((int64_t)(keys[mid] >> shift) < k) lo = mid + 1; else hi = mid;
+  }
+  ptr[k] = (int32_t)lo;
+}
+
+__global__ void k_plan_items(const int32_t* src, const uint32_t* key, const int32_t* centry, const int32_t* cdest,
+                             const int32_t* cptr, const uint64_t* hk, const int32_t* halo_ptr, int64_t n, int C,
+                             uint32_t* it_pack, int32_t* it_dest, int* bad) {
+  int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  int32_t i = src[j];
+  int32_t e = centry[i];
+  int32_t cell = e / 169; int pair = e - cell * 169;
+  int32_t d = cdest[i];
+  uint32_t k = key[j] >> 2;
+  int slot;
+  if ((uint32_t)(cell / C) == k) slot = cell - (int32_t)k * C;
+  else {
+    uint64_t want = ((uint64_t)k << 32) | (uint32_t)cell;
+    int32_t lo = halo_ptr[k], hi = halo_ptr[k + 1];
+    const int32_t base = lo;
+    while (lo < hi) { int32_t mid = (lo + hi) >> 1; if (hk[mid] < want) lo = mid + 1; else hi = mid; }
+    slot = C + (lo - base);
+  }
+  int32_t first = cptr[d], len = cptr[d + 1] - first;
+  if (slot > 255 || len > 127) atomicOr(bad, 1);
+  it_pack[j] = (uint32_t)slot | ((uint32_t)pair << 8) | ((first == i) ? (1u << 16) : 0u) | ((uint32_t)len << 17);
+  it_dest[j] = d;
+}
+
+__global__ void k_plan_halo_cells(const uint64_t* hk, int64_t n, int32_t* cells) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) cells[i] = (int32_t)(hk[i] & 0xffffffffu);
+}
+
+// tpos[k] = position of block (col,row) for k = (row,col), row != col
+__global__ void k_plan_tpos(const int32_t* rowptr, const int32_t* colidx, int64_t nb, int32_t* tpos) {
+  int64_t row = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (row >= nb) return;
+  for (int32_t k = rowptr[row]; k < rowptr[row + 1]; ++k) {
+    int32_t col = colidx[k];
+    int32_t res = -1;
+    if (col != row) {
+      int32_t lo = rowptr[col], hi = rowptr[col + 1] - 1;
+      while (lo <= hi) {
+        int32_t mid = (lo + hi) >> 1; int32_t v = colidx[mid];
+        if (v == (int32_t)row) { res = mid; break; }
+        if (v < (int32_t)row) lo = mid + 1; else hi = mid - 1;
+      }
+    }
+    tpos[k] = res;
+  }
 }
 
 int bits_for(uint64_t v) { int b = 0; while (v) { ++b; v >>= 1; } return b < 1 ? 1 : b; }
@@ -321,5 +426,112 @@ int penalty_build(femo_ctx* c, const uint8_t* von) {
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   c->launches += 1;
   dev_free(&drows); dev_free(&dcols);
+  return 0;
+}
+
+// Chunked symmetric assembly plan.  The contribution list of pattern_build
+// (sorted by destination, ascending cell inside a destination) is filtered to destinations with
+// row <= col and stable-sorted by (owner chunk, type): inside one chunk the items are grouped by
+// type (uu | theta-theta | u-theta), then by destination, then by cell -> fixed summation order.
+int asm_plan_build(femo_ctx* c) {
+  c->plan_ok = false;
+  dev_free(&c->it_pack); dev_free(&c->it_dest); dev_free(&c->chunk_ptr); dev_free(&c->halo_ptr);
+  dev_free(&c->halo_cells); dev_free(&c->tpos);
+  const char* envc = getenv("FEMO_ASM_CHUNK");
+  int C = envc ? atoi(envc) : 8;
+  if (C < 1) return 0;                       // FEMO_ASM_CHUNK=0 disables the plan (gather kernel is used)
+  if (C > 64) C = 64;
+  c->plan_C = C;
+  const int64_t n = c->ncontrib;
+  const int64_t nchunks = cdiv(c->nc, C);
+  c->nchunks = nchunks;
+  uint8_t* flag = nullptr; int32_t *sel = nullptr, *src = nullptr, *dnum = nullptr;
+  uint32_t *key_in = nullptr, *key = nullptr;
+  TRY(dev_alloc(&flag, n)); TRY(dev_alloc(&sel, n)); TRY(dev_alloc(&dnum, 1));
+  k_plan_flag<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(c->centry, c->cell_blocks, n, flag);
+  TRY(check_launch(c, "k_plan_flag"));
+  size_t tb = 0; void* tmp = nullptr;
+  cub::CountingInputIterator<int32_t> count_it(0);
+  cub::DeviceSelect::Flagged(nullptr, tb, count_it, flag, sel, dnum, (int)n, c->stream);
+  CUDA_TRY(cudaMalloc(&tmp, tb));
+  cub::DeviceSelect::Flagged(tmp, tb, count_it, flag, sel, dnum, (int)n, c->stream);
+  int32_t ni32 = 0;
+  CUDA_TRY(cudaMemcpyAsync(&ni32, dnum, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  cudaFree(tmp); tmp = nullptr; dev_free(&flag);
+  const int64_t ni = ni32;
+  c->n_items = ni;
+  TRY(dev_alloc(&key_in, ni)); TRY(dev_alloc(&key, ni)); TRY(dev_alloc(&src, ni));
+  k_plan_keys<<<(unsigned)cdiv(ni, 256), 256, 0, c->stream>>>(sel, c->centry, c->cdest, c->cptr, ni, C, key_in);
+  TRY(check_launch(c, "k_plan_keys"));
+  const int kbits = bits_for((uint64_t)nchunks) + 2;
+  tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, key_in, key, sel, src, (int)ni, 0, kbits, c->stream);
+  CUDA_TRY(cudaMalloc(&tmp, tb));
+  cub::DeviceRadixSort::SortPairs(tmp, tb, key_in, key, sel, src, (int)ni, 0, kbits, c->stream);   // stable
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  cudaFree(tmp); tmp = nullptr; dev_free(&key_in); dev_free(&sel);
+  TRY(dev_alloc(&c->chunk_ptr, (size_t)nchunks + 1));
+  k_plan_lower_bound<uint32_t><<<(unsigned)cdiv(nchunks + 1, 256), 256, 0, c->stream>>>(key, ni, 2, nchunks, c->chunk_ptr);
+  TRY(check_launch(c, "k_plan_lower_bound"));
+  // halo cells: unique (chunk, cell) pairs with cell outside the chunk
+  uint64_t *hkey = nullptr, *hsel = nullptr, *hsorted = nullptr, *hk = nullptr; uint8_t* hflag = nullptr;
+  TRY(dev_alloc(&hkey, ni)); TRY(dev_alloc(&hflag, ni)); TRY(dev_alloc(&hsel, ni));
+  k_plan_halo_keys<<<(unsigned)cdiv(ni, 256), 256, 0, c->stream>>>(src, key, c->centry, ni, C, hkey, hflag);
+  TRY(check_launch(c, "k_plan_halo_keys"));
+  tb = 0;
+  cub::DeviceSelect::Flagged(nullptr, tb, hkey, hflag, hsel, dnum, (int)ni, c->stream);
+  CUDA_TRY(cudaMalloc(&tmp, tb));
+  cub::DeviceSelect::Flagged(tmp, tb, hkey, hflag, hsel, dnum, (int)ni, c->stream);
+  int32_t nh32 = 0;
+  CUDA_TRY(cudaMemcpyAsync(&nh32, dnum, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  cudaFree(tmp); tmp = nullptr; dev_free(&hkey);
+  int64_t nh = nh32, nu = 0;
+  TRY(dev_alloc(&hsorted, nh)); TRY(dev_alloc(&hk, nh));
+  if (nh > 0) {
+    tb = 0;
+    const int hbits = 32 + bits_for((uint64_t)nchunks);
+    cub::DeviceRadixSort::SortKeys(nullptr, tb, hsel, hsorted, (int)nh, 0, hbits, c->stream);
+    CUDA_TRY(cudaMalloc(&tmp, tb));
+    cub::DeviceRadixSort::SortKeys(tmp, tb, hsel, hsorted, (int)nh, 0, hbits, c->stream);
+    cudaFree(tmp); tmp = nullptr;
+    k_plan_unique64<<<(unsigned)cdiv(nh, 256), 256, 0, c->stream>>>(hsorted, nh, hflag);
+    tb = 0;
+    cub::DeviceSelect::Flagged(nullptr, tb, hsorted, hflag, hk, dnum, (int)nh, c->stream);
+    CUDA_TRY(cudaMalloc(&tmp, tb));
+    cub::DeviceSelect::Flagged(tmp, tb, hsorted, hflag, hk, dnum, (int)nh, c->stream);
+    int32_t nu32 = 0;
+    CUDA_TRY(cudaMemcpyAsync(&nu32, dnum, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    cudaFree(tmp); tmp = nullptr;
+    nu = nu32;
+  }
+  dev_free(&hsel); dev_free(&hsorted); dev_free(&hflag);
+  c->n_halo = nu;
+  TRY(dev_alloc(&c->halo_ptr, (size_t)nchunks + 1)); TRY(dev_alloc(&c->halo_cells, (size_t)nu));
+  k_plan_lower_bound<uint64_t><<<(unsigned)cdiv(nchunks + 1, 256), 256, 0, c->stream>>>(hk, nu, 32, nchunks, c->halo_ptr);
+  if (nu > 0) k_plan_halo_cells<<<(unsigned)cdiv(nu, 256), 256, 0, c->stream>>>(hk, nu, c->halo_cells);
+  TRY(check_launch(c, "k_plan_halo"));
+  TRY(dev_alloc(&c->it_pack, (size_t)ni)); TRY(dev_alloc(&c->it_dest, (size_t)ni));
+  int* bad = nullptr; TRY(dev_alloc(&bad, 1));
+  CUDA_TRY(cudaMemsetAsync(bad, 0, sizeof(int), c->stream));
+  k_plan_items<<<(unsigned)cdiv(ni, 256), 256, 0, c->stream>>>(src, key, c->centry, c->cdest, c->cptr, hk, c->halo_ptr, ni, C,
+                                                            c->it_pack, c->it_dest, bad);
+  TRY(check_launch(c, "k_plan_items"));
+  TRY(dev_alloc(&c->tpos, (size_t)c->nnzb));
+  k_plan_tpos<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colidx, c->nb, c->tpos);
+  TRY(check_launch(c, "k_plan_tpos"));
+  int badh = 0;
+  std::vector<int32_t> hp((size_t)nchunks + 1);
+  CUDA_TRY(cudaMemcpyAsync(&badh, bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaMemcpyAsync(hp.data(), c->halo_ptr, sizeof(int32_t) * (nchunks + 1), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  dev_free(&bad); dev_free(&src); dev_free(&key); dev_free(&hk);
+  int maxh = 0;
+  for (int64_t k = 0; k < nchunks; ++k) maxh = std::max(maxh, hp[k + 1] - hp[k]);
+  c->plan_max_slots = C + maxh;
+  c->launches += 10;
+  c->plan_ok = !badh;
   return 0;
 }

@@ -284,3 +284,8 @@ class ShellDevice:
         tf = C.c_double(0.0); gb = C.c_double(0.0)
         L.check(self.lib.femo_measure_peaks(self._ctx, C.byref(tf), C.byref(gb)))
         return tf.value, gb.value
+
+    def dmma_tflops(self):
+        tf = C.c_double(0.0)
+        L.check(self.lib.femo_last_dmma_tflops(self._ctx, C.byref(tf)))
+        return tf.value

@@ -162,6 +162,8 @@ int femo_pcg_fixed(femo_ctx* ctx, int n_iter, double* ms_total);
 /* micro-benchmarks for the roofline denominators: fp64 FMA throughput (TFLOP/s) and a device
  * copy (GB/s) measured on this GPU */
 int femo_measure_peaks(femo_ctx* ctx, double* fp64_tflops, double* copy_gbs);
+/* fp64 tensor-core (mma.sync m8n8k4 f64) rate measured by the last femo_measure_peaks call, TFLOP/s */
+int femo_last_dmma_tflops(femo_ctx* ctx, double* tflops);
 
 #ifdef __cplusplus
 }
