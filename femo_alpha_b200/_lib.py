@@ -68,6 +68,12 @@ SIGNATURES = {
     "femo_pnorm_stress": [_P, C.c_int, _D],
     "femo_pnorm_stress_grad": [_P, C.c_int, C.c_int, _P, C.c_int],
     "femo_stress_field": [_P, C.c_int, _P, C.c_int],
+    "femo_nccl_unique_id": [_P],
+    "femo_dist_setup": [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, C.c_int64],
+    "femo_dist_init": [_P, _P],
+    "femo_halo_exchange": [_P, _P, C.c_int],
+    "femo_dist_allreduce": [_P, _D, C.c_int],
+    "femo_dist_counts": [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
     "femo_launch_count": [_P, C.POINTER(C.c_int64)],
     "femo_last_timings": [_P, _D],
     "femo_pcg_fixed": [_P, C.c_int, _D],

@@ -179,6 +179,7 @@ int femo_ctx_destroy(femo_ctx* c) {
   if (!c) return 0;
   DevGuard g(c->device);
   cudaStreamSynchronize(c->stream);
+  dist_free(c);
   void* ptrs[] = {c->xyz, c->cv, c->ce, c->edges, c->cell_blocks, c->hE, c->tab, c->h, c->E, c->nu, c->rho, c->f, c->uhat,
                   c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
                   c->nc_adj, c->rec, c->bcmask, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
@@ -249,7 +250,7 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   double** vecs[] = {&c->w, &c->b, &c->r, &c->z, &c->p, &c->Ap, &c->tmp, &c->tmp2};
   for (double** v : vecs) { TRY(dev_alloc(v, n)); CUDA_TRY(cudaMemsetAsync(*v, 0, sizeof(double) * n, c->stream)); }
   TRY(dev_alloc(&c->dinv6, (size_t)c->nn * 36)); TRY(dev_alloc(&c->dinv3, (size_t)(c->ne + c->nc) * 9));
-  TRY(dev_alloc(&c->red, 8 * 1184)); TRY(dev_alloc(&c->scal, 16));
+  TRY(dev_alloc(&c->red, 8 * 1184)); TRY(dev_alloc(&c->scal, 32));
   TRY(dev_alloc(&c->cellbuf, (size_t)c->nc * 39));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   c->setup_done = true; c->jac_valid = false; c->prec_valid = false;

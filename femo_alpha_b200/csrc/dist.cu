@@ -1,0 +1,210 @@
+// Multi-GPU plumbing of libfemo_b200.so: one process per GPU, NCCL over NVLink 5 / NVSwitch.
+//
+// The reference is serial (its dolfinx wrapper never passes a communicator beyond COMM_WORLD size 1,
+// SURVEY 2.1), so this file replaces nothing line-for-line; it implements SURVEY 8(e):
+//   * owner mask per block node, key-ordered send / receive lists per neighbour (built on the host by
+//     femo_alpha_b200/partition.py),
+//   * halo exchange = pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel, all on the context's stream,
+//   * in-place ncclAllReduce of the Krylov scalars.
+// Assembly needs none of it (owner-computes with one layer of ghost cells).
+//
+// NCCL is bound at run time (dlopen): single-GPU users and the CPU-side ABI tests never load it.  If the
+// process already holds a libnccl.so.2 (torch's bundled copy), that one is reused.
+#include <dlfcn.h>
+#include <nccl.h>
+#include <cstdlib>
+#include <cstring>
+#include "femo_internal.cuh"
+
+namespace {
+
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+
+int nccl_load() {
+  if (g_nccl.handle) return 0;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);          // already in the process (torch)?
+  const char* env = getenv("FEMO_NCCL_LIB");
+  if (!h && env) h = dlopen(env, RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return femo_fail(std::string("cannot load libnccl.so.2: ") + dlerror());
+#define BIND(field, name)                                                             \
+  *(void**)(&g_nccl.field) = dlsym(h, name);                                          \
+  if (!g_nccl.field) return femo_fail(std::string("libnccl: missing symbol ") + name)
+  BIND(GetUniqueId, "ncclGetUniqueId"); BIND(CommInitRank, "ncclCommInitRank"); BIND(CommDestroy, "ncclCommDestroy");
+  BIND(AllReduce, "ncclAllReduce"); BIND(Send, "ncclSend"); BIND(Recv, "ncclRecv");
+  BIND(GroupStart, "ncclGroupStart"); BIND(GroupEnd, "ncclGroupEnd"); BIND(GetErrorString, "ncclGetErrorString");
+#undef BIND
+  g_nccl.handle = h;
+  return 0;
+}
+
+#define NCCL_TRY(expr)                                                                          \
+  do {                                                                                          \
+    ncclResult_t _r = (expr);                                                                   \
+    if (_r != ncclSuccess)                                                                      \
+      return femo_fail(std::string(#expr) + ": " + g_nccl.GetErrorString(_r));                  \
+  } while (0)
+
+__global__ void k_halo_pack(const double* __restrict__ x, const int32_t* __restrict__ blocks, int64_t n,
+                            double* __restrict__ buf) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= 3 * n) return;
+  int64_t b = i / 3; int k = (int)(i - 3 * b);
+  buf[i] = x[3 * (int64_t)blocks[b] + k];
+}
+__global__ void k_halo_unpack(double* __restrict__ x, const int32_t* __restrict__ blocks, int64_t n,
+                              const double* __restrict__ buf) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= 3 * n) return;
+  int64_t b = i / 3; int k = (int)(i - 3 * b);
+  x[3 * (int64_t)blocks[b] + k] = buf[i];
+}
+
+struct DevGuard2 {
+  int prev = 0;
+  explicit DevGuard2(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); }
+  ~DevGuard2() { cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+int halo_exchange(femo_ctx* c, double* x) {
+  if (c->world <= 1) return 0;
+  if (!c->nccl_comm) return femo_fail("halo_exchange: communicator not initialised (femo_dist_init)");
+  ncclComm_t comm = (ncclComm_t)c->nccl_comm;
+  if (c->n_send > 0) {
+    k_halo_pack<<<(unsigned)cdiv(3 * c->n_send, 256), 256, 0, c->stream>>>(x, c->send_blocks, c->n_send, c->send_buf);
+    c->launches += 1;
+  }
+  NCCL_TRY(g_nccl.GroupStart());
+  for (int i = 0; i < c->n_nbr; ++i) {
+    const int ns = c->send_off[i + 1] - c->send_off[i], nr = c->recv_off[i + 1] - c->recv_off[i];
+    if (ns > 0) NCCL_TRY(g_nccl.Send(c->send_buf + 3 * (int64_t)c->send_off[i], 3 * (size_t)ns, ncclDouble, c->nbr_rank[i], comm, c->stream));
+    if (nr > 0) NCCL_TRY(g_nccl.Recv(c->recv_buf + 3 * (int64_t)c->recv_off[i], 3 * (size_t)nr, ncclDouble, c->nbr_rank[i], comm, c->stream));
+  }
+  NCCL_TRY(g_nccl.GroupEnd());
+  if (c->n_recv > 0) {
+    k_halo_unpack<<<(unsigned)cdiv(3 * c->n_recv, 256), 256, 0, c->stream>>>(x, c->recv_blocks, c->n_recv, c->recv_buf);
+    c->launches += 1;
+  }
+  c->halo_count += 1;
+  return check_launch(c, "halo exchange");
+}
+
+int dist_allreduce_sum(femo_ctx* c, double* v, int n) {
+  if (c->world <= 1) return 0;
+  if (!c->nccl_comm) return femo_fail("allreduce: communicator not initialised (femo_dist_init)");
+  NCCL_TRY(g_nccl.AllReduce(v, v, (size_t)n, ncclDouble, ncclSum, (ncclComm_t)c->nccl_comm, c->stream));
+  c->allreduce_count += 1;
+  return 0;
+}
+
+int dist_allreduce_host(femo_ctx* c, double* hv, int n) {
+  if (c->world <= 1) return 0;
+  if (n > 8) return femo_fail("dist_allreduce_host: at most 8 values");
+  CUDA_TRY(cudaMemcpyAsync(c->scal + 16, hv, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+  TRY(dist_allreduce_sum(c, c->scal + 16, n));
+  CUDA_TRY(cudaMemcpyAsync(hv, c->scal + 16, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+void dist_free(femo_ctx* c) {
+  if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->nccl_comm);
+  c->nccl_comm = nullptr;
+  dev_free(&c->send_blocks); dev_free(&c->recv_blocks); dev_free(&c->send_buf); dev_free(&c->recv_buf); dev_free(&c->own);
+}
+
+extern "C" {
+
+int femo_nccl_unique_id(void* id128) {
+  if (!id128) return femo_fail("femo_nccl_unique_id: null buffer");
+  TRY(nccl_load());
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  NCCL_TRY(g_nccl.GetUniqueId(&id));
+  memcpy(id128, &id, sizeof(id));
+  return 0;
+}
+
+int femo_dist_setup(femo_ctx* c, int rank, int world, int n_nbr, const int32_t* nbr_ranks, const int32_t* send_off,
+                    const int32_t* send_blocks, const int32_t* recv_off, const int32_t* recv_blocks,
+                    const uint8_t* own_block, int64_t n_owned_cells) {
+  if (!c || !c->setup_done) return femo_fail("femo_dist_setup: context not set up");
+  if (world < 1 || rank < 0 || rank >= world) return femo_fail("femo_dist_setup: bad rank / world");
+  if (n_owned_cells < 0 || n_owned_cells > c->nc) return femo_fail("femo_dist_setup: bad owned-cell count");
+  DevGuard2 g(c->device);
+  c->rank = rank; c->world = world; c->n_nbr = n_nbr; c->nc_owned = n_owned_cells;
+  c->nbr_rank.assign(nbr_ranks, nbr_ranks + n_nbr);
+  c->send_off.assign(send_off, send_off + n_nbr + 1);
+  c->recv_off.assign(recv_off, recv_off + n_nbr + 1);
+  c->n_send = n_nbr ? send_off[n_nbr] : 0; c->n_recv = n_nbr ? recv_off[n_nbr] : 0;
+  for (int64_t i = 0; i < c->n_send; ++i)
+    if (send_blocks[i] < 0 || send_blocks[i] >= c->nb) return femo_fail("femo_dist_setup: send block out of range");
+  for (int64_t i = 0; i < c->n_recv; ++i)
+    if (recv_blocks[i] < 0 || recv_blocks[i] >= c->nb) return femo_fail("femo_dist_setup: recv block out of range");
+  TRY(dev_alloc(&c->send_blocks, (size_t)c->n_send)); TRY(dev_alloc(&c->recv_blocks, (size_t)c->n_recv));
+  TRY(dev_alloc(&c->send_buf, (size_t)3 * c->n_send)); TRY(dev_alloc(&c->recv_buf, (size_t)3 * c->n_recv));
+  if (c->n_send) CUDA_TRY(cudaMemcpy(c->send_blocks, send_blocks, sizeof(int32_t) * c->n_send, cudaMemcpyHostToDevice));
+  if (c->n_recv) CUDA_TRY(cudaMemcpy(c->recv_blocks, recv_blocks, sizeof(int32_t) * c->n_recv, cudaMemcpyHostToDevice));
+  std::vector<double> own((size_t)c->nb);
+  for (int64_t i = 0; i < c->nb; ++i) own[i] = own_block[i] ? 1.0 : 0.0;
+  TRY(dev_alloc(&c->own, (size_t)c->nb));
+  CUDA_TRY(cudaMemcpy(c->own, own.data(), sizeof(double) * c->nb, cudaMemcpyHostToDevice));
+  c->prec_valid = false;
+  return 0;
+}
+
+int femo_dist_init(femo_ctx* c, const void* id128) {
+  if (!c || !id128) return femo_fail("femo_dist_init: null argument");
+  if (c->world <= 1) return 0;
+  TRY(nccl_load());
+  DevGuard2 g(c->device);
+  ncclUniqueId id;
+  memcpy(&id, id128, sizeof(id));
+  ncclComm_t comm = nullptr;
+  NCCL_TRY(g_nccl.CommInitRank(&comm, c->world, id, c->rank));
+  c->nccl_comm = comm;
+  return 0;
+}
+
+int femo_halo_exchange(femo_ctx* c, double* x, int on_device) {
+  if (!c || !c->setup_done) return femo_fail("femo_halo_exchange: context not set up");
+  DevGuard2 g(c->device);
+  double* xd = x;
+  if (!on_device) {
+    xd = c->tmp2;
+    CUDA_TRY(cudaMemcpyAsync(xd, x, sizeof(double) * c->ndof, cudaMemcpyHostToDevice, c->stream));
+  }
+  TRY(halo_exchange(c, xd));
+  if (!on_device) CUDA_TRY(cudaMemcpyAsync(x, xd, sizeof(double) * c->ndof, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int femo_dist_allreduce(femo_ctx* c, double* vals, int n) {
+  if (!c) return femo_fail("null context");
+  DevGuard2 g(c->device);
+  return dist_allreduce_host(c, vals, n);
+}
+
+int femo_dist_counts(femo_ctx* c, int64_t* halo_exchanges, int64_t* allreduces) {
+  if (!c) return femo_fail("null context");
+  if (halo_exchanges) *halo_exchanges = c->halo_count;
+  if (allreduces) *allreduces = c->allreduce_count;
+  return 0;
+}
+
+}  // extern "C"

@@ -129,6 +129,17 @@ struct femo_ctx {
   int64_t n_pen_rows = 0;
   int32_t* pen_row = nullptr;        // n_pen_rows: row block
   int32_t* pen_row_ptr = nullptr;    // n_pen_rows+1 -> into destinations
+  // multi-GPU (one process per GPU): owner mask, halo lists, NCCL communicator (dist.cu)
+  int world = 1, rank = 0;
+  void* nccl_comm = nullptr;
+  int n_nbr = 0;
+  std::vector<int> nbr_rank, send_off, recv_off;   // neighbour ranks and block offsets (n_nbr+1)
+  int64_t n_send = 0, n_recv = 0;                 // blocks
+  int32_t *send_blocks = nullptr, *recv_blocks = nullptr;
+  double *send_buf = nullptr, *recv_buf = nullptr;
+  double* own = nullptr;        // nb: 1 = block node owned by this rank, 0 = ghost (null when world == 1)
+  int64_t nc_owned = 0;         // owned cells come first in the local cell order
+  int64_t halo_count = 0, allreduce_count = 0;
   // solver state
   double *w = nullptr, *b = nullptr, *r = nullptr, *z = nullptr, *p = nullptr, *Ap = nullptr, *tmp = nullptr;
   double *tmp2 = nullptr;
@@ -178,6 +189,10 @@ int out_grad(femo_ctx* c, int which, int arg, double* g_dev);             // out
 int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out);   // outputs.cu
 int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out);      // outputs.cu
 int measure_peaks(femo_ctx* c, double* tf, double* gbs);                  // solver.cu
+int halo_exchange(femo_ctx* c, double* x);                                // dist.cu: ghost entries <- owners
+int dist_allreduce_sum(femo_ctx* c, double* dev_vals, int n);             // dist.cu: in-place on the stream
+int dist_allreduce_host(femo_ctx* c, double* host_vals, int n);           // dist.cu
+void dist_free(femo_ctx* c);                                              // dist.cu
 int pnorm_value(femo_ctx* c, int tag, double* val);                       // outputs.cu
 int pnorm_grad(femo_ctx* c, int tag, int arg, double* g);                 // outputs.cu
 int stress_field(femo_ctx* c, int surface, double* out);                  // outputs.cu

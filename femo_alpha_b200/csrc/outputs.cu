@@ -420,10 +420,13 @@ int run_cell_op(femo_ctx* c, const CellArgs& A) {
 int sum_cells(femo_ctx* c, double* val) {
   const int NB = 296;
   double* part = c->red + 6 * 1184;
-  k_sum_cells<<<NB, 256, 0, c->stream>>>(c->cellbuf, 39, c->nc, part);
+  // multi-GPU: every cell is integrated by exactly one rank (owned cells come first), then summed over ranks
+  const int64_t ncs = c->world > 1 ? c->nc_owned : c->nc;
+  k_sum_cells<<<NB, 256, 0, c->stream>>>(c->cellbuf, 39, ncs, part);
   k_sum_final<<<1, 32, 0, c->stream>>>(part, NB, c->scal + 9);
   TRY(check_launch(c, "k_sum_cells"));
   c->launches += 2;
+  if (c->world > 1) TRY(dist_allreduce_sum(c, c->scal + 9, 1));
   CUDA_TRY(cudaMemcpyAsync(val, c->scal + 9, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   return 0;

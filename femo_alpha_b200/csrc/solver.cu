@@ -63,7 +63,7 @@ template <int LANES>
 __global__ void __launch_bounds__(256)
 k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const double* __restrict__ vals,
        const double* __restrict__ x, const double* __restrict__ mask, int64_t nb, double* __restrict__ y,
-       double* __restrict__ dot_part) {
+       double* __restrict__ dot_part, const double* __restrict__ own) {
   const int lane = threadIdx.x % LANES;
   constexpr int GPW = 32 / LANES;                       // row groups per warp
   const int sub = (threadIdx.x & 31) / LANES;
@@ -98,7 +98,8 @@ k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, c
         y0 = m0 * y0 + (1.0 - m0) * xr0; y1 = m1 * y1 + (1.0 - m1) * xr1; y2 = m2 * y2 + (1.0 - m2) * xr2;
       }
       y[3 * row] = y0; y[3 * row + 1] = y1; y[3 * row + 2] = y2;
-      dacc += xr0 * y0 + xr1 * y1 + xr2 * y2;
+      const double ow = own ? own[row] : 1.0;
+      dacc += ow * (xr0 * y0 + xr1 * y1 + xr2 * y2);
     }
   }
   if (dot_part) {
@@ -146,10 +147,11 @@ __device__ __forceinline__ void spd_inverse(double* A) {
 // block-Jacobi set-up: 6x6 (u_v, theta_v) at vertices, 3x3 at edge / centre nodes, of A (with BCs)
 __global__ void k_precond_setup(const double* __restrict__ vals, const int32_t* __restrict__ diag_pos,
                                 const int32_t* __restrict__ ut_pos, const int32_t* __restrict__ tu_pos,
-                                const double* __restrict__ mask, int64_t nn, int64_t nq2,
-                                double* __restrict__ dinv6, double* __restrict__ dinv3) {
+                                const double* __restrict__ mask, const double* __restrict__ own, int64_t nn,
+                                int64_t nq2, double* __restrict__ dinv6, double* __restrict__ dinv3) {
   int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (I >= nq2) return;
+  const double ow = own ? own[I] : 1.0;           // ghost nodes: rows are incomplete -> identity block
   if (I < nn) {
     double A[36];
     const double* uu = vals + (int64_t)diag_pos[I] * 9;
@@ -157,7 +159,7 @@ __global__ void k_precond_setup(const double* __restrict__ vals, const int32_t* 
     const double* ut = vals + (int64_t)ut_pos[I] * 9;
     const double* tu = vals + (int64_t)tu_pos[I] * 9;
     double m[6];
-    for (int i = 0; i < 3; ++i) { m[i] = mask[3 * I + i]; m[3 + i] = mask[3 * (nq2 + I) + i]; }
+    for (int i = 0; i < 3; ++i) { m[i] = ow * mask[3 * I + i]; m[3 + i] = ow * mask[3 * (nq2 + I) + i]; }
     for (int i = 0; i < 3; ++i)
       for (int j = 0; j < 3; ++j) {
         A[i * 6 + j] = uu[3 * i + j]; A[i * 6 + 3 + j] = ut[3 * i + j];
@@ -170,7 +172,7 @@ __global__ void k_precond_setup(const double* __restrict__ vals, const int32_t* 
   } else {
     double A[9];
     const double* uu = vals + (int64_t)diag_pos[I] * 9;
-    double m[3] = {mask[3 * I], mask[3 * I + 1], mask[3 * I + 2]};
+    double m[3] = {ow * mask[3 * I], ow * mask[3 * I + 1], ow * mask[3 * I + 2]};
     for (int i = 0; i < 3; ++i)
       for (int j = 0; j < 3; ++j) A[3 * i + j] = m[i] * m[j] * uu[3 * i + j] + ((i == j) ? (1.0 - m[i]) : 0.0);
     spd_inverse<3>(A);
@@ -202,22 +204,23 @@ __global__ void __launch_bounds__(RED_THREADS)
 k_pcg_init(const double* __restrict__ b, const double* __restrict__ Ax, const double* __restrict__ dinv6,
            const double* __restrict__ dinv3, int64_t nn, int64_t nq2, double* __restrict__ r, double* __restrict__ z,
            double* __restrict__ p, double* __restrict__ part_rz, double* __restrict__ part_rr,
-           double* __restrict__ part_bb) {
+           double* __restrict__ part_bb, const double* __restrict__ own) {
   double rz = 0, rr = 0, bb = 0;
   for (int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; I < nq2; I += gridDim.x * (int64_t)blockDim.x) {
     int nd = I < nn ? 6 : 3;
+    const double ow = own ? own[I] : 1.0;
     double rl[6], zl[6];
     for (int i = 0; i < nd; ++i) {
       int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
       double bv = b[d];
       rl[i] = bv - Ax[d];
-      bb += bv * bv;
+      bb += ow * bv * bv;
     }
     precond_node(I, nn, nq2, dinv6, dinv3, rl, zl);
     for (int i = 0; i < nd; ++i) {
       int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
       r[d] = rl[i]; z[d] = zl[i]; p[d] = zl[i];
-      rz += rl[i] * zl[i]; rr += rl[i] * rl[i];
+      rz += ow * rl[i] * zl[i]; rr += ow * rl[i] * rl[i];
     }
   }
   block_sum3(rz, rr, bb);
@@ -226,17 +229,18 @@ k_pcg_init(const double* __restrict__ b, const double* __restrict__ Ax, const do
 
 // alpha = rz_old / pAp; x += alpha p; r -= alpha Ap; z = M^-1 r; partials of r.z and r.r
 __global__ void __launch_bounds__(RED_THREADS)
-k_pcg_update(const double* __restrict__ part_pAp, int n_pAp, const double* __restrict__ part_rz_old,
-             const double* __restrict__ p, const double* __restrict__ Ap, const double* __restrict__ dinv6,
+k_pcg_update(const double* __restrict__ part_pAp, int n_pAp, const double* __restrict__ part_rz_old, int n_rz_old,
+             const double* __restrict__ own, const double* __restrict__ p, const double* __restrict__ Ap, const double* __restrict__ dinv6,
              const double* __restrict__ dinv3, int64_t nn, int64_t nq2, double* __restrict__ x,
              double* __restrict__ r, double* __restrict__ z, double* __restrict__ part_rz_new,
              double* __restrict__ part_rr) {
   const double pAp = sum_partials(part_pAp, n_pAp);
-  const double rz_old = sum_partials(part_rz_old, RED_BLOCKS);
+  const double rz_old = sum_partials(part_rz_old, n_rz_old);
   const double alpha = (pAp != 0.0) ? rz_old / pAp : 0.0;
   double rz = 0, rr = 0, dummy = 0;
   for (int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; I < nq2; I += gridDim.x * (int64_t)blockDim.x) {
     int nd = I < nn ? 6 : 3;
+    const double ow = own ? own[I] : 1.0;
     double rl[6], zl[6];
     for (int i = 0; i < nd; ++i) {
       int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
@@ -247,7 +251,7 @@ k_pcg_update(const double* __restrict__ part_pAp, int n_pAp, const double* __res
     for (int i = 0; i < nd; ++i) {
       int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
       r[d] = rl[i]; z[d] = zl[i];
-      rz += rl[i] * zl[i]; rr += rl[i] * rl[i];
+      rz += ow * rl[i] * zl[i]; rr += ow * rl[i] * rl[i];
     }
   }
   block_sum3(rz, rr, dummy);
@@ -257,13 +261,13 @@ k_pcg_update(const double* __restrict__ part_pAp, int n_pAp, const double* __res
 // beta = rz_new / rz_old; p = z + beta p; CTA 0 publishes r.r
 __global__ void __launch_bounds__(RED_THREADS)
 k_pcg_dir(const double* __restrict__ part_rz_new, const double* __restrict__ part_rz_old,
-          const double* __restrict__ part_rr, const double* __restrict__ z, int64_t n, double* __restrict__ p,
-          double* __restrict__ rr_out) {
-  const double rzn = sum_partials(part_rz_new, RED_BLOCKS);
-  const double rzo = sum_partials(part_rz_old, RED_BLOCKS);
+          const double* __restrict__ part_rr, int n_part, const double* __restrict__ z, int64_t n,
+          double* __restrict__ p, double* __restrict__ rr_out) {
+  const double rzn = sum_partials(part_rz_new, n_part);
+  const double rzo = sum_partials(part_rz_old, n_part);
   const double beta = (rzo != 0.0) ? rzn / rzo : 0.0;
   if (blockIdx.x == 0) {
-    double rr = sum_partials(part_rr, RED_BLOCKS);
+    double rr = sum_partials(part_rr, n_part);
     if (threadIdx.x == 0) *rr_out = rr;
   }
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x)
@@ -276,6 +280,25 @@ k_dot(const double* __restrict__ a, const double* __restrict__ b, int64_t n, dou
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x) s += a[i] * b[i];
   block_sum3(s, u, v);
   if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+// owner-masked dot (multi-GPU): own is per block node
+__global__ void __launch_bounds__(RED_THREADS)
+k_dot_own(const double* __restrict__ a, const double* __restrict__ b, const double* __restrict__ own, int64_t nb,
+          double* __restrict__ part) {
+  double s = 0, u = 0, v = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nb; i += gridDim.x * (int64_t)blockDim.x)
+    s += own[i] * (a[3 * i] * b[3 * i] + a[3 * i + 1] * b[3 * i + 1] + a[3 * i + 2] * b[3 * i + 2]);
+  block_sum3(s, u, v);
+  if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+// CTA k reduces partial array k (up to 3 arrays) into out[k]
+__global__ void k_sum_partials3(const double* __restrict__ p0, const double* __restrict__ p1,
+                                const double* __restrict__ p2, int n, double* __restrict__ out) {
+  const double* part = blockIdx.x == 0 ? p0 : (blockIdx.x == 1 ? p1 : p2);
+  double v = sum_partials(part, n);
+  if (threadIdx.x == 0) out[blockIdx.x] = v;
 }
 
 __global__ void k_sum_partials(const double* __restrict__ part, int n, double* __restrict__ out) {
@@ -316,7 +339,7 @@ __global__ void k_copy(const double4* __restrict__ a, double4* __restrict__ b, i
 int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc) {
   if (!c->jac_valid) return femo_fail("Jacobian not assembled");
   k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, x, with_bc ? c->bcmask : nullptr, c->nb, y,
-                                                 nullptr);
+                                                 nullptr, nullptr);
   TRY(check_launch(c, "k_spmv"));
   c->launches += 1;
   return 0;
@@ -334,7 +357,7 @@ int penalty_apply(femo_ctx* c, const double* x, double* y, double sign) {
 int precond_setup(femo_ctx* c) {
   if (!c->jac_valid) return femo_fail("Jacobian not assembled");
   k_precond_setup<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(c->vals, c->diag_pos, c->ut_pos, c->tu_pos, c->bcmask,
-                                                                     c->nn, c->nq2, c->dinv6, c->dinv3);
+                                                                     c->own, c->nn, c->nq2, c->dinv6, c->dinv3);
   TRY(check_launch(c, "k_precond_setup"));
   c->launches += 1;
   c->prec_valid = true;
@@ -343,32 +366,52 @@ int precond_setup(femo_ctx* c) {
 
 int dev_dot(femo_ctx* c, const double* a, const double* b, int64_t n, double* out) {
   double* part = c->red + 6 * RED_BLOCKS;
-  k_dot<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(a, b, n, part);
+  const bool dist = c->world > 1 && c->own && n == c->ndof;     // state-sized vectors: owner-masked, summed over ranks
+  if (dist) k_dot_own<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(a, b, c->own, c->nb, part);
+  else k_dot<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(a, b, n, part);
   k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(part, RED_BLOCKS, c->scal + 8);
   TRY(check_launch(c, "k_dot"));
   c->launches += 2;
+  if (dist) TRY(dist_allreduce_sum(c, c->scal + 8, 1));
   CUDA_TRY(cudaMemcpyAsync(out, c->scal + 8, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   return 0;
 }
 
 // red layout: [0]=pAp partials (SPMV_BLOCKS) | [1],[2] = rz ping-pong | [3] = rr | [4] = bb | [5] spare | [6] dot
+// scal layout: [0]=bb [1]=rr (host reads) [2]=pAp | [10..11],[12..13] = (rz, rr) ping-pong pairs (multi-GPU)
+//
+// Multi-GPU (world > 1): ghost entries of the operand are refreshed before every SpMV (halo exchange),
+// the dot-product partials are owner-masked, reduced to scalars on the device and summed over ranks with one
+// ncclAllReduce per reduction point (pAp; (rz, rr)); the consumer kernels then read the scalar (n = 1).
 int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, int* iters, double* relres,
               bool fixed_iters) {
   if (!c->jac_valid) return femo_fail("pcg: Jacobian not assembled");
   if (!c->prec_valid) TRY(precond_setup(c));
+  const bool dist = c->world > 1;
+  if (dist && !c->nccl_comm) return femo_fail("pcg: multi-GPU context without communicator (femo_dist_init)");
   double* P_pAp = c->red;
   double* P_rz[2] = {c->red + 1 * SPMV_BLOCKS, c->red + 2 * SPMV_BLOCKS};
   double* P_rr = c->red + 3 * SPMV_BLOCKS;
   double* P_bb = c->red + 4 * SPMV_BLOCKS;
+  double* S_pair[2] = {c->scal + 10, c->scal + 12};
   const int64_t n = c->ndof;
   cudaEventRecord(c->ev0, c->stream);
   // r0 = b - A x0
-  k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, x, c->bcmask, c->nb, c->Ap, nullptr);
+  if (dist) TRY(halo_exchange(c, x));
+  k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, x, c->bcmask, c->nb, c->Ap, nullptr, nullptr);
   k_pcg_init<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(b, c->Ap, c->dinv6, c->dinv3, c->nn, c->nq2, c->r, c->z, c->p,
-                                                        P_rz[0], P_rr, P_bb);
-  k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_bb, RED_BLOCKS, c->scal + 0);
-  k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_rr, RED_BLOCKS, c->scal + 1);
+                                                        P_rz[0], P_rr, P_bb, c->own);
+  if (dist) {
+    // scal[0..2] <- (bb, rr, rz) summed over ranks; pair[0] = (rz, rr)
+    k_sum_partials3<<<3, RED_THREADS, 0, c->stream>>>(P_bb, P_rr, P_rz[0], RED_BLOCKS, c->scal + 0);
+    TRY(dist_allreduce_sum(c, c->scal + 0, 3));
+    CUDA_TRY(cudaMemcpyAsync(S_pair[0], c->scal + 2, sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(S_pair[0] + 1, c->scal + 1, sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  } else {
+    k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_bb, RED_BLOCKS, c->scal + 0);
+    k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_rr, RED_BLOCKS, c->scal + 1);
+  }
   TRY(check_launch(c, "pcg init"));
   c->launches += 4;
   double hs[2];
@@ -391,10 +434,24 @@ int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, 
     int nloop = std::min(check_every, max_it - it);
     for (int k = 0; k < nloop; ++k, ++it) {
       int cur = it & 1, nxt = cur ^ 1;
-      k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->p, c->bcmask, c->nb, c->Ap, P_pAp);
-      k_pcg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_pAp, SPMV_BLOCKS, P_rz[cur], c->p, c->Ap, c->dinv6,
-                                                              c->dinv3, c->nn, c->nq2, x, c->r, c->z, P_rz[nxt], P_rr);
-      k_pcg_dir<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_rz[nxt], P_rz[cur], P_rr, c->z, n, c->p, c->scal + 1);
+      if (dist) {
+        TRY(halo_exchange(c, c->p));
+        k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->p, c->bcmask, c->nb, c->Ap, P_pAp, c->own);
+        k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_pAp, SPMV_BLOCKS, c->scal + 2);
+        TRY(dist_allreduce_sum(c, c->scal + 2, 1));
+        k_pcg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(c->scal + 2, 1, S_pair[cur], 1, c->own, c->p, c->Ap, c->dinv6,
+                                                                c->dinv3, c->nn, c->nq2, x, c->r, c->z, P_rz[nxt], P_rr);
+        k_sum_partials3<<<2, RED_THREADS, 0, c->stream>>>(P_rz[nxt], P_rr, P_rr, RED_BLOCKS, S_pair[nxt]);
+        TRY(dist_allreduce_sum(c, S_pair[nxt], 2));
+        k_pcg_dir<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(S_pair[nxt], S_pair[cur], S_pair[nxt] + 1, 1, c->z, n, c->p,
+                                                             c->scal + 1);
+        c->launches += 2;
+      } else {
+        k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->p, c->bcmask, c->nb, c->Ap, P_pAp, nullptr);
+        k_pcg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_pAp, SPMV_BLOCKS, P_rz[cur], RED_BLOCKS, nullptr, c->p, c->Ap,
+                                                                c->dinv6, c->dinv3, c->nn, c->nq2, x, c->r, c->z, P_rz[nxt], P_rr);
+        k_pcg_dir<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_rz[nxt], P_rz[cur], P_rr, RED_BLOCKS, c->z, n, c->p, c->scal + 1);
+      }
     }
     c->launches += 3 * (int64_t)nloop;
     TRY(check_launch(c, "pcg iteration"));
@@ -404,6 +461,7 @@ int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, 
     if (!(rel == rel)) return femo_fail("pcg: NaN residual (matrix not SPD?)");
     if (!fixed_iters && rel <= rtol) done = true;
   }
+  if (dist) TRY(halo_exchange(c, x));      // ghost entries of the solution follow their owners
   cudaEventRecord(c->ev1, c->stream);
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   float ms = 0;

@@ -151,6 +151,25 @@ int femo_pnorm_stress_grad(femo_ctx* ctx, int tag, int arg, double* g, int on_de
  * cell-wise L2 projection, out (n_cells,4) in tensor vertex order; surface 0 Top, 1 Mid, 2 Bot */
 int femo_stress_field(femo_ctx* ctx, int surface, double* out, int on_device);
 
+/* ---- multi-GPU: one process per GPU (the reference is serial) ------------------- */
+/* rank 0 creates the NCCL id (128 bytes); the host broadcasts it (torch.distributed / MPI) */
+int femo_nccl_unique_id(void* id128);
+/* partition of this rank (femo_alpha_b200/partition.py): neighbour ranks, per-neighbour offsets (n_nbr+1,
+ * in block nodes) into the key-ordered send / receive block lists, owner flag per local block node, and the
+ * number of owned cells (owned cells come first in the local cell order; the rest is the ghost layer).
+ * After this call dot products are owner-masked, scalar outputs are summed over owned cells and over ranks,
+ * and every operator application is preceded by a halo exchange. */
+int femo_dist_setup(femo_ctx* ctx, int rank, int world, int n_nbr, const int32_t* nbr_ranks,
+                    const int32_t* send_off, const int32_t* send_blocks, const int32_t* recv_off,
+                    const int32_t* recv_blocks, const uint8_t* own_block, int64_t n_owned_cells);
+/* collective: ncclCommInitRank with the broadcast id */
+int femo_dist_init(femo_ctx* ctx, const void* id128);
+/* ghost entries of x (n_dof) <- owners' values; collective */
+int femo_halo_exchange(femo_ctx* ctx, double* x, int on_device);
+/* sum n <= 8 host scalars over ranks; collective */
+int femo_dist_allreduce(femo_ctx* ctx, double* vals, int n);
+int femo_dist_counts(femo_ctx* ctx, int64_t* halo_exchanges, int64_t* allreduces);
+
 /* ---- instrumentation ---------------------------------------------------------------- */
 /* number of kernels this context has launched so far */
 int femo_launch_count(femo_ctx* ctx, int64_t* n);
