@@ -9,9 +9,9 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfemo_b200.so")
-SOURCES = ["api.cu", "topology.cu", "assemble.cu", "solver.cu", "outputs.cu", "dist.cu"]
+SOURCES = ["api.cu", "topology.cu", "assemble.cu", "assemble_tiles.cu", "solver.cu", "outputs.cu", "dist.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC", "--use_fast_math=false"]
+              "-Xcompiler", "-fPIC", "-Xcompiler", "-fopenmp", "--use_fast_math=false"]
 
 
 def _nvcc():
@@ -29,7 +29,7 @@ def _stale(target, deps):
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    headers = [os.path.join(CSRC, "femo_internal.cuh"), os.path.join(HERE, "..", "include", "femo_b200.h")]
+    headers = [os.path.join(CSRC, "femo_internal.cuh"), os.path.join(CSRC, "tile_plan.hpp"), os.path.join(HERE, "..", "include", "femo_b200.h")]
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     nvcc = _nvcc()
@@ -50,7 +50,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
     if force or _stale(LIB, objs):
-        cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-lcudart", "-ldl"]
+        cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-lcudart", "-ldl", "-lgomp"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))

@@ -180,6 +180,7 @@ int femo_ctx_destroy(femo_ctx* c) {
   DevGuard g(c->device);
   cudaStreamSynchronize(c->stream);
   dist_free(c);
+  tile_plan_free(c);
   void* ptrs[] = {c->xyz, c->cv, c->ce, c->edges, c->cell_blocks, c->hE, c->tab, c->h, c->E, c->nu, c->rho, c->f, c->uhat,
                   c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
                   c->nc_adj, c->rec, c->bcmask, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
@@ -232,7 +233,8 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   c->nq4 = 9;
   c->area_cache.clear();
   TRY(pattern_build(c));
-  if (c->all_planar) TRY(asm_plan_build(c));
+  if (c->all_planar) TRY(tile_plan_setup(c));
+  if (c->all_planar && !c->tile_ok) TRY(asm_plan_build(c));
   c->n_mat = c->ewm ? c->nc : c->nn;
   c->n_f = 3 * (c->ewp ? c->nc : c->nn);
   TRY(dev_alloc(&c->h, c->n_mat)); TRY(dev_alloc(&c->E, c->n_mat)); TRY(dev_alloc(&c->nu, c->n_mat));
@@ -243,7 +245,7 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   c->uhat_zero = 1;
   c->rec_nqf = c->all_planar ? REC_NQF_PLANAR : REC_NQF_WARPED;
   c->rec_stride = REC_HEADER + c->nq * c->rec_nqf;
-  TRY(dev_alloc(&c->rec, (size_t)c->nc * c->rec_stride));
+  if (!c->tile_ok) TRY(dev_alloc(&c->rec, (size_t)c->nc * c->rec_stride));
   const int64_t n = c->ndof;
   TRY(dev_alloc(&c->bcmask, n)); TRY(fill(c, c->bcmask, n, 1.0));
   c->n_bc = 0;

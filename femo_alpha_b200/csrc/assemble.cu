@@ -586,10 +586,8 @@ __global__ void k_load(const double* __restrict__ xyz, const int32_t* __restrict
 
 }  // namespace
 
-int assemble_jacobian(femo_ctx* c) {
-  if (!c->setup_done) return femo_fail("femo_assemble_jacobian: call femo_shell_setup first");
-  const double* uh = c->uhat_zero ? nullptr : c->uhat;
-  cudaEventRecord(c->ev0, c->stream);
+// older kernels: warped (non-planar) meshes, FEMO_TILE=0, or a tile plan that does not fit shared memory
+static int assemble_jacobian_legacy(femo_ctx* c, const double* uh) {
   k_cell_records<<<(unsigned)cdiv(c->nc * c->nq, 128), 128, 0, c->stream>>>(
       c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->nc, c->nq, c->ewm, c->rec_nqf, c->rec_stride, c->rec);
   TRY(check_launch(c, "k_cell_records"));
@@ -610,6 +608,18 @@ int assemble_jacobian(femo_ctx* c) {
     k_gather<false><<<grid, GATHER_THREADS, 0, c->stream>>>(c->centry, c->cdest, c->cptr, c->rec, c->rec_stride, c->tab,
                                                             c->nq, c->ncontrib, c->vals);
   TRY(check_launch(c, "k_gather"));
+  return 0;
+}
+
+int assemble_jacobian(femo_ctx* c) {
+  if (!c->setup_done) return femo_fail("femo_assemble_jacobian: call femo_shell_setup first");
+  const double* uh = c->uhat_zero ? nullptr : c->uhat;
+  cudaEventRecord(c->ev0, c->stream);
+  if (c->tile_ok) {
+    TRY(assemble_jacobian_tiles(c, uh));
+  } else {
+    TRY(assemble_jacobian_legacy(c, uh));
+  }
   cudaEvent_t ev2; cudaEventCreate(&ev2);
   cudaEventRecord(ev2, c->stream);
   c->launches += 2;

@@ -107,6 +107,15 @@ struct femo_ctx {
   int32_t *halo_cells = nullptr;
   int32_t *tpos = nullptr;      // nnzb: position of the transposed block, -1 on the diagonal
   int32_t *ut_pos = nullptr, *tu_pos = nullptr;   // nn: positions of (v, nq2+v) and (nq2+v, v)
+  // tiled planar assembly (assemble_tiles.cu, tile_plan.hpp): chunks of 32 cells in processing order
+  bool tile_ok = false;
+  int64_t tl_nchunks = 0, tl_ndest = 0, tl_nref = 0, tl_nhitem = 0;
+  int tl_hitem_cap = 0, tl_hcell_cap = 0, tl_dest_cap = 0, tl_ref_cap = 0;
+  size_t tl_smem = 0;
+  int32_t *tl_cell_order = nullptr, *tl_dest_ptr = nullptr, *tl_dest_pos = nullptr, *tl_dest_tpos = nullptr;
+  uint32_t *tl_dest_info = nullptr, *tl_refs = nullptr, *tl_hitems = nullptr;
+  int32_t *tl_ref_ptr = nullptr, *tl_hitem_ptr = nullptr, *tl_hcell_ptr = nullptr, *tl_hcells = nullptr;
+  double *tl_rec = nullptr, *tl_frame = nullptr;  // [chunk][q][12 fields][32 lanes], [slot][9]
   // block node -> (cell, local index) adjacency, cell-ascending
   int32_t *nc_ptr = nullptr;    // nb+1
   int32_t *nc_adj = nullptr;    // nc*13 entries = cell*13 + a
@@ -176,6 +185,9 @@ int topo_build(femo_ctx* c, const int32_t* conn_vtk_host);                // top
 int pattern_build(femo_ctx* c);                                           // topology.cu
 int penalty_build(femo_ctx* c, const uint8_t* vertex_on_host);            // topology.cu
 int asm_plan_build(femo_ctx* c);                                          // topology.cu
+int tile_plan_setup(femo_ctx* c);                                         // assemble_tiles.cu
+void tile_plan_free(femo_ctx* c);                                         // assemble_tiles.cu
+int assemble_jacobian_tiles(femo_ctx* c, const double* uhat);             // assemble_tiles.cu (records + assembly)
 int assemble_jacobian(femo_ctx* c);                                       // assemble.cu
 int assemble_load(femo_ctx* c, double* F_dev);                            // assemble.cu
 int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc);       // solver.cu

@@ -160,22 +160,66 @@ def test_stress_functionals(name, built_lib):
     assert np.isfinite(d.pnorm_stress())
 
 
+def _sym_check(Kd):
+    A = Kd.toarray()
+    D = A - A.T
+    blk = np.arange(A.shape[0]) // 3
+    off = blk[:, None] != blk[None, :]
+    assert not D[off].any()                     # block and transposed block are written from one value
+    assert np.abs(D).max() <= 1e-14 * np.abs(A).max()   # 3x3 diagonal blocks: symmetric to round-off
+
+
 @pytest.mark.parametrize("chunk", ["0", "1", "3", "5", "64"])
 @pytest.mark.parametrize("name", ["plate_varh", "skew_planar", "plate_dg0"])
 def test_chunked_symmetric_assembly_any_chunk_size(built_lib, monkeypatch, name, chunk):
-    """The planar assembly kernel owns destinations per chunk of cells and pulls halo cells; every chunk
-    size (0 = plan disabled, contribution-gather kernel) must give the oracle's matrix, symmetric to the bit."""
+    """Second-generation planar kernel (FEMO_TILE=0): destinations owned per chunk of cells, halo cells pulled;
+    every chunk size (0 = plan disabled, contribution-gather kernel) must give the oracle's matrix."""
+    monkeypatch.setenv("FEMO_TILE", "0")
     monkeypatch.setenv("FEMO_ASM_CHUNK", chunk)
     p = make_problem(name)
     o, d = oracle_for(p), device_for(p)
     K = o.assemble_dRdu().tocsr()
     Kd = d.get_csr()
     assert rel(Kd.toarray(), K.toarray()) <= 1e-12
-    if chunk != "0":
-        A = Kd.toarray()
-        D = A - A.T
-        blk = np.arange(A.shape[0]) // 3
-        off = blk[:, None] != blk[None, :]
-        assert not D[off].any()                     # block and transposed block are written from one value
-        assert np.abs(D).max() <= 1e-14 * np.abs(A).max()   # 3x3 diagonal blocks: symmetric to round-off
+    if chunk not in ("0", "64"):                # 64: the plan needs more shared memory than a CTA has -> gather kernel
+        _sym_check(Kd)
     d.close()
+
+
+@pytest.mark.parametrize("order", ["morton", "identity"])
+@pytest.mark.parametrize("name", ["plate_4x20", "plate_varh", "skew_planar", "plate_dg0"])
+def test_tiled_assembly(built_lib, monkeypatch, name, order):
+    """Default planar kernel (assemble_tiles.cu): register-tiled moments per chunk of 32 cells in Morton (or the
+    caller's) order; the matrix is the oracle's, symmetric to the bit, and identical from run to run."""
+    monkeypatch.setenv("FEMO_TILE_ORDER", order)
+    p = make_problem(name)
+    o, d = oracle_for(p), device_for(p)
+    K = o.assemble_dRdu().tocsr()
+    Kd = d.get_csr()
+    assert rel(Kd.toarray(), K.toarray()) <= 1e-12
+    _sym_check(Kd)
+    d.assemble_jacobian()
+    assert np.array_equal(d.get_csr().data, Kd.data)
+    d.close()
+
+
+def test_tiled_assembly_many_chunks(built_lib):
+    """A 23 x 17 plate spans 13 chunks with halo contributions across chunk borders (quadrature degree 2, 4, 6)."""
+    from oracle.rm_shell_ref import plate_mesh, RMShellOracle
+    from femo_alpha_b200.shell_device import ShellDevice
+    rng = np.random.default_rng(7)
+    nodes, quads = plate_mesh(23, 17, 4.0, 3.0)
+    nn = nodes.shape[0]
+    nodes[:, :2] += 0.02 * rng.standard_normal((nn, 2))
+    inp = dict(thickness=0.05 * (1 + 0.5 * rng.random(nn)), E=1e6 * (1 + 0.2 * rng.random(nn)),
+               nu=0.25 + 0.1 * rng.random(nn))
+    for deg in (2, 4, 6):
+        o = RMShellOracle(nodes, quads, False, False, deg)
+        o.set_inputs(**inp)
+        d = ShellDevice(nodes, quads, False, False, deg)
+        for k, v in inp.items():
+            d.set_input(k, v)
+        Kd = d.get_csr()
+        assert rel(Kd.toarray(), o.assemble_dRdu(with_penalty=False).toarray()) <= 1e-12
+        _sym_check(Kd)
+        d.close()
