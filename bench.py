@@ -6,7 +6,7 @@ Workload (BASELINE.json configs[2], SURVEY 8d cfg 3): synthetic refined RM-shell
 h(x,y) = 0.1 (1 + 0.5 sin(2 pi x/10) cos(2 pi y/10)), E = 1e8, nu = 0.3, f = (0,0,5), clamp x = 0.
 
 A "step" = one pass of the assembly hot path: recompute the BSR(3x3) values of dR/du from the
-inputs resident in HBM (quadrature records + deterministic gather).  `value` = n_dof / step time.
+inputs resident in HBM (quadrature records + tiled deterministic assembly kernel).  `value` = n_dof / step time.
 `e2e` = the same through the plugin API with HOST buffers (H2D of thickness, F_solid, E, nu, uhat;
 assemble; D2H of the residual vector).  `solve` = PCG (block-Jacobi) iteration time on A = dR/du.
 
@@ -279,7 +279,14 @@ def run_ours(args, rank, world, local_rank):
     g_ms = float(np.mean(gather_ms)); r_ms = float(np.mean(rec_ms))
     achieved = CELL_BYTES * d.nc / (g_ms * 1e-3) / 1e9
     pcg_bytes = 12.0 * d.nnzb * 9 + 188.0 * d.ndof
-    cpu, _, _ = cpu_baseline(n)
+    cpu, _, _ = cpu_baseline(n) if world == 1 else (None, None, None)
+    traffic = None
+    try:                                            # DRAM bytes of one launch from the committed ncu --set full capture
+        tj = json.load(open(os.path.join(ROOT, "profiles", "asm_traffic.json")))
+        if tj.get("workload") == "rm_shell_plate_%dx%d_q2q1_cfg3" % (n, n) and world == 1:
+            traffic = float(tj["dram_bytes_per_launch"])
+    except Exception:
+        pass
     out = {
         "metric": "rm_shell_jacobian_assembly_throughput", "value": ndof_total / (ms * 1e-3) / 1e9, "unit": "GDOF/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
@@ -293,8 +300,8 @@ def run_ours(args, rank, world, local_rank):
                 "api": "ShellDevice.set_input x5 (host) + assemble_residual(host out)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"kernel": "k_asm_planar (chunked symmetric assembly)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "roofline": {"kernel": "k_asm_tiles_ws (register-tiled moments, warp-specialised compute/writer roles, deterministic)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": CELL_BYTES * d.nc, "avg_launch_ms": g_ms,
                      "records_kernel_ms": r_ms},
         "solve": {"krylov": "PCG + block-Jacobi (6x6 vertex / 3x3 edge, centre)", "iters_timed": kiters,

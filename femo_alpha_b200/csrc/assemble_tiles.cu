@@ -50,63 +50,67 @@ struct TileTab {                       // reference tables staged once per CTA (
   double n1[FEMO_MAX_NQ][4];
 };
 
-// one thread per (processing slot, quadrature point); consecutive lanes = consecutive slots -> coalesced records
+// one thread per processing slot (cell): vertex data and the cell frame are set up once, then the quadrature loop
+// writes the [chunk][q][field][lane] records (16 consecutive lanes = 128 contiguous bytes per field)
 __global__ void k_cell_records_tiles(const double* __restrict__ xyz, const int32_t* __restrict__ cv,
                                      const double* __restrict__ uhat, const double* __restrict__ h,
                                      const double* __restrict__ E, const double* __restrict__ nu,
                                      const double* __restrict__ hE, const Tables* __restrict__ tab,
                                      const int32_t* __restrict__ cell_order, int64_t nchunks, int nq, int ewm,
                                      double* __restrict__ rec, double* __restrict__ frame) {
-  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (i >= nchunks * nq * C) return;
-  const int lane = (int)(i % C);
-  const int q = (int)((i / C) % nq);
-  const int64_t chunk = i / ((int64_t)C * nq);
-  const int64_t p = chunk * C + lane;
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= nchunks * C) return;
+  const int lane = (int)(p % C);
+  const int64_t chunk = p / C;
   const int32_t cell = cell_order[p];
-  double* r = rec + ((chunk * nq + q) * TL_NF) * C + lane;
+  double* r0 = rec + chunk * ((int64_t)nq * TL_NF * C) + lane;
+  double* fr = frame + p * 9;
   if (cell < 0) {                                       // padding slot of the last chunk
+    for (int q = 0; q < nq; ++q)
 #pragma unroll
-    for (int f = 0; f < TL_NF; ++f) r[f * C] = 0.0;
-    if (q == 0)
-      for (int k = 0; k < 9; ++k) frame[p * 9 + k] = 0.0;
+      for (int f = 0; f < TL_NF; ++f) r0[(q * TL_NF + f) * C] = 0.0;
+    for (int k = 0; k < 9; ++k) fr[k] = 0.0;
     return;
   }
   V3 xv[4], uh[4];
   int32_t vid[4];
+  double hv[4], Ev[4], nv[4];
 #pragma unroll
   for (int v = 0; v < 4; ++v) {
     vid[v] = cv[(int64_t)cell * 4 + v];
     xv[v] = ldv3(xyz + 3 * (int64_t)vid[v]);
     if (uhat) uh[v] = ldv3(uhat + 3 * (int64_t)vid[v]);
+    const int64_t mi = ewm ? (int64_t)cell : (int64_t)vid[v];
+    hv[v] = h[mi]; Ev[v] = E[mi]; nv[v] = nu[mi];
   }
-  QpGeom g;
-  qp_geometry(xv, uhat ? uh : nullptr, tab->X0[q], tab->X1[q], g);
-  double hq, Eq, nuq;
-  if (ewm) { hq = h[cell]; Eq = E[cell]; nuq = nu[cell]; }
-  else {
-    hq = Eq = nuq = 0;
-#pragma unroll
-    for (int v = 0; v < 4; ++v) { double N = tab->n1[q][v]; hq += N * h[vid[v]]; Eq += N * E[vid[v]]; nuq += N * nu[vid[v]]; }
-  }
-  const Coefs cf = clt_coefs(hq, Eq, nuq, hE[cell], g.Ju, 0);
-  const double wd = tab->W[q] * g.detJ;
   // planar cell: one constant in-plane frame per cell, taken at the cell centre (isotropic CLT)
   QpGeom gc;
   qp_geometry(xv, nullptr, 0.5, 0.5, gc);
-  if (q == 0) {
-    double* fr = frame + p * 9;
-    fr[0] = gc.E0.x; fr[1] = gc.E0.y; fr[2] = gc.E0.z;
-    fr[3] = gc.E1.x; fr[4] = gc.E1.y; fr[5] = gc.E1.z;
-    fr[6] = gc.E2.x; fr[7] = gc.E2.y; fr[8] = gc.E2.z;
+  fr[0] = gc.E0.x; fr[1] = gc.E0.y; fr[2] = gc.E0.z;
+  fr[3] = gc.E1.x; fr[4] = gc.E1.y; fr[5] = gc.E1.z;
+  fr[6] = gc.E2.x; fr[7] = gc.E2.y; fr[8] = gc.E2.z;
+  const double hEc = hE[cell];
+  for (int q = 0; q < nq; ++q) {
+    QpGeom g;
+    qp_geometry(xv, uhat ? uh : nullptr, tab->X0[q], tab->X1[q], g);
+    double hq, Eq, nuq;
+    if (ewm) { hq = hv[0]; Eq = Ev[0]; nuq = nv[0]; }
+    else {
+      hq = Eq = nuq = 0;
+#pragma unroll
+      for (int v = 0; v < 4; ++v) { const double N = tab->n1[q][v]; hq += N * hv[v]; Eq += N * Ev[v]; nuq += N * nv[v]; }
+    }
+    const Coefs cf = clt_coefs(hq, Eq, nuq, hEc, g.Ju, 0);
+    const double wd = tab->W[q] * g.detJ;
+    const double cm33 = wd * cf.cm33, cd = wd * cf.cd;
+    double* r = r0 + q * (TL_NF * C);
+    r[TF_K00 * C] = dot(g.Kx0, gc.E0); r[TF_K01 * C] = dot(g.Kx0, gc.E1);
+    r[TF_K10 * C] = dot(g.Kx1, gc.E0); r[TF_K11 * C] = dot(g.Kx1, gc.E1);
+    r[TF_CM11 * C] = wd * cf.cm11; r[TF_CM12 * C] = wd * cf.cm12;
+    r[TF_C3P * C] = cm33 + 0.25 * cd; r[TF_C3M * C] = cm33 - 0.25 * cd;
+    r[TF_CS * C] = wd * cf.cs; r[TF_CD * C] = cd;
+    r[TF_CM33 * C] = cm33; r[TF_HB * C] = hq * hq / 12.0;
   }
-  const double cm33 = wd * cf.cm33, cd = wd * cf.cd;
-  r[TF_K00 * C] = dot(g.Kx0, gc.E0); r[TF_K01 * C] = dot(g.Kx0, gc.E1);
-  r[TF_K10 * C] = dot(g.Kx1, gc.E0); r[TF_K11 * C] = dot(g.Kx1, gc.E1);
-  r[TF_CM11 * C] = wd * cf.cm11; r[TF_CM12 * C] = wd * cf.cm12;
-  r[TF_C3P * C] = cm33 + 0.25 * cd; r[TF_C3M * C] = cm33 - 0.25 * cd;
-  r[TF_CS * C] = wd * cf.cs; r[TF_CD * C] = cd;
-  r[TF_CM33 * C] = cm33; r[TF_HB * C] = hq * hq / 12.0;
 }
 
 // ---- phase 1: register-tiled local-frame moments -------------------------------------------------------------
@@ -166,15 +170,17 @@ __device__ __forceinline__ void tile_uu(const double* __restrict__ rc, const Til
 }
 
 // Q1-Q1 tile: 10 symmetric pairs, moments (t00, t01, t10, t11, t22)
+// qb, qs: this thread visits quadrature points qb, qb+qs, ...; part: 0 = store the result, 1 = store a partial sum
+// (odd points of a q-split half-warp pair), 2 = add the partner's partial sum, then store
 __device__ __forceinline__ void tile_tt(const double* __restrict__ rc, const TileTab& R, int nq,
-                                        double* __restrict__ mom) {
+                                        double* __restrict__ mom, int qb = 0, int qs = 1, int part = 0) {
   double acc[10][5];
 #pragma unroll
   for (int i = 0; i < 10; ++i)
 #pragma unroll
     for (int m = 0; m < 5; ++m) acc[i][m] = 0.0;
 #pragma unroll 1
-  for (int q = 0; q < nq; ++q) {
+  for (int q = qb; q < nq; q += qs) {
     const double* r = rc + q * (TL_NF * C);
     const double k00 = r[TF_K00 * C], k01 = r[TF_K01 * C], k10 = r[TF_K10 * C], k11 = r[TF_K11 * C];
     const double hb = r[TF_HB * C], cs = r[TF_CS * C], cd = r[TF_CD * C];
@@ -201,15 +207,24 @@ __device__ __forceinline__ void tile_tt(const double* __restrict__ rc, const Til
       }
     }
   }
+  if (part == 1) {
 #pragma unroll
-  for (int i = 0; i < 10; ++i)
+    for (int i = 0; i < 10; ++i)
 #pragma unroll
-    for (int m = 0; m < 5; ++m) mom[MOM_TT + 5 * i + m] = acc[i][m];
+      for (int m = 0; m < 5; ++m) mom[MOM_TT + 5 * i + m] = acc[i][m];
+  }
+  if (part != 0) __syncwarp();
+  if (part != 1) {
+#pragma unroll
+    for (int i = 0; i < 10; ++i)
+#pragma unroll
+      for (int m = 0; m < 5; ++m) mom[MOM_TT + 5 * i + m] = part == 2 ? acc[i][m] + mom[MOM_TT + 5 * i + m] : acc[i][m];
+  }
 }
 
 // Q2-Q1 tile I: displacement nodes 3I..3I+2 x rotation nodes 0..3, moments (A0, A1, D0, D1)
 __device__ __forceinline__ void tile_ut(const double* __restrict__ rc, const TileTab& R, int nq, int I,
-                                        double* __restrict__ mom) {
+                                        double* __restrict__ mom, int qb = 0, int qs = 1, int part = 0) {
   double acc[3][4][4];
 #pragma unroll
   for (int i = 0; i < 3; ++i)
@@ -218,7 +233,7 @@ __device__ __forceinline__ void tile_ut(const double* __restrict__ rc, const Til
 #pragma unroll
       for (int m = 0; m < 4; ++m) acc[i][j][m] = 0.0;
 #pragma unroll 1
-  for (int q = 0; q < nq; ++q) {
+  for (int q = qb; q < nq; q += qs) {
     const double* r = rc + q * (TL_NF * C);
     const double k00 = r[TF_K00 * C], k01 = r[TF_K01 * C], k10 = r[TF_K10 * C], k11 = r[TF_K11 * C];
     const double cs = r[TF_CS * C], cd = r[TF_CD * C];
@@ -239,13 +254,28 @@ __device__ __forceinline__ void tile_ut(const double* __restrict__ rc, const Til
       }
     }
   }
+  if (part == 1) {
 #pragma unroll
-  for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 3; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+      for (int j = 0; j < 4; ++j)
 #pragma unroll
-      for (int m = 0; m < 4; ++m) mom[MOM_UT + 4 * ((3 * I + i) * 4 + j) + m] = acc[i][j][m];
+        for (int m = 0; m < 4; ++m) mom[MOM_UT + 4 * ((3 * I + i) * 4 + j) + m] = acc[i][j][m];
+  }
+  if (part != 0) __syncwarp();
+  if (part != 1) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          double* o = mom + MOM_UT + 4 * ((3 * I + i) * 4 + j) + m;
+          *o = part == 2 ? acc[i][j][m] + *o : acc[i][j][m];
+        }
+  }
 }
+
 
 // one halo contribution (cell of another chunk, local pair lo <= hi): same moments, one pair per thread
 __device__ __forceinline__ void halo_item(const double* __restrict__ rc, const TileTab& R, int nq, int a, int b,
@@ -469,6 +499,264 @@ k_asm_tiles(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__ de
   }
 }
 
+// ---- warp-specialised persistent variant ------------------------------------------------------------------------
+// One CTA per SM, 12 warps.  Six COMPUTE warps run phase 1 of chunk k+1 while six WRITER warps run the halo items,
+// phase 2 and the stores of chunk k: the fp64 pipe no longer idles during the memory phases.  The tile moments are
+// double-buffered in shared memory and handed over with named barriers (producer: bar.arrive full / bar.sync empty;
+// consumer: bar.sync full / bar.arrive empty).  Warp roles are laid out so that every SM sub-partition (warp id mod 4)
+// carries one Q2-Q2 warp or the Q1-Q1 / Q2-Q1 warps, plus writers:
+//   compute: w0 w1 w2 = Q2-Q2 tile pairs; w3 = Q1-Q1 tile, quadrature points split over the two half-warps;
+//            w7 = Q2-Q1 tiles 0 | 1; w11 = Q2-Q1 tile 2, quadrature points split
+//   writers: w4 w5 w6 w8 w9 w10
+#define WS_THREADS 384
+#define WS_ROLE 192
+#define WS_DPT 2        /* destinations per writer thread and round */
+#define BAR_FULL 1      /* +buf */
+#define BAR_EMPTY 3     /* +buf */
+#define BAR_COMPUTE 5
+#define BAR_WRITER 6
+
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+struct WsSmem { int mom0, mom_stride, hmom0, hmom_stride, frame, rec0, rec_stride, sk, plan, flags, total; };   // offsets in doubles
+
+__host__ __device__ inline WsSmem ws_smem_layout(int nq, int hitem_cap, int hcell_cap, int dest_cap, int ref_cap) {
+  WsSmem L;
+  int o = (int)(sizeof(TileTab) / sizeof(double));
+  L.mom0 = o; L.mom_stride = MOM_HALO_BASE + 1; o += 2 * L.mom_stride;
+  L.hmom0 = o; L.hmom_stride = MOM_HALO * hitem_cap; o += 2 * L.hmom_stride;
+  L.frame = o; o += (C + hcell_cap) * 9;
+  o = (o + 1) & ~1;
+  L.rec0 = o; L.rec_stride = nq * TL_NF * C; o += 2 * L.rec_stride;
+  L.sk = o; o += WS_DPT * WS_ROLE * 9;
+  L.plan = o; o += (3 * dest_cap + ref_cap + 1) / 2 + 1;
+  L.flags = o; o += 4;
+  L.total = o;
+  return L;
+}
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+__global__ void __launch_bounds__(WS_THREADS, 1)
+k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__ dest_pos,
+               const int32_t* __restrict__ dest_tpos, const uint32_t* __restrict__ dest_info,
+               const int32_t* __restrict__ ref_ptr, const uint32_t* __restrict__ refs,
+               const int32_t* __restrict__ hitem_ptr, const uint32_t* __restrict__ hitems,
+               const int32_t* __restrict__ hcell_ptr, const int32_t* __restrict__ hcells,
+               const double* __restrict__ rec, const double* __restrict__ frame, const Tables* __restrict__ tab, int nq,
+               int hitem_cap, int hcell_cap, int dest_cap, int ref_cap, int64_t nchunks, double* __restrict__ vals) {
+  extern __shared__ __align__(16) double smem[];
+  const WsSmem L = ws_smem_layout(nq, hitem_cap, hcell_cap, dest_cap, ref_cap);
+  TileTab& R = *reinterpret_cast<TileTab*>(smem);
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int slot = lane & (C - 1), half = lane >> 4;
+  {
+    double* d = &R.dphi2[0][0][0]; const double* s0 = &tab->dphi2[0][0][0];
+    for (int i = tid; i < nq * 18; i += WS_THREADS) d[i] = s0[i];
+    double* d1 = &R.dn1[0][0][0]; const double* s1 = &tab->dn1[0][0][0];
+    for (int i = tid; i < nq * 8; i += WS_THREADS) d1[i] = s1[i];
+    double* d2 = &R.n1[0][0]; const double* s2 = &tab->n1[0][0];
+    for (int i = tid; i < nq * 4; i += WS_THREADS) d2[i] = s2[i];
+  }
+  __syncthreads();
+  const int64_t G = gridDim.x;
+  const int64_t first = blockIdx.x;
+  const int n_it = first < nchunks ? (int)((nchunks - first + G - 1) / G) : 0;
+  const bool compute = wid < 4 || wid == 7 || wid == 11;
+  const int64_t rec_chunk = (int64_t)nq * TL_NF * C;
+  if (compute) {
+    // ================================ COMPUTE WARPS: phase 1 ================================
+    const int cw = wid < 4 ? wid : (wid == 7 ? 4 : 5);
+    const int ctid = cw * 32 + lane;
+    const int n2 = (int)(rec_chunk / 2);
+    if (n_it > 0) {
+      const double2* g = reinterpret_cast<const double2*>(rec + first * rec_chunk);
+      double2* sr = reinterpret_cast<double2*>(smem + L.rec0);
+      for (int i = ctid; i < n2; i += WS_ROLE) cp_async16(sr + i, g + i);
+    }
+    cp_async_commit();
+    for (int it = 0; it < n_it; ++it) {
+      const int64_t chunk = first + it * G;
+      const int buf = it & 1;
+      cp_async_wait<0>();
+      bar_sync(BAR_COMPUTE, WS_ROLE);               // rec[buf] complete; everybody left rec[buf ^ 1] (iteration it-1)
+      if (it + 1 < n_it) {
+        const double2* g = reinterpret_cast<const double2*>(rec + (chunk + G) * rec_chunk);
+        double2* sr = reinterpret_cast<double2*>(smem + L.rec0 + (buf ^ 1) * L.rec_stride);
+        for (int i = ctid; i < n2; i += WS_ROLE) cp_async16(sr + i, g + i);
+      }
+      cp_async_commit();
+      if (it >= 2) bar_sync(BAR_EMPTY + buf, WS_THREADS);   // writers are done with mom[buf] (chunk it-2)
+      const double* rc = smem + L.rec0 + buf * L.rec_stride + slot;
+      double* mom = smem + L.mom0 + buf * L.mom_stride + slot * MOM_CELL;
+      if (cw < 3) {
+        const int t = 2 * cw + half;                 // tiles (0,0) (0,1) (0,2) (1,1) (1,2) (2,2)
+        const int I = t < 3 ? 0 : (t < 5 ? 1 : 2);
+        const int J = t < 3 ? t : (t < 5 ? t - 2 : 2);
+        tile_uu(rc, R, nq, I, J, mom);
+      } else if (cw == 3) {
+        tile_tt(rc, R, nq, mom, half, 2, half ? 1 : 2);
+      } else if (cw == 4) {
+        tile_ut(rc, R, nq, half, mom);
+      } else {
+        tile_ut(rc, R, nq, 2, mom, half, 2, half ? 1 : 2);
+      }
+      if (cw >= 3) {                                   // halo items on the three lighter warps: one pair per thread
+        const int h0 = hitem_ptr[chunk], nh = hitem_ptr[chunk + 1] - h0;
+        double* hm = smem + L.hmom0 + buf * L.hmom_stride;
+        for (int i = (cw - 3) * 32 + lane; i < nh; i += 96) {
+          const uint32_t item = hitems[h0 + i];
+          const int64_t p = item >> 8;
+          const int code = item & 0xff, a = code / 13, b = code - 13 * a;
+          const double* rh = rec + (p / C) * rec_chunk + (p % C);
+          halo_item(rh, R, nq, a, b, hm + MOM_HALO * i);
+        }
+      }
+      __threadfence_block();
+      bar_arrive(BAR_FULL + buf, WS_THREADS);
+    }
+    cp_async_wait<0>();
+  } else {
+    // ================================ WRITER WARPS: halo items, phase 2, stores ================================
+    const int ww = wid < 7 ? wid - 4 : wid - 5;
+    const int wtid = ww * 32 + lane;
+    double* sFrame = smem + L.frame;
+    double* sK = smem + L.sk;
+    uint32_t* sInfo = reinterpret_cast<uint32_t*>(smem + L.plan);
+    int* sPos = reinterpret_cast<int*>(sInfo + dest_cap);
+    int* sTpos = sPos + dest_cap;
+    uint32_t* sRefs = reinterpret_cast<uint32_t*>(sTpos + dest_cap);
+    int* sFlag = reinterpret_cast<int*>(smem + L.flags);
+    for (int it = 0; it < n_it; ++it) {
+      const int64_t chunk = first + it * G;
+      const int buf = it & 1;
+      const int d0 = dest_ptr[chunk], nd = dest_ptr[chunk + 1] - d0;
+      const int r0 = ref_ptr[chunk], nr = ref_ptr[chunk + 1] - r0;
+      const int hc0 = hcell_ptr[chunk], nhc = hcell_ptr[chunk + 1] - hc0;
+      bar_sync(BAR_WRITER, WS_ROLE);                 // previous chunk's stores issued: plan, frames, sK reusable
+      for (int i = wtid; i < nd; i += WS_ROLE) {
+        cp_async4(sInfo + i, dest_info + d0 + i); cp_async4(sPos + i, dest_pos + d0 + i); cp_async4(sTpos + i, dest_tpos + d0 + i);
+      }
+      for (int i = wtid; i < nr; i += WS_ROLE) cp_async4(sRefs + i, refs + r0 + i);
+      cp_async_commit();
+      {
+        const double* f0 = frame + chunk * (C * 9);
+        for (int i = wtid; i < C * 9; i += WS_ROLE) sFrame[i] = f0[i];
+        for (int i = wtid; i < nhc * 9; i += WS_ROLE) {
+          const int s = i / 9, k = i - 9 * s;
+          sFrame[(C + s) * 9 + k] = frame[(int64_t)hcells[hc0 + s] * 9 + k];
+        }
+      }
+      if (it + 1 < n_it) {                           // pull the next chunk's plan towards L2 while this one is processed
+        const int64_t nx = chunk + G;
+        const int e0 = dest_ptr[nx], ne = dest_ptr[nx + 1] - e0, q0 = ref_ptr[nx], nqr = ref_ptr[nx + 1] - q0;
+        const int l1 = (ne + 31) / 32, l2 = (nqr + 31) / 32;      // 128-byte lines per array
+        for (int i = wtid; i < 3 * l1 + l2 + 10; i += WS_ROLE) {
+          const void* a;
+          if (i < l1) a = dest_info + e0 + 32 * i;
+          else if (i < 2 * l1) a = dest_pos + e0 + 32 * (i - l1);
+          else if (i < 3 * l1) a = dest_tpos + e0 + 32 * (i - 2 * l1);
+          else if (i < 3 * l1 + l2) a = refs + q0 + 32 * (i - 3 * l1);
+          else a = frame + nx * (C * 9) + 16 * (i - 3 * l1 - l2 < 9 ? i - 3 * l1 - l2 : 8);
+          prefetch_l2(a);
+        }
+      }
+      cp_async_wait<0>();
+      bar_sync(BAR_FULL + buf, WS_THREADS);          // moments of this chunk are in mom[buf] / hmom[buf]; all writers are here
+      {                                              // do all cells of this chunk (and its halo) share one frame?
+        const int nf = (C + nhc) * 9;
+        bool same = true;
+        for (int i = wtid; i < nf; i += WS_ROLE)
+          same = same && (__double_as_longlong(sFrame[i]) == __double_as_longlong(sFrame[i % 9]));
+        same = __all_sync(0xffffffffu, same);
+        if (lane == 0) sFlag[ww] = same ? 1 : 0;
+      }
+      bar_sync(BAR_WRITER, WS_ROLE);
+      const bool uniform = (sFlag[0] & sFlag[1] & sFlag[2] & sFlag[3] & sFlag[4] & sFlag[5]) != 0;
+      const V3 F0 = ldv3(sFrame), F1 = ldv3(sFrame + 3), F2 = ldv3(sFrame + 6);
+      const double* sMom = smem + L.mom0 + buf * L.mom_stride;
+      const double* sHm = smem + L.hmom0 + buf * L.hmom_stride;
+      for (int base = 0; base < nd; base += WS_DPT * WS_ROLE) {
+#pragma unroll
+        for (int u = 0; u < WS_DPT; ++u) {
+        const int di = base + u * WS_ROLE + wtid;
+        if (di < nd) {
+          const uint32_t info = sInfo[di];
+          const int start = info & 0xFFFFF, n = info >> 20;
+          double K[9];
+#pragma unroll
+          for (int k = 0; k < 9; ++k) K[k] = 0.0;
+          if (uniform) {
+            // flat patch: add the local-frame moments of all contributions first (fixed order), rotate once
+            double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+            int type = 0;
+            for (int r = 0; r < n; ++r) {
+              const uint32_t w = sRefs[start + r];
+              const int off = w & 0xFFFF;
+              const double* m = off < MOM_HALO_BASE ? sMom + off : sHm + (off - MOM_HALO_BASE);
+              type = (w >> 16) & 3;
+              const bool tr = (w >> 18) & 1;
+              a0 += m[0]; a3 += m[3];
+              a1 += tr ? m[2] : m[1]; a2 += tr ? m[1] : m[2];
+              if (type < 2) a4 += m[4];
+            }
+            if (type < 2) {
+              outer_acc(K, a0 * F0 + a2 * F1, F0);
+              outer_acc(K, a1 * F0 + a3 * F1, F1);
+              outer_acc(K, a4 * F2, F2);
+            } else {
+              outer_acc(K, F2, a0 * F1 - a1 * F0);
+              outer_acc(K, 0.5 * (a3 * F0 - a2 * F1), F2);
+            }
+          } else {
+            for (int r = 0; r < n; ++r) {                                 // fixed (processing-order) summation
+              const uint32_t w = sRefs[start + r];
+              const int off = w & 0xFFFF;
+              const double* m = off < MOM_HALO_BASE ? sMom + off : sHm + (off - MOM_HALO_BASE);
+              const int type = (w >> 16) & 3;
+              const double* fr = sFrame + (w >> 19) * 9;
+              const V3 E0 = ldv3(fr), E1 = ldv3(fr + 3), E2 = ldv3(fr + 6);
+              if (type < 2) {
+                const double m00 = m[0], m11 = m[3], sv = m[4];
+                double m01 = m[1], m10 = m[2];
+                if ((w >> 18) & 1) { const double t = m01; m01 = m10; m10 = t; }
+                outer_acc(K, m00 * E0 + m10 * E1, E0);
+                outer_acc(K, m01 * E0 + m11 * E1, E1);
+                outer_acc(K, sv * E2, E2);
+              } else {
+                const double A0 = m[0], A1 = m[1], D0 = m[2], D1 = m[3];
+                outer_acc(K, E2, A0 * E1 - A1 * E0);
+                outer_acc(K, 0.5 * (D1 * E0 - D0 * E1), E2);
+              }
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 9; ++k) sK[(u * WS_ROLE + wtid) * 9 + k] = K[k];
+        }
+        }
+        bar_sync(BAR_WRITER, WS_ROLE);
+        const int cnt = min(WS_DPT * WS_ROLE, nd - base);
+        if (wtid < 189) {                                                 // 21 blocks x 9 entries per pass, k fixed per thread
+          const int k = wtid % 9, kt = (k % 3) * 3 + k / 3;
+#pragma unroll 3
+          for (int hh = wtid / 9; hh < cnt; hh += 21) {
+            const double v = sK[hh * 9 + k];
+            vals[(int64_t)sPos[base + hh] * 9 + k] = v;
+            const int tp = sTpos[base + hh];
+            if (tp >= 0) vals[(int64_t)tp * 9 + kt] = v;
+          }
+        }
+        bar_sync(BAR_WRITER, WS_ROLE);
+      }
+      if (it + 2 < n_it) {
+        __threadfence_block();
+        bar_arrive(BAR_EMPTY + buf, WS_THREADS);       // mom[buf] may be overwritten (chunk it+2)
+      }
+    }
+  }
+}
+
 template <typename T>
 int upload(T** dst, const std::vector<T>& v) {
   TRY(dev_alloc(dst, v.size()));
@@ -517,12 +805,17 @@ int tile_plan_setup(femo_ctx* c) {
   }
   femo_tiles::Plan P;
   std::string err = femo_tiles::build(c->nc, c->nb, rowptr.data(), colidx.data(), nc_ptr.data(), nc_adj.data(),
-                                      order.empty() ? nullptr : order.data(), P);
+                                      order.empty() ? nullptr : order.data(), P,
+                                      getenv("FEMO_TILE_SORT") ? atoi(getenv("FEMO_TILE_SORT")) : 2);   // 0 position, 1 (type, position), 2 (type, n, position)
   if (!err.empty()) return femo_fail(err);
   const int hitem_cap = (P.max_hitems + 1) & ~1, hcell_cap = P.max_hcells;
   const int dest_cap = P.max_dests, ref_cap = P.max_refs;
-  const size_t smem = sizeof(double) * (size_t)tile_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap).total;
+  size_t smem = sizeof(double) * (size_t)tile_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap).total;
   if (smem > 227 * 1024) return 0;                      // halo too large for one CTA: older kernels take over
+  const size_t smem_ws = sizeof(double) * (size_t)ws_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap).total;
+  const char* ews = getenv("FEMO_TILE_WS");             // FEMO_TILE_WS=0: two independent CTAs per SM instead of warp roles
+  c->tl_ws = smem_ws <= 227 * 1024 && !(ews && atoi(ews) == 0);
+  if (c->tl_ws) smem = smem_ws;
   TRY(upload(&c->tl_cell_order, P.cell_order)); TRY(upload(&c->tl_dest_ptr, P.dest_ptr));
   TRY(upload(&c->tl_dest_pos, P.dest_pos)); TRY(upload(&c->tl_dest_tpos, P.dest_tpos));
   TRY(upload(&c->tl_dest_info, P.dest_info)); TRY(upload(&c->tl_ref_ptr, P.ref_ptr)); TRY(upload(&c->tl_refs, P.refs));
@@ -535,6 +828,12 @@ int tile_plan_setup(femo_ctx* c) {
   TRY(dev_alloc(&c->tl_rec, (size_t)P.nchunks * c->nq * TL_NF * C));
   TRY(dev_alloc(&c->tl_frame, (size_t)P.nchunks * C * 9));
   CUDA_TRY(cudaFuncSetAttribute(k_asm_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  CUDA_TRY(cudaFuncSetAttribute(k_asm_tiles_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  {
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, c->device));
+    c->tl_sms = prop.multiProcessorCount;
+  }
   if (getenv("FEMO_VERBOSE"))
     fprintf(stderr, "[femo] tile plan: %lld chunks of %d cells, %lld dests, %lld refs, %lld halo items (max/chunk %d), smem %zu B\n",
             (long long)P.nchunks, C, (long long)c->tl_ndest, (long long)c->tl_nref, (long long)c->tl_nhitem, P.max_hitems, smem);
@@ -544,12 +843,20 @@ int tile_plan_setup(femo_ctx* c) {
 
 // records + tiled assembly on c->stream; c->ev0 / c->ev1 bracket the records kernel (timed by the caller)
 int assemble_jacobian_tiles(femo_ctx* c, const double* uh) {
-  const int64_t nthreads = c->tl_nchunks * c->nq * C;
-  k_cell_records_tiles<<<(unsigned)cdiv(nthreads, 128), 128, 0, c->stream>>>(
+  const int64_t nthreads = c->tl_nchunks * C;
+  k_cell_records_tiles<<<(unsigned)cdiv(nthreads, 64), 64, 0, c->stream>>>(
       c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->tl_cell_order, c->tl_nchunks, c->nq, c->ewm, c->tl_rec,
       c->tl_frame);
   TRY(check_launch(c, "k_cell_records_tiles"));
   cudaEventRecord(c->ev1, c->stream);
+  if (c->tl_ws) {
+    const unsigned grid = (unsigned)std::min<int64_t>(c->tl_nchunks, c->tl_sms);
+    k_asm_tiles_ws<<<grid, WS_THREADS, c->tl_smem, c->stream>>>(
+        c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
+        c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap,
+        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals);
+    return check_launch(c, "k_asm_tiles_ws");
+  }
   k_asm_tiles<<<(unsigned)c->tl_nchunks, TL_THREADS, c->tl_smem, c->stream>>>(
       c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
       c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap, c->tl_hcell_cap,

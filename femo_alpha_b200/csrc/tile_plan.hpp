@@ -86,7 +86,7 @@ inline int matches(const int32_t* nc_ptr, const int32_t* nc_adj, const int32_t* 
 
 // order: nc cell ids in processing order (null = identity).  Returns "" or an error text.
 inline std::string build(int64_t nc, int64_t nb, const int32_t* rowptr, const int32_t* colidx, const int32_t* nc_ptr,
-                         const int32_t* nc_adj, const int32_t* order, Plan& P) {
+                         const int32_t* nc_adj, const int32_t* order, Plan& P, int sort_mode = 2) {
   const int CAP = 64;
   const int64_t nchunks = (nc + C - 1) / C;
   P = Plan();
@@ -154,7 +154,7 @@ inline std::string build(int64_t nc, int64_t nb, const int32_t* rowptr, const in
         if (!fill) {
           int type = 0, off, tr, lohi;
           pair_code(m[0].a, m[0].b, &type, &off, &tr, &lohi);
-          dkey.push_back(((uint32_t)type << 12) | (uint32_t)std::min(n, 4095));
+          dkey.push_back(sort_mode == 2 ? (((uint32_t)type << 12) | (uint32_t)std::min(n, 4095)) : (sort_mode == 1 ? ((uint32_t)type << 12) : 0u));
         }
         if (fill) {
           int32_t tp = -1;
