@@ -508,9 +508,6 @@ k_asm_tiles(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__ de
 //   compute: w0 w1 w2 = Q2-Q2 tile pairs; w3 = Q1-Q1 tile, quadrature points split over the two half-warps;
 //            w7 = Q2-Q1 tiles 0 | 1; w11 = Q2-Q1 tile 2, quadrature points split
 //   writers: w4 w5 w6 w8 w9 w10
-#define WS_THREADS 384
-#define WS_ROLE 192
-#define WS_DPT 2        /* destinations per writer thread and round */
 #define BAR_FULL 1      /* +buf */
 #define BAR_EMPTY 3     /* +buf */
 #define BAR_COMPUTE 5
@@ -529,16 +526,31 @@ __host__ __device__ inline WsSmem ws_smem_layout(int nq, int hitem_cap, int hcel
   L.frame = o; o += (C + hcell_cap) * 9;
   o = (o + 1) & ~1;
   L.rec0 = o; L.rec_stride = nq * TL_NF * C; o += 2 * L.rec_stride;
-  L.sk = o; o += WS_DPT * WS_ROLE * 9;
+  L.sk = o; o += 384 * 9;
   L.plan = o; o += (3 * dest_cap + ref_cap + 1) / 2 + 1;
-  L.flags = o; o += 4;
+  L.flags = o; o += 8;
   L.total = o;
   return L;
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
-__global__ void __launch_bounds__(WS_THREADS, 1)
+// MODE 0: 12 warps, 6 compute (w0-3, w7, w11) + 6 writers, all at the compiler's register count.
+// MODE 1: 16 warps, 8 compute-class warps (two warpgroups: six tile warps + two halo-item warps, raised from 128 to 168
+//         registers with setmaxnreg) + 8 writer warps (two warpgroups, lowered to 80).  The registers the writers give
+//         back (256 x 48) must cover what the compute warps ask for (256 x 40): setmaxnreg.inc only draws from the CTA pool.
+template <int MODE>
+struct WsCfg {
+  static constexpr int NT = MODE ? 512 : 384;       // threads per CTA
+  static constexpr int CT = MODE ? 256 : 192;       // compute threads
+  static constexpr int WT = MODE ? 256 : 192;       // writer threads
+  static constexpr int DPT = MODE ? 1 : 2;          // destinations per writer thread and round
+  static constexpr int HALO0 = MODE ? 4 : 3;        // first compute warp that takes halo items
+  static constexpr int NCW = MODE ? 8 : 6;          // compute warps
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(WsCfg<MODE>::NT, 1)
 k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__ dest_pos,
                const int32_t* __restrict__ dest_tpos, const uint32_t* __restrict__ dest_info,
                const int32_t* __restrict__ ref_ptr, const uint32_t* __restrict__ refs,
@@ -546,6 +558,8 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
                const int32_t* __restrict__ hcell_ptr, const int32_t* __restrict__ hcells,
                const double* __restrict__ rec, const double* __restrict__ frame, const Tables* __restrict__ tab, int nq,
                int hitem_cap, int hcell_cap, int dest_cap, int ref_cap, int64_t nchunks, double* __restrict__ vals) {
+  using Cfg = WsCfg<MODE>;
+  constexpr int WS_THREADS = Cfg::NT, CT = Cfg::CT, WT = Cfg::WT, DPT = Cfg::DPT;
   extern __shared__ __align__(16) double smem[];
   const WsSmem L = ws_smem_layout(nq, hitem_cap, hcell_cap, dest_cap, ref_cap);
   TileTab& R = *reinterpret_cast<TileTab*>(smem);
@@ -563,28 +577,29 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
   const int64_t G = gridDim.x;
   const int64_t first = blockIdx.x;
   const int n_it = first < nchunks ? (int)((nchunks - first + G - 1) / G) : 0;
-  const bool compute = wid < 4 || wid == 7 || wid == 11;
+  const bool compute = MODE ? wid < 8 : (wid < 4 || wid == 7 || wid == 11);
   const int64_t rec_chunk = (int64_t)nq * TL_NF * C;
   if (compute) {
     // ================================ COMPUTE WARPS: phase 1 ================================
-    const int cw = wid < 4 ? wid : (wid == 7 ? 4 : 5);
+    if (MODE) asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
+    const int cw = MODE ? wid : (wid < 4 ? wid : (wid == 7 ? 4 : 5));
     const int ctid = cw * 32 + lane;
     const int n2 = (int)(rec_chunk / 2);
     if (n_it > 0) {
       const double2* g = reinterpret_cast<const double2*>(rec + first * rec_chunk);
       double2* sr = reinterpret_cast<double2*>(smem + L.rec0);
-      for (int i = ctid; i < n2; i += WS_ROLE) cp_async16(sr + i, g + i);
+      for (int i = ctid; i < n2; i += CT) cp_async16(sr + i, g + i);
     }
     cp_async_commit();
     for (int it = 0; it < n_it; ++it) {
       const int64_t chunk = first + it * G;
       const int buf = it & 1;
       cp_async_wait<0>();
-      bar_sync(BAR_COMPUTE, WS_ROLE);               // rec[buf] complete; everybody left rec[buf ^ 1] (iteration it-1)
+      bar_sync(BAR_COMPUTE, CT);               // rec[buf] complete; everybody left rec[buf ^ 1] (iteration it-1)
       if (it + 1 < n_it) {
         const double2* g = reinterpret_cast<const double2*>(rec + (chunk + G) * rec_chunk);
         double2* sr = reinterpret_cast<double2*>(smem + L.rec0 + (buf ^ 1) * L.rec_stride);
-        for (int i = ctid; i < n2; i += WS_ROLE) cp_async16(sr + i, g + i);
+        for (int i = ctid; i < n2; i += CT) cp_async16(sr + i, g + i);
       }
       cp_async_commit();
       if (it >= 2) bar_sync(BAR_EMPTY + buf, WS_THREADS);   // writers are done with mom[buf] (chunk it-2)
@@ -599,13 +614,13 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
         tile_tt(rc, R, nq, mom, half, 2, half ? 1 : 2);
       } else if (cw == 4) {
         tile_ut(rc, R, nq, half, mom);
-      } else {
+      } else if (cw == 5) {
         tile_ut(rc, R, nq, 2, mom, half, 2, half ? 1 : 2);
       }
-      if (cw >= 3) {                                   // halo items on the three lighter warps: one pair per thread
+      if (cw >= Cfg::HALO0) {                          // halo items on the lighter warps: one pair per thread
         const int h0 = hitem_ptr[chunk], nh = hitem_ptr[chunk + 1] - h0;
         double* hm = smem + L.hmom0 + buf * L.hmom_stride;
-        for (int i = (cw - 3) * 32 + lane; i < nh; i += 96) {
+        for (int i = (cw - Cfg::HALO0) * 32 + lane; i < nh; i += (Cfg::NCW - Cfg::HALO0) * 32) {
           const uint32_t item = hitems[h0 + i];
           const int64_t p = item >> 8;
           const int code = item & 0xff, a = code / 13, b = code - 13 * a;
@@ -619,7 +634,8 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
     cp_async_wait<0>();
   } else {
     // ================================ WRITER WARPS: halo items, phase 2, stores ================================
-    const int ww = wid < 7 ? wid - 4 : wid - 5;
+    if (MODE) asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+    const int ww = MODE ? wid - 8 : (wid < 7 ? wid - 4 : wid - 5);
     const int wtid = ww * 32 + lane;
     double* sFrame = smem + L.frame;
     double* sK = smem + L.sk;
@@ -634,16 +650,16 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       const int d0 = dest_ptr[chunk], nd = dest_ptr[chunk + 1] - d0;
       const int r0 = ref_ptr[chunk], nr = ref_ptr[chunk + 1] - r0;
       const int hc0 = hcell_ptr[chunk], nhc = hcell_ptr[chunk + 1] - hc0;
-      bar_sync(BAR_WRITER, WS_ROLE);                 // previous chunk's stores issued: plan, frames, sK reusable
-      for (int i = wtid; i < nd; i += WS_ROLE) {
+      bar_sync(BAR_WRITER, WT);                 // previous chunk's stores issued: plan, frames, sK reusable
+      for (int i = wtid; i < nd; i += WT) {
         cp_async4(sInfo + i, dest_info + d0 + i); cp_async4(sPos + i, dest_pos + d0 + i); cp_async4(sTpos + i, dest_tpos + d0 + i);
       }
-      for (int i = wtid; i < nr; i += WS_ROLE) cp_async4(sRefs + i, refs + r0 + i);
+      for (int i = wtid; i < nr; i += WT) cp_async4(sRefs + i, refs + r0 + i);
       cp_async_commit();
       {
         const double* f0 = frame + chunk * (C * 9);
-        for (int i = wtid; i < C * 9; i += WS_ROLE) sFrame[i] = f0[i];
-        for (int i = wtid; i < nhc * 9; i += WS_ROLE) {
+        for (int i = wtid; i < C * 9; i += WT) sFrame[i] = f0[i];
+        for (int i = wtid; i < nhc * 9; i += WT) {
           const int s = i / 9, k = i - 9 * s;
           sFrame[(C + s) * 9 + k] = frame[(int64_t)hcells[hc0 + s] * 9 + k];
         }
@@ -652,7 +668,7 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
         const int64_t nx = chunk + G;
         const int e0 = dest_ptr[nx], ne = dest_ptr[nx + 1] - e0, q0 = ref_ptr[nx], nqr = ref_ptr[nx + 1] - q0;
         const int l1 = (ne + 31) / 32, l2 = (nqr + 31) / 32;      // 128-byte lines per array
-        for (int i = wtid; i < 3 * l1 + l2 + 10; i += WS_ROLE) {
+        for (int i = wtid; i < 3 * l1 + l2 + 10; i += WT) {
           const void* a;
           if (i < l1) a = dest_info + e0 + 32 * i;
           else if (i < 2 * l1) a = dest_pos + e0 + 32 * (i - l1);
@@ -667,20 +683,22 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       {                                              // do all cells of this chunk (and its halo) share one frame?
         const int nf = (C + nhc) * 9;
         bool same = true;
-        for (int i = wtid; i < nf; i += WS_ROLE)
+        for (int i = wtid; i < nf; i += WT)
           same = same && (__double_as_longlong(sFrame[i]) == __double_as_longlong(sFrame[i % 9]));
         same = __all_sync(0xffffffffu, same);
         if (lane == 0) sFlag[ww] = same ? 1 : 0;
       }
-      bar_sync(BAR_WRITER, WS_ROLE);
-      const bool uniform = (sFlag[0] & sFlag[1] & sFlag[2] & sFlag[3] & sFlag[4] & sFlag[5]) != 0;
+      bar_sync(BAR_WRITER, WT);
+      bool uniform = true;
+#pragma unroll
+      for (int w = 0; w < WT / 32; ++w) uniform = uniform && sFlag[w] != 0;
       const V3 F0 = ldv3(sFrame), F1 = ldv3(sFrame + 3), F2 = ldv3(sFrame + 6);
       const double* sMom = smem + L.mom0 + buf * L.mom_stride;
       const double* sHm = smem + L.hmom0 + buf * L.hmom_stride;
-      for (int base = 0; base < nd; base += WS_DPT * WS_ROLE) {
+      for (int base = 0; base < nd; base += DPT * WT) {
 #pragma unroll
-        for (int u = 0; u < WS_DPT; ++u) {
-        const int di = base + u * WS_ROLE + wtid;
+        for (int u = 0; u < DPT; ++u) {
+        const int di = base + u * WT + wtid;
         if (di < nd) {
           const uint32_t info = sInfo[di];
           const int start = info & 0xFFFFF, n = info >> 20;
@@ -732,22 +750,22 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
             }
           }
 #pragma unroll
-          for (int k = 0; k < 9; ++k) sK[(u * WS_ROLE + wtid) * 9 + k] = K[k];
+          for (int k = 0; k < 9; ++k) sK[(u * WT + wtid) * 9 + k] = K[k];
         }
         }
-        bar_sync(BAR_WRITER, WS_ROLE);
-        const int cnt = min(WS_DPT * WS_ROLE, nd - base);
-        if (wtid < 189) {                                                 // 21 blocks x 9 entries per pass, k fixed per thread
+        bar_sync(BAR_WRITER, WT);
+        const int cnt = min(DPT * WT, nd - base);
+        if (wtid < (WT / 9) * 9) {                                        // WT/9 blocks x 9 entries per pass, k fixed per thread
           const int k = wtid % 9, kt = (k % 3) * 3 + k / 3;
 #pragma unroll 3
-          for (int hh = wtid / 9; hh < cnt; hh += 21) {
+          for (int hh = wtid / 9; hh < cnt; hh += WT / 9) {
             const double v = sK[hh * 9 + k];
             vals[(int64_t)sPos[base + hh] * 9 + k] = v;
             const int tp = sTpos[base + hh];
             if (tp >= 0) vals[(int64_t)tp * 9 + kt] = v;
           }
         }
-        bar_sync(BAR_WRITER, WS_ROLE);
+        bar_sync(BAR_WRITER, WT);
       }
       if (it + 2 < n_it) {
         __threadfence_block();
@@ -814,7 +832,7 @@ int tile_plan_setup(femo_ctx* c) {
   if (smem > 227 * 1024) return 0;                      // halo too large for one CTA: older kernels take over
   const size_t smem_ws = sizeof(double) * (size_t)ws_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap).total;
   const char* ews = getenv("FEMO_TILE_WS");             // FEMO_TILE_WS=0: two independent CTAs per SM instead of warp roles
-  c->tl_ws = smem_ws <= 227 * 1024 && !(ews && atoi(ews) == 0);
+  c->tl_ws = smem_ws <= 227 * 1024 ? (ews ? atoi(ews) : 2) : 0;   // 1: 6+6 warps, 2: 8+8 warps with setmaxnreg
   if (c->tl_ws) smem = smem_ws;
   TRY(upload(&c->tl_cell_order, P.cell_order)); TRY(upload(&c->tl_dest_ptr, P.dest_ptr));
   TRY(upload(&c->tl_dest_pos, P.dest_pos)); TRY(upload(&c->tl_dest_tpos, P.dest_tpos));
@@ -828,7 +846,8 @@ int tile_plan_setup(femo_ctx* c) {
   TRY(dev_alloc(&c->tl_rec, (size_t)P.nchunks * c->nq * TL_NF * C));
   TRY(dev_alloc(&c->tl_frame, (size_t)P.nchunks * C * 9));
   CUDA_TRY(cudaFuncSetAttribute(k_asm_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CUDA_TRY(cudaFuncSetAttribute(k_asm_tiles_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  CUDA_TRY(cudaFuncSetAttribute(k_asm_tiles_ws<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  CUDA_TRY(cudaFuncSetAttribute(k_asm_tiles_ws<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   {
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, c->device));
@@ -851,7 +870,13 @@ int assemble_jacobian_tiles(femo_ctx* c, const double* uh) {
   cudaEventRecord(c->ev1, c->stream);
   if (c->tl_ws) {
     const unsigned grid = (unsigned)std::min<int64_t>(c->tl_nchunks, c->tl_sms);
-    k_asm_tiles_ws<<<grid, WS_THREADS, c->tl_smem, c->stream>>>(
+    if (c->tl_ws == 2)
+      k_asm_tiles_ws<1><<<grid, WsCfg<1>::NT, c->tl_smem, c->stream>>>(
+        c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
+        c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap,
+        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals);
+    else
+      k_asm_tiles_ws<0><<<grid, WsCfg<0>::NT, c->tl_smem, c->stream>>>(
         c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
         c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap,
         c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals);

@@ -108,7 +108,8 @@ struct femo_ctx {
   int32_t *tpos = nullptr;      // nnzb: position of the transposed block, -1 on the diagonal
   int32_t *ut_pos = nullptr, *tu_pos = nullptr;   // nn: positions of (v, nq2+v) and (nq2+v, v)
   // tiled planar assembly (assemble_tiles.cu, tile_plan.hpp): chunks of 32 cells in processing order
-  bool tile_ok = false, tl_ws = false;
+  bool tile_ok = false;
+  int tl_ws = 0;
   int tl_sms = 148;
   int64_t tl_nchunks = 0, tl_ndest = 0, tl_nref = 0, tl_nhitem = 0;
   int tl_hitem_cap = 0, tl_hcell_cap = 0, tl_dest_cap = 0, tl_ref_cap = 0;

@@ -186,14 +186,14 @@ def test_chunked_symmetric_assembly_any_chunk_size(built_lib, monkeypatch, name,
     d.close()
 
 
-@pytest.mark.parametrize("ws", ["1", "0"])
+@pytest.mark.parametrize("ws", ["2", "1", "0"])
 @pytest.mark.parametrize("order", ["morton", "identity"])
 @pytest.mark.parametrize("name", ["plate_4x20", "plate_varh", "skew_planar", "plate_dg0"])
 def test_tiled_assembly(built_lib, monkeypatch, name, order, ws):
     """Default planar kernel (assemble_tiles.cu): register-tiled moments per chunk of 32 cells in Morton (or the
     caller's) order; the matrix is the oracle's, symmetric to the bit, and identical from run to run."""
     monkeypatch.setenv("FEMO_TILE_ORDER", order)
-    monkeypatch.setenv("FEMO_TILE_WS", ws)          # 1: warp-specialised persistent kernel, 0: two CTAs per SM
+    monkeypatch.setenv("FEMO_TILE_WS", ws)          # 2: 8+8 warp roles (setmaxnreg), 1: 6+6 warp roles, 0: two plain CTAs per SM
     p = make_problem(name)
     o, d = oracle_for(p), device_for(p)
     K = o.assemble_dRdu().tocsr()
@@ -206,11 +206,13 @@ def test_tiled_assembly(built_lib, monkeypatch, name, order, ws):
 
 
 @pytest.mark.parametrize("shape", [(23, 17), (150, 40)])
-def test_tiled_assembly_many_chunks(built_lib, shape):
+@pytest.mark.parametrize("ws", ["2", "1"])
+def test_tiled_assembly_many_chunks(built_lib, monkeypatch, shape, ws):
     """Plates spanning 25 / 375 chunks (the larger one gives every persistent CTA several chunks, so the
     double-buffered moment hand-over between compute and writer warps is exercised); quadrature degree 2, 4, 6."""
     from oracle.rm_shell_ref import plate_mesh, RMShellOracle
     from femo_alpha_b200.shell_device import ShellDevice
+    monkeypatch.setenv("FEMO_TILE_WS", ws)
     rng = np.random.default_rng(7)
     nodes, quads = plate_mesh(shape[0], shape[1], 4.0, 3.0)
     nn = nodes.shape[0]
