@@ -1,0 +1,456 @@
+// Geometric multigrid preconditioner for the state / adjoint solves  A x = b  (A = dR/du with BCs).
+//
+// Replaces the MUMPS LU behind FEA.solve / solveLinearBwd (femo_alpha/fea/utils_dolfinx.py:438-468,514-531;
+// fea_dolfinx.py:159-203) when the mesh comes with a hierarchy of uniformly refined quad meshes
+// (femo_alpha_b200/multigrid.py): block-Jacobi PCG needs O(1e5) iterations at 1e7 DOF on thin shells, a V-cycle
+// preconditioned PCG ~1e2, mesh-independently (scripts/mg_study.py).
+//
+//   level l        a femo_ctx holding the Q2xQ1 discretisation of mesh l (re-discretised, not Galerkin), BCs set
+//   smoother       Chebyshev polynomial of degree `deg` in  D^-1 A  (D = the 6x6 / 3x3 block-Jacobi of solver.cu),
+//                  on [lmax/10, 1.1 lmax], lmax by power iteration: linear and A-self-adjoint -> the V-cycle is SPD
+//   transfer       nested Q2xQ1 spaces: P = coarse basis evaluated at the fine nodes (block-scalar CSR, rows = fine
+//                  block nodes), R = P^T stored as its own CSR so that both directions are gathers (no atomics)
+//   coarsest       dense inverse (cuSOLVER potrf + potri, bound at run time) applied as one GEMV
+#include <dlfcn.h>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include "femo_internal.cuh"
+
+struct MgLevel {
+  femo_ctx* c = nullptr;
+  int64_t nbf = 0, nbc = 0;
+  int32_t *P_ptr = nullptr, *P_col = nullptr, *R_ptr = nullptr, *R_col = nullptr;
+  double *P_w = nullptr, *R_w = nullptr;
+  double lmax = 0;
+  double *x = nullptr, *b = nullptr, *r = nullptr, *d = nullptr, *t = nullptr;
+};
+
+struct femo_mg {
+  std::vector<MgLevel> L;
+  int deg = 3;
+  double* Cinv = nullptr;      // dense inverse of the coarsest operator (n x n)
+  int64_t ncoarse = 0;
+  bool ready = false;
+  double *pr = nullptr, *pz = nullptr, *pp = nullptr, *pAp = nullptr, *px = nullptr, *pb = nullptr;   // PCG vectors (level 0)
+  int64_t vcycles = 0;
+};
+
+namespace {
+
+__device__ __forceinline__ void mg_precond_node(int64_t I, int64_t nn, const double* __restrict__ dinv6,
+                                                const double* __restrict__ dinv3, const double* rl, double* zl) {
+  if (I < nn) {
+    const double* D = dinv6 + I * 36;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      double s = 0;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) s += D[i * 6 + j] * rl[j];
+      zl[i] = s;
+    }
+  } else {
+    const double* D = dinv3 + (I - nn) * 9;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) zl[i] = D[3 * i] * rl[0] + D[3 * i + 1] * rl[1] + D[3 * i + 2] * rl[2];
+  }
+}
+
+// one Chebyshev step, fused per Jacobi group (vertex: u_v and theta_v, 6 dofs; edge / centre node: 3 dofs):
+//   r <- r0 - sr * Ad        (r0 = b when first, else r)
+//   d <- cd * d + cz * D^-1 r
+//   x <- (first ? 0 : x) + d
+__global__ void k_cheb_step(const double* r0, const double* __restrict__ Ad, double sr, double cd, double cz,
+                            int zero_x, const double* __restrict__ dinv6, const double* __restrict__ dinv3, int64_t nn,
+                            int64_t nq2, double* r, double* d, double* x) {
+  const int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= nq2) return;
+  const int nd = I < nn ? 6 : 3;
+  double rl[6], zl[6];
+  for (int i = 0; i < nd; ++i) {
+    const int64_t k = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+    rl[i] = r0[k] - (Ad ? sr * Ad[k] : 0.0);
+  }
+  mg_precond_node(I, nn, dinv6, dinv3, rl, zl);
+  for (int i = 0; i < nd; ++i) {
+    const int64_t k = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+    const double dn = (cd != 0.0 ? cd * d[k] : 0.0) + cz * zl[i];
+    r[k] = rl[i]; d[k] = dn;
+    x[k] = (zero_x ? 0.0 : x[k]) + dn;
+  }
+}
+
+__global__ void k_axpby(int64_t n, double a, const double* x, double b, const double* y, double* o) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) o[i] = a * x[i] + (b != 0.0 ? b * y[i] : 0.0);
+}
+
+// y[3 i + c] (+)= mask * sum_k w_k x[3 col_k + c]      (block-scalar CSR, one thread per (row, component))
+__global__ void k_transfer(const int32_t* __restrict__ ptr, const int32_t* __restrict__ col, const double* __restrict__ w,
+                           const double* __restrict__ x, const double* __restrict__ mask, int64_t nrows, int add,
+                           double* __restrict__ y) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= 3 * nrows) return;
+  const int64_t i = t / 3; const int cmp = (int)(t - 3 * i);
+  double s = 0;
+  for (int32_t k = ptr[i]; k < ptr[i + 1]; ++k) s += w[k] * x[3 * (int64_t)col[k] + cmp];
+  s *= mask[t];
+  y[t] = add ? y[t] + s : s;
+}
+
+// dense copy of the BC-modified operator: rows/cols of clamped dofs replaced by the identity (column-major = row-major)
+__global__ void k_dense_fill(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+                             const double* __restrict__ vals, const double* __restrict__ bcmask, int64_t nb, int64_t n,
+                             double* __restrict__ A) {
+  const int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= nb) return;
+  for (int32_t k = rowptr[I]; k < rowptr[I + 1]; ++k) {
+    const int64_t J = colidx[k];
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) {
+        const int64_t r = 3 * I + i, cc = 3 * J + j;
+        double v = vals[(int64_t)k * 9 + 3 * i + j] * bcmask[r] * bcmask[cc];
+        if (r == cc && bcmask[r] == 0.0) v = 1.0;
+        A[r * n + cc] = v;
+      }
+  }
+}
+
+// potri(LOWER, column-major) leaves the inverse in the entries (i >= j) at [j n + i], i.e. the row-major UPPER
+// triangle: mirror it into the row-major lower one
+__global__ void k_dense_mirror(double* A, int64_t n) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= n * n) return;
+  const int64_t r = t / n, cc = t - r * n;
+  if (cc < r) A[r * n + cc] = A[cc * n + r];
+}
+
+__global__ void k_mg_mask(int64_t n, const double* __restrict__ mask, double* __restrict__ x) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) x[i] *= mask[i];
+}
+
+// y = A x, dense row-major symmetric, one warp per row, fixed summation order
+__global__ void k_dense_gemv(const double* __restrict__ A, const double* __restrict__ x, int64_t n, double* __restrict__ y) {
+  const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= n) return;
+  const double* a = A + row * n;
+  double s = 0;
+  for (int64_t j = lane; j < n; j += 32) s += a[j] * x[j];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) y[row] = s;
+}
+
+// ---- cuSOLVER (dense Cholesky + inverse of the coarsest operator), bound at run time -----------------------------
+struct CusolverApi {
+  void* handle = nullptr;
+  int (*Create)(void**) = nullptr;
+  int (*Destroy)(void*) = nullptr;
+  int (*SetStream)(void*, cudaStream_t) = nullptr;
+  int (*potrf_bufferSize)(void*, int, int, double*, int, int*) = nullptr;
+  int (*potrf)(void*, int, int, double*, int, double*, int, int*) = nullptr;
+  int (*potri_bufferSize)(void*, int, int, double*, int, int*) = nullptr;
+  int (*potri)(void*, int, int, double*, int, double*, int, int*) = nullptr;
+};
+CusolverApi g_cs;
+
+int cusolver_load() {
+  if (g_cs.handle) return 0;
+  const char* env = getenv("FEMO_CUSOLVER_LIB");
+  void* h = env ? dlopen(env, RTLD_NOW | RTLD_GLOBAL) : nullptr;
+  const char* names[] = {"libcusolver.so.11", "libcusolver.so.12", "libcusolver.so", "/usr/local/cuda/lib64/libcusolver.so.11"};
+  for (const char* nm : names)
+    if (!h) h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return femo_fail(std::string("multigrid: cannot load libcusolver (set FEMO_CUSOLVER_LIB): ") + dlerror());
+#define BINDS(field, name)                                                            \
+  *(void**)(&g_cs.field) = dlsym(h, name);                                            \
+  if (!g_cs.field) return femo_fail(std::string("libcusolver: missing symbol ") + name)
+  BINDS(Create, "cusolverDnCreate"); BINDS(Destroy, "cusolverDnDestroy"); BINDS(SetStream, "cusolverDnSetStream");
+  BINDS(potrf_bufferSize, "cusolverDnDpotrf_bufferSize"); BINDS(potrf, "cusolverDnDpotrf");
+  BINDS(potri_bufferSize, "cusolverDnDpotri_bufferSize"); BINDS(potri, "cusolverDnDpotri");
+#undef BINDS
+  g_cs.handle = h;
+  return 0;
+}
+
+int mg_smooth(femo_mg* m, int l, bool zero_guess) {
+  MgLevel& Lv = m->L[l];
+  femo_ctx* c = Lv.c;
+  const double lo = 0.1 * Lv.lmax, hi = 1.1 * Lv.lmax;
+  const double theta = 0.5 * (hi + lo), delta = 0.5 * (hi - lo), sigma = theta / delta;
+  double rho = 1.0 / sigma;
+  const unsigned grid = (unsigned)cdiv(c->nq2, 128);
+  for (int k = 0; k < m->deg; ++k) {
+    if (k == 0) {
+      if (zero_guess) {
+        k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, nullptr, 0.0, 0.0, 1.0 / theta, 1, c->dinv6, c->dinv3, c->nn, c->nq2,
+                                                 Lv.r, Lv.d, Lv.x);
+      } else {
+        TRY(bsr_spmv(c, Lv.x, Lv.t, 1));
+        k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, Lv.t, 1.0, 0.0, 1.0 / theta, 0, c->dinv6, c->dinv3, c->nn, c->nq2,
+                                                 Lv.r, Lv.d, Lv.x);
+      }
+    } else {
+      TRY(bsr_spmv(c, Lv.d, Lv.t, 1));
+      const double rho_new = 1.0 / (2.0 * sigma - rho);
+      k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.r, Lv.t, 1.0, rho_new * rho, 2.0 * rho_new / delta, 0, c->dinv6, c->dinv3,
+                                               c->nn, c->nq2, Lv.r, Lv.d, Lv.x);
+      rho = rho_new;
+    }
+    c->launches += 1;
+  }
+  return check_launch(c, "k_cheb_step");
+}
+
+// L[l].b -> L[l].x
+int mg_vcycle(femo_mg* m, int l) {
+  MgLevel& Lv = m->L[l];
+  femo_ctx* c = Lv.c;
+  const int64_t n = c->ndof;
+  if (l == (int)m->L.size() - 1) {
+    k_dense_gemv<<<(unsigned)cdiv(n * 32, 256), 256, 0, c->stream>>>(m->Cinv, Lv.b, n, Lv.x);
+    c->launches += 1;
+    return check_launch(c, "k_dense_gemv");
+  }
+  MgLevel& Lc = m->L[l + 1];
+  TRY(mg_smooth(m, l, true));
+  TRY(bsr_spmv(c, Lv.x, Lv.t, 1));
+  k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, Lv.b, -1.0, Lv.t, Lv.r);
+  k_transfer<<<(unsigned)cdiv(3 * Lv.nbc, 256), 256, 0, c->stream>>>(Lv.R_ptr, Lv.R_col, Lv.R_w, Lv.r, Lc.c->bcmask, Lv.nbc, 0, Lc.b);
+  TRY(check_launch(c, "mg restrict"));
+  c->launches += 2;
+  TRY(mg_vcycle(m, l + 1));
+  k_transfer<<<(unsigned)cdiv(3 * Lv.nbf, 256), 256, 0, c->stream>>>(Lv.P_ptr, Lv.P_col, Lv.P_w, Lc.x, c->bcmask, Lv.nbf, 1, Lv.x);
+  TRY(check_launch(c, "mg prolong"));
+  c->launches += 1;
+  return mg_smooth(m, l, false);
+}
+
+int mg_lambda_max(femo_mg* m, int l) {
+  MgLevel& Lv = m->L[l];
+  femo_ctx* c = Lv.c;
+  const int64_t n = c->ndof;
+  std::vector<double> v((size_t)n);
+  for (int64_t i = 0; i < n; ++i) v[i] = sin(0.37 * (double)i + 0.11) + 0.5 * cos(1.3 * (double)(i % 1013));
+  CUDA_TRY(cudaMemcpyAsync(Lv.x, v.data(), sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  double lam = 1.0;
+  for (int it = 0; it < 16; ++it) {
+    double nrm2 = 0;
+    TRY(dev_dot(c, Lv.x, Lv.x, n, &nrm2));
+    if (!(nrm2 > 0)) return femo_fail("multigrid: zero vector in the power iteration");
+    if (it > 0) lam = sqrt(nrm2);
+    k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0 / sqrt(nrm2), Lv.x, 0.0, Lv.x, Lv.b);
+    TRY(bsr_spmv(c, Lv.b, Lv.t, 1));
+    k_cheb_step<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(Lv.t, nullptr, 0.0, 0.0, 1.0, 1, c->dinv6, c->dinv3, c->nn,
+                                                                    c->nq2, Lv.r, Lv.d, Lv.x);
+    TRY(check_launch(c, "mg power iteration"));
+  }
+  Lv.lmax = lam;
+  return 0;
+}
+
+int mg_coarse_inverse(femo_mg* m) {
+  femo_ctx* c = m->L.back().c;
+  const int64_t n = c->ndof;
+  if (n > 46000) return femo_fail("multigrid: coarsest level too large for a dense inverse (" + std::to_string(n) + " dofs); add levels");
+  TRY(cusolver_load());
+  if (m->ncoarse != n) { dev_free(&m->Cinv); TRY(dev_alloc(&m->Cinv, (size_t)n * n)); m->ncoarse = n; }
+  CUDA_TRY(cudaMemsetAsync(m->Cinv, 0, sizeof(double) * n * n, c->stream));
+  k_dense_fill<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->bcmask, c->nb, n, m->Cinv);
+  TRY(check_launch(c, "k_dense_fill"));
+  void* h = nullptr;
+  if (g_cs.Create(&h) != 0) return femo_fail("cusolverDnCreate failed");
+  g_cs.SetStream(h, c->stream);
+  int lw1 = 0, lw2 = 0;
+  const int LOWER = 0;
+  if (g_cs.potrf_bufferSize(h, LOWER, (int)n, m->Cinv, (int)n, &lw1) != 0) { g_cs.Destroy(h); return femo_fail("potrf_bufferSize failed"); }
+  if (g_cs.potri_bufferSize(h, LOWER, (int)n, m->Cinv, (int)n, &lw2) != 0) { g_cs.Destroy(h); return femo_fail("potri_bufferSize failed"); }
+  double* work = nullptr; int* info = nullptr;
+  TRY(dev_alloc(&work, (size_t)std::max(lw1, lw2))); TRY(dev_alloc(&info, 2));
+  int r1 = g_cs.potrf(h, LOWER, (int)n, m->Cinv, (int)n, work, lw1, info);
+  int r2 = g_cs.potri(h, LOWER, (int)n, m->Cinv, (int)n, work, lw2, info + 1);
+  int hinfo[2] = {0, 0};
+  cudaMemcpyAsync(hinfo, info, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+  cudaStreamSynchronize(c->stream);
+  g_cs.Destroy(h);
+  dev_free(&work); dev_free(&info);
+  if (r1 != 0 || r2 != 0 || hinfo[0] != 0 || hinfo[1] != 0)
+    return femo_fail("multigrid: dense Cholesky of the coarsest operator failed (not SPD? status " + std::to_string(r1) + "/" +
+                     std::to_string(r2) + ", info " + std::to_string(hinfo[0]) + "/" + std::to_string(hinfo[1]) + ")");
+  k_dense_mirror<<<(unsigned)cdiv(n * n, 256), 256, 0, c->stream>>>(m->Cinv, n);
+  TRY(check_launch(c, "k_dense_mirror"));
+  c->launches += 2;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int femo_mg_create(int n_levels, femo_ctx** ctxs, femo_mg** out) {
+  if (n_levels < 2 || !ctxs || !out) return femo_fail("femo_mg_create: need at least two levels");
+  femo_mg* m = new femo_mg();
+  m->L.resize(n_levels);
+  for (int l = 0; l < n_levels; ++l) {
+    if (!ctxs[l] || !ctxs[l]->setup_done) { delete m; return femo_fail("femo_mg_create: level context not set up"); }
+    if (ctxs[l]->world > 1) { delete m; return femo_fail("femo_mg_create: multigrid levels are single-GPU contexts"); }
+    if (ctxs[l]->device != ctxs[0]->device) { delete m; return femo_fail("femo_mg_create: levels must share one device"); }
+    m->L[l].c = ctxs[l];
+    ctxs[l]->stream = ctxs[0]->stream;
+  }
+  *out = m;
+  return 0;
+}
+
+static void mg_free_level(MgLevel& Lv) {
+  dev_free(&Lv.P_ptr); dev_free(&Lv.P_col); dev_free(&Lv.P_w); dev_free(&Lv.R_ptr); dev_free(&Lv.R_col); dev_free(&Lv.R_w);
+  dev_free(&Lv.x); dev_free(&Lv.b); dev_free(&Lv.r); dev_free(&Lv.d); dev_free(&Lv.t);
+}
+
+int femo_mg_destroy(femo_mg* m) {
+  if (!m) return 0;
+  cudaSetDevice(m->L[0].c->device);
+  for (auto& Lv : m->L) mg_free_level(Lv);
+  dev_free(&m->Cinv); dev_free(&m->pr); dev_free(&m->pz); dev_free(&m->pp); dev_free(&m->pAp); dev_free(&m->px); dev_free(&m->pb);
+  delete m;
+  return 0;
+}
+
+// transfer between level l (fine) and l+1 (coarse): P has n_fine_blocks rows, R = P^T has n_coarse_blocks rows
+int femo_mg_set_transfer(femo_mg* m, int l, const int32_t* P_ptr, const int32_t* P_col, const double* P_w,
+                         const int32_t* R_ptr, const int32_t* R_col, const double* R_w) {
+  if (!m || l < 0 || l + 1 >= (int)m->L.size()) return femo_fail("femo_mg_set_transfer: bad level");
+  MgLevel& Lv = m->L[l];
+  cudaSetDevice(Lv.c->device);
+  Lv.nbf = Lv.c->nb; Lv.nbc = m->L[l + 1].c->nb;
+  const int64_t nnz = P_ptr[Lv.nbf];
+  if (R_ptr[Lv.nbc] != nnz) return femo_fail("femo_mg_set_transfer: P and R differ in size");
+  TRY(dev_alloc(&Lv.P_ptr, (size_t)Lv.nbf + 1)); TRY(dev_alloc(&Lv.P_col, (size_t)nnz)); TRY(dev_alloc(&Lv.P_w, (size_t)nnz));
+  TRY(dev_alloc(&Lv.R_ptr, (size_t)Lv.nbc + 1)); TRY(dev_alloc(&Lv.R_col, (size_t)nnz)); TRY(dev_alloc(&Lv.R_w, (size_t)nnz));
+  CUDA_TRY(cudaMemcpy(Lv.P_ptr, P_ptr, sizeof(int32_t) * (Lv.nbf + 1), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(Lv.P_col, P_col, sizeof(int32_t) * nnz, cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(Lv.P_w, P_w, sizeof(double) * nnz, cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(Lv.R_ptr, R_ptr, sizeof(int32_t) * (Lv.nbc + 1), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(Lv.R_col, R_col, sizeof(int32_t) * nnz, cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(Lv.R_w, R_w, sizeof(double) * nnz, cudaMemcpyHostToDevice));
+  m->ready = false;
+  return 0;
+}
+
+// (re)build the preconditioner from the levels' current inputs: assemble every level, block-Jacobi inverses,
+// spectral bounds, dense inverse of the coarsest operator
+int femo_mg_setup(femo_mg* m, int cheb_degree) {
+  if (!m) return femo_fail("null multigrid handle");
+  cudaSetDevice(m->L[0].c->device);
+  m->deg = cheb_degree > 0 ? cheb_degree : 3;
+  const bool verbose = getenv("FEMO_VERBOSE") != nullptr;
+  cudaEvent_t e0, e1, e2, e3;
+  cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2); cudaEventCreate(&e3);
+  cudaStream_t st = m->L[0].c->stream;
+  cudaEventRecord(e0, st);
+  for (size_t l = 0; l < m->L.size(); ++l) {
+    femo_ctx* c = m->L[l].c;
+    if (!c->jac_valid) TRY(assemble_jacobian(c));
+    TRY(precond_setup(c));
+  }
+  cudaEventRecord(e1, st);
+  for (size_t l = 0; l < m->L.size(); ++l) {
+    MgLevel& Lv = m->L[l];
+    femo_ctx* c = Lv.c;
+    if (l + 1 < m->L.size() && !Lv.P_ptr) return femo_fail("femo_mg_setup: transfer operators missing");
+    const size_t n = (size_t)c->ndof;
+    if (!Lv.x) { TRY(dev_alloc(&Lv.x, n)); TRY(dev_alloc(&Lv.b, n)); TRY(dev_alloc(&Lv.r, n)); TRY(dev_alloc(&Lv.d, n)); TRY(dev_alloc(&Lv.t, n)); }
+    if (l + 1 < m->L.size()) TRY(mg_lambda_max(m, (int)l));
+  }
+  cudaEventRecord(e2, st);
+  TRY(mg_coarse_inverse(m));
+  cudaEventRecord(e3, st);
+  cudaEventSynchronize(e3);
+  if (verbose) {
+    float a = 0, b = 0, d = 0;
+    cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2); cudaEventElapsedTime(&d, e2, e3);
+    fprintf(stderr, "[femo] mg setup: assemble + block-Jacobi %.1f ms, spectral bounds %.1f ms, coarse inverse (n = %lld) %.1f ms\n",
+            a, b, (long long)m->L.back().c->ndof, d);
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
+  if (!m->pr) {
+    const size_t n = (size_t)m->L[0].c->ndof;
+    TRY(dev_alloc(&m->pr, n)); TRY(dev_alloc(&m->pz, n)); TRY(dev_alloc(&m->pp, n)); TRY(dev_alloc(&m->pAp, n));
+    TRY(dev_alloc(&m->px, n)); TRY(dev_alloc(&m->pb, n));
+  }
+  m->ready = true;
+  return 0;
+}
+
+int femo_mg_get_lambda(femo_mg* m, int l, double* lam) {
+  if (!m || l < 0 || l >= (int)m->L.size()) return femo_fail("bad level");
+  *lam = m->L[l].lmax;
+  return 0;
+}
+
+// PCG on the finest level with one V-cycle as preconditioner.  rhs / sol: n_dof doubles (host or device);
+// clamped entries of rhs are ignored (homogeneous Dirichlet), x0 = 0; zero_bc zeroes the clamped entries of sol
+// (state_operation.py:217-218).
+int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
+                  int on_device, int zero_bc) {
+  if (!m || !m->ready) return femo_fail("femo_mg_solve: call femo_mg_setup first (and again after the inputs change)");
+  femo_ctx* c = m->L[0].c;
+  cudaSetDevice(c->device);
+  if (!c->jac_valid) return femo_fail("femo_mg_solve: inputs changed since femo_mg_setup");
+  const int64_t n = c->ndof;
+  MgLevel& L0 = m->L[0];
+  CUDA_TRY(cudaMemcpyAsync(m->pb, rhs, sizeof(double) * n, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+  // b <- mask * b, x = 0, r = b
+  k_mg_mask<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, c->bcmask, m->pb);
+  CUDA_TRY(cudaMemsetAsync(m->px, 0, sizeof(double) * n, c->stream));
+  CUDA_TRY(cudaMemcpyAsync(m->pr, m->pb, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+  cudaEventRecord(c->ev0, c->stream);
+  double bb = 0, rz = 0, rr = 0;
+  TRY(dev_dot(c, m->pb, m->pb, n, &bb));
+  const double bnorm = sqrt(bb);
+  int it = 0;
+  double rel = 0;
+  if (bnorm > 0) {
+    rr = bb; rel = 1.0;
+    while (it < max_it) {
+      CUDA_TRY(cudaMemcpyAsync(L0.b, m->pr, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+      TRY(mg_vcycle(m, 0));
+      m->vcycles += 1;
+      double rz_new = 0;
+      TRY(dev_dot(c, m->pr, L0.x, n, &rz_new));
+      if (!(rz_new > 0)) return femo_fail("femo_mg_solve: preconditioner is not positive definite (r.z = " + std::to_string(rz_new) + ")");
+      if (it == 0) CUDA_TRY(cudaMemcpyAsync(m->pp, L0.x, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+      else k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, L0.x, rz_new / rz, m->pp, m->pp);
+      rz = rz_new;
+      TRY(bsr_spmv(c, m->pp, m->pAp, 1));
+      double pAp = 0;
+      TRY(dev_dot(c, m->pp, m->pAp, n, &pAp));
+      if (!(pAp > 0)) return femo_fail("femo_mg_solve: operator is not positive definite");
+      const double alpha = rz / pAp;
+      k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, m->px, alpha, m->pp, m->px);
+      k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, m->pr, -alpha, m->pAp, m->pr);
+      c->launches += 3;
+      ++it;
+      TRY(dev_dot(c, m->pr, m->pr, n, &rr));
+      rel = sqrt(rr) / bnorm;
+      if (!(rel == rel)) return femo_fail("femo_mg_solve: NaN residual");
+      if (rel <= rtol) break;
+    }
+  }
+  if (zero_bc) k_mg_mask<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, c->bcmask, m->px);
+  cudaEventRecord(c->ev1, c->stream);
+  CUDA_TRY(cudaMemcpyAsync(sol, m->px, sizeof(double) * n, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  c->t_solve = ms; c->t_iter = it > 0 ? ms / it : 0.0;
+  if (iters) *iters = it;
+  if (relres) *relres = rel;
+  return 0;
+}
+
+}  // extern "C"

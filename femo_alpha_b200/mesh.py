@@ -100,20 +100,13 @@ def readPickleMesh(path):
 
 
 def refine_uniform(mesh, levels=1):
-    """Uniform 1->4 quad subdivision (keeps non-manifold junctions); used for synthetic refinements."""
-    x, cells = mesh.geometry.x, mesh.cells.astype(np.int64)
+    """Uniform 1->4 quad subdivision (keeps non-manifold junctions); used for synthetic refinements.
+    The returned mesh remembers its parents (`mg_meshes`, coarse to fine): RMShellPDE then builds the nested
+    Q2xQ1 hierarchy and the state / adjoint solves run multigrid-preconditioned (femo_alpha_b200/multigrid.py)."""
+    from .multigrid import refine_quads
+    chain = list(getattr(mesh, "mg_meshes", None) or [(mesh.geometry.x, mesh.cells)])
     for _ in range(levels):
-        nn = x.shape[0]
-        ce = np.stack([cells, np.roll(cells, -1, axis=1)], 2)            # (nc,4,2) cyclic edges
-        key = np.sort(ce, axis=2).reshape(-1, 2)
-        ukey, inv = np.unique(key[:, 0] * nn + key[:, 1], return_inverse=True)
-        mid = 0.5 * (x[ukey // nn] + x[ukey % nn])
-        em = nn + inv.reshape(-1, 4)
-        cc = nn + ukey.size + np.arange(cells.shape[0])
-        ctr = x[cells].mean(axis=1)
-        new = []
-        for k in range(4):
-            new.append(np.stack([cells[:, k], em[:, k], cc, em[:, (k - 1) % 4]], 1))
-        x = np.concatenate([x, mid, ctr], 0)
-        cells = np.concatenate(new, 0)
-    return ShellMesh(x, cells)
+        chain.append(refine_quads(*chain[-1]))
+    fine = ShellMesh(*chain[-1])
+    fine.mg_meshes = chain
+    return fine

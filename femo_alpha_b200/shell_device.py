@@ -35,6 +35,7 @@ class ShellDevice:
         self.nq2 = self.nn + self.ne + self.nc
         self.n_mat, self.n_f = s.n_material, s.n_force
         self.last_solve = dict(iters=0, relres=0.0)
+        self._mg = None                 # ShellHierarchy this device is the finest level of (multigrid.py)
 
     def close(self):
         if getattr(self, "_ctx", None) is not None and self._ctx.value:
@@ -78,10 +79,16 @@ class ShellDevice:
     def set_strong_bc(self, dofs):
         d = np.ascontiguousarray(dofs, dtype=np.int32)
         L.check(self.lib.femo_set_strong_bc(self._ctx, d.size, L.ptr(d)))
+        if self._mg is not None:
+            self._mg._coarse_bcs(d)
 
     def set_penalty_bc(self, vertex_on):
         v = np.ascontiguousarray(vertex_on, dtype=np.uint8)
         L.check(self.lib.femo_set_penalty_bc(self._ctx, v.size, L.ptr(v)))
+        if self._mg is not None and v.any():
+            import warnings
+            warnings.warn("femo_alpha_b200: penalty BCs are not carried to the coarse levels; multigrid is switched off")
+            self._mg = None
 
     # ---- inputs / state ----------------------------------------------------------
     def set_input(self, name, values):
@@ -92,6 +99,8 @@ class ShellDevice:
         else:
             n = values.numel()
         L.check(self.lib.femo_set_input(self._ctx, which, L.ptr(values), n, L.on_device(values)))
+        if self._mg is not None:
+            self._mg._coarse_inputs(name, values)
 
     def get_input(self, name):
         which = self._arg_id(name)
@@ -147,6 +156,8 @@ class ShellDevice:
 
     # ---- solves -------------------------------------------------------------------------
     def solve_state(self, rtol=1e-12, max_it=200000):
+        if self._mg is not None:          # nested mesh hierarchy available: V-cycle preconditioned PCG (csrc/mg.cu)
+            return self._mg.solve_state(rtol, min(max_it, 5000))
         it = C.c_int(0); rr = C.c_double(0.0)
         L.check(self.lib.femo_solve_state(self._ctx, float(rtol), int(max_it), C.byref(it), C.byref(rr)))
         self.last_solve = dict(iters=it.value, relres=rr.value)
@@ -154,6 +165,10 @@ class ShellDevice:
 
     def _solve(self, fn, rhs, rtol, max_it):
         rhs = np.ascontiguousarray(rhs, dtype=np.float64)
+        if self._mg is not None:
+            out = self._mg.solve(rhs, rtol, min(max_it, 5000), zero_bc=(fn is self.lib.femo_solve_adjoint))
+            self.last_solve = dict(self._mg.last_solve)
+            return out
         out = np.empty(self.ndof)
         it = C.c_int(0); rr = C.c_double(0.0)
         L.check(fn(self._ctx, L.ptr(rhs), L.ptr(out), float(rtol), int(max_it), C.byref(it), C.byref(rr), 0))

@@ -170,6 +170,26 @@ int femo_halo_exchange(femo_ctx* ctx, double* x, int on_device);
 int femo_dist_allreduce(femo_ctx* ctx, double* vals, int n);
 int femo_dist_counts(femo_ctx* ctx, int64_t* halo_exchanges, int64_t* allreduces);
 
+/* ---- geometric multigrid preconditioner for the state / adjoint solves --------------------------------
+ * Replaces the sparse LU (MUMPS through PETSc `preonly + lu`, femo_alpha/fea/utils_dolfinx.py:438-468 setUpKSP /
+ * NewtonSolver and :514-531 setUpKSP_MUMPS; fea_dolfinx.py:159-203 FEA.solve / solveLinearBwd) on meshes that come
+ * with a hierarchy of uniformly refined quad meshes: level 0 = the mesh of the analysis, level l+1 = its parent.
+ * Every level is an ordinary context (same inputs sampled on its own nodes, same BC predicate). */
+typedef struct femo_mg femo_mg;
+int femo_mg_create(int n_levels, femo_ctx** level_ctxs, femo_mg** out);
+int femo_mg_destroy(femo_mg* mg);
+/* transfer between level l (fine) and l+1 (coarse) in block-node numbering: P (rows = fine blocks) and
+ * R = P^T (rows = coarse blocks) as CSR with one scalar weight per (fine block, coarse block) pair */
+int femo_mg_set_transfer(femo_mg* mg, int level, const int32_t* P_rowptr, const int32_t* P_col, const double* P_w,
+                         const int32_t* R_rowptr, const int32_t* R_col, const double* R_w);
+/* (re)build after the inputs changed: assembles every level, block-Jacobi inverses, spectral bounds of the
+ * Chebyshev smoother (degree cheb_degree, default 3), dense inverse of the coarsest operator */
+int femo_mg_setup(femo_mg* mg, int cheb_degree);
+int femo_mg_get_lambda(femo_mg* mg, int level, double* lambda_max);
+/* PCG with one V-cycle per iteration on A x = rhs (A = dR/du with BCs, x0 = 0); zero_bc as femo_solve_adjoint */
+int femo_mg_solve(femo_mg* mg, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
+                  int on_device, int zero_bc);
+
 /* ---- instrumentation ---------------------------------------------------------------- */
 /* number of kernels this context has launched so far */
 int femo_launch_count(femo_ctx* ctx, int64_t* n);

@@ -1,0 +1,118 @@
+"""Multigrid-preconditioned state / adjoint solves (csrc/mg.cu) against the oracle's direct solve."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.mark.parametrize("levels,deg", [(2, 3), (3, 3), (3, 2)])
+def test_mg_solves_match_direct(built_lib, levels, deg):
+    from femo_alpha_b200.multigrid import ShellHierarchy, refine_quads
+    from oracle.rm_shell_ref import RMShellOracle, plate_mesh
+    rng = np.random.default_rng(11)
+    nodes, quads = plate_mesh(6, 4, 3.0, 2.0)
+    nodes[:, :2] += 0.03 * rng.standard_normal((nodes.shape[0], 2)) * (nodes[:, :1] > 1e-9)
+    thick = lambda x: 0.05 * (1.0 + 0.3 * np.sin(2.0 * x[0]) * np.cos(1.5 * x[1]))
+    clamp = lambda x: np.less(x[0], 3e-16)
+    h = ShellHierarchy(nodes, quads, levels, cheb_degree=deg)
+    nf, qf = h.meshes[0]
+    nn = nf.shape[0]
+    F = np.tile([0.0, 0.0, 5.0], nn) + 0.1 * rng.standard_normal(3 * nn)
+    h.set_input("thickness", thick)
+    h.set_input("E", 1e6); h.set_input("nu", 0.3); h.set_input("density", 2.0)
+    h.set_input("F_solid", F)
+    h.set_strong_bc(clamp)
+    o = RMShellOracle(nf, qf, False, False, 6)
+    o.set_inputs(thickness=thick(nf.T), E=np.full(nn, 1e6), nu=np.full(nn, 0.3), density=np.full(nn, 2.0), F_solid=F)
+    o.set_strong_bc(clamp)
+    w = o.solve_state()
+    it, rr = h.solve_state(rtol=1e-11)
+    assert rr <= 1e-11 and it <= 150
+    assert rel(h.fine.get_state(), w) <= 1e-8
+    # block-Jacobi PCG on the same level needs far more iterations
+    h.fine._mg = None
+    itj, _ = h.fine.solve_state(rtol=1e-11)
+    h.fine._mg = h
+    assert itj > 5 * it
+    rhs = rng.standard_normal(o.topo.ndof)
+    lam = h.solve_adjoint(rhs, rtol=1e-11)
+    assert rel(lam, o.solve_adjoint(rhs)) <= 1e-8
+    # inputs change -> the preconditioner is rebuilt on the next solve
+    h.set_input("thickness", lambda x: 1.3 * thick(x))
+    o.set_inputs(thickness=1.3 * thick(nf.T))
+    w2 = o.solve_state()
+    h.solve_state(rtol=1e-11)
+    assert rel(h.fine.get_state(), w2) <= 1e-8
+    h.close()
+
+
+def test_mg_junction_mesh(built_lib):
+    """Non-manifold hierarchy: plate with a wall along one edge line, clamped at x = 0."""
+    from femo_alpha_b200.multigrid import ShellHierarchy
+    from oracle.rm_shell_ref import RMShellOracle, plate_mesh
+    base, quads = plate_mesh(4, 3, 2.0, 1.5)
+    n2, q2 = plate_mesh(4, 2, 2.0, 1.0)
+    wall = np.stack([n2[:, 0], np.zeros(len(n2)), n2[:, 1]], 1)
+    on_line = np.isclose(wall[:, 2], 0.0)
+    remap = np.full(len(wall), -1)
+    for i in np.nonzero(on_line)[0]:
+        remap[i] = int(np.nonzero(np.isclose(base[:, 0], wall[i, 0]) & np.isclose(base[:, 1], 0.0))[0][0])
+    new = np.nonzero(~on_line)[0]
+    remap[new] = len(base) + np.arange(new.size)
+    nodes = np.concatenate([base, wall[new]])
+    quads = np.concatenate([quads, remap[q2]])
+    clamp = lambda x: np.less(x[0], 3e-16)
+    h = ShellHierarchy(nodes, quads, 3)
+    nf, qf = h.meshes[0]
+    nn = nf.shape[0]
+    for k, v in (("thickness", 0.04), ("E", 2e6), ("nu", 0.25), ("density", 1.0)):
+        h.set_input(k, v)
+    F = np.tile([0.3, -0.2, 1.0], nn)
+    h.set_input("F_solid", F)
+    h.set_strong_bc(clamp)
+    o = RMShellOracle(nf, qf, False, False, 6)
+    o.set_inputs(thickness=np.full(nn, 0.04), E=np.full(nn, 2e6), nu=np.full(nn, 0.25), density=np.full(nn, 1.0), F_solid=F)
+    o.set_strong_bc(clamp)
+    w = o.solve_state()
+    it, rr = h.solve_state(rtol=1e-11)
+    assert rr <= 1e-11 and it <= 300
+    assert rel(h.fine.get_state(), w) <= 1e-8
+    h.close()
+
+
+def test_operator_surface_uses_multigrid(built_lib):
+    """RMShellPDE on a mesh from refine_uniform attaches the hierarchy: FEA-level solves go through the V-cycle PCG and
+    give the same state / adjoint as the block-Jacobi path."""
+    from femo_alpha_b200.mesh import createRectangleMesh, refine_uniform
+    from femo_alpha_b200.rm_shell.rm_shell_pde import RMShellPDE
+    coarse = createRectangleMesh((0.0, 0.0), (10.0, 2.0), 10, 2)
+    mesh = refine_uniform(coarse, 2)
+    assert len(mesh.mg_meshes) == 3 and mesh.cells.shape[0] == 320
+    pde = RMShellPDE(mesh)
+    d = pde.device
+    assert pde.hierarchy is not None and d._mg is pde.hierarchy
+    nn = d.nn
+    for k, v in (("thickness", np.full(nn, 0.1)), ("E", np.full(nn, 1e8)), ("nu", np.full(nn, 0.3)),
+                 ("density", np.full(nn, 10.0)), ("F_solid", np.tile([0.0, 0.0, 5.0], nn))):
+        d.set_input(k, v)
+    on = d.block_coords()[:, 0] < 3e-16
+    blocks = np.nonzero(on)[0]
+    d.set_strong_bc(np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel()))
+    it, rr = d.solve_state(rtol=1e-11)
+    u_mg = d.get_state().copy()
+    rhs = d.output_grad("compliance", "disp_solid")
+    lam_mg = d.solve_adjoint(rhs, rtol=1e-11)
+    assert it <= 150 and d.last_solve["iters"] <= 150
+    d._mg = None
+    itj, _ = d.solve_state(rtol=1e-11)
+    assert itj > 5 * it
+    assert rel(u_mg, d.get_state()) <= 1e-8
+    assert rel(lam_mg, d.solve_adjoint(rhs, rtol=1e-11)) <= 1e-8
+    tip = np.abs(u_mg.reshape(-1, 3)[:nn, 2]).max()
+    assert abs(tip - 0.75) < 0.02                     # Euler-Bernoulli tip deflection, ex_simple_shell_opt.py:100-105
+    d._mg = pde.hierarchy
+    pde.hierarchy.close()

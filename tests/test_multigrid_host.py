@@ -1,0 +1,68 @@
+"""Host side of the multigrid hierarchy (femo_alpha_b200/multigrid.py): subdivision and the nested Q2xQ1 prolongation,
+checked on the CPU with the oracle's dofmap (the device numbers block nodes the same way, tests/test_gpu_parity.py)."""
+import numpy as np
+
+from femo_alpha_b200.multigrid import prolongation, refine_quads
+from oracle.rm_shell_ref import ShellTopology, plate_mesh
+
+
+def _levels(nodes, quads):
+    nf, qf = refine_quads(nodes, quads)
+    return ShellTopology(nodes, quads), ShellTopology(nf, qf), nf, qf
+
+
+def test_refine_counts_and_geometry():
+    nodes, quads = plate_mesh(3, 2, 3.0, 2.0)
+    tc, tf, nf, qf = _levels(nodes, quads)
+    assert qf.shape == (4 * 6, 4) and nf.shape[0] == tc.nn + tc.ne + tc.nc
+    assert np.allclose(nf[:tc.nn], nodes)                       # parent vertices keep their numbers
+    # children tile the parent: areas add up, orientation (z normal) preserved
+    def area(n, q):
+        a, b, c, d = n[q[:, 0]], n[q[:, 1]], n[q[:, 2]], n[q[:, 3]]
+        return 0.5 * np.cross(c - a, d - b)[:, 2]
+    assert np.all(area(nf, qf) > 0) and np.isclose(area(nf, qf).sum(), area(nodes, quads).sum())
+    assert np.allclose(area(nf, qf).reshape(6, 4).sum(1), area(nodes, quads))
+
+
+def test_prolongation_reproduces_polynomials_on_affine_mesh():
+    nodes, quads = plate_mesh(4, 3, 2.0, 1.5)
+    S = np.array([[1.0, 0.3, 0.0], [0.1, 0.9, 0.0], [0.2, -0.1, 1.0]])   # affine map: parallelograms out of plane
+    nodes = nodes @ S.T
+    tc, tf, nf, qf = _levels(nodes, quads)
+    P = prolongation(tf.cell_blocks, tc.cell_blocks, tf.nb, tc.nb)
+    xc, xf = tc.block_coords(), tf.block_coords()
+    quad = lambda x: 1.0 + 2.0 * x[:, 0] - x[:, 1] + 0.5 * x[:, 0] * x[:, 1] + 0.3 * x[:, 0] ** 2 - 0.7 * x[:, 1] ** 2
+    lin = lambda x: 0.5 - x[:, 0] + 2.0 * x[:, 1] + 0.4 * x[:, 2]
+    f_c = np.where(np.arange(tc.nb) < tc.nq2, quad(xc), lin(xc))          # Q2 block nodes: quadratic, Q1: linear
+    f_f = np.where(np.arange(tf.nb) < tf.nq2, quad(xf), lin(xf))
+    assert np.abs(P @ f_c - f_f).max() <= 1e-12
+    # Q2 rows only touch coarse Q2 nodes, Q1 rows only coarse Q1 nodes
+    Pc = P.tocoo()
+    assert np.all((Pc.row < tf.nq2) == (Pc.col < tc.nq2))
+
+
+def test_prolongation_partition_of_unity_on_skew_and_junction_meshes():
+    rng = np.random.default_rng(3)
+    nodes, quads = plate_mesh(5, 4, 2.0, 1.5)
+    nodes[:, :2] += 0.05 * rng.standard_normal((nodes.shape[0], 2))
+    # T-junction: a wall attached along y = 0 (three cells share each edge of that line)
+    n2, q2 = plate_mesh(5, 2, 2.0, 1.0)
+    base = plate_mesh(5, 4, 2.0, 1.5)[0]
+    wall = np.stack([n2[:, 0], np.zeros(len(n2)), n2[:, 1]], 1)
+    on_line = np.isclose(wall[:, 2], 0.0)
+    remap = np.full(len(wall), -1)
+    for i in np.nonzero(on_line)[0]:
+        remap[i] = int(np.nonzero(np.isclose(base[:, 0], wall[i, 0]) & np.isclose(base[:, 1], 0.0))[0][0])
+    new = np.nonzero(~on_line)[0]
+    remap[new] = len(nodes) + np.arange(new.size)
+    nodes = np.concatenate([nodes, wall[new]])
+    quads = np.concatenate([quads, remap[q2]])
+    tc, tf, nf, qf = _levels(nodes, quads)
+    P = prolongation(tf.cell_blocks, tc.cell_blocks, tf.nb, tc.nb)
+    assert np.abs(np.asarray(P.sum(axis=1)).ravel() - 1.0).max() <= 1e-13
+    # coarse vertices are fine vertices: injection rows
+    sub = P[:tc.nn].tocsr()
+    assert sub.nnz == tc.nn and np.allclose(sub.diagonal(), 1.0)
+    # nested geometry: coordinates are reproduced at the fine Q1 / vertex nodes (bilinear map)
+    xc, xf = tc.block_coords(), tf.block_coords()
+    assert np.abs((P @ xc)[tf.nq2:] - xf[tf.nq2:]).max() <= 1e-13
