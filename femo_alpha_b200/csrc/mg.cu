@@ -343,7 +343,7 @@ int femo_mg_set_transfer(femo_mg* m, int l, const int32_t* P_ptr, const int32_t*
 
 // (re)build the preconditioner from the levels' current inputs: assemble every level, block-Jacobi inverses,
 // spectral bounds, dense inverse of the coarsest operator
-int femo_mg_setup(femo_mg* m, int cheb_degree) {
+int femo_mg_setup(femo_mg* m, int cheb_degree, int reuse_coarse_inverse) {
   if (!m) return femo_fail("null multigrid handle");
   cudaSetDevice(m->L[0].c->device);
   m->deg = cheb_degree > 0 ? cheb_degree : 3;
@@ -367,7 +367,8 @@ int femo_mg_setup(femo_mg* m, int cheb_degree) {
     if (l + 1 < m->L.size()) TRY(mg_lambda_max(m, (int)l));
   }
   cudaEventRecord(e2, st);
-  TRY(mg_coarse_inverse(m));
+  // a lagged coarse inverse (from the previous inputs) is still SPD: a valid, slightly weaker preconditioner
+  if (!(reuse_coarse_inverse && m->Cinv && m->ncoarse == m->L.back().c->ndof)) TRY(mg_coarse_inverse(m));
   cudaEventRecord(e3, st);
   cudaEventSynchronize(e3);
   if (verbose) {

@@ -121,7 +121,7 @@ class ShellHierarchy:
     """Levels 0 (finest, the analysis mesh) .. levels-1 (the mesh handed in), each a ShellDevice on one GPU."""
 
     def __init__(self, coarse_nodes, coarse_quads, levels, element_wise_material=False, elementwise_pressure=False,
-                 quadrature_degree=6, device=0, cheb_degree=3, meshes=None, fine_device=None):
+                 quadrature_degree=6, device=0, cheb_degree=3, meshes=None, fine_device=None, coarse_refresh=1):
         if element_wise_material or elementwise_pressure:
             raise ValueError("ShellHierarchy: nodal (CG1) inputs only; cell-wise inputs have no canonical coarse sampling")
         if meshes is None:
@@ -139,6 +139,10 @@ class ShellHierarchy:
         self.fine = self.levels[0]
         self.fine._mg = self
         self.cheb_degree = int(cheb_degree)
+        # the dense coarse inverse is recomputed at every `coarse_refresh`-th set-up (1 = always); in between the
+        # previous one is reused (lagged coarse solve)
+        self.coarse_refresh = max(1, int(coarse_refresh))
+        self._n_setups = 0
         self.lib = L.load()
         arr = (C.c_void_p * levels)(*[d._ctx for d in self.levels])
         self._mg = C.c_void_p()
@@ -204,8 +208,11 @@ class ShellHierarchy:
             c.set_strong_bc(dofs)
         self._dirty = True
 
-    def setup(self):
-        L.check(self.lib.femo_mg_setup(self._mg, self.cheb_degree))
+    def setup(self, reuse_coarse=None):
+        if reuse_coarse is None:
+            reuse_coarse = self._n_setups % self.coarse_refresh != 0
+        L.check(self.lib.femo_mg_setup(self._mg, self.cheb_degree, int(bool(reuse_coarse))))
+        self._n_setups += 1
         self._dirty = False
 
     def lambda_max(self, level):

@@ -183,8 +183,10 @@ int femo_mg_destroy(femo_mg* mg);
 int femo_mg_set_transfer(femo_mg* mg, int level, const int32_t* P_rowptr, const int32_t* P_col, const double* P_w,
                          const int32_t* R_rowptr, const int32_t* R_col, const double* R_w);
 /* (re)build after the inputs changed: assembles every level, block-Jacobi inverses, spectral bounds of the
- * Chebyshev smoother (degree cheb_degree, default 3), dense inverse of the coarsest operator */
-int femo_mg_setup(femo_mg* mg, int cheb_degree);
+ * Chebyshev smoother (degree cheb_degree, default 3), dense inverse of the coarsest operator.
+ * reuse_coarse_inverse != 0 keeps the coarse inverse of the previous set-up (lagged: still SPD, cheaper set-up
+ * inside an optimisation loop with small steps, a few more iterations) */
+int femo_mg_setup(femo_mg* mg, int cheb_degree, int reuse_coarse_inverse);
 int femo_mg_get_lambda(femo_mg* mg, int level, double* lambda_max);
 /* PCG with one V-cycle per iteration on A x = rhs (A = dR/du with BCs, x0 = 0); zero_bc as femo_solve_adjoint */
 int femo_mg_solve(femo_mg* mg, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
