@@ -122,8 +122,7 @@ class ShellHierarchy:
 
     def __init__(self, coarse_nodes, coarse_quads, levels, element_wise_material=False, elementwise_pressure=False,
                  quadrature_degree=6, device=0, cheb_degree=3, meshes=None, fine_device=None, coarse_refresh=1):
-        if element_wise_material or elementwise_pressure:
-            raise ValueError("ShellHierarchy: nodal (CG1) inputs only; cell-wise inputs have no canonical coarse sampling")
+        self.ewm, self.ewp = bool(element_wise_material), bool(elementwise_pressure)
         if meshes is None:
             meshes = [(np.asarray(coarse_nodes, dtype=np.float64), np.asarray(coarse_quads, dtype=np.int32))]
             for _ in range(levels - 1):
@@ -135,7 +134,7 @@ class ShellHierarchy:
         meshes = meshes[::-1]                                  # level 0 = finest
         self.meshes = meshes
         self.levels = [fine_device if (l == 0 and fine_device is not None) else
-                       ShellDevice(n, q, False, False, quadrature_degree, device) for l, (n, q) in enumerate(meshes)]
+                       ShellDevice(n, q, self.ewm, self.ewp, quadrature_degree, device) for l, (n, q) in enumerate(meshes)]
         self.fine = self.levels[0]
         self.fine._mg = self
         self.cheb_degree = int(cheb_degree)
@@ -160,34 +159,47 @@ class ShellHierarchy:
         self.last_solve = dict(iters=0, relres=0.0)
 
     @classmethod
-    def for_device(cls, fine_device, mesh_chain, quadrature_degree=6, device=0, cheb_degree=3):
+    def for_device(cls, fine_device, mesh_chain, quadrature_degree=6, device=0, cheb_degree=3,
+                   element_wise_material=False, elementwise_pressure=False):
         """Hierarchy under an existing finest-level device; `mesh_chain` = [(nodes, quads), ...] coarse to fine as
         recorded by femo_alpha_b200.mesh.refine_uniform."""
-        return cls(None, None, len(mesh_chain), quadrature_degree=quadrature_degree, device=device, cheb_degree=cheb_degree,
-                   meshes=mesh_chain, fine_device=fine_device)
+        return cls(None, None, len(mesh_chain), element_wise_material, elementwise_pressure, quadrature_degree, device,
+                   cheb_degree, meshes=mesh_chain, fine_device=fine_device)
 
     def set_input(self, name, values):
         """`values`: callable of the vertex coordinates x (3, n) returning (n,) or (n, 3), a scalar, or the finest
         level's array.  The finest device forwards it to the coarser levels (ShellDevice.set_input)."""
-        nodes = self.meshes[0][0]
-        nn = nodes.shape[0]
+        nodes, quads = self.meshes[0]
+        cellwise = self._cellwise(name)
+        n = quads.shape[0] if cellwise else nodes.shape[0]
         if callable(values):
-            v = np.asarray(values(nodes.T), dtype=np.float64)
+            x = nodes[quads].mean(axis=1) if cellwise else nodes
+            v = np.asarray(values(x.T), dtype=np.float64)
         else:
             v = np.asarray(values, dtype=np.float64)
             if v.size == 1:
-                v = np.full(nn, float(v))
-        if name in ("F_solid", "uhat") and v.size == nn:
-            raise ValueError(name + " needs 3 components per vertex")
+                v = np.full(n, float(v))
+        if name in ("F_solid", "uhat") and v.size == n:
+            raise ValueError(name + " needs 3 components per entry")
         self.fine.set_input(name, np.ascontiguousarray(v).ravel())
 
-    # the parent's vertices keep their numbers under refine_quads: a nodal array of the finest level restricts by slicing
+    def _cellwise(self, name):
+        return (self.ewm and name in ("thickness", "E", "nu", "density")) or (self.ewp and name == "F_solid")
+
+    # the parent's vertices keep their numbers under refine_quads: a nodal array of the finest level restricts by slicing;
+    # cell-wise arrays (children 4 c .. 4 c + 3 of cell c) restrict by averaging
     def _coarse_inputs(self, name, values):
         if hasattr(values, "detach"):
             values = values.detach().cpu().numpy()
-        v = np.asarray(values, dtype=np.float64).reshape(self.meshes[0][0].shape[0], -1)
-        for lvl, (nodes, _) in zip(self.levels[1:], self.meshes[1:]):
-            lvl.set_input(name, np.ascontiguousarray(v[:nodes.shape[0]]).ravel())
+        if self._cellwise(name):
+            v = np.asarray(values, dtype=np.float64).reshape(self.meshes[0][1].shape[0], -1)
+            for lvl in self.levels[1:]:
+                v = v.reshape(v.shape[0] // 4, 4, -1).mean(axis=1)
+                lvl.set_input(name, np.ascontiguousarray(v).ravel())
+        else:
+            v = np.asarray(values, dtype=np.float64).reshape(self.meshes[0][0].shape[0], -1)
+            for lvl, (nodes, _) in zip(self.levels[1:], self.meshes[1:]):
+                lvl.set_input(name, np.ascontiguousarray(v[:nodes.shape[0]]).ravel())
         self._dirty = True
 
     def set_strong_bc(self, predicate):

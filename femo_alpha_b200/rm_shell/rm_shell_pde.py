@@ -40,12 +40,13 @@ class RMShellPDE:
         # a mesh produced by refine_uniform remembers its parents: nested hierarchy -> multigrid-preconditioned solves
         self.hierarchy = None
         chain = getattr(mesh, "mg_meshes", None)
-        if chain and len(chain) >= 2 and not element_wise_material and not elementwise_pressure \
-                and os.environ.get("FEMO_MG", "1") != "0":
+        if chain and len(chain) >= 2 and os.environ.get("FEMO_MG", "1") != "0":
             n_coarse = 3 * (2 * chain[0][0].shape[0] + 3 * chain[0][1].shape[0])      # upper bound of the coarsest dof count
             if n_coarse <= 46000:
                 from ..multigrid import ShellHierarchy
-                self.hierarchy = ShellHierarchy.for_device(dev, chain, quadrature_degree, device)
+                self.hierarchy = ShellHierarchy.for_device(dev, chain, quadrature_degree, device,
+                                                           element_wise_material=element_wise_material,
+                                                           elementwise_pressure=elementwise_pressure)
         nn, nc = dev.nn, dev.nc
         self.W = FunctionSpace(mesh, "W", dev.ndof, dev, "CG2CG1")
         self.VT = FunctionSpace(mesh, "VT", nc if element_wise_material else nn, dev,

@@ -116,3 +116,37 @@ def test_operator_surface_uses_multigrid(built_lib):
     assert abs(tip - 0.75) < 0.02                     # Euler-Bernoulli tip deflection, ex_simple_shell_opt.py:100-105
     d._mg = pde.hierarchy
     pde.hierarchy.close()
+
+
+def test_mg_refined_wingbox(built_lib):
+    """BASELINE config 2, synthetically refined: the reference's wing-box mesh (warped skins, rib / spar junctions,
+    element-wise material) subdivided once; two-level V-cycle PCG against block-Jacobi PCG and the true residual."""
+    import os
+    from femo_alpha_b200.mesh import ShellMesh, refine_uniform
+    from femo_alpha_b200.rm_shell.rm_shell_pde import RMShellPDE
+    m = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "wingbox_mesh.npz"))
+    fine = refine_uniform(ShellMesh(m["nodes"], m["quads"]), 1)
+    pde = RMShellPDE(fine, element_wise_material=True)
+    d = pde.device
+    assert pde.hierarchy is not None and d.sizes.all_planar == 0 and d.nc == 4 * 2244
+    h = 0.05 * 0.0254
+    d.set_input("thickness", np.full(d.nc, h)); d.set_input("E", np.full(d.nc, 73.1e9)); d.set_input("nu", np.full(d.nc, 0.33))
+    d.set_input("density", np.full(d.nc, 2780.0))
+    d.set_input("F_solid", np.tile([0.0, 0.0, -9.81 * 2780.0 * h], d.nn))
+    on = d.block_coords()[:, 1] <= 1e-3
+    blocks = np.nonzero(on)[0]
+    d.set_strong_bc(np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel()))
+    it, rr = d.solve_state(rtol=1e-12)
+    u = d.get_state().copy()
+    F = d.assemble_load()
+    free = np.ones(d.ndof, bool); free[np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel())] = False
+    res = (d.jacobian_apply(u, with_bc=True) - F)[free]
+    print("wing box x4: %d dof, %d V-cycle PCG iterations, relres %.1e, true residual %.1e" %
+          (d.ndof, it, rr, np.linalg.norm(res) / np.linalg.norm(F[free])))
+    assert it <= 1000 and np.linalg.norm(res) <= 1e-8 * np.linalg.norm(F[free])
+    d._mg = None
+    itj, rrj = d.solve_state(rtol=1e-12, max_it=400000)
+    print("block-Jacobi PCG: %d iterations, relres %.1e" % (itj, rrj))
+    assert rel(u, d.get_state()) <= 1e-5 and itj > 4 * it
+    d._mg = pde.hierarchy
+    pde.hierarchy.close()
