@@ -1,4 +1,5 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 900 python scripts/mg_wingbox.py > gpurun_out/mg_wingbox.log 2>&1; echo "rc=$?"; tail -n 20 gpurun_out/mg_wingbox.log
+T=${TAG:-r01f}
+timeout 1200 python -m pytest tests -m gpu -q > gpurun_out/${T}_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -n 8 gpurun_out/${T}_pytest_gpu.log
