@@ -76,6 +76,15 @@ __global__ void k_mask_clear(double* mask, const int32_t* dofs, int64_t n) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) mask[dofs[i]] = 0.0;
 }
+__global__ void k_bc_bits(const double* __restrict__ mask, int64_t nb, uint8_t* __restrict__ bits) {
+  int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (b < nb) bits[b] = (uint8_t)((mask[3 * b] == 0.0 ? 1 : 0) | (mask[3 * b + 1] == 0.0 ? 2 : 0) | (mask[3 * b + 2] == 0.0 ? 4 : 0));
+}
+__global__ void k_col_bc(const int32_t* __restrict__ colidx, const uint8_t* __restrict__ bits, int64_t nnzb,
+                         uint32_t* __restrict__ colbc) {
+  int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k < nnzb) { const uint32_t col = (uint32_t)colidx[k]; colbc[k] = col | ((uint32_t)bits[col] << 29); }
+}
 __global__ void k_mul(const double* a, const double* m, int64_t n, double* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) out[i] = a[i] * m[i];
@@ -183,7 +192,7 @@ int femo_ctx_destroy(femo_ctx* c) {
   tile_plan_free(c);
   void* ptrs[] = {c->xyz, c->cv, c->ce, c->edges, c->cell_blocks, c->hE, c->tab, c->h, c->E, c->nu, c->rho, c->f, c->uhat,
                   c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
-                  c->nc_adj, c->rec, c->bcmask, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
+                  c->nc_adj, c->rec, c->bcmask, c->bcbits, c->colbc, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
                   c->pen_val, c->pen_dest_col, c->tab4, c->cell_tags, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
                   c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf, c->it_pack, c->it_dest, c->chunk_ptr, c->halo_ptr,
                   c->halo_cells, c->tpos};
@@ -248,6 +257,11 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   if (!c->tile_ok) TRY(dev_alloc(&c->rec, (size_t)c->nc * c->rec_stride));
   const int64_t n = c->ndof;
   TRY(dev_alloc(&c->bcmask, n)); TRY(fill(c, c->bcmask, n, 1.0));
+  TRY(dev_alloc(&c->bcbits, (size_t)c->nb)); CUDA_TRY(cudaMemsetAsync(c->bcbits, 0, (size_t)c->nb, c->stream));
+  if (c->nb >= (int64_t)1 << 29) return femo_fail("femo_shell_setup: more than 2^29 block nodes");
+  TRY(dev_alloc(&c->colbc, (size_t)c->nnzb));
+  k_col_bc<<<(unsigned)cdiv(c->nnzb, 256), 256, 0, c->stream>>>(c->colidx, c->bcbits, c->nnzb, c->colbc);
+  TRY(check_launch(c, "k_col_bc"));
   c->n_bc = 0;
   double** vecs[] = {&c->w, &c->b, &c->r, &c->z, &c->p, &c->Ap, &c->tmp, &c->tmp2};
   for (double** v : vecs) { TRY(dev_alloc(v, n)); CUDA_TRY(cudaMemsetAsync(*v, 0, sizeof(double) * n, c->stream)); }
@@ -304,6 +318,11 @@ int femo_set_strong_bc(femo_ctx* c, int64_t n, const int32_t* dofs) {
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     dev_free(&d);
   }
+  k_bc_bits<<<(unsigned)cdiv(c->nb, 256), 256, 0, c->stream>>>(c->bcmask, c->nb, c->bcbits);
+  TRY(check_launch(c, "k_bc_bits"));
+  k_col_bc<<<(unsigned)cdiv(c->nnzb, 256), 256, 0, c->stream>>>(c->colidx, c->bcbits, c->nnzb, c->colbc);
+  TRY(check_launch(c, "k_col_bc"));
+  c->launches += 2;
   c->prec_valid = false;
   return 0;
 }

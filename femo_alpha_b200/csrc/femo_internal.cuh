@@ -126,6 +126,8 @@ struct femo_ctx {
   int rec_nqf = 0, rec_stride = 0;
   // boundary conditions
   double* bcmask = nullptr;     // ndof: 1 free, 0 clamped
+  uint8_t* bcbits = nullptr;    // nb: bit d set = dof 3 b + d clamped (same information, 1 byte per block node)
+  uint32_t* colbc = nullptr;    // nnzb: colidx | bcbits[colidx] << 29 (SpMV reads column and clamp flags in one word)
   int64_t n_bc = 0;
   // penalty (edge, cell) adjacencies
   int64_t n_pen = 0;            // number of (edge,cell) pairs

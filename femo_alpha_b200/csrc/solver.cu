@@ -57,12 +57,16 @@ __device__ __forceinline__ double sum_partials(const double* __restrict__ part, 
   return r;
 }
 
-// y = K x (with_bc = 0) or y = A x (with_bc = 1).  LANES lanes cooperate on one block row.
+// Column words: low 29 bits = block column, top 3 bits = clamp flags of its dofs (femo_ctx::colbc); with plain
+// colidx (K x, no BC) the flags are 0.  `rbits` (per block row clamp flags) is null for K x.
+#define COL_OF(w) ((int64_t)((w) & 0x1fffffffu))
+
+// y = K x or y = A x.  LANES lanes cooperate on one block row, one block per lane and pass.
 // Optionally accumulates the partial dot x.y per CTA (deterministic) into dot_part[blockIdx.x].
-template <int LANES>
-__global__ void __launch_bounds__(256)
-k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const double* __restrict__ vals,
-       const double* __restrict__ x, const double* __restrict__ mask, int64_t nb, double* __restrict__ y,
+template <int LANES, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+k_spmv(const int32_t* __restrict__ rowptr, const uint32_t* __restrict__ colw, const double* __restrict__ vals,
+       const double* __restrict__ x, const uint8_t* __restrict__ rbits, int64_t nb, double* __restrict__ y,
        double* __restrict__ dot_part, const double* __restrict__ own) {
   const int lane = threadIdx.x % LANES;
   constexpr int GPW = 32 / LANES;                       // row groups per warp
@@ -77,10 +81,13 @@ k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, c
     const int32_t s = valid ? rowptr[row] : 0, e = valid ? rowptr[row + 1] : 0;
     double y0 = 0, y1 = 0, y2 = 0;
     for (int32_t k = s + lane; k < e; k += LANES) {
-      const int64_t col = colidx[k];
-      const double* a = vals + (int64_t)k * 9;
-      double x0 = x[3 * col], x1 = x[3 * col + 1], x2 = x[3 * col + 2];
-      if (mask) { x0 *= mask[3 * col]; x1 *= mask[3 * col + 1]; x2 *= mask[3 * col + 2]; }
+      const uint32_t w = colw[k];
+      const double* ap = vals + (int64_t)k * 9;
+      double a[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) a[i] = ap[i];
+      const double* xp = x + 3 * COL_OF(w);
+      const double x0 = (w & 0x20000000u) ? 0.0 : xp[0], x1 = (w & 0x40000000u) ? 0.0 : xp[1], x2 = (w & 0x80000000u) ? 0.0 : xp[2];
       y0 += a[0] * x0 + a[1] * x1 + a[2] * x2;
       y1 += a[3] * x0 + a[4] * x1 + a[5] * x2;
       y2 += a[6] * x0 + a[7] * x1 + a[8] * x2;
@@ -92,10 +99,12 @@ k_spmv(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, c
       y2 += __shfl_down_sync(0xffffffffu, y2, o, LANES);
     }
     if (lane == 0 && valid) {
-      double xr0 = x[3 * row], xr1 = x[3 * row + 1], xr2 = x[3 * row + 2];
-      if (mask) {
-        double m0 = mask[3 * row], m1 = mask[3 * row + 1], m2 = mask[3 * row + 2];
-        y0 = m0 * y0 + (1.0 - m0) * xr0; y1 = m1 * y1 + (1.0 - m1) * xr1; y2 = m2 * y2 + (1.0 - m2) * xr2;
+      const double xr0 = x[3 * row], xr1 = x[3 * row + 1], xr2 = x[3 * row + 2];
+      if (rbits) {
+        const unsigned b = rbits[row];
+        if (b & 1u) y0 = xr0;
+        if (b & 2u) y1 = xr1;
+        if (b & 4u) y2 = xr2;
       }
       y[3 * row] = y0; y[3 * row + 1] = y1; y[3 * row + 2] = y2;
       const double ow = own ? own[row] : 1.0;
@@ -334,12 +343,21 @@ __global__ void k_copy(const double4* __restrict__ a, double4* __restrict__ b, i
 
 }  // namespace
 
-#define SPMV_BLOCKS (148 * 8)
-
+#define SPMV_BLOCKS (148 * 8)   /* stride of the partial arrays in `red` (>= spmv_grid(), RED_BLOCKS) */
+// 8 lanes per block row, 6 CTAs of 256 threads per SM in one wave (40 registers).  Measured at cfg 3 (ncu, one launch):
+// 16 lanes + fp64 mask gathers 1.76 ms -> packed column/flag words, single wave 1.38 ms -> 8 lanes ~1.2 ms;
+// a 27-lane coalesced layout (2.27 ms) and a cp.async-staged pipeline (2.3 - 3.1 ms) lose to the memory-level
+// parallelism of one block (12 independent loads) per lane.
+static int spmv_grid() { return 148 * 6; }
+static int launch_spmv(femo_ctx* c, const double* x, bool with_bc, double* y, double* dot_part, const double* own) {
+  const uint32_t* colw = with_bc ? c->colbc : reinterpret_cast<const uint32_t*>(c->colidx);
+  const uint8_t* rbits = with_bc ? c->bcbits : nullptr;
+  k_spmv<8, 6><<<spmv_grid(), 256, 0, c->stream>>>(c->rowptr, colw, c->vals, x, rbits, c->nb, y, dot_part, own);
+  return 0;
+}
 int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc) {
   if (!c->jac_valid) return femo_fail("Jacobian not assembled");
-  k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, x, with_bc ? c->bcmask : nullptr, c->nb, y,
-                                                 nullptr, nullptr);
+  TRY(launch_spmv(c, x, with_bc != 0, y, nullptr, nullptr));
   TRY(check_launch(c, "k_spmv"));
   c->launches += 1;
   return 0;
@@ -399,7 +417,7 @@ int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, 
   cudaEventRecord(c->ev0, c->stream);
   // r0 = b - A x0
   if (dist) TRY(halo_exchange(c, x));
-  k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, x, c->bcmask, c->nb, c->Ap, nullptr, nullptr);
+  TRY(launch_spmv(c, x, true, c->Ap, nullptr, nullptr));
   k_pcg_init<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(b, c->Ap, c->dinv6, c->dinv3, c->nn, c->nq2, c->r, c->z, c->p,
                                                         P_rz[0], P_rr, P_bb, c->own);
   if (dist) {
@@ -436,8 +454,8 @@ int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, 
       int cur = it & 1, nxt = cur ^ 1;
       if (dist) {
         TRY(halo_exchange(c, c->p));
-        k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->p, c->bcmask, c->nb, c->Ap, P_pAp, c->own);
-        k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_pAp, SPMV_BLOCKS, c->scal + 2);
+        TRY(launch_spmv(c, c->p, true, c->Ap, P_pAp, c->own));
+        k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(P_pAp, spmv_grid(), c->scal + 2);
         TRY(dist_allreduce_sum(c, c->scal + 2, 1));
         k_pcg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(c->scal + 2, 1, S_pair[cur], 1, c->own, c->p, c->Ap, c->dinv6,
                                                                 c->dinv3, c->nn, c->nq2, x, c->r, c->z, P_rz[nxt], P_rr);
@@ -447,8 +465,8 @@ int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, 
                                                              c->scal + 1);
         c->launches += 2;
       } else {
-        k_spmv<16><<<SPMV_BLOCKS, 256, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->p, c->bcmask, c->nb, c->Ap, P_pAp, nullptr);
-        k_pcg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_pAp, SPMV_BLOCKS, P_rz[cur], RED_BLOCKS, nullptr, c->p, c->Ap,
+        TRY(launch_spmv(c, c->p, true, c->Ap, P_pAp, nullptr));
+        k_pcg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_pAp, spmv_grid(), P_rz[cur], RED_BLOCKS, nullptr, c->p, c->Ap,
                                                                 c->dinv6, c->dinv3, c->nn, c->nq2, x, c->r, c->z, P_rz[nxt], P_rr);
         k_pcg_dir<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(P_rz[nxt], P_rz[cur], P_rr, RED_BLOCKS, c->z, n, c->p, c->scal + 1);
       }
