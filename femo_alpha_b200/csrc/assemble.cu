@@ -555,33 +555,53 @@ __global__ void k_penalty_add(const int32_t* __restrict__ dest_pos, const int32_
 
 // ------------------------------------------------------------------------------------------
 // load vector: F_I = sum_{cells containing Q2 node I} sum_q w detJ J phi2_a f(q)   (model:320)
-__global__ void k_load(const double* __restrict__ xyz, const int32_t* __restrict__ cv,
-                       const double* __restrict__ uhat, const double* __restrict__ f,
-                       const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
-                       const Tables* __restrict__ tab, int nq, int ewp, int64_t nq2, double* __restrict__ F) {
-  int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (I >= nq2) return;
-  V3 acc = v3(0, 0, 0);
-  for (int32_t k = nc_ptr[I]; k < nc_ptr[I + 1]; ++k) {
-    int32_t e = nc_adj[k];
-    int64_t cell = e / 13; int a = e - (int32_t)cell * 13;
-    V3 xv[4], uh[4], fv[4];
-    for (int v = 0; v < 4; ++v) {
-      int32_t id = cv[cell * 4 + v];
-      xv[v] = ldv3(xyz + 3 * (int64_t)id);
-      if (uhat) uh[v] = ldv3(uhat + 3 * (int64_t)id);
-      if (!ewp) fv[v] = ldv3(f + 3 * (int64_t)id);
-    }
-    V3 fc = ewp ? ldv3(f + 3 * cell) : v3(0, 0, 0);
-    for (int q = 0; q < nq; ++q) {
-      QpGeom g;
-      qp_geometry(xv, uhat ? uh : nullptr, tab->X0[q], tab->X1[q], g);
-      V3 fq = fc;
-      if (!ewp) fq = tab->n1[q][0] * fv[0] + tab->n1[q][1] * fv[1] + tab->n1[q][2] * fv[2] + tab->n1[q][3] * fv[3];
-      acc = acc + (tab->W[q] * g.detJ * g.Ju * tab->phi2[q][a]) * fq;
-    }
+// Two passes, both deterministic: one thread per cell integrates its 9 nodal contributions (27 doubles into
+// `cellbuf`, stride 39), then one thread per Q2 node sums its <= 4 (more at junctions) cells in ascending order.
+__global__ void __launch_bounds__(128)
+k_load_cells(const double* __restrict__ xyz, const int32_t* __restrict__ cv, const double* __restrict__ uhat,
+             const double* __restrict__ f, const Tables* __restrict__ tab, int nq, int ewp, int64_t nc,
+             double* __restrict__ cellbuf) {
+  const int64_t cell = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (cell >= nc) return;
+  V3 xv[4], uh[4], fv[4];
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    const int32_t id = cv[cell * 4 + v];
+    xv[v] = ldv3(xyz + 3 * (int64_t)id);
+    if (uhat) uh[v] = ldv3(uhat + 3 * (int64_t)id);
+    if (!ewp) fv[v] = ldv3(f + 3 * (int64_t)id);
   }
-  F[3 * I] = acc.x; F[3 * I + 1] = acc.y; F[3 * I + 2] = acc.z;
+  const V3 fc = ewp ? ldv3(f + 3 * cell) : v3(0, 0, 0);
+  V3 acc[9];
+#pragma unroll
+  for (int a = 0; a < 9; ++a) acc[a] = v3(0, 0, 0);
+  for (int q = 0; q < nq; ++q) {
+    QpGeom g;
+    qp_geometry(xv, uhat ? uh : nullptr, tab->X0[q], tab->X1[q], g);
+    V3 fq = fc;
+    if (!ewp) fq = tab->n1[q][0] * fv[0] + tab->n1[q][1] * fv[1] + tab->n1[q][2] * fv[2] + tab->n1[q][3] * fv[3];
+    const V3 sf = (tab->W[q] * g.detJ * g.Ju) * fq;
+#pragma unroll
+    for (int a = 0; a < 9; ++a) acc[a] = acc[a] + tab->phi2[q][a] * sf;
+  }
+  double* out = cellbuf + cell * 39;
+#pragma unroll
+  for (int a = 0; a < 9; ++a) { out[3 * a] = acc[a].x; out[3 * a + 1] = acc[a].y; out[3 * a + 2] = acc[a].z; }
+}
+
+__global__ void k_load_gather(const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
+                              const double* __restrict__ cellbuf, int64_t nq2, double* __restrict__ F) {
+  const int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= nq2) return;
+  double a0 = 0, a1 = 0, a2 = 0;
+  for (int32_t k = nc_ptr[I]; k < nc_ptr[I + 1]; ++k) {
+    const int32_t e = nc_adj[k];
+    const int64_t cell = e / 13;
+    const int a = e - (int32_t)cell * 13;
+    const double* s = cellbuf + cell * 39 + 3 * a;
+    a0 += s[0]; a1 += s[1]; a2 += s[2];
+  }
+  F[3 * I] = a0; F[3 * I + 1] = a1; F[3 * I + 2] = a2;
 }
 
 }  // namespace
@@ -644,9 +664,9 @@ int assemble_jacobian(femo_ctx* c) {
 int assemble_load(femo_ctx* c, double* F) {
   const double* uh = c->uhat_zero ? nullptr : c->uhat;
   CUDA_TRY(cudaMemsetAsync(F, 0, sizeof(double) * c->ndof, c->stream));
-  k_load<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(c->xyz, c->cv, uh, c->f, c->nc_ptr, c->nc_adj, c->tab, c->nq,
-                                                            c->ewp, c->nq2, F);
+  k_load_cells<<<(unsigned)cdiv(c->nc, 128), 128, 0, c->stream>>>(c->xyz, c->cv, uh, c->f, c->tab, c->nq, c->ewp, c->nc, c->cellbuf);
+  k_load_gather<<<(unsigned)cdiv(c->nq2, 256), 256, 0, c->stream>>>(c->nc_ptr, c->nc_adj, c->cellbuf, c->nq2, F);
   TRY(check_launch(c, "k_load"));
-  c->launches += 1;
+  c->launches += 2;
   return 0;
 }
