@@ -14,10 +14,11 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfemo_b200.so")
 
 THICKNESS, F_SOLID, E, NU, DENSITY, UHAT = range(6)
-COMPLIANCE, MASS, ELASTIC_ENERGY, PNORM_STRESS = range(4)
+COMPLIANCE, MASS, ELASTIC_ENERGY, PNORM_STRESS, VOLUME = range(5)
 ARG_STATE = 100
 INPUT_IDS = {"thickness": THICKNESS, "F_solid": F_SOLID, "E": E, "nu": NU, "density": DENSITY, "uhat": UHAT}
-OUTPUT_IDS = {"compliance": COMPLIANCE, "mass": MASS, "elastic_energy": ELASTIC_ENERGY, "pnorm_stress": PNORM_STRESS}
+OUTPUT_IDS = {"compliance": COMPLIANCE, "mass": MASS, "elastic_energy": ELASTIC_ENERGY, "pnorm_stress": PNORM_STRESS,
+              "volume": VOLUME}
 
 
 class ShellOpts(C.Structure):
@@ -80,6 +81,23 @@ SIGNATURES = {
     "femo_mg_setup": [_P, C.c_int, C.c_int],
     "femo_mg_get_lambda": [_P, C.c_int, _D],
     "femo_mg_solve": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int), _D, C.c_int, C.c_int],
+    "femo_dyn_create": [_P, C.c_double, C.c_int, C.c_int, C.c_double, C.POINTER(_P)],
+    "femo_dyn_destroy": [_P],
+    "femo_dyn_set_mg": [_P, _P],
+    "femo_dyn_setup": [_P, C.c_int],
+    "femo_dyn_solve": [_P, _P, C.c_int64, C.c_double, C.c_int, C.POINTER(C.c_int64), C.c_int],
+    "femo_dyn_get_history": [_P, _P, C.c_int],
+    "femo_dyn_set_history": [_P, _P, C.c_int],
+    "femo_dyn_get_energies": [_P, _P],
+    "femo_dyn_solve_adjoint": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int64), C.c_int],
+    "femo_dyn_solve_forward": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int64), C.c_int],
+    "femo_dyn_dRdw_apply": [_P, _P, _P, C.c_int, C.c_int],
+    "femo_dyn_dRdh_T_apply": [_P, _P, _P, C.c_int],
+    "femo_dyn_dRdh_apply": [_P, _P, _P, C.c_int],
+    "femo_dyn_total_strain_energy": [_P, _D],
+    "femo_dyn_total_strain_energy_grad": [_P, C.c_int, _P, C.c_int],
+    "femo_dyn_mass_apply": [_P, _P, _P, C.c_int],
+    "femo_dyn_info": [_P, _D, _D, C.POINTER(C.c_int)],
     "femo_launch_count": [_P, C.POINTER(C.c_int64)],
     "femo_last_timings": [_P, _D],
     "femo_pcg_fixed": [_P, C.c_int, _D],

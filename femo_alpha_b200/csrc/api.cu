@@ -195,7 +195,7 @@ int femo_ctx_destroy(femo_ctx* c) {
                   c->nc_adj, c->rec, c->bcmask, c->bcbits, c->colbc, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
                   c->pen_val, c->pen_dest_col, c->tab4, c->cell_tags, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
                   c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf, c->it_pack, c->it_dest, c->chunk_ptr, c->halo_ptr,
-                  c->halo_cells, c->tpos};
+                  c->halo_cells, c->tpos, c->tabm, c->vals_K, c->mvals, c->mass_me};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
@@ -240,6 +240,10 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   TRY(dev_alloc(&c->tab4, 1));
   CUDA_TRY(cudaMemcpy(c->tab4, &t4, sizeof(Tables), cudaMemcpyHostToDevice));
   c->nq4 = 9;
+  Tables tm;
+  build_tables(tm, 4);            // 4x4 rule of the mass form (dynamic.cu)
+  TRY(dev_alloc(&c->tabm, 1));
+  CUDA_TRY(cudaMemcpy(c->tabm, &tm, sizeof(Tables), cudaMemcpyHostToDevice));
   c->area_cache.clear();
   TRY(pattern_build(c));
   if (c->all_planar) TRY(tile_plan_setup(c));
@@ -355,7 +359,8 @@ int femo_set_input(femo_ctx* c, int which, const double* data, int64_t n, int on
     }
   }
   CUDA_TRY(cudaStreamSynchronize(c->stream));
-  if (which != FEMO_DENSITY && which != FEMO_F_SOLID) { c->jac_valid = false; c->prec_valid = false; }
+  // the dynamic operator A_eff = (2/dt^2) M + K/2 also depends on the density
+  if ((which != FEMO_DENSITY || c->dyn_on) && which != FEMO_F_SOLID) { c->jac_valid = false; c->prec_valid = false; }
   return 0;
 }
 

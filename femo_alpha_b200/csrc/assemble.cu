@@ -631,7 +631,7 @@ static int assemble_jacobian_legacy(femo_ctx* c, const double* uh) {
   return 0;
 }
 
-int assemble_jacobian(femo_ctx* c) {
+int assemble_stiffness(femo_ctx* c) {
   if (!c->setup_done) return femo_fail("femo_assemble_jacobian: call femo_shell_setup first");
   const double* uh = c->uhat_zero ? nullptr : c->uhat;
   cudaEventRecord(c->ev0, c->stream);

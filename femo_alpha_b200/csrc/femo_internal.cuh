@@ -165,6 +165,14 @@ struct femo_ctx {
   double t_rec = 0, t_asm = 0, t_solve = 0, t_iter = 0;
   double dmma_tf = 0;           // last measured fp64 mma.sync rate (TFLOP/s)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // dynamic (time-stepped) operator, dynamic.cu: while dyn_on, `vals` holds A_eff = (2/dt^2) M + K/2 (the matrix every
+  // solver / preconditioner / multigrid level works on) and `vals_K` the stiffness K; `mvals` one scalar per BSR block
+  // (the mass matrix is block-scalar: rho h int phi_a phi_b on u-u blocks, rho h hE^2 int N_a N_b on theta-theta blocks)
+  int dyn_on = 0;
+  bool dyn_swapped = false;
+  double dyn_dt = 0.0;
+  double *vals_K = nullptr, *mvals = nullptr, *mass_me = nullptr;
+  Tables* tabm = nullptr;       // 4x4 rule of the mass form
 };
 
 // ---- host-side helpers (context.cu) ---------------------------------------
@@ -192,9 +200,11 @@ int asm_plan_build(femo_ctx* c);                                          // top
 int tile_plan_setup(femo_ctx* c);                                         // assemble_tiles.cu
 void tile_plan_free(femo_ctx* c);                                         // assemble_tiles.cu
 int assemble_jacobian_tiles(femo_ctx* c, const double* uhat);             // assemble_tiles.cu (records + assembly)
-int assemble_jacobian(femo_ctx* c);                                       // assemble.cu
+int assemble_stiffness(femo_ctx* c);                                      // assemble.cu: K -> c->vals
+int assemble_jacobian(femo_ctx* c);                                       // dynamic.cu: K, or A_eff while c->dyn_on
 int assemble_load(femo_ctx* c, double* F_dev);                            // assemble.cu
 int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc);       // solver.cu
+int bsr_spmv_vals(femo_ctx* c, const double* vals, const double* x, double* y, int with_bc);   // solver.cu
 int penalty_apply(femo_ctx* c, const double* x, double* y, double sign);  // solver.cu  y += sign * P x
 int precond_setup(femo_ctx* c);                                           // solver.cu
 int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, int* iters,
@@ -212,6 +222,21 @@ void dist_free(femo_ctx* c);                                              // dis
 int pnorm_value(femo_ctx* c, int tag, double* val);                       // outputs.cu
 int pnorm_grad(femo_ctx* c, int tag, int arg, double* g);                 // outputs.cu
 int stress_field(femo_ctx* c, int surface, double* out);                  // outputs.cu
+// dynamic path: element kernels (outputs.cu) and dense factor (mg.cu)
+inline const double* stiffness_vals(const femo_ctx* c) { return c->dyn_swapped ? c->vals_K : c->vals; }
+int mass_elements(femo_ctx* c, double* me);                               // (nc,97): 81 Q2xQ2 + 16 Q1xQ1 scalars
+int mass_param_T(femo_ctx* c, const double* acc, const double* lam, double g_acc, bool accumulate);   // -> cellbuf[0..3]
+int stiff_param_T(femo_ctx* c, const double* w, const double* lam, bool accumulate);                  // -> cellbuf[0..3]
+int mass_param_fwd(femo_ctx* c, const double* acc, const double* dh, double g_acc, double* out);     // (dM/dh dh) acc - dW/dh dh
+int stiff_param_fwd(femo_ctx* c, const double* w, const double* dh, double* out);
+int cellbuf_to_material(femo_ctx* c, double* out);
+int self_weight_load(femo_ctx* c, double g_acc, double* out);
+struct femo_mg;
+int mg_num_levels(femo_mg* m);                                            // mg.cu
+femo_ctx* mg_level_ctx(femo_mg* m, int l);
+void mg_invalidate(femo_mg* m);
+int dense_inverse_build(femo_ctx* c, double** Cinv, int64_t* n_have);     // inverse of the BC-applied c->vals
+int dense_inverse_apply(femo_ctx* c, const double* Cinv, const double* b, double* x);
 
 // ---- device maths --------------------------------------------------------------
 #ifdef __CUDACC__

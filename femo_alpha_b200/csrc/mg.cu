@@ -253,26 +253,26 @@ int mg_lambda_max(femo_mg* m, int l) {
   return 0;
 }
 
-int mg_coarse_inverse(femo_mg* m) {
-  femo_ctx* c = m->L.back().c;
+int dense_inverse_impl(femo_ctx* c, double** Cinv_p, int64_t* n_have) {
   const int64_t n = c->ndof;
-  if (n > 46000) return femo_fail("multigrid: coarsest level too large for a dense inverse (" + std::to_string(n) + " dofs); add levels");
+  if (n > 46000) return femo_fail("dense inverse: operator too large (" + std::to_string(n) + " dofs); add multigrid levels or use the iterative solver");
   TRY(cusolver_load());
-  if (m->ncoarse != n) { dev_free(&m->Cinv); TRY(dev_alloc(&m->Cinv, (size_t)n * n)); m->ncoarse = n; }
-  CUDA_TRY(cudaMemsetAsync(m->Cinv, 0, sizeof(double) * n * n, c->stream));
-  k_dense_fill<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->bcmask, c->nb, n, m->Cinv);
+  if (*n_have != n || !*Cinv_p) { dev_free(Cinv_p); TRY(dev_alloc(Cinv_p, (size_t)n * n)); *n_have = n; }
+  double* Cinv = *Cinv_p;
+  CUDA_TRY(cudaMemsetAsync(Cinv, 0, sizeof(double) * n * n, c->stream));
+  k_dense_fill<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->bcmask, c->nb, n, Cinv);
   TRY(check_launch(c, "k_dense_fill"));
   void* h = nullptr;
   if (g_cs.Create(&h) != 0) return femo_fail("cusolverDnCreate failed");
   g_cs.SetStream(h, c->stream);
   int lw1 = 0, lw2 = 0;
   const int LOWER = 0;
-  if (g_cs.potrf_bufferSize(h, LOWER, (int)n, m->Cinv, (int)n, &lw1) != 0) { g_cs.Destroy(h); return femo_fail("potrf_bufferSize failed"); }
-  if (g_cs.potri_bufferSize(h, LOWER, (int)n, m->Cinv, (int)n, &lw2) != 0) { g_cs.Destroy(h); return femo_fail("potri_bufferSize failed"); }
+  if (g_cs.potrf_bufferSize(h, LOWER, (int)n, Cinv, (int)n, &lw1) != 0) { g_cs.Destroy(h); return femo_fail("potrf_bufferSize failed"); }
+  if (g_cs.potri_bufferSize(h, LOWER, (int)n, Cinv, (int)n, &lw2) != 0) { g_cs.Destroy(h); return femo_fail("potri_bufferSize failed"); }
   double* work = nullptr; int* info = nullptr;
   TRY(dev_alloc(&work, (size_t)std::max(lw1, lw2))); TRY(dev_alloc(&info, 2));
-  int r1 = g_cs.potrf(h, LOWER, (int)n, m->Cinv, (int)n, work, lw1, info);
-  int r2 = g_cs.potri(h, LOWER, (int)n, m->Cinv, (int)n, work, lw2, info + 1);
+  int r1 = g_cs.potrf(h, LOWER, (int)n, Cinv, (int)n, work, lw1, info);
+  int r2 = g_cs.potri(h, LOWER, (int)n, Cinv, (int)n, work, lw2, info + 1);
   int hinfo[2] = {0, 0};
   cudaMemcpyAsync(hinfo, info, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
   cudaStreamSynchronize(c->stream);
@@ -281,13 +281,26 @@ int mg_coarse_inverse(femo_mg* m) {
   if (r1 != 0 || r2 != 0 || hinfo[0] != 0 || hinfo[1] != 0)
     return femo_fail("multigrid: dense Cholesky of the coarsest operator failed (not SPD? status " + std::to_string(r1) + "/" +
                      std::to_string(r2) + ", info " + std::to_string(hinfo[0]) + "/" + std::to_string(hinfo[1]) + ")");
-  k_dense_mirror<<<(unsigned)cdiv(n * n, 256), 256, 0, c->stream>>>(m->Cinv, n);
+  k_dense_mirror<<<(unsigned)cdiv(n * n, 256), 256, 0, c->stream>>>(Cinv, n);
   TRY(check_launch(c, "k_dense_mirror"));
   c->launches += 2;
   return 0;
 }
 
+int mg_coarse_inverse(femo_mg* m) { return dense_inverse_impl(m->L.back().c, &m->Cinv, &m->ncoarse); }
+
 }  // namespace
+
+int mg_num_levels(femo_mg* m) { return m ? (int)m->L.size() : 0; }
+femo_ctx* mg_level_ctx(femo_mg* m, int l) { return m->L[l].c; }
+void mg_invalidate(femo_mg* m) { if (m) m->ready = false; }
+int dense_inverse_build(femo_ctx* c, double** Cinv, int64_t* n_have) { return dense_inverse_impl(c, Cinv, n_have); }
+int dense_inverse_apply(femo_ctx* c, const double* Cinv, const double* b, double* x) {
+  const int64_t n = c->ndof;
+  k_dense_gemv<<<(unsigned)cdiv(n * 32, 256), 256, 0, c->stream>>>(Cinv, b, n, x);
+  c->launches += 1;
+  return check_launch(c, "k_dense_gemv");
+}
 
 extern "C" {
 

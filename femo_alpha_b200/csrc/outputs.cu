@@ -28,7 +28,14 @@ enum CellOp {
   OP_PNORM_DW = 12,   // d/dw of the above                                                           -> 39
   OP_PNORM_DP = 13,   // d/d(h|E|nu) nodal (mode 1|2|3)                                              -> 4 (or 1)
   OP_VM_PROJ = 14,    // cell-wise L2 projection of von Mises onto DG1                               -> 4
-  OP_AREA = 15        // sum_q wJ                                                                    -> 1
+  OP_AREA = 15,       // sum_q wJ                                                                    -> 1
+  // dynamic path (dynamic.cu; femo_alpha/dynamic_rm_shell): mass form of linear_shell_model.py:335-348, 4x4 rule
+  OP_MASS_ELEM = 16,     // coef = rho h: int coef phi_a phi_b J (81), int coef hE^2 N_a N_b J (16)                -> 97
+  OP_MASS_PARAM_T = 17,  // sum_q N_v [wJ rho (a_u.l_u + hE^2 a_t.l_t) - wd rho g l_uz]                           -> 4 (or 1)
+  OP_MASS_PARAM_FWD = 18, // sum_q dh(q) [wJ rho (phi_a a_u ; hE^2 N_b a_t) - wd rho g phi_a e_z]                  -> 39
+  OP_WEIGHT = 19,        // self weight  sum_q wd rho h g phi_a e_z  (plate_sim.py:203-213)                        -> 27
+  OP_VOLUME = 20,        // sum_q wd h  (volume_operation.py:68)                                                   -> 1
+  OP_DVOLUME_DH = 21     // sum_q wd N_v                                                                           -> 4 (or 1)
 };
 
 struct CellArgs {
@@ -42,6 +49,8 @@ struct CellArgs {
   double* out; int out_stride;
   double sm, srho, xi_sign;  // p-norm parameters (m, rho) and through-thickness position xi2 = xi_sign * h/2
   const int32_t* tags; int tag;   // optional sub-domain restriction
+  int accumulate;         // OP_PARAM_T / OP_MASS_PARAM_T: add to `out` instead of overwriting (sum over time levels)
+  double g_acc;           // self-weight acceleration g_factor * 9.81 (0: none)
 };
 
 __device__ __forceinline__ double lane_sum(double v) {
@@ -130,8 +139,9 @@ __global__ void __launch_bounds__(128) k_cell_op(CellArgs A) {
     if (A.uhat) uh[v] = ldv3(A.uhat + 3 * (int64_t)vid[v]);
   }
   constexpr bool need_w = (OP == OP_PARAM_T || OP == OP_PARAM_FWD || OP == OP_MASS_U || OP == OP_UU || OP == OP_PNORM ||
-                            OP == OP_PNORM_DW || OP == OP_PNORM_DP || OP == OP_VM_PROJ);
-  constexpr bool need_l = (OP == OP_PARAM_T || OP == OP_F_T);
+                            OP == OP_PNORM_DW || OP == OP_PNORM_DP || OP == OP_VM_PROJ || OP == OP_MASS_PARAM_T ||
+                            OP == OP_MASS_PARAM_FWD);
+  constexpr bool need_l = (OP == OP_PARAM_T || OP == OP_F_T || OP == OP_MASS_PARAM_T);
   if (need_w || need_l) {
     for (int i = lane; i < 39; i += 32) {
       int64_t d = 3 * (int64_t)A.cb[cell * 13 + i / 3] + (i % 3);
@@ -169,9 +179,12 @@ __global__ void __launch_bounds__(128) k_cell_op(CellArgs A) {
 #pragma unroll
       for (int i = 0; i < 9; ++i) gq += sl[i] * sig[i];
       gq *= wd;
-      if (A.ewm) { double t = lane_sum(gq); if (lane == 0) out[0] = t; }
+      if (A.ewm) { double t = lane_sum(gq); if (lane == 0) out[0] = A.accumulate ? out[0] + t : t; }
       else
-        for (int v = 0; v < 4; ++v) { double t = lane_sum(gq * tab->n1[q][v]); if (lane == 0) out[v] = t; }
+        for (int v = 0; v < 4; ++v) {
+          double t = lane_sum(gq * tab->n1[q][v]);
+          if (lane == 0) out[v] = A.accumulate ? out[v] + t : t;
+        }
     } else {
       // perturbation of the parameter at this point
       double dp;
@@ -256,6 +269,64 @@ __global__ void __launch_bounds__(128) k_cell_op(CellArgs A) {
   } else if (OP == OP_AREA) {
     double t = lane_sum(wJ);
     if (lane == 0) out[0] = t;
+  } else if (OP == OP_MASS_ELEM) {
+    const double cu = wJ * rhoq * hq, ct = cu * A.hE[cell] * A.hE[cell];
+    for (int a = 0; a < 9; ++a)
+      for (int b = 0; b < 9; ++b) {
+        double t = lane_sum(cu * tab->phi2[q][a] * tab->phi2[q][b]);
+        if (lane == 0) out[9 * a + b] = t;
+      }
+    for (int a = 0; a < 4; ++a)
+      for (int b = 0; b < 4; ++b) {
+        double t = lane_sum(ct * tab->n1[q][a] * tab->n1[q][b]);
+        if (lane == 0) out[81 + 4 * a + b] = t;
+      }
+  } else if (OP == OP_MASS_PARAM_T || OP == OP_MASS_PARAM_FWD) {
+    // acceleration (vec_w) at the point
+    V3 au = v3(0, 0, 0), at = v3(0, 0, 0);
+    for (int a = 0; a < 9; ++a) au = au + tab->phi2[q][a] * ldv3(s_w[wid] + 3 * a);
+    for (int b = 0; b < 4; ++b) at = at + tab->n1[q][b] * ldv3(s_w[wid] + 27 + 3 * b);
+    const double cu = wJ * rhoq, ct = cu * A.hE[cell] * A.hE[cell], cg = wd * rhoq * A.g_acc;
+    if (OP == OP_MASS_PARAM_T) {
+      V3 lu = v3(0, 0, 0), lt = v3(0, 0, 0);
+      for (int a = 0; a < 9; ++a) lu = lu + tab->phi2[q][a] * ldv3(s_l[wid] + 3 * a);
+      for (int b = 0; b < 4; ++b) lt = lt + tab->n1[q][b] * ldv3(s_l[wid] + 27 + 3 * b);
+      const double gq = cu * dot(au, lu) + ct * dot(at, lt) - cg * lu.z;
+      if (A.ewm) { double t = lane_sum(gq); if (lane == 0) out[0] = A.accumulate ? out[0] + t : t; }
+      else
+        for (int v = 0; v < 4; ++v) {
+          double t = lane_sum(gq * tab->n1[q][v]);
+          if (lane == 0) out[v] = A.accumulate ? out[v] + t : t;
+        }
+    } else {
+      double dp;
+      if (A.ewm) dp = A.vec_l[cell];
+      else { dp = 0; for (int v = 0; v < 4; ++v) dp += tab->n1[q][v] * A.vec_l[vid[v]]; }
+      const V3 ru = (dp * cu) * au - v3(0, 0, dp * cg), rt = (dp * ct) * at;
+      for (int a = 0; a < 9; ++a) {
+        double sN = tab->phi2[q][a];
+        double x = lane_sum(sN * ru.x), y = lane_sum(sN * ru.y), z = lane_sum(sN * ru.z);
+        if (lane == 0) { out[3 * a] = x; out[3 * a + 1] = y; out[3 * a + 2] = z; }
+      }
+      for (int b = 0; b < 4; ++b) {
+        double sN = tab->n1[q][b];
+        double x = lane_sum(sN * rt.x), y = lane_sum(sN * rt.y), z = lane_sum(sN * rt.z);
+        if (lane == 0) { out[27 + 3 * b] = x; out[27 + 3 * b + 1] = y; out[27 + 3 * b + 2] = z; }
+      }
+    }
+  } else if (OP == OP_WEIGHT) {
+    const double cg = wd * rhoq * hq * A.g_acc;
+    for (int a = 0; a < 9; ++a) {
+      double z = lane_sum(cg * tab->phi2[q][a]);
+      if (lane == 0) { out[3 * a] = 0.0; out[3 * a + 1] = 0.0; out[3 * a + 2] = z; }
+    }
+  } else if (OP == OP_VOLUME) {
+    double t = lane_sum(wd * hq);
+    if (lane == 0) out[0] = t;
+  } else if (OP == OP_DVOLUME_DH) {
+    if (A.ewm) { double t = lane_sum(wd); if (lane == 0) out[0] = t; }
+    else
+      for (int v = 0; v < 4; ++v) { double t = lane_sum(wd * tab->n1[q][v]); if (lane == 0) out[v] = t; }
   } else if (OP == OP_PNORM || OP == OP_PNORM_DW || OP == OP_PNORM_DP || OP == OP_VM_PROJ) {
     const bool in_dom = (A.tags == nullptr || A.tag < 0 || A.tags[cell] == A.tag);
     double hv[4] = {0, 0, 0, 0};
@@ -406,6 +477,7 @@ CellArgs base_args(femo_ctx* c) {
   A.nc = c->nc; A.nq = c->nq; A.ewm = c->ewm; A.ewp = c->ewp;
   A.vec_w = c->w; A.vec_l = nullptr; A.mode = 0; A.out = c->cellbuf; A.out_stride = 39;
   A.sm = c->stress_m; A.srho = c->stress_rho; A.xi_sign = 1.0; A.tags = c->cell_tags; A.tag = -1;
+  A.accumulate = 0; A.g_acc = 0.0;
   return A;
 }
 
@@ -456,6 +528,47 @@ int mode_of(int arg) { return arg == FEMO_THICKNESS ? 1 : arg == FEMO_E ? 2 : ar
 
 }  // namespace
 
+// ---- dynamic path helpers (called from dynamic.cu) ---------------------------------------------------
+static CellArgs mass_args(femo_ctx* c) {
+  CellArgs A = base_args(c);
+  A.tab = c->tabm; A.nq = 16;       // 4x4 rule of the mass form
+  return A;
+}
+int mass_elements(femo_ctx* c, double* me) {
+  CellArgs A = mass_args(c);
+  A.out = me; A.out_stride = 97;
+  return run_cell_op<OP_MASS_ELEM>(c, A);
+}
+int mass_param_T(femo_ctx* c, const double* acc, const double* lam, double g_acc, bool accumulate) {
+  CellArgs A = mass_args(c);
+  A.vec_w = acc; A.vec_l = lam; A.g_acc = g_acc; A.accumulate = accumulate ? 1 : 0;
+  return run_cell_op<OP_MASS_PARAM_T>(c, A);
+}
+int stiff_param_T(femo_ctx* c, const double* w, const double* lam, bool accumulate) {
+  CellArgs A = base_args(c);
+  A.vec_w = w; A.vec_l = lam; A.mode = 1; A.accumulate = accumulate ? 1 : 0;
+  return run_cell_op<OP_PARAM_T>(c, A);
+}
+int mass_param_fwd(femo_ctx* c, const double* acc, const double* dh, double g_acc, double* out) {
+  CellArgs A = mass_args(c);
+  A.vec_w = acc; A.vec_l = dh; A.g_acc = g_acc;
+  TRY(run_cell_op<OP_MASS_PARAM_FWD>(c, A));
+  return gather_dofs(c, out, true);
+}
+int stiff_param_fwd(femo_ctx* c, const double* w, const double* dh, double* out) {
+  CellArgs A = base_args(c);
+  A.vec_w = w; A.vec_l = dh; A.mode = 1;
+  TRY(run_cell_op<OP_PARAM_FWD>(c, A));
+  return gather_dofs(c, out, true);
+}
+int cellbuf_to_material(femo_ctx* c, double* out) { return gather_material(c, out); }
+int self_weight_load(femo_ctx* c, double g_acc, double* out) {
+  CellArgs A = mass_args(c);
+  A.g_acc = g_acc;
+  TRY(run_cell_op<OP_WEIGHT>(c, A));
+  return gather_dofs(c, out, false);
+}
+
 int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out) {
   CellArgs A = base_args(c);
   A.vec_l = lam;
@@ -498,7 +611,7 @@ int out_scalar(femo_ctx* c, int which, double* val) {
   if (which == FEMO_MASS) { TRY(run_cell_op<OP_MASS>(c, A)); return sum_cells(c, val); }
   if (which == FEMO_ELASTIC_ENERGY) {
     if (!c->jac_valid) TRY(assemble_jacobian(c));
-    TRY(bsr_spmv(c, c->w, c->tmp, 0));
+    TRY(bsr_spmv_vals(c, stiffness_vals(c), c->w, c->tmp, 0));
     TRY(penalty_apply(c, c->w, c->tmp, -1.0));
     double d = 0;
     TRY(dev_dot(c, c->w, c->tmp, c->ndof, &d));
@@ -506,6 +619,7 @@ int out_scalar(femo_ctx* c, int which, double* val) {
     return 0;
   }
   if (which == FEMO_PNORM_STRESS) return pnorm_value(c, -1, val);
+  if (which == FEMO_VOLUME) { TRY(run_cell_op<OP_VOLUME>(c, A)); return sum_cells(c, val); }
   return femo_fail("femo_output: output not implemented");
 }
 
@@ -534,7 +648,7 @@ int out_grad(femo_ctx* c, int which, int arg, double* g) {
   if (which == FEMO_ELASTIC_ENERGY) {
     if (arg == FEMO_ARG_STATE) {
       if (!c->jac_valid) TRY(assemble_jacobian(c));
-      TRY(bsr_spmv(c, c->w, g, 0));
+      TRY(bsr_spmv_vals(c, stiffness_vals(c), c->w, g, 0));
       return penalty_apply(c, c->w, g, -1.0);
     }
     if (arg == FEMO_THICKNESS || arg == FEMO_E || arg == FEMO_NU) {
@@ -547,6 +661,11 @@ int out_grad(femo_ctx* c, int which, int arg, double* g) {
     return 0;
   }
   if (which == FEMO_PNORM_STRESS) return pnorm_grad(c, -1, arg, g);
+  if (which == FEMO_VOLUME) {
+    if (arg == FEMO_THICKNESS) { TRY(run_cell_op<OP_DVOLUME_DH>(c, A)); return gather_material(c, g); }
+    CUDA_TRY(cudaMemsetAsync(g, 0, sizeof(double) * n_arg, c->stream));
+    return 0;
+  }
   return femo_fail("femo_output_grad: output not implemented");
 }
 

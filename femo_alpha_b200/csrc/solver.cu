@@ -363,6 +363,16 @@ int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc) {
   return 0;
 }
 
+// y = (vals) x with the pattern of this context (K while the dynamic operator A_eff occupies c->vals)
+int bsr_spmv_vals(femo_ctx* c, const double* vals, const double* x, double* y, int with_bc) {
+  const uint32_t* colw = with_bc ? c->colbc : reinterpret_cast<const uint32_t*>(c->colidx);
+  const uint8_t* rbits = with_bc ? c->bcbits : nullptr;
+  k_spmv<8, 6><<<spmv_grid(), 256, 0, c->stream>>>(c->rowptr, colw, vals, x, rbits, c->nb, y, nullptr, nullptr);
+  TRY(check_launch(c, "k_spmv"));
+  c->launches += 1;
+  return 0;
+}
+
 int penalty_apply(femo_ctx* c, const double* x, double* y, double sign) {
   if (c->n_pen_rows == 0) return 0;
   k_penalty_apply<<<(unsigned)cdiv(c->n_pen_rows, 128), 128, 0, c->stream>>>(c->pen_row, c->pen_row_ptr, c->pen_dest_col,

@@ -31,7 +31,8 @@ enum femo_input {
 };
 /* scalar outputs: rm_shell/rm_shell_model.py:219-230 (fea.add_output) */
 enum femo_output_id {
-  FEMO_COMPLIANCE = 0, FEMO_MASS = 1, FEMO_ELASTIC_ENERGY = 2, FEMO_PNORM_STRESS = 3
+  FEMO_COMPLIANCE = 0, FEMO_MASS = 1, FEMO_ELASTIC_ENERGY = 2, FEMO_PNORM_STRESS = 3,
+  FEMO_VOLUME = 4   /* int t dx, dynamic_rm_shell/volume_operation.py:57-70 */
 };
 /* pseudo-argument for femo_output_grad: derivative w.r.t. the state 'disp_solid' */
 #define FEMO_ARG_STATE 100
@@ -191,6 +192,55 @@ int femo_mg_get_lambda(femo_mg* mg, int level, double* lambda_max);
 /* PCG with one V-cycle per iteration on A x = rhs (A = dR/du with BCs, x0 = 0); zero_bc as femo_solve_adjoint */
 int femo_mg_solve(femo_mg* mg, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
                   int on_device, int zero_bc);
+
+/* ---- dynamic (time-stepped) RM shell: SURVEY 8 f1, BASELINE config 4 ------------------------------------------
+ * Replaces femo_alpha/dynamic_rm_shell: PlateSim.solve_dynamic_problem (plate_sim.py:281-361), the residual
+ * M wddot + K w_mid - F - W of PlateSim.SVK_residual (:190-215) under the implicit midpoint rule (:135-140), and the
+ * forward / reverse sweeps of StateOperation.apply_inverse_jacobian and .compute_jacvec_product
+ * (state_operation_dynamic.py:140-432,447-702).  The reference assembles and LU-factorises the (step-invariant)
+ * Jacobian in every step and keeps N^2 work vectors in the reverse sweep; here A_eff = (2/dt^2) M + K/2 is assembled
+ * once (dense inverse up to 46 000 dofs, else block-Jacobi PCG or V-cycle PCG on the levels of an attached
+ * multigrid), every step is one K product, one M product and one solve, the whole state history stays in HBM
+ * ((n_steps+1) x n_dof doubles, level-major like utils.py:9-16) and the reverse sweep is the two-field (w, wdot)
+ * recurrence with O(1) work vectors.  Mass form: linear_shell_model.py:335-348, 4x4 Gauss rule; density = the
+ * FEMO_DENSITY input.  Homogeneous strong Dirichlet BCs (femo_set_strong_bc) only.
+ * While a femo_dyn exists its context is in "dynamic mode": the operator of every solve on it is A_eff. */
+typedef struct femo_dyn femo_dyn;
+/* add_self_weight: body force rho t g e_z with g = g_factor * 9.81 (plate_sim.py:203-213; g_factor -1 = downwards) */
+int femo_dyn_create(femo_ctx* ctx, double dt, int n_steps, int add_self_weight, double g_factor, femo_dyn** out);
+int femo_dyn_destroy(femo_dyn* d);
+/* optional: V-cycle PCG for the step solves; every level context of `mg` is switched to dynamic mode with the same dt */
+int femo_dyn_set_mg(femo_dyn* d, femo_mg* mg);
+/* (re)build after the inputs changed: K, M, A_eff, preconditioner / dense inverse.
+ * solver: 0 auto (dense if n_dof <= 46000, else multigrid if attached, else PCG), 1 dense, 2 PCG, 3 multigrid */
+int femo_dyn_setup(femo_dyn* d, int solver);
+/* time loop from zero initial conditions; f_history (n_rows, n_force) row-major, rows beyond the last repeat it
+ * (plate_sim.py:314-319).  Fills the resident history and the strain energy of every level (plate_sim.py:337). */
+int femo_dyn_solve(femo_dyn* d, const double* f_history, int64_t n_rows, double rtol, int max_it,
+                   int64_t* total_iters, int on_device);
+int femo_dyn_get_history(femo_dyn* d, double* w_hist, int on_device);      /* (n_steps+1, n_dof) */
+int femo_dyn_set_history(femo_dyn* d, const double* w_hist, int on_device);
+int femo_dyn_get_energies(femo_dyn* d, double* energies);                  /* host, n_steps+1 */
+/* apply_inverse_jacobian 'rev' (state_operation_dynamic.py:562-690): (dR/dw)^T lam = d_out, clamped entries and
+ * level 0 of lam are zero; 'fwd' (:516-560): (dR/dw) x = d_res */
+int femo_dyn_solve_adjoint(femo_dyn* d, const double* d_out_hist, double* lam_hist, double rtol, int max_it,
+                           int64_t* total_iters, int on_device);
+int femo_dyn_solve_forward(femo_dyn* d, const double* d_res_hist, double* x_hist, double rtol, int max_it,
+                           int64_t* total_iters, int on_device);
+/* compute_jacvec_product on the state (state_operation_dynamic.py:224-275,316-372): y = (dR/dw) x or (dR/dw)^T x */
+int femo_dyn_dRdw_apply(femo_dyn* d, const double* x_hist, double* y_hist, int transpose, int on_device);
+/* compute_jacvec_product on the thickness (:277-309,374-404), at the resident history:
+ * out = sum_i (dR_i/dh)^T lam_i  (n_material)  /  out_hist[i] = (dR_i/dh) dh */
+int femo_dyn_dRdh_T_apply(femo_dyn* d, const double* lam_hist, double* out, int on_device);
+int femo_dyn_dRdh_apply(femo_dyn* d, const double* dh, double* out_hist, int on_device);
+/* TotalStrainEnergyOperation (total_strain_energy_operation.py:56-125) at the resident history;
+ * arg = FEMO_THICKNESS (n_material) or FEMO_ARG_STATE ((n_steps+1) x n_dof) */
+int femo_dyn_total_strain_energy(femo_dyn* d, double* value);
+int femo_dyn_total_strain_energy_grad(femo_dyn* d, int arg, double* g, int on_device);
+/* y = M x (no BCs; test / diagnostic) */
+int femo_dyn_mass_apply(femo_dyn* d, const double* x, double* y, int on_device);
+/* device time of the last femo_dyn_solve / femo_dyn_solve_adjoint (ms) and the solver in use (1 dense, 2 PCG, 3 MG) */
+int femo_dyn_info(femo_dyn* d, double* ms_forward, double* ms_adjoint, int* solver);
 
 /* ---- instrumentation ---------------------------------------------------------------- */
 /* number of kernels this context has launched so far */
