@@ -52,9 +52,9 @@ class OutputOperation(csdl.CustomExplicitOperation):
         for arg_name in input_vals:
             update(self.args_dict[arg_name]["function"], input_vals[arg_name])
         for arg_name in input_vals:
-            if arg_name == 'uhat':
+            if arg_name == 'uhat' and self.output_name not in ('compliance', 'mass', 'elastic_energy', 'volume'):
                 if not OutputOperation._uhat_warned:
-                    warnings.warn("femo_alpha_b200: d(output)/d(uhat) is not implemented; returned as zero")
+                    warnings.warn("femo_alpha_b200: d(%s)/d(uhat) is not implemented; returned as zero" % self.output_name)
                     OutputOperation._uhat_warned = True
                 derivatives[self.output_name, arg_name] = np.zeros(len(input_vals[arg_name]))
                 continue

@@ -4,10 +4,9 @@ femo_alpha/csdl_alpha_opt/state_operation.py:8-295 (same ctor, methods, dict pro
 Differences by design: derivatives are refreshed at EVERY evaluation
 (B1: the reference only assembles them at opt_iter == 1 for linear problems, leaving a stale
 adjoint afterwards; set `reference_stale_derivatives=True` to emulate), the partials dR/df are
-matrix-free device operators, forward mode works (B5), and d/d(uhat) is not available yet.
+matrix-free device operators (including the shape partial dR/d(uhat), csrc/shape_partials.cuh), and forward mode
+works (B5).
 """
-import warnings
-
 import numpy as np
 
 from ..csdl_compat import csdl
@@ -75,9 +74,6 @@ class StateOperation(csdl.experimental.CustomImplicitOperation):
                     d_residuals[state_name] += computeMatVecProductFwd(self.dRdu, self.fea_du)
                 for arg_name in self.dR_df_dict:
                     if arg_name in d_inputs:
-                        if arg_name == 'uhat':
-                            self._warn_uhat()
-                            continue
                         update(self.dR_df_dict[arg_name]['fea_df'], d_inputs[arg_name])
                         d_residuals[state_name] += computeMatVecProductFwd(
                             self.dR_df_dict[arg_name]['dRdf'], self.dR_df_dict[arg_name]['fea_df'])
@@ -86,9 +82,6 @@ class StateOperation(csdl.experimental.CustomImplicitOperation):
                 update(self.fea_dR, d_residuals[state_name])
                 for arg_name in self.dR_df_dict:
                     if arg_name in d_inputs:
-                        if arg_name == 'uhat':
-                            self._warn_uhat()
-                            continue
                         d_inputs[arg_name] += computeMatVecProductBwd(self.dR_df_dict[arg_name]['dRdf'], self.fea_dR)
         else:
             raise ValueError("mode must be either 'fwd' or 'rev'.")
@@ -129,10 +122,3 @@ class StateOperation(csdl.experimental.CustomImplicitOperation):
         self.dRdu = assembleMatrix(self.fea_state['dR_du'])
         self.A, _ = assembleSystem(self.fea_state['dR_du'], self.fea_state['residual_form'], bcs=self.fea.bc)
         self.ksp = setUpKSP_MUMPS(self.A)
-
-    _uhat_warned = False
-
-    def _warn_uhat(self):
-        if not StateOperation._uhat_warned:
-            warnings.warn("femo_alpha_b200: dR/d(uhat) (shape partial) is not implemented; its contribution is omitted")
-            StateOperation._uhat_warned = True

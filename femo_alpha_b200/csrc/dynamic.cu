@@ -187,7 +187,20 @@ int dyn_linear_solve(femo_dyn* d, const double* b, double* x, double rtol, int m
     TRY(dense_inverse_apply(c, d->Cinv, b, x));
     it = 1;
   } else if (d->solver == 3) {
-    TRY(femo_mg_solve(d->mg, b, x, rtol, max_it, &it, &rr, 1, 0));
+    // warm start (femo_mg_solve starts from zero): solve A delta = b - A x0 to the tolerance rtol |b| / |b - A x0|
+    const int64_t n = c->ndof;
+    double bb = 0, r0 = 0;
+    TRY(dev_dot(c, b, b, n, &bb));
+    TRY(bsr_spmv(c, x, d->t1, 1));
+    TRY(lin4(c, 1.0, b, -1.0, d->t1, 0, nullptr, 0, nullptr, c->bcmask, d->t1));
+    TRY(dev_dot(c, d->t1, d->t1, n, &r0));
+    if (bb > 0 && r0 > rtol * rtol * bb) {
+      const double rt = std::min(0.5, rtol * sqrt(bb / r0));
+      TRY(femo_mg_solve(d->mg, d->t1, d->t2, rt, max_it, &it, &rr, 1, 1));
+      TRY(lin4(c, 1.0, x, 1.0, d->t2, 0, nullptr, 0, nullptr, c->bcmask, x));
+    } else if (!(bb > 0)) {
+      CUDA_TRY(cudaMemsetAsync(x, 0, sizeof(double) * n, c->stream));
+    }
   } else {
     TRY(pcg_solve(c, b, x, rtol, max_it, &it, &rr, false));
   }
@@ -404,7 +417,9 @@ int femo_dyn_solve_adjoint(femo_dyn* d, const double* d_out_hist, double* lam_hi
       TRY(lin4(c, 1.0, di, 1.0, d->t2, 0, nullptr, 0, nullptr, c->bcmask, d->rhs));
       std::swap(d->mu, d->lm);
     }
-    CUDA_TRY(cudaMemsetAsync(li, 0, sizeof(double) * n, c->stream));
+    // initial guess of the iterative solvers: the adjoint of the level above (smooth in time)
+    if (i == d->levels - 1) CUDA_TRY(cudaMemsetAsync(li, 0, sizeof(double) * n, c->stream));
+    else CUDA_TRY(cudaMemcpyAsync(li, L + (size_t)(i + 1) * n, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
     TRY(dyn_linear_solve(d, d->rhs, li, rtol, max_it, &iters));
     TRY(lin4(c, 1.0, li, 0, nullptr, 0, nullptr, 0, nullptr, c->bcmask, li));
   }

@@ -240,18 +240,20 @@ int dense_inverse_apply(femo_ctx* c, const double* Cinv, const double* b, double
 
 // ---- device maths --------------------------------------------------------------
 #ifdef __CUDACC__
+// host + device: the element maths can be exercised on the CPU by nvcc-compiled test harnesses (tests/shape_host.cu)
+#define FEMO_HD __host__ __device__ __forceinline__
 struct V3 { double x, y, z; };
-__device__ __forceinline__ V3 v3(double x, double y, double z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ V3 operator*(double s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
-__device__ __forceinline__ double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+FEMO_HD V3 v3(double x, double y, double z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+FEMO_HD V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+FEMO_HD V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+FEMO_HD V3 operator*(double s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
+FEMO_HD double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+FEMO_HD V3 cross(V3 a, V3 b) {
   return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
-__device__ __forceinline__ V3 ldv3(const double* p) { return v3(p[0], p[1], p[2]); }
+FEMO_HD V3 ldv3(const double* p) { return v3(p[0], p[1], p[2]); }
 // K[i][j] += a_i * b_j
-__device__ __forceinline__ void outer_acc(double* K, V3 a, V3 b) {
+FEMO_HD void outer_acc(double* K, V3 a, V3 b) {
   K[0] += a.x * b.x; K[1] += a.x * b.y; K[2] += a.x * b.z;
   K[3] += a.y * b.x; K[4] += a.y * b.y; K[5] += a.y * b.z;
   K[6] += a.z * b.x; K[7] += a.z * b.y; K[8] += a.z * b.z;
@@ -268,7 +270,7 @@ struct QpGeom {
   double Finv[9];
 };
 
-__device__ __forceinline__ void inv3x3(const double* A, double* Ai, double* det) {
+FEMO_HD void inv3x3(const double* A, double* Ai, double* det) {
   double c00 = A[4] * A[8] - A[5] * A[7], c01 = A[5] * A[6] - A[3] * A[8], c02 = A[3] * A[7] - A[4] * A[6];
   double d = A[0] * c00 + A[1] * c01 + A[2] * c02;
   double id = 1.0 / d;
@@ -279,7 +281,7 @@ __device__ __forceinline__ void inv3x3(const double* A, double* Ai, double* det)
 }
 
 // xv: 4 tensor-ordered vertex coordinates, uh: nodal mesh displacement (may be null -> zero)
-__device__ __forceinline__ void qp_geometry(const V3* xv, const V3* uh, double X0, double X1, QpGeom& g) {
+FEMO_HD void qp_geometry(const V3* xv, const V3* uh, double X0, double X1, QpGeom& g) {
   // bilinear derivatives
   double dN0[4] = {-(1 - X1), (1 - X1), -X1, X1};
   double dN1[4] = {-(1 - X0), -X0, (1 - X0), X0};
@@ -327,7 +329,7 @@ __device__ __forceinline__ void qp_geometry(const V3* xv, const V3* uh, double X
 // material coefficients at a point (no quadrature weight), linear_shell_model.py:136-157,284-296
 //   mode 0: value, 1: d/dh, 2: d/dE, 3: d/dnu
 struct Coefs { double cm11, cm12, cm33, cb11, cb12, cb33, cs, cd; };
-__device__ __forceinline__ Coefs clt_coefs(double h, double E, double nu, double hE, double Ju, int mode) {
+FEMO_HD Coefs clt_coefs(double h, double E, double nu, double hE, double Ju, int mode) {
   Coefs c;
   double om = 1.0 / (1.0 - nu * nu);
   double c0 = E * om;                 // E/(1-nu^2)
@@ -360,7 +362,7 @@ __device__ __forceinline__ Coefs clt_coefs(double h, double E, double nu, double
 // strain rows (as global 3-vectors) of one displacement node / one rotation node at a point
 struct URows { V3 e0, e1, e2, g0, g1, dr; };
 struct TRows { V3 k0, k1, k2, g0, g1, dr; };
-__device__ __forceinline__ URows u_rows(double d0, double d1, V3 E0, V3 E1, V3 E2) {
+FEMO_HD URows u_rows(double d0, double d1, V3 E0, V3 E1, V3 E2) {
   URows r;
   r.e0 = d0 * E0; r.e1 = d1 * E1; r.e2 = d1 * E0 + d0 * E1;     // membrane   model:232-239
   r.g0 = d0 * E2; r.g1 = d1 * E2;                                // shear      model:245-258
@@ -368,7 +370,7 @@ __device__ __forceinline__ URows u_rows(double d0, double d1, V3 E0, V3 E1, V3 E
   return r;
 }
 // gq0,gq1: g_q = sum_alpha k_alpha,q dE2/dX_alpha (zero on planar cells)
-__device__ __forceinline__ TRows t_rows(double N, double d0, double d1, V3 E0, V3 E1, V3 E2, V3 gq0, V3 gq1) {
+FEMO_HD TRows t_rows(double N, double d0, double d1, V3 E0, V3 E1, V3 E2, V3 gq0, V3 gq1) {
   TRows r;
   V3 r00 = N * cross(E0, gq0) - d0 * E1;
   V3 r11 = d1 * E0 + N * cross(E1, gq1);

@@ -9,6 +9,7 @@
 // `cellbuf` (lane reduction by shuffles, fixed order), then a per-node gather that sums the
 // adjacent cells in ascending cell order.  No atomics: results are bitwise reproducible.
 #include "femo_internal.cuh"
+#include "shape_partials.cuh"
 
 namespace {
 
@@ -35,7 +36,11 @@ enum CellOp {
   OP_MASS_PARAM_FWD = 18, // sum_q dh(q) [wJ rho (phi_a a_u ; hE^2 N_b a_t) - wd rho g phi_a e_z]                  -> 39
   OP_WEIGHT = 19,        // self weight  sum_q wd rho h g phi_a e_z  (plate_sim.py:203-213)                        -> 27
   OP_VOLUME = 20,        // sum_q wd h  (volume_operation.py:68)                                                   -> 1
-  OP_DVOLUME_DH = 21     // sum_q wd N_v                                                                           -> 4 (or 1)
+  OP_DVOLUME_DH = 21,    // sum_q wd N_v                                                                           -> 4 (or 1)
+  // shape partials (shape_partials.cuh)
+  OP_SHAPE_T = 22,       // d(lam^T R)/d uhat_v, mode 1: with the load term                                        -> 12
+  OP_SHAPE_FWD = 23,     // (dR_e/duhat) duhat                                                                      -> 39
+  OP_SHAPE_MEASURE = 24  // d/duhat_v sum_q wd J c(q), mode 0: c = u.u (compliance), 1: c = rho h (mass)            -> 12
 };
 
 struct CellArgs {
@@ -140,8 +145,8 @@ __global__ void __launch_bounds__(128) k_cell_op(CellArgs A) {
   }
   constexpr bool need_w = (OP == OP_PARAM_T || OP == OP_PARAM_FWD || OP == OP_MASS_U || OP == OP_UU || OP == OP_PNORM ||
                             OP == OP_PNORM_DW || OP == OP_PNORM_DP || OP == OP_VM_PROJ || OP == OP_MASS_PARAM_T ||
-                            OP == OP_MASS_PARAM_FWD);
-  constexpr bool need_l = (OP == OP_PARAM_T || OP == OP_F_T || OP == OP_MASS_PARAM_T);
+                            OP == OP_MASS_PARAM_FWD || OP == OP_SHAPE_T || OP == OP_SHAPE_FWD || OP == OP_SHAPE_MEASURE);
+  constexpr bool need_l = (OP == OP_PARAM_T || OP == OP_F_T || OP == OP_MASS_PARAM_T || OP == OP_SHAPE_T);
   if (need_w || need_l) {
     for (int i = lane; i < 39; i += 32) {
       int64_t d = 3 * (int64_t)A.cb[cell * 13 + i / 3] + (i % 3);
@@ -320,6 +325,36 @@ __global__ void __launch_bounds__(128) k_cell_op(CellArgs A) {
       double z = lane_sum(cg * tab->phi2[q][a]);
       if (lane == 0) { out[3 * a] = 0.0; out[3 * a + 1] = 0.0; out[3 * a + 2] = z; }
     }
+  } else if (OP == OP_SHAPE_T || OP == OP_SHAPE_FWD) {
+    const Coefs cf = clt_coefs(hq, Eq, nuq, A.hE[cell], g.Ju, 0);
+    V3 fq = v3(0, 0, 0);
+    if (A.ewp) fq = ldv3(A.f + 3 * cell);
+    else for (int v = 0; v < 4; ++v) fq = fq + tab->n1[q][v] * ldv3(A.f + 3 * (int64_t)vid[v]);
+    if (OP == OP_SHAPE_T) {
+      double o12[12];
+      shape_T_qp(g, tab, q, s_w[wid], s_l[wid], cf, fq, wd, A.mode, o12);
+#pragma unroll
+      for (int i = 0; i < 12; ++i) { double t = lane_sum(o12[i]); if (lane == 0) out[i] = t; }
+    } else {
+      V3 duh[4];
+#pragma unroll
+      for (int v = 0; v < 4; ++v) duh[v] = ldv3(A.vec_l + 3 * (int64_t)vid[v]);
+      double o39[39];
+      shape_fwd_qp(g, tab, q, s_w[wid], cf, fq, wd, duh, o39);
+#pragma unroll
+      for (int i = 0; i < 39; ++i) { double t = lane_sum(o39[i]); if (lane == 0) out[i] = t; }
+    }
+  } else if (OP == OP_SHAPE_MEASURE) {
+    double cq;
+    if (A.mode == 0) {
+      V3 u = v3(0, 0, 0);
+      for (int a = 0; a < 9; ++a) u = u + tab->phi2[q][a] * ldv3(s_w[wid] + 3 * a);
+      cq = dot(u, u);
+    } else cq = rhoq * hq;
+    double o12[12];
+    shape_measure_qp(g, tab, q, wd * cq, o12);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) { double t = lane_sum(o12[i]); if (lane == 0) out[i] = t; }
   } else if (OP == OP_VOLUME) {
     double t = lane_sum(wd * hq);
     if (lane == 0) out[0] = t;
@@ -569,9 +604,22 @@ int self_weight_load(femo_ctx* c, double g_acc, double* out) {
   return gather_dofs(c, out, false);
 }
 
+// cellbuf[cell][v][3] -> vertex vector (nn,3), adjacent cells summed in ascending order
+static int gather_vertices3(femo_ctx* c, double* out) {
+  k_node_gather<<<(unsigned)cdiv(c->nn, 256), 256, 0, c->stream>>>(c->nc_ptr, c->nc_adj, c->cellbuf, 39, c->nq2, c->nn, 9, 3, out);
+  TRY(check_launch(c, "gather_vertices3"));
+  c->launches += 1;
+  return 0;
+}
+
 int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out) {
   CellArgs A = base_args(c);
   A.vec_l = lam;
+  if (arg == FEMO_UHAT) {                       // shape partial; strong-BC residual (no penalty terms)
+    A.mode = 1;
+    TRY(run_cell_op<OP_SHAPE_T>(c, A));
+    return gather_vertices3(c, out);
+  }
   if (arg == FEMO_F_SOLID) {
     TRY(run_cell_op<OP_F_T>(c, A));
     if (c->ewp) k_copy_cell3<<<(unsigned)cdiv(c->nc, 256), 256, 0, c->stream>>>(c->cellbuf, 39, c->nc, out);
@@ -589,6 +637,10 @@ int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out) {
 int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out) {
   CellArgs A = base_args(c);
   A.vec_l = df;
+  if (arg == FEMO_UHAT) {
+    TRY(run_cell_op<OP_SHAPE_FWD>(c, A));
+    return gather_dofs(c, out, true);
+  }
   if (arg == FEMO_F_SOLID) {
     TRY(run_cell_op<OP_F_FWD>(c, A));
     return gather_dofs(c, out, false);
@@ -626,7 +678,23 @@ int out_scalar(femo_ctx* c, int which, double* val) {
 int out_grad(femo_ctx* c, int which, int arg, double* g) {
   CellArgs A = base_args(c);
   const int64_t n_arg = (arg == FEMO_ARG_STATE) ? c->ndof : (arg == FEMO_F_SOLID) ? c->n_f : (arg == FEMO_UHAT) ? 3 * c->nn : c->n_mat;
-  if (arg == FEMO_UHAT) return femo_fail("derivatives w.r.t. uhat (shape) are not implemented");
+  if (arg == FEMO_UHAT) {                       // shape partials of the outputs
+    if (which == FEMO_COMPLIANCE || which == FEMO_MASS) {
+      A.mode = (which == FEMO_COMPLIANCE) ? 0 : 1;
+      TRY(run_cell_op<OP_SHAPE_MEASURE>(c, A));
+      return gather_vertices3(c, g);
+    }
+    if (which == FEMO_ELASTIC_ENERGY) {         // 1/2 w^T dK/duhat w
+      A.vec_l = c->w; A.mode = 0;
+      TRY(run_cell_op<OP_SHAPE_T>(c, A));
+      TRY(gather_vertices3(c, g));
+      k_scale<<<(unsigned)cdiv(n_arg, 256), 256, 0, c->stream>>>(g, n_arg, 0.5);
+      c->launches += 1;
+      return check_launch(c, "k_scale");
+    }
+    if (which == FEMO_VOLUME) { CUDA_TRY(cudaMemsetAsync(g, 0, sizeof(double) * n_arg, c->stream)); return 0; }
+    return femo_fail("d(pnorm_stress)/d(uhat) is not implemented");
+  }
   if (which == FEMO_COMPLIANCE) {
     if (arg == FEMO_ARG_STATE) {
       TRY(run_cell_op<OP_MASS_U>(c, A));

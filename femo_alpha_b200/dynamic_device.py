@@ -6,6 +6,7 @@ the reference (femo_alpha/dynamic_rm_shell/utils.py:9-16, ravel order 'F' of (n_
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -27,10 +28,16 @@ class DynamicShellDevice:
         L.check(self.lib.femo_dyn_create(device._ctx, self.dt, self.n_steps, int(bool(add_self_weight)), gf,
                                          C.byref(self._h)))
         self.last_iters = 0
+        self._configured = False        # femo_dyn_setup(solver) runs on first use; the library keeps the choice afterwards
+        self._hier = None
+        device._children.append(weakref.ref(self))     # the context must outlive this handle (ShellDevice.close)
 
     def close(self):
+        """Destroy the handle.  Must run before the context (and an attached hierarchy) is destroyed; ShellDevice.close
+        and ShellHierarchy.close call it for the handles registered with them."""
         if getattr(self, "_h", None) is not None and self._h.value:
-            self.lib.femo_dyn_destroy(self._h)
+            if getattr(self.dev, "_ctx", None) is not None and self.dev._ctx.value:
+                self.lib.femo_dyn_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
@@ -48,11 +55,19 @@ class DynamicShellDevice:
     def attach_multigrid(self, hierarchy):
         L.check(self.lib.femo_dyn_set_mg(self._h, hierarchy._mg))
         self._hier = hierarchy
+        hierarchy._children.append(weakref.ref(self))
+        self._configured = False
 
     def setup(self):
         L.check(self.lib.femo_dyn_setup(self._h, self.solver))
+        self._configured = True
+
+    def _ensure(self):
+        if not self._configured:
+            self.setup()
 
     def solve(self, f_history):
+        self._ensure()
         f = np.ascontiguousarray(np.atleast_2d(np.asarray(f_history, dtype=np.float64)))
         if f.shape[1] != self.dev.n_f:
             raise ValueError("force history must have %d columns, got %d" % (self.dev.n_f, f.shape[1]))
@@ -71,11 +86,13 @@ class DynamicShellDevice:
         L.check(self.lib.femo_dyn_set_history(self._h, L.ptr(w), L.on_device(w)))
 
     def energies(self):
+        self._ensure()
         e = np.empty(self.levels)
         L.check(self.lib.femo_dyn_get_energies(self._h, L.ptr(e)))
         return e
 
     def _sweep(self, fn, rhs):
+        self._ensure()
         rhs = self._hist(rhs)
         out = self._hist()
         it = C.c_int64(0)
@@ -90,29 +107,34 @@ class DynamicShellDevice:
         return self._sweep(self.lib.femo_dyn_solve_forward, d_res_hist)
 
     def dRdw_apply(self, x_hist, transpose=False):
+        self._ensure()
         x = self._hist(x_hist)
         y = self._hist()
         L.check(self.lib.femo_dyn_dRdw_apply(self._h, L.ptr(x), L.ptr(y), int(bool(transpose)), 0))
         return y
 
     def dRdh_T_apply(self, lam_hist):
+        self._ensure()
         lam = self._hist(lam_hist)
         out = np.empty(self.dev.n_mat)
         L.check(self.lib.femo_dyn_dRdh_T_apply(self._h, L.ptr(lam), L.ptr(out), 0))
         return out
 
     def dRdh_apply(self, dh):
+        self._ensure()
         dh = np.ascontiguousarray(dh, dtype=np.float64)
         out = self._hist()
         L.check(self.lib.femo_dyn_dRdh_apply(self._h, L.ptr(dh), L.ptr(out), 0))
         return out
 
     def total_strain_energy(self):
+        self._ensure()
         v = C.c_double(0.0)
         L.check(self.lib.femo_dyn_total_strain_energy(self._h, C.byref(v)))
         return v.value
 
     def total_strain_energy_grad(self, arg):
+        self._ensure()
         if arg in ("thickness", L.THICKNESS):
             out = np.empty(self.dev.n_mat)
             L.check(self.lib.femo_dyn_total_strain_energy_grad(self._h, L.THICKNESS, L.ptr(out), 0))
@@ -122,6 +144,7 @@ class DynamicShellDevice:
         return out
 
     def mass_apply(self, x):
+        self._ensure()
         x = np.ascontiguousarray(x, dtype=np.float64)
         y = np.empty(self.dev.ndof)
         L.check(self.lib.femo_dyn_mass_apply(self._h, L.ptr(x), L.ptr(y), 0))

@@ -156,6 +156,7 @@ class ShellHierarchy:
                  np.ascontiguousarray(R.indices, np.int32), np.ascontiguousarray(R.data, np.float64)]
             L.check(self.lib.femo_mg_set_transfer(self._mg, l, *[L.ptr(v) for v in a]))
         self._dirty = True
+        self._children = []             # weak references to DynamicShellDevice handles that use this hierarchy
         self.last_solve = dict(iters=0, relres=0.0)
 
     @classmethod
@@ -259,6 +260,11 @@ class ShellHierarchy:
         return self.solve(rhs, rtol, max_it, zero_bc=True)
 
     def close(self):
+        for ref in getattr(self, "_children", []):
+            child = ref()
+            if child is not None:
+                child.close()
+        self._children = []
         if getattr(self, "_mg", None) is not None and self._mg.value:
             self.lib.femo_mg_destroy(self._mg)
             self._mg = C.c_void_p()

@@ -36,8 +36,14 @@ class ShellDevice:
         self.n_mat, self.n_f = s.n_material, s.n_force
         self.last_solve = dict(iters=0, relres=0.0)
         self._mg = None                 # ShellHierarchy this device is the finest level of (multigrid.py)
+        self._children = []             # weak references to handles that borrow this context (DynamicShellDevice)
 
     def close(self):
+        for ref in getattr(self, "_children", []):
+            child = ref()
+            if child is not None:
+                child.close()
+        self._children = []
         if getattr(self, "_ctx", None) is not None and self._ctx.value:
             self.lib.femo_ctx_destroy(self._ctx)
             self._ctx = C.c_void_p()

@@ -260,7 +260,7 @@ def clt_matrix(h, E, nu, hE, Ju, mode="value"):
         C[:, 2, 2] = c * 0.5 * (1 - nu)
         return C
 
-    D = np.zeros((nc, 9, 9))
+    D = np.zeros((nc, 9, 9), dtype=np.result_type(np.float64, np.asarray(Ju).dtype))   # complex Ju: oracle/shape_ref.py
     if mode == "value":
         C = Cmat(E, nu); G = E / 2 / (1 + nu)
         D[:, 0:3, 0:3] = h[:, None, None] * C

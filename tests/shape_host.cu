@@ -1,0 +1,77 @@
+// CPU harness around femo_alpha_b200/csrc/shape_partials.cuh for tests/test_shape_host.py: the same
+// __host__ __device__ functions the CUDA kernels call (k_cell_op<OP_SHAPE_*> in outputs.cu), run on the host by an
+// nvcc-compiled shared object (no GPU needed), one cell at a time with the quadrature sum of the kernel.
+#include "../femo_alpha_b200/csrc/shape_partials.cuh"
+#include "../femo_alpha_b200/csrc/tables.hpp"
+
+// stubs: femo_internal.cuh declares these for the library
+int femo_fail(const std::string&) { return 1; }
+
+namespace {
+struct CellIn {
+  V3 xv[4], uh[4];
+  double h[4], E[4], nu[4], rho[4];
+  V3 f[4];
+};
+void load_cell(int64_t c, const double* xv, const double* uh, const double* hv, const double* Ev, const double* nuv,
+               const double* rhov, const double* fv, CellIn& I) {
+  for (int v = 0; v < 4; ++v) {
+    I.xv[v] = ldv3(xv + (c * 4 + v) * 3);
+    I.uh[v] = ldv3(uh + (c * 4 + v) * 3);
+    I.h[v] = hv[c * 4 + v]; I.E[v] = Ev[c * 4 + v]; I.nu[v] = nuv[c * 4 + v]; I.rho[v] = rhov[c * 4 + v];
+    I.f[v] = ldv3(fv + (c * 4 + v) * 3);
+  }
+}
+}  // namespace
+
+extern "C" {
+
+// per-cell inputs: xv, uh, fv (nc,4,3); hv, Ev, nuv, rhov (nc,4) (vertex values; repeat the cell value for DG0);
+// we, le (nc,39); hE (nc).  op 0: shape_T (out nc x 12, with_load = flag), 1: shape_fwd (duh (nc,4,3), out nc x 39),
+// 2: measure (flag 0: u.u, 1: rho h; out nc x 12)
+int shape_host(int op, int m, int64_t nc, const double* xv, const double* uh, const double* we, const double* le,
+               const double* hv, const double* Ev, const double* nuv, const double* rhov, const double* hE,
+               const double* fv, const double* duh, int flag, double* out) {
+  Tables T;
+  build_tables(T, m);
+  const int nout = op == 1 ? 39 : 12;
+  for (int64_t c = 0; c < nc; ++c) {
+    CellIn I;
+    load_cell(c, xv, uh, hv, Ev, nuv, rhov, fv, I);
+    double acc[39];
+    for (int i = 0; i < nout; ++i) acc[i] = 0.0;
+    for (int q = 0; q < T.nq; ++q) {
+      QpGeom g;
+      qp_geometry(I.xv, I.uh, T.X0[q], T.X1[q], g);
+      const double wd = T.W[q] * g.detJ;
+      double hq = 0, Eq = 0, nuq = 0, rhoq = 0;
+      V3 fq = v3(0, 0, 0);
+      for (int v = 0; v < 4; ++v) {
+        const double N = T.n1[q][v];
+        hq += N * I.h[v]; Eq += N * I.E[v]; nuq += N * I.nu[v]; rhoq += N * I.rho[v];
+        fq = fq + N * I.f[v];
+      }
+      const Coefs cf = clt_coefs(hq, Eq, nuq, hE[c], g.Ju, 0);
+      double o[39];
+      if (op == 0) shape_T_qp(g, &T, q, we + c * 39, le + c * 39, cf, fq, wd, flag, o);
+      else if (op == 1) {
+        V3 d[4];
+        for (int v = 0; v < 4; ++v) d[v] = ldv3(duh + (c * 4 + v) * 3);
+        shape_fwd_qp(g, &T, q, we + c * 39, cf, fq, wd, d, o);
+      } else {
+        double cq;
+        if (flag == 0) {
+          V3 u = v3(0, 0, 0);
+          for (int a = 0; a < 9; ++a) u = u + T.phi2[q][a] * ldv3(we + c * 39 + 3 * a);
+          cq = dot(u, u);
+        } else cq = rhoq * hq;
+        shape_measure_qp(g, &T, q, wd * cq, o);
+      }
+      for (int i = 0; i < nout; ++i) acc[i] += o[i];
+    }
+    for (int i = 0; i < nout; ++i) out[c * nout + i] = acc[i];
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,85 @@
+"""The shape-partial element maths of the CUDA kernels (femo_alpha_b200/csrc/shape_partials.cuh) run on
+the CPU -- the same __host__ __device__ functions, compiled by nvcc into a host harness (tests/shape_host.cu) -- and
+checked against the complex-step oracle (oracle/shape_ref.py).  No GPU needed; the GPU parity test of the kernels
+themselves is tests/test_gpu_shape.py."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import shape_ref as S
+from tests.problems import make_problem, oracle_for
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "..", "femo_alpha_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def host_lib():
+    out = os.path.join(HERE, "_build", "libshape_host.so")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    src = os.path.join(HERE, "shape_host.cu")
+    deps = [src] + [os.path.join(CSRC, f) for f in ("shape_partials.cuh", "femo_internal.cuh", "tables.hpp")]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        nvcc = "/usr/local/cuda/bin/nvcc" if os.path.exists("/usr/local/cuda/bin/nvcc") else "nvcc"
+        subprocess.run([nvcc, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC",
+                        "-o", out, src], check=True)
+    return ctypes.CDLL(out)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def run(lib, o, op, w, lam=None, duhat=None, flag=0):
+    t = o.topo
+    nc = t.nc
+    per = lambda a: np.ascontiguousarray(np.repeat(a[:, None], 4, 1) if o.ewm else a[t.cv])
+    xv = np.ascontiguousarray(t.x[t.cv]); uh = np.ascontiguousarray(o.uhat.reshape(-1, 3)[t.cv])
+    f3 = o.f.reshape(-1, 3)
+    fv = np.ascontiguousarray(np.repeat(f3[:, None, :], 4, 1) if o.ewp else f3[t.cv])
+    we = np.ascontiguousarray(w[t.cell_dofs]); le = np.ascontiguousarray((w if lam is None else lam)[t.cell_dofs])
+    du = np.ascontiguousarray((np.zeros(3 * t.nn) if duhat is None else duhat).reshape(-1, 3)[t.cv])
+    nout = 39 if op == 1 else 12
+    out = np.zeros((nc, nout))
+    rc = lib.shape_host(op, o.m, ctypes.c_int64(nc), _p(xv), _p(uh), _p(we), _p(le), _p(per(o.h)), _p(per(o.E)), _p(per(o.nu)),
+                        _p(per(o.rho)), _p(np.ascontiguousarray(o.hE)), _p(fv), _p(du), flag, _p(out))
+    assert rc == 0
+    if op == 1:
+        r = np.zeros(t.ndof); np.add.at(r, t.cell_dofs.ravel(), out.ravel())
+        return r
+    g = np.zeros((t.nn, 3)); np.add.at(g, t.cv.ravel(), out.reshape(-1, 3))
+    return g.ravel()
+
+
+def rel(a, b):
+    return np.abs(a - b).max() / np.abs(b).max()
+
+
+@pytest.mark.parametrize("name", ["warped", "skew_planar", "plate_varh", "plate_dg0"])
+def test_shape_partials_against_complex_step(host_lib, name):
+    p = make_problem(name)
+    o = oracle_for(p)
+    rng = np.random.default_rng(0)
+    n = o.topo.ndof
+    w, lam, du = rng.standard_normal(n), rng.standard_normal(n), rng.standard_normal(3 * o.topo.nn)
+    assert rel(run(host_lib, o, 0, w, lam, flag=1), S.dRduhat_T_apply(o, w, lam)) < 1e-11
+    assert rel(run(host_lib, o, 1, w, duhat=du), S.dRduhat_apply(o, w, du)) < 1e-11
+    assert rel(run(host_lib, o, 2, w, flag=0), S.doutput_duhat(o, "compliance", w)) < 1e-11
+    assert rel(run(host_lib, o, 2, w, flag=1), S.doutput_duhat(o, "mass", w)) < 1e-11
+    assert rel(0.5 * run(host_lib, o, 0, w, w, flag=0), S.doutput_duhat(o, "elastic_energy", w)) < 1e-11
+
+
+def test_complex_step_oracle_against_finite_differences():
+    p = make_problem("warped")
+    o = oracle_for(p)
+    rng = np.random.default_rng(1)
+    w, du = rng.standard_normal(o.topo.ndof), rng.standard_normal(3 * o.topo.nn)
+    assert rel(S.residual_at(o, w, o.uhat), o.assemble_residual(w)) < 1e-13
+    eps = 1e-6
+    fd = (S.residual_at(o, w, o.uhat + eps * du) - S.residual_at(o, w, o.uhat - eps * du)) / (2 * eps)
+    assert rel(S.dRduhat_apply(o, w, du), fd) < 1e-8
+    lam = rng.standard_normal(o.topo.ndof)
+    assert np.isclose(lam @ S.dRduhat_apply(o, w, du), S.dRduhat_T_apply(o, w, lam) @ du, rtol=1e-12)
