@@ -8,7 +8,7 @@
 // gradient map) every strain is linear in k, and the shear / drilling stiffnesses and the load carry one factor J:
 //     s(uhat) = lam^T R = sum_q wd [ eps(lam; k)^T D(J) eps(w; k) - J f . lam_u ]
 //     d k_ab = -(Kx_a . duhat_v) (gN_v F^-1 E_b),        dJ = J duhat_v . (F^-T gN_v),     gN_v = dN_v/dX Kinv
-// Host + device (FEMO_HD): tests/shape_host.cu runs the same functions on the CPU against the complex-step oracle.
+// Host + device (FEMO_HD): tests/shape_host.cu runs the same functions on the CPU against a complex-step checker.
 #pragma once
 #include "femo_internal.cuh"
 
