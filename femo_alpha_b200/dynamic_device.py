@@ -36,7 +36,10 @@ class DynamicShellDevice:
         """Destroy the handle.  Must run before the context (and an attached hierarchy) is destroyed; ShellDevice.close
         and ShellHierarchy.close call it for the handles registered with them."""
         if getattr(self, "_h", None) is not None and self._h.value:
-            if getattr(self.dev, "_ctx", None) is not None and self.dev._ctx.value:
+            hier = getattr(self, "_hier", None)
+            ctx_alive = getattr(self.dev, "_ctx", None) is not None and self.dev._ctx.value
+            hier_alive = hier is None or (getattr(hier, "_mg", None) is not None and hier._mg.value)
+            if ctx_alive and hier_alive:
                 self.lib.femo_dyn_destroy(self._h)
             self._h = C.c_void_p()
 

@@ -137,6 +137,9 @@ class ShellHierarchy:
                        ShellDevice(n, q, self.ewm, self.ewp, quadrature_degree, device) for l, (n, q) in enumerate(meshes)]
         self.fine = self.levels[0]
         self.fine._mg = self
+        self._closing = False
+        for d in self.levels:           # whichever object is finalised first, the tear-down runs through close() below
+            d._owner = self
         self.cheb_degree = int(cheb_degree)
         # the dense coarse inverse is recomputed at every `coarse_refresh`-th set-up (1 = always); in between the
         # previous one is reused (lagged coarse solve)
@@ -260,6 +263,11 @@ class ShellHierarchy:
         return self.solve(rhs, rtol, max_it, zero_bc=True)
 
     def close(self):
+        """Ordered tear-down: dynamic handles, then the multigrid object, then the level contexts (the C side keeps
+        plain pointers between them)."""
+        if getattr(self, "_closing", False):
+            return
+        self._closing = True
         for ref in getattr(self, "_children", []):
             child = ref()
             if child is not None:
@@ -270,6 +278,7 @@ class ShellHierarchy:
             self._mg = C.c_void_p()
         for d in getattr(self, "levels", []):
             d._mg = None
+            d._owner = None
             d.close()
 
     def __del__(self):

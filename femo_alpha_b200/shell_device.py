@@ -37,8 +37,13 @@ class ShellDevice:
         self.last_solve = dict(iters=0, relres=0.0)
         self._mg = None                 # ShellHierarchy this device is the finest level of (multigrid.py)
         self._children = []             # weak references to handles that borrow this context (DynamicShellDevice)
+        self._owner = None              # ShellHierarchy this device is a level of: it tears down in order (handles, mg, levels)
 
     def close(self):
+        owner = getattr(self, "_owner", None)
+        if owner is not None and not owner._closing:
+            owner.close()               # closes every level, this one included
+            return
         for ref in getattr(self, "_children", []):
             child = ref()
             if child is not None:
