@@ -11,6 +11,7 @@
 // Host + device (FEMO_HD): tests/shape_host.cu runs the same functions on the CPU against a complex-step checker.
 #pragma once
 #include "femo_internal.cuh"
+#include "stress_point.cuh"
 
 #ifdef __CUDACC__
 
@@ -164,6 +165,43 @@ FEMO_HD void shape_measure_qp(const QpGeom& g, const Tables* tab, int q, double 
   for (int v = 0; v < 4; ++v) {
     const ShapeVert sv = shape_vert(g, dN0[v], dN1[v]);
     const V3 r = (wdc * g.Ju) * sv.c;
+    out12[3 * v] = r.x; out12[3 * v + 1] = r.y; out12[3 * v + 2] = r.z;
+  }
+}
+
+// d/duhat_v of  wd J (m sigma_vm)^rho  at one quadrature point (the integrand of pnorm_stress, rm_shell_pde.py:112-128;
+// the area normalisation alpha is a constant of the form).  sigma_vm (top / mid / bottom surface) depends on uhat
+// through the membrane and bending strains and through grad(h) (CG1 thickness), all linear in the gradient map k.
+//   hv: nodal thickness (ignored when ewm), P: the point evaluated by vm_at at the actual k
+FEMO_HD void shape_pnorm_qp(const QpGeom& g, const Tables* tab, int q, const double* we, const double* hv, int ewm,
+                            double xi_sign, const VmPoint& P, double wd, double sm, double srho, double* out12) {
+  const double pw = pow(sm * P.vm, srho);
+  const double G = (P.vm > 0) ? wd * g.Ju * srho * sm * pow(sm * P.vm, srho - 1.0) : 0.0;
+  double Gk[4];
+#pragma unroll
+  for (int ab = 0; ab < 4; ++ab) {
+    KMap e; e.k00 = (ab == 0); e.k01 = (ab == 1); e.k10 = (ab == 2); e.k11 = (ab == 3);
+    double s[9];
+    strains_k(g, tab, q, we, e, 0.0, s);
+    double gh0 = 0.0, gh1 = 0.0;
+    if (!ewm)
+      for (int v = 0; v < 4; ++v) {
+        gh0 += 0.5 * xi_sign * hv[v] * (tab->dn1[q][v][0] * e.k00 + tab->dn1[q][v][1] * e.k10);
+        gh1 += 0.5 * xi_sign * hv[v] * (tab->dn1[q][v][0] * e.k01 + tab->dn1[q][v][1] * e.k11);
+      }
+    const double de0 = s[0] - P.xi * s[3] - P.b0 * gh0;
+    const double de1 = s[1] - P.xi * s[4] - P.b1 * gh1;
+    const double de2 = s[2] - P.xi * s[5] - (P.b0 * gh1 + P.b1 * gh0);
+    Gk[ab] = G * (P.t[0] * de0 + P.t[1] * de1 + P.t[2] * de2);
+  }
+  const double GJ = wd * pw * g.Ju;
+  const double dN0[4] = {-(1 - tab->X1[q]), (1 - tab->X1[q]), -tab->X1[q], tab->X1[q]};
+  const double dN1[4] = {-(1 - tab->X0[q]), -tab->X0[q], (1 - tab->X0[q]), tab->X0[q]};
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    const ShapeVert sv = shape_vert(g, dN0[v], dN1[v]);
+    const double c0 = -(Gk[0] * sv.a0 + Gk[1] * sv.a1), c1 = -(Gk[2] * sv.a0 + Gk[3] * sv.a1);
+    const V3 r = c0 * g.Kx0 + c1 * g.Kx1 + GJ * sv.c;
     out12[3 * v] = r.x; out12[3 * v + 1] = r.y; out12[3 * v + 2] = r.z;
   }
 }

@@ -161,3 +161,30 @@ def test_operator_surface_check_totals():
     with pytest.raises(ValueError):
         StateOperation(plate_sim=ps, record=False).apply_inverse_jacobian(
             {'thickness': thickness.value}, {'disp_history': disp_history.value}, {}, {'disp_history': disp_history.value}, 'sideways')
+
+
+def test_energy_balance_at_scale():
+    """Size-independent property at a size the oracle cannot reach (320x64 cells, 3.1e5 dofs, V-cycle PCG): for a
+    constant load the implicit midpoint rule conserves  kinetic + strain energy - work  exactly (to the solver
+    tolerance), level by level."""
+    from femo_alpha_b200.mesh import createRectangleMesh, refine_uniform
+    from femo_alpha_b200.dynamic_rm_shell.plate_sim import PlateSim
+    mesh = refine_uniform(createRectangleMesh((0., 0.), (10., 2.), 40, 8), 3)
+    nn = mesh.geometry.x.shape[0]
+    n_steps, dt = 8, 0.015
+    ps = PlateSim(mesh, 1e8, 0.3, 10., dt, n_steps, quad_deg=6, solver="multigrid", rtol=1e-12)
+    f = np.tile([0., 0., -5.], nn)[None, :]
+    ps.update_t(np.full(nn, 0.1)); ps.update_f_history(f)
+    w = ps.solve_dynamic_problem(ps.SVK_residual()).T                 # (levels, ndof)
+    assert ps._dyn.info()["solver"] == "multigrid" and ps.fe_dofs == 310662
+    strain = ps._dyn.energies()
+    F = ps.device.assemble_load()
+    F[ps.bc_dofs] = 0.0
+    v = np.zeros(ps.fe_dofs)
+    bal = []
+    for i in range(1, n_steps + 1):
+        v = 2.0 / dt * (w[i] - w[i - 1]) - v
+        bal.append(0.5 * v @ ps._dyn.mass_apply(v) + strain[i] - F @ w[i])
+    scale = abs(F @ w[-1])
+    assert scale > 0 and np.ptp(bal) < 1e-8 * scale and abs(bal[0]) < 1e-8 * scale
+    ps.hierarchy.close()
