@@ -1,6 +1,5 @@
 """Explicit CSDL operations for scalar and field outputs -- drop-in for
 femo_alpha/csdl_alpha_opt/output_operation.py:6-128."""
-import warnings
 
 import numpy as np
 
@@ -46,18 +45,10 @@ class OutputOperation(csdl.CustomExplicitOperation):
             update(self.args_dict[arg_name]["function"], input_vals[arg_name])
         output_vals[self.output_name] = assemble(self.fea_output["form"])
 
-    _uhat_warned = False
-
     def compute_derivatives(self, input_vals, output_vals, derivatives):
         for arg_name in input_vals:
             update(self.args_dict[arg_name]["function"], input_vals[arg_name])
         for arg_name in input_vals:
-            if arg_name == 'uhat' and self.output_name not in ('compliance', 'mass', 'elastic_energy', 'volume'):
-                if not OutputOperation._uhat_warned:
-                    warnings.warn("femo_alpha_b200: d(%s)/d(uhat) is not implemented; returned as zero" % self.output_name)
-                    OutputOperation._uhat_warned = True
-                derivatives[self.output_name, arg_name] = np.zeros(len(input_vals[arg_name]))
-                continue
             derivatives[self.output_name, arg_name] = assemble(
                 computePartials(self.fea_output["form"], self.args_dict[arg_name]["function"]),
                 dim=self.output_dim + 1)

@@ -96,3 +96,32 @@ def _cell_output(o, name, w, uh_cells):
 def doutput_duhat(o, name, w):
     """d output / d uhat (3 nn) for compliance, mass, elastic_energy."""
     return _vertex_gradient(o, lambda uh: _cell_output(o, name, w, uh))
+
+
+def _cell_pnorm(o, w, uh_cells, m, rho, cells=None):
+    """Per-cell  int (m vm)^rho J dx  (degree-4 rule), uhat cell-local and possibly complex (rm_shell_pde.py:112-121)."""
+    from .rm_shell_ref import _von_mises_at, gauss01
+    t = o.topo
+    xv = t.x[t.cv]
+    we = w[t.cell_dofs]
+    pick = (lambda a: a) if o.ewm else (lambda a: a[t.cv])
+    gx, gw = gauss01(3)
+    mask = np.ones(t.nc) if cells is None else np.isin(np.arange(t.nc), cells).astype(float)
+    out = np.zeros(t.nc, dtype=uh_cells.dtype)
+    for i in range(3):
+        for j in range(3):
+            g = qp_geometry(xv, uh_cells, gx[i], gx[j])
+            vm = _von_mises_at(g, we.astype(uh_cells.dtype), pick(o.h), pick(o.E), pick(o.nu), o.ewm)
+            out += mask * gw[i] * gw[j] * g.detJ * g.Ju * (m * vm) ** rho
+    return out
+
+
+def dpnorm_duhat(o, w, m=1e-6, rho=100, cells=None):
+    """d pnorm_stress / d uhat (3 nn); the area normalisation alpha is a constant of the form (pde:122-127)."""
+    t = o.topo
+    xv = t.x[t.cv]
+    mask = np.ones(t.nc) if cells is None else np.isin(np.arange(t.nc), cells).astype(float)
+    area = 0.0
+    for X0, X1, wq in o.qp:
+        area += np.sum(mask * wq * qp_geometry(xv, np.zeros_like(xv), X0, X1).detJ)
+    return _vertex_gradient(o, lambda uh: _cell_pnorm(o, w, uh, m, rho, cells)) / area

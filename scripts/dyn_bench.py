@@ -99,10 +99,15 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--large", action="store_true")
     ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--only", default="", help="run a single small mesh, e.g. 40x8 (profiling)")
     a = ap.parse_args()
     from femo_alpha_b200.mesh import createRectangleMesh, refine_uniform
     res = dict(config="BASELINE config 4: plate 2x10, quad_deg=3, E=1e8, nu=0.3, rho=10, h=0.1, 1-cos gust, f_z = 0.1 V_g(t)",
                gpu=[], cpu=[], large=[])
+    if a.only:
+        nx, ny = [int(v) for v in a.only.split("x")]
+        print(json.dumps(run_gpu(createRectangleMesh((0., 0.), (10., 2.), nx, ny), a.steps, "auto")), flush=True)
+        return
     for nx, ny in ((10, 2), (20, 4), (40, 8)):
         mesh = createRectangleMesh((0., 0.), (10., 2.), nx, ny)
         r = run_gpu(mesh, a.steps, "auto"); r["mesh"] = "%dx%d" % (nx, ny); res["gpu"].append(r)

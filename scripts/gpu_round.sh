@@ -1,17 +1,31 @@
 #!/bin/bash
-# One GPU-box pass: parity tests, smoke, bench, ncu launch list, ncu full capture of the top kernel.
+# One GPU-box session (run through `gpurun -- bash scripts/gpu_round.sh <sections...>`); every section is guarded by
+# its own timeout and writes under gpurun_out/${TAG}_*.  Sections:
+#   suite   full `pytest -m gpu` + smoke()
+#   bench   bench.py (ours) + bench.py --impl reference
+#   dyn     config-4 timings (scripts/dyn_bench.py --large)
+#   ncu     launch list of a short bench run and of a short dynamic run (per-launch durations, no clock control)
+#   dist    2-GPU parity test + 2-GPU bench line (needs `gpurun --gpus 2`)
 set -u
 mkdir -p gpurun_out
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/smoke.log
-python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
-tail -c 3000 gpurun_out/bench.json
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench ref rc=$?"
-SHORT="python bench.py --steps 2 --warmup 3 --krylov-iters 3"
-$SHORT > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv $SHORT > gpurun_out/ncu_list.log 2>&1
-echo "ncu list rc=$?"
-$SHORT > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k_gather -s 3 -c 1 -o gpurun_out/prof_gather $SHORT > gpurun_out/ncu_full.log 2>&1
-echo "ncu full rc=$?"
+T=${TAG:-r01}
+for sec in "$@"; do
+  case "$sec" in
+    suite)
+      timeout 1500 python -m pytest tests -m gpu -q --tb=short > gpurun_out/${T}_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -n 30 gpurun_out/${T}_pytest_gpu.log
+      python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.log 2>&1; echo "smoke rc=$?"; tail -n 3 gpurun_out/${T}_smoke.log ;;
+    bench)
+      timeout 900 python bench.py --krylov-iters 50 > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench rc=$?"; cat gpurun_out/${T}_bench.json; tail -n 3 gpurun_out/${T}_bench.err
+      timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_reference.json 2>> gpurun_out/${T}_bench.err; echo "bench ref rc=$?"; cat gpurun_out/${T}_bench_reference.json ;;
+    dyn)
+      timeout 600 python scripts/dyn_bench.py --large --out gpurun_out/${T}_dyn_bench.json > gpurun_out/${T}_dyn_bench.log 2>&1; echo "dyn bench rc=$?"; tail -n 12 gpurun_out/${T}_dyn_bench.log ;;
+    ncu)
+      SHORT="python bench.py --steps 2 --warmup 3 --krylov-iters 3 --no-mg"
+      timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches_bench_steps2.csv $SHORT > gpurun_out/${T}_ncu_list.log 2>&1; echo "ncu list rc=$?"
+      timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${T}_launches_dyn_40x8.csv python scripts/dyn_bench.py --steps 20 --only 40x8 > gpurun_out/${T}_ncu_dyn.log 2>&1; echo "ncu dyn rc=$?" ;;
+    dist)
+      timeout 900 python -m pytest tests/test_gpu_dist.py -m gpu -q --tb=short > gpurun_out/${T}_pytest_gpu_dist.log 2>&1; echo "pytest dist rc=$?"; tail -n 8 gpurun_out/${T}_pytest_gpu_dist.log
+      timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29544 bench.py --gpus 2 --steps 10 --warmup 3 --krylov-iters 50 > gpurun_out/${T}_bench_2gpu.json 2> gpurun_out/${T}_bench_2gpu.err; echo "bench 2gpu rc=$?"; cat gpurun_out/${T}_bench_2gpu.json; tail -n 3 gpurun_out/${T}_bench_2gpu.err ;;
+    *) echo "unknown section $sec" ;;
+  esac
+done

@@ -28,10 +28,11 @@ extern "C" {
 
 // per-cell inputs: xv, uh, fv (nc,4,3); hv, Ev, nuv, rhov (nc,4) (vertex values; repeat the cell value for DG0);
 // we, le (nc,39); hE (nc).  op 0: shape_T (out nc x 12, with_load = flag), 1: shape_fwd (duh (nc,4,3), out nc x 39),
-// 2: measure (flag 0: u.u, 1: rho h; out nc x 12)
+// 2: measure (flag 0: u.u, 1: rho h; out nc x 12), 3: pnorm integrand (flag: element-wise material; pm, prho; degree-4 rule
+// is the caller's choice of m)
 int shape_host(int op, int m, int64_t nc, const double* xv, const double* uh, const double* we, const double* le,
                const double* hv, const double* Ev, const double* nuv, const double* rhov, const double* hE,
-               const double* fv, const double* duh, int flag, double* out) {
+               const double* fv, const double* duh, int flag, double pm, double prho, double* out) {
   Tables T;
   build_tables(T, m);
   const int nout = op == 1 ? 39 : 12;
@@ -58,6 +59,10 @@ int shape_host(int op, int m, int64_t nc, const double* xv, const double* uh, co
         V3 d[4];
         for (int v = 0; v < 4; ++v) d[v] = ldv3(duh + (c * 4 + v) * 3);
         shape_fwd_qp(g, &T, q, we + c * 39, cf, fq, wd, d, o);
+      } else if (op == 3) {
+        VmPoint P;
+        vm_at(g, &T, q, we + c * 39, hq, Eq, nuq, I.h, flag, 1.0, P);
+        shape_pnorm_qp(g, &T, q, we + c * 39, I.h, flag, 1.0, P, wd, pm, prho, o);
       } else {
         double cq;
         if (flag == 0) {

@@ -27,8 +27,12 @@ def test_shape_partials(name):
     for out in ("compliance", "mass", "elastic_energy"):
         assert rel(d.output_grad(out, "uhat"), S.doutput_duhat(o, out, w)) < 1e-9
     assert np.abs(d.output_grad("volume", "uhat")).max() == 0.0
-    with pytest.raises(RuntimeError):
-        d.output_grad("pnorm_stress", "uhat")
+    d.set_stress_params(1e-6, 6.0)
+    assert rel(d.output_grad("pnorm_stress", "uhat"), S.dpnorm_duhat(o, w, 1e-6, 6.0)) < 1e-9
+    cells = np.arange(o.topo.nc)[::2]
+    tags = np.full(o.topo.nc, 3, dtype=np.int32); tags[cells] = 7
+    d.set_cell_tags(tags)
+    assert rel(d.pnorm_stress_grad("uhat", tag=7), S.dpnorm_duhat(o, w, 1e-6, 6.0, cells=cells)) < 1e-9
 
 
 def test_total_shape_derivative_of_the_compliance():

@@ -33,7 +33,7 @@ def _p(a):
     return a.ctypes.data_as(ctypes.c_void_p)
 
 
-def run(lib, o, op, w, lam=None, duhat=None, flag=0):
+def run(lib, o, op, w, lam=None, duhat=None, flag=0, m1d=None, pm=1e-6, prho=100.0):
     t = o.topo
     nc = t.nc
     per = lambda a: np.ascontiguousarray(np.repeat(a[:, None], 4, 1) if o.ewm else a[t.cv])
@@ -44,8 +44,9 @@ def run(lib, o, op, w, lam=None, duhat=None, flag=0):
     du = np.ascontiguousarray((np.zeros(3 * t.nn) if duhat is None else duhat).reshape(-1, 3)[t.cv])
     nout = 39 if op == 1 else 12
     out = np.zeros((nc, nout))
-    rc = lib.shape_host(op, o.m, ctypes.c_int64(nc), _p(xv), _p(uh), _p(we), _p(le), _p(per(o.h)), _p(per(o.E)), _p(per(o.nu)),
-                        _p(per(o.rho)), _p(np.ascontiguousarray(o.hE)), _p(fv), _p(du), flag, _p(out))
+    rc = lib.shape_host(op, o.m if m1d is None else m1d, ctypes.c_int64(nc), _p(xv), _p(uh), _p(we), _p(le), _p(per(o.h)),
+                        _p(per(o.E)), _p(per(o.nu)), _p(per(o.rho)), _p(np.ascontiguousarray(o.hE)), _p(fv), _p(du), flag,
+                        ctypes.c_double(pm), ctypes.c_double(prho), _p(out))
     assert rc == 0
     if op == 1:
         r = np.zeros(t.ndof); np.add.at(r, t.cell_dofs.ravel(), out.ravel())
@@ -70,6 +71,13 @@ def test_shape_partials_against_complex_step(host_lib, name):
     assert rel(run(host_lib, o, 2, w, flag=0), S.doutput_duhat(o, "compliance", w)) < 1e-11
     assert rel(run(host_lib, o, 2, w, flag=1), S.doutput_duhat(o, "mass", w)) < 1e-11
     assert rel(0.5 * run(host_lib, o, 0, w, w, flag=0), S.doutput_duhat(o, "elastic_energy", w)) < 1e-11
+    # p-norm of the von Mises stress (degree-4 rule = 3 points per direction); moderate exponent and scale keep the
+    # integrand well inside the fp64 range for a random state
+    pm, prho = 1e-6, 6.0
+    t = o.topo
+    area = sum(wq * S.qp_geometry(t.x[t.cv], np.zeros((t.nc, 4, 3)), X0, X1).detJ.sum() for X0, X1, wq in o.qp)
+    got = run(host_lib, o, 3, w, flag=int(o.ewm), m1d=3, pm=pm, prho=prho) / area
+    assert rel(got, S.dpnorm_duhat(o, w, pm, prho)) < 1e-10
 
 
 def test_complex_step_oracle_against_finite_differences():
