@@ -35,9 +35,45 @@ def summarize(o, name):
     print(name, t.ndof, K.nnz, d["compliance"])
 
 
+DYN_CASES = [("plate_varh", 6, False), ("plate_dg0", 3, True), ("warped", 6, True)]      # (problem, quad_deg, self weight)
+
+
+def dynamic_and_shape(name, deg, sw):
+    """Fixtures of the time-stepped path (oracle/dynamic_ref.py; config-4 style: 6 implicit midpoint steps, dt = 0.01)
+    and of the shape partials (oracle/shape_ref.py, complex step)."""
+    from oracle.dynamic_ref import DynamicShellOracle
+    from oracle import shape_ref
+    p = make_problem(name)
+    o = oracle_for(p, quadrature_degree=deg)
+    rng = np.random.default_rng(11)
+    n_steps, dt = 6, 0.01
+    f_hist = np.stack([p["F_solid"] * (0.4 + 0.1 * i) for i in range(n_steps + 1)])
+    od = DynamicShellOracle(o, dt, n_steps, add_self_weight=sw)
+    w = od.solve(f_hist)
+    dE = od.dtotal_strain_energy_dw(w)
+    lam = od.adjoint_recurrence(dE)
+    x = rng.standard_normal(o.topo.ndof)
+    d = dict(quad_deg=deg, self_weight=int(sw), dt=dt, n_steps=n_steps, f_hist=f_hist, w_hist=w, energies=od.energy,
+             total_strain_energy=od.total_strain_energy(w), lam_hist=lam,
+             grad_total=od.dtotal_strain_energy_dh(w) - od.dRdh_T(w, lam), probe=x, M_probe=od.mass_matrix() @ x,
+             volume=od.volume())
+    o.set_inputs(F_solid=p["F_solid"])
+    ws = rng.standard_normal(o.topo.ndof); ls = rng.standard_normal(o.topo.ndof); du = rng.standard_normal(3 * o.topo.nn)
+    d.update(shape_w=ws, shape_lam=ls, shape_du=du, dRduhat_T=shape_ref.dRduhat_T_apply(o, ws, ls),
+             dRduhat=shape_ref.dRduhat_apply(o, ws, du), dcompliance_duhat=shape_ref.doutput_duhat(o, "compliance", ws),
+             dmass_duhat=shape_ref.doutput_duhat(o, "mass", ws), dpnorm_duhat=shape_ref.dpnorm_duhat(o, ws, 1e-6, 6.0))
+    np.savez_compressed(os.path.join(OUT, "dyn_shape_" + name + ".npz"), **d)
+    print("dyn_shape", name, d["total_strain_energy"])
+
+
 if __name__ == "__main__":
-    for name in PROBLEMS:
-        summarize(oracle_for(make_problem(name)), name)
+    if "--dynamic-only" not in sys.argv:
+        for name in PROBLEMS:
+            summarize(oracle_for(make_problem(name)), name)
+    for case in DYN_CASES:
+        dynamic_and_shape(*case)
+    if "--dynamic-only" in sys.argv:
+        sys.exit(0)
     # wing box of the reference tree (the only real mesh in the checkout), clamp y <= 1e-3, Al, -z pressure
     wb = "/root/reference/examples/advanced_examples/lpc_shell_opt/data_files/mesh_bay_data.pickle"
     if os.path.exists(wb):

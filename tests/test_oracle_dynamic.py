@@ -120,3 +120,19 @@ def test_volume():
     p, o, d, _ = small_dynamic("plate_varh")
     g = d.dvolume_dh()
     assert np.isclose(g @ o.h, d.volume(), rtol=1e-13)     # volume is linear in the nodal thickness
+
+
+@pytest.mark.parametrize("name", ["plate_varh", "plate_dg0", "warped"])
+def test_golden_fixtures_are_reproduced(name):
+    """tests/golden/dyn_shape_*.npz (the fixtures the GPU box checks against) are what the oracles produce today."""
+    import os
+    from oracle import shape_ref
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "dyn_shape_" + name + ".npz"))
+    p = make_problem(name)
+    o = oracle_for(p, quadrature_degree=int(g["quad_deg"]))
+    d = DynamicShellOracle(o, float(g["dt"]), int(g["n_steps"]), add_self_weight=bool(g["self_weight"]))
+    w = d.solve(g["f_hist"])
+    assert np.abs(w - g["w_hist"]).max() <= 1e-12 * np.abs(g["w_hist"]).max()
+    o.set_inputs(F_solid=p["F_solid"])
+    got = shape_ref.dRduhat_T_apply(o, g["shape_w"], g["shape_lam"])
+    assert np.abs(got - g["dRduhat_T"]).max() <= 1e-12 * np.abs(g["dRduhat_T"]).max()
