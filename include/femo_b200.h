@@ -215,7 +215,8 @@ int femo_dyn_set_mg(femo_dyn* d, femo_mg* mg);
  * solver: 0 auto (dense if n_dof <= 46000, else multigrid if attached, else PCG), 1 dense, 2 PCG, 3 multigrid */
 int femo_dyn_setup(femo_dyn* d, int solver);
 /* time loop from zero initial conditions; f_history (n_rows, n_force) row-major, rows beyond the last repeat it
- * (plate_sim.py:314-319).  Fills the resident history and the strain energy of every level (plate_sim.py:337). */
+ * (plate_sim.py:314-319).  Fills the resident history and the strain energy of every level (plate_sim.py:337).
+ * The FEMO_F_SOLID input of the context is left at the last row used (as PlateSim.update_f does). */
 int femo_dyn_solve(femo_dyn* d, const double* f_history, int64_t n_rows, double rtol, int max_it,
                    int64_t* total_iters, int on_device);
 int femo_dyn_get_history(femo_dyn* d, double* w_hist, int on_device);      /* (n_steps+1, n_dof) */
