@@ -25,6 +25,7 @@
 // PCG when a multigrid hierarchy is attached (its levels carry their own A).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 #include "femo_internal.cuh"
 
@@ -44,6 +45,13 @@ struct femo_dyn {
   double* Cinv = nullptr; int64_t ncinv = 0;
   double *v = nullptr, *kw = nullptr, *t1 = nullptr, *t2 = nullptr, *rhs = nullptr, *W = nullptr, *mu = nullptr, *lm = nullptr;
   double* dh = nullptr;
+  double *fh = nullptr, *en_dev = nullptr;    // load history (levels x n_force) and per-level w.Kw on the device
+  // the forward loop of the dense solver is launch-bound (13 small launches per step): captured once into a CUDA
+  // graph and replayed by every later femo_dyn_solve of the same shape (FEMO_DYN_GRAPH=0 disables)
+  cudaStream_t gstream = nullptr;             // capture needs a non-default stream: the context runs on it for the call
+  cudaGraphExec_t fwd_graph = nullptr;
+  int64_t fwd_graph_rows = -1;
+  int fwd_graph_nodes = 0;
   std::vector<double> energies;
   double ms_fwd = 0, ms_adj = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -55,6 +63,14 @@ struct DevGuard {
   int prev = 0;
   explicit DevGuard(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); }
   ~DevGuard() { cudaSetDevice(prev); }
+};
+
+// run the context on another stream for the lifetime of this object (both streams drained at the switches)
+struct StreamSwap {
+  femo_ctx* c = nullptr;
+  cudaStream_t old = nullptr;
+  StreamSwap(femo_ctx* ctx, cudaStream_t s) : c(ctx), old(ctx->stream) { cudaStreamSynchronize(old); c->stream = s; }
+  ~StreamSwap() { cudaStreamSynchronize(c->stream); c->stream = old; }
 };
 
 // mvals[d] = sum over the contributions (cell, a, b) of destination block d, ascending cell order, of the scalar
@@ -267,8 +283,11 @@ int femo_dyn_destroy(femo_dyn* d) {
   cudaStreamSynchronize(c->stream);
   if (d->mg) { for (int l = 0; l < mg_num_levels(d->mg); ++l) dyn_disable(mg_level_ctx(d->mg, l)); mg_invalidate(d->mg); }
   dyn_disable(c);
-  double** vecs[] = {&d->hist, &d->io1, &d->io2, &d->Cinv, &d->v, &d->kw, &d->t1, &d->t2, &d->rhs, &d->W, &d->mu, &d->lm, &d->dh};
+  double** vecs[] = {&d->hist, &d->io1, &d->io2, &d->Cinv, &d->v, &d->kw, &d->t1, &d->t2, &d->rhs, &d->W, &d->mu, &d->lm, &d->dh,
+                     &d->fh, &d->en_dev};
   for (double** v : vecs) dev_free(v);
+  if (d->fwd_graph) cudaGraphExecDestroy(d->fwd_graph);
+  if (d->gstream) cudaStreamDestroy(d->gstream);
   if (d->e0) cudaEventDestroy(d->e0);
   if (d->e1) cudaEventDestroy(d->e1);
   delete d;
@@ -308,6 +327,7 @@ int femo_dyn_setup(femo_dyn* d, int solver) {
   if (d->self_weight) TRY(self_weight_load(c, d->g_acc, d->W));
   else CUDA_TRY(cudaMemsetAsync(d->W, 0, sizeof(double) * c->ndof, c->stream));
   d->solver = s; d->ready = true; d->energies_valid = false;
+  if (d->fwd_graph) { cudaGraphExecDestroy(d->fwd_graph); d->fwd_graph = nullptr; }     // buffers may have moved
   return 0;
 }
 
@@ -320,32 +340,72 @@ int femo_dyn_solve(femo_dyn* d, const double* f_history, int64_t n_rows, double 
   const int64_t n = c->ndof;
   const double cm = 2.0 / (d->dt * d->dt), c2 = 2.0 / d->dt;
   int64_t iters = 0;
+  const char* genv = getenv("FEMO_DYN_GRAPH");
+  const bool use_graph = d->solver == 1 && !(genv && genv[0] == '0');
+  if (use_graph && !d->gstream) CUDA_TRY(cudaStreamCreateWithFlags(&d->gstream, cudaStreamNonBlocking));
+  StreamSwap sw(c, use_graph ? d->gstream : c->stream);
+  // the rows of the load history that are used (row min(i, n_rows - 1) at level i, plate_sim.py:314-319) go to the
+  // device in one copy; per-level strain energies are reduced on the device and read back once
+  const int64_t rows = std::min<int64_t>(n_rows, d->levels);
+  if (!d->fh) TRY(dev_alloc(&d->fh, (size_t)d->levels * c->n_f));
+  if (!d->en_dev) TRY(dev_alloc(&d->en_dev, (size_t)d->levels));
+  CUDA_TRY(cudaMemcpyAsync(d->fh, f_history, sizeof(double) * rows * c->n_f,
+                           on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+  CUDA_TRY(cudaMemsetAsync(d->en_dev, 0, sizeof(double) * d->levels, c->stream));
+
+  auto issue_steps = [&]() -> int {
+    CUDA_TRY(cudaMemsetAsync(d->hist, 0, sizeof(double) * n, c->stream));    // zero initial conditions (plate_sim.py:305-309)
+    CUDA_TRY(cudaMemsetAsync(d->v, 0, sizeof(double) * n, c->stream));
+    CUDA_TRY(cudaMemsetAsync(d->kw, 0, sizeof(double) * n, c->stream));
+    for (int i = 1; i < d->levels; ++i) {
+      const int64_t row = std::min<int64_t>(i, rows - 1);
+      CUDA_TRY(cudaMemcpyAsync(c->f, d->fh + row * c->n_f, sizeof(double) * c->n_f, cudaMemcpyDeviceToDevice, c->stream));
+      TRY(assemble_load(c, c->b));
+      const double* wo = d->hist + (size_t)(i - 1) * n;
+      double* wi = d->hist + (size_t)i * n;
+      // rhs = F + W - B w_old - C v_old = F + W - K w_old / 2 + M (c w_old + 2/dt v_old)
+      TRY(lin4(c, cm, wo, c2, d->v, 0, nullptr, 0, nullptr, nullptr, d->t1));
+      TRY(mass_spmv(c, d->t1, d->t2));
+      TRY(lin4(c, 1.0, c->b, 1.0, d->W, -0.5, d->kw, 1.0, d->t2, c->bcmask, d->rhs));
+      if (d->solver != 1)                                                    // warm start of the iterative solvers
+        CUDA_TRY(cudaMemcpyAsync(wi, wo, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+      TRY(dyn_linear_solve(d, d->rhs, wi, rtol, max_it, &iters));
+      TRY(lin4(c, c2, wi, -c2, wo, -1.0, d->v, 0, nullptr, nullptr, d->v));   // wdot_i (plate_sim.py:243-244)
+      TRY(bsr_spmv_vals(c, c->vals_K, wi, d->kw, 0));
+      TRY(dev_dot_async(c, wi, d->kw, n, d->en_dev + i));                     // 2 x strain energy (plate_sim.py:337)
+    }
+    return 0;
+  };
+
   cudaEventRecord(d->e0, c->stream);
-  CUDA_TRY(cudaMemsetAsync(d->hist, 0, sizeof(double) * n, c->stream));      // zero initial conditions (plate_sim.py:305-309)
-  CUDA_TRY(cudaMemsetAsync(d->v, 0, sizeof(double) * n, c->stream));
-  CUDA_TRY(cudaMemsetAsync(d->kw, 0, sizeof(double) * n, c->stream));
-  d->energies.assign(d->levels, 0.0);
-  for (int i = 1; i < d->levels; ++i) {
-    const int64_t row = std::min<int64_t>(i, n_rows - 1);                     // plate_sim.py:314-319
-    CUDA_TRY(cudaMemcpyAsync(c->f, f_history + row * c->n_f, sizeof(double) * c->n_f,
-                             on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    TRY(assemble_load(c, c->b));
-    const double* wo = d->hist + (size_t)(i - 1) * n;
-    double* wi = d->hist + (size_t)i * n;
-    // rhs = F + W - B w_old - C v_old = F + W - K w_old / 2 + M (c w_old + 2/dt v_old)
-    TRY(lin4(c, cm, wo, c2, d->v, 0, nullptr, 0, nullptr, nullptr, d->t1));
-    TRY(mass_spmv(c, d->t1, d->t2));
-    TRY(lin4(c, 1.0, c->b, 1.0, d->W, -0.5, d->kw, 1.0, d->t2, c->bcmask, d->rhs));
-    CUDA_TRY(cudaMemcpyAsync(wi, wo, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));   // warm start
-    TRY(dyn_linear_solve(d, d->rhs, wi, rtol, max_it, &iters));
-    TRY(lin4(c, c2, wi, -c2, wo, -1.0, d->v, 0, nullptr, nullptr, d->v));     // wdot_i (plate_sim.py:243-244)
-    TRY(bsr_spmv_vals(c, c->vals_K, wi, d->kw, 0));
-    double e = 0;
-    TRY(dev_dot(c, wi, d->kw, n, &e));                                        // strain energy (plate_sim.py:337)
-    d->energies[i] = 0.5 * e;
+  if (use_graph) {
+    if (!d->fwd_graph || d->fwd_graph_rows != rows) {
+      if (d->fwd_graph) { cudaGraphExecDestroy(d->fwd_graph); d->fwd_graph = nullptr; }
+      const int64_t l0 = c->launches;
+      cudaGraph_t graph = nullptr;
+      CUDA_TRY(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+      const int rc = issue_steps();
+      const cudaError_t ce = cudaStreamEndCapture(c->stream, &graph);
+      if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
+      if (ce != cudaSuccess) return femo_fail(std::string("femo_dyn_solve: stream capture failed: ") + cudaGetErrorString(ce));
+      const cudaError_t ie = cudaGraphInstantiate(&d->fwd_graph, graph, 0);
+      cudaGraphDestroy(graph);
+      if (ie != cudaSuccess) { d->fwd_graph = nullptr; return femo_fail(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ie)); }
+      d->fwd_graph_rows = rows;
+      d->fwd_graph_nodes = (int)(c->launches - l0);
+      c->launches = l0;
+    }
+    CUDA_TRY(cudaGraphLaunch(d->fwd_graph, c->stream));
+    c->launches += d->fwd_graph_nodes;
+    iters = d->n_steps;
+  } else {
+    TRY(issue_steps());
   }
   cudaEventRecord(d->e1, c->stream);
+  d->energies.assign(d->levels, 0.0);
+  CUDA_TRY(cudaMemcpyAsync(d->energies.data(), d->en_dev, sizeof(double) * d->levels, cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
+  for (double& e : d->energies) e *= 0.5;
   float ms = 0; cudaEventElapsedTime(&ms, d->e0, d->e1); d->ms_fwd = ms;
   d->energies_valid = true;
   if (total_iters) *total_iters = iters;

@@ -406,6 +406,16 @@ int dev_dot(femo_ctx* c, const double* a, const double* b, int64_t n, double* ou
   return 0;
 }
 
+// out_dev[0] = a . b without host synchronisation (single GPU; capturable in a CUDA graph)
+int dev_dot_async(femo_ctx* c, const double* a, const double* b, int64_t n, double* out_dev) {
+  double* part = c->red + 6 * RED_BLOCKS;
+  k_dot<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(a, b, n, part);
+  k_sum_partials<<<1, RED_THREADS, 0, c->stream>>>(part, RED_BLOCKS, out_dev);
+  TRY(check_launch(c, "k_dot"));
+  c->launches += 2;
+  return 0;
+}
+
 // red layout: [0]=pAp partials (SPMV_BLOCKS) | [1],[2] = rz ping-pong | [3] = rr | [4] = bb | [5] spare | [6] dot
 // scal layout: [0]=bb [1]=rr (host reads) [2]=pAp | [10..11],[12..13] = (rz, rr) ping-pong pairs (multi-GPU)
 //
