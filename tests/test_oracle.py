@@ -130,3 +130,28 @@ def test_golden_fixtures(name):
     assert abs(o.mass() - float(g["mass"])) <= 1e-12 * float(g["mass"])
     assert np.abs(o.total_dcompliance_dh() - g["dCdh_total"]).max() <= 1e-7 * np.abs(g["dCdh_total"]).max()
     assert abs(o.pnorm_stress(w, m=1e-4, rho=6.0) - float(g["pnorm"])) <= 1e-7 * float(g["pnorm"])
+
+
+def test_navier_simply_supported_plate():
+    """Second analytic pin of the oracle (besides the Euler-Bernoulli cantilever of ex_simple_shell_opt.py:100-105): the
+    Navier series solution of the simply supported square Kirchhoff plate under uniform pressure,
+    w_max = 0.00406235 q a^4 / D (nu = 0.3), which the thin Reissner-Mindlin plate (a/h = 100) must reproduce;
+    it exercises bending, twisting and the shear coupling in both directions, which the cantilever does not."""
+    import numpy as np
+    from oracle.rm_shell_ref import RMShellOracle, plate_mesh
+    a, h, E, nu, q = 1.0, 0.01, 2.0e11, 0.3, 1.0e3
+    nodes, quads = plate_mesh(24, 24, a, a)      # the fully integrated Q2xQ1 element locks mildly on coarser meshes (0.83 at 6x6)
+    nn = nodes.shape[0]
+    o = RMShellOracle(nodes, quads)
+    o.set_inputs(thickness=np.full(nn, h), E=np.full(nn, E), nu=np.full(nn, nu), density=np.ones(nn),
+                 F_solid=np.tile([0.0, 0.0, q], nn))
+    xc = o.topo.block_coords()
+    on = (np.abs(xc[:, 0]) < 1e-12) | (np.abs(xc[:, 0] - a) < 1e-12) | (np.abs(xc[:, 1]) < 1e-12) | (np.abs(xc[:, 1] - a) < 1e-12)
+    ub = np.nonzero(on[:o.topo.nq2])[0]                    # displacement nodes on the edges: u = 0, rotations free
+    o.bc_dofs = np.sort((3 * ub[:, None] + np.arange(3)[None, :]).ravel())
+    w = o.solve_state()
+    centre = int(np.argmin(np.linalg.norm(nodes - [0.5 * a, 0.5 * a, 0.0], axis=1)))
+    D = E * h ** 3 / (12 * (1 - nu ** 2))
+    w_navier = 0.00406235 * q * a ** 4 / D
+    w_shear = 0.07367 * q * a ** 2 / (0.833 * E / (2 * (1 + nu)) * h)        # Mindlin correction of the SS plate (5e-4 here)
+    assert abs(w[3 * centre + 2] / (w_navier + w_shear) - 1.0) < 2e-3, (w[3 * centre + 2], w_navier)
