@@ -189,3 +189,37 @@ def test_energy_balance_at_scale():
     # w^T K w loses ~8 digits to the membrane / bending / shear scale separation at this element size (cf. test_gpu_golden)
     assert scale > 0 and np.ptp(bal) < 1e-5 * scale and abs(bal[0]) < 1e-5 * scale, (bal, scale)
     ps.hierarchy.close()
+
+
+def test_dynamic_edge_cases():
+    """Single step, over-long and all-zero load histories, history round trip, argument errors."""
+    from oracle.dynamic_ref import DynamicShellOracle
+    from femo_alpha_b200.dynamic_device import DynamicShellDevice
+    p = make_problem("plate_dg0")
+    o, d = oracle_for(p), device_for(p)
+    # one step; the history has more rows than time levels: only rows 0..1 are used
+    od, dd = DynamicShellOracle(o, 0.02, 1), DynamicShellDevice(d, 0.02, 1)
+    f_long = np.stack([p["F_solid"] * (1.0 + i) for i in range(5)])
+    w_ref = od.solve(f_long)
+    assert dd.solve(f_long) == 1
+    assert rel(dd.history(), w_ref) < 1e-8 and dd.energies()[0] == 0.0
+    # zero loads: the plate stays at rest, and so do the adjoints of a zero right-hand side
+    dd.solve(np.zeros((1, d.n_f)))
+    assert np.abs(dd.history()).max() == 0.0 and dd.total_strain_energy() == 0.0
+    assert np.abs(dd.solve_adjoint(np.zeros((2, d.ndof)))).max() == 0.0
+    # history round trip through the device
+    rng = np.random.default_rng(4)
+    h = rng.standard_normal((2, d.ndof))
+    dd.set_history(h)
+    assert np.array_equal(dd.history(), h)
+    with pytest.raises(ValueError):
+        dd.solve(np.zeros((2, d.n_f + 1)))
+    dd.close()
+    with pytest.raises(RuntimeError, match="multigrid"):
+        DynamicShellDevice(d, 0.02, 2, solver="multigrid").solve(f_long)
+    with pytest.raises(RuntimeError):
+        DynamicShellDevice(d, -1.0, 2)
+    # the context is back in static mode once the handles are gone: K, not A
+    import gc; gc.collect()
+    x = rng.standard_normal(d.ndof)
+    assert rel(d.jacobian_apply(x), o.assemble_dRdu() @ x) < 1e-12
