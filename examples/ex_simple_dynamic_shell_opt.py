@@ -59,4 +59,4 @@ recorder.stop()
 print("total strain energy:", total_strain_energy.value, " mass:", volume.value * rho_val)
 print("max |tip displacement|:", np.abs(plate_sim.tip_disp_history).max(), " solver:", plate_sim._dyn.info())
 sim = csdl.experimental.PySimulator(recorder)
-sim.check_totals([total_strain_energy], [thickness], step_size=1e-6)
+sim.check_totals([total_strain_energy], [thickness], step_size=2e-5)

@@ -47,4 +47,4 @@ print("Reissner-Mindlin FE deflection:", np.abs(out.disp_extracted.value).max())
 print("Compliance:", out.compliance.value, " Mass:", out.mass.value, " Aggregated stress:", out.aggregated_stress.value)
 
 sim = csdl.experimental.PySimulator(recorder)
-rep = sim.check_totals([out.compliance], [thickness], step_size=1e-6)
+rep = sim.check_totals([out.compliance], [thickness], step_size=2e-5)
