@@ -100,10 +100,22 @@ def main():
     ap.add_argument("--large", action="store_true")
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--only", default="", help="run a single small mesh, e.g. 40x8 (profiling)")
+    ap.add_argument("--cfg3", type=int, default=0, metavar="STEPS",
+                    help="time STEPS steps on the 816x816 plate of BASELINE config 3 (10.0 M dofs, 5-level V-cycle PCG)")
     a = ap.parse_args()
     from femo_alpha_b200.mesh import createRectangleMesh, refine_uniform
     res = dict(config="BASELINE config 4: plate 2x10, quad_deg=3, E=1e8, nu=0.3, rho=10, h=0.1, 1-cos gust, f_z = 0.1 V_g(t)",
                gpu=[], cpu=[], large=[])
+    if a.cfg3:
+        mesh = refine_uniform(createRectangleMesh((0., 0.), (10., 10.), 51, 51), 4)
+        t0 = time.perf_counter()
+        r = run_gpu(mesh, a.cfg3, "multigrid", quad_deg=6, adjoint=True, dt_steps=a.steps)
+        r.update(mesh="816x816", quad_deg=6, wall_s_total=time.perf_counter() - t0,
+                 workload="dynamic RM shell on the config-3 plate [0,10]^2, h = 0.1, dt = %.4g s, 1-cos gust" % r["dt"])
+        print(json.dumps(r), flush=True)
+        if a.out:
+            json.dump(r, open(a.out, "w"), indent=1)
+        return
     if a.only:
         nx, ny = [int(v) for v in a.only.split("x")]
         print(json.dumps(run_gpu(createRectangleMesh((0., 0.), (10., 2.), nx, ny), a.steps, "auto")), flush=True)
