@@ -154,7 +154,9 @@ int mass_spmv(femo_ctx* c, const double* x, double* y) {
 }
 
 int dyn_enable(femo_ctx* c, double dt) {
-  if (c->world > 1) return femo_fail("dynamic path: single-GPU contexts only");
+  // multi-GPU contexts (femo_dist_setup): every operand of an M / K product is ghost-consistent by construction
+  // (solutions leave pcg_solve with their halo exchanged, and the recurrences combine them entry by entry); products
+  // are complete on owned rows, which is all the owner-masked PCG and dot products read
   if (c->n_pen > 0) return femo_fail("dynamic path: strong Dirichlet BCs only (femo_set_strong_bc)");
   if (!c->vals_K) TRY(dev_alloc(&c->vals_K, (size_t)c->nnzb * 9));
   if (!c->mvals) TRY(dev_alloc(&c->mvals, (size_t)c->nnzb));
@@ -313,6 +315,10 @@ int femo_dyn_setup(femo_dyn* d, int solver) {
   if (!c->dyn_on) return femo_fail("femo_dyn_setup: context left dynamic mode");
   d->solver_req = solver;
   int s = solver;
+  if (c->world > 1) {
+    if (s == 1 || s == 3) return femo_fail("femo_dyn_setup: multi-GPU contexts step with the distributed block-Jacobi PCG (solver 0 or 2)");
+    s = 2;
+  }
   if (s == 0) s = (c->ndof <= 46000) ? 1 : (d->mg ? 3 : 2);
   if (s == 3 && !d->mg) return femo_fail("femo_dyn_setup: no multigrid hierarchy attached (femo_dyn_set_mg)");
   if (s < 1 || s > 3) return femo_fail("femo_dyn_setup: solver must be 0 (auto), 1 (dense), 2 (PCG) or 3 (multigrid)");
@@ -352,6 +358,7 @@ int femo_dyn_solve(femo_dyn* d, const double* f_history, int64_t n_rows, double 
   CUDA_TRY(cudaMemcpyAsync(d->fh, f_history, sizeof(double) * rows * c->n_f,
                            on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
   CUDA_TRY(cudaMemsetAsync(d->en_dev, 0, sizeof(double) * d->levels, c->stream));
+  d->energies.assign(d->levels, 0.0);
 
   auto issue_steps = [&]() -> int {
     CUDA_TRY(cudaMemsetAsync(d->hist, 0, sizeof(double) * n, c->stream));    // zero initial conditions (plate_sim.py:305-309)
@@ -372,7 +379,13 @@ int femo_dyn_solve(femo_dyn* d, const double* f_history, int64_t n_rows, double 
       TRY(dyn_linear_solve(d, d->rhs, wi, rtol, max_it, &iters));
       TRY(lin4(c, c2, wi, -c2, wo, -1.0, d->v, 0, nullptr, nullptr, d->v));   // wdot_i (plate_sim.py:243-244)
       TRY(bsr_spmv_vals(c, c->vals_K, wi, d->kw, 0));
-      TRY(dev_dot_async(c, wi, d->kw, n, d->en_dev + i));                     // 2 x strain energy (plate_sim.py:337)
+      if (c->world > 1) {                                                     // owner-masked, summed over ranks
+        double e = 0;
+        TRY(dev_dot(c, wi, d->kw, n, &e));
+        d->energies[i] = e;
+      } else {
+        TRY(dev_dot_async(c, wi, d->kw, n, d->en_dev + i));                   // 2 x strain energy (plate_sim.py:337)
+      }
     }
     return 0;
   };
@@ -402,8 +415,10 @@ int femo_dyn_solve(femo_dyn* d, const double* f_history, int64_t n_rows, double 
     TRY(issue_steps());
   }
   cudaEventRecord(d->e1, c->stream);
-  d->energies.assign(d->levels, 0.0);
-  CUDA_TRY(cudaMemcpyAsync(d->energies.data(), d->en_dev, sizeof(double) * d->levels, cudaMemcpyDeviceToHost, c->stream));
+  if (c->world == 1) {
+    d->energies.assign(d->levels, 0.0);
+    CUDA_TRY(cudaMemcpyAsync(d->energies.data(), d->en_dev, sizeof(double) * d->levels, cudaMemcpyDeviceToHost, c->stream));
+  }
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   for (double& e : d->energies) e *= 0.5;
   float ms = 0; cudaEventElapsedTime(&ms, d->e0, d->e1); d->ms_fwd = ms;

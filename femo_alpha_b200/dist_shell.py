@@ -95,6 +95,20 @@ class DistributedShell:
     def output(self, name):
         return self.dev.output(name)
 
+    # ---- time-stepped path (SURVEY 8 f1 on N GPUs) ----------------------------------------------------
+    def dynamic(self, dt, n_steps, add_self_weight=False, g_factor=None, rtol=1e-12, max_it=20000):
+        """DynamicShellDevice on this rank's context.  Every rank steps its own rows; the effective operator
+        cM + K/2 is solved by the distributed block-Jacobi PCG (halo exchange + all-reduce per iteration), the
+        recurrences in between need no communication (csrc/dynamic.cu, dyn_enable)."""
+        from .dynamic_device import DynamicShellDevice
+        return DynamicShellDevice(self.dev, dt, n_steps, add_self_weight, g_factor, "pcg", rtol, max_it)
+
+    def slice_force_history(self, f_history_global):
+        """(rows, 3*n_global) force history in mesh order -> this rank's (rows, n_f) columns."""
+        f = np.atleast_2d(np.asarray(f_history_global, dtype=np.float64))
+        idx = self.lp.cell_global if self.ewp else self.lp.vertex_global
+        return np.ascontiguousarray(f.reshape(f.shape[0], -1, 3)[:, idx, :].reshape(f.shape[0], -1))
+
     def halo_exchange(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64)
         L.check(self.dev.lib.femo_halo_exchange(self.dev._ctx, L.ptr(x), 0))

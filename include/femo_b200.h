@@ -212,7 +212,10 @@ int femo_dyn_destroy(femo_dyn* d);
 /* optional: V-cycle PCG for the step solves; every level context of `mg` is switched to dynamic mode with the same dt */
 int femo_dyn_set_mg(femo_dyn* d, femo_mg* mg);
 /* (re)build after the inputs changed: K, M, A_eff, preconditioner / dense inverse.
- * solver: 0 auto (dense if n_dof <= 46000, else multigrid if attached, else PCG), 1 dense, 2 PCG, 3 multigrid */
+ * solver: 0 auto (dense if n_dof <= 46000, else multigrid if attached, else PCG), 1 dense, 2 PCG, 3 multigrid.
+ * On a multi-GPU context (femo_dist_setup) every rank steps its own rows with the distributed block-Jacobi PCG
+ * (0 and 2 accepted, 1 and 3 rejected); histories and sweeps are then in the rank's local block order and every
+ * femo_dyn_* call that solves or reduces is collective. */
 int femo_dyn_setup(femo_dyn* d, int solver);
 /* time loop from zero initial conditions; f_history (n_rows, n_force) row-major, rows beyond the last repeat it
  * (plate_sim.py:314-319).  Fills the resident history and the strain energy of every level (plate_sim.py:337).

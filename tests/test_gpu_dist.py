@@ -25,3 +25,15 @@ def test_two_gpu_solve_matches_oracle(built_lib, name):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     sys.stdout.write(r.stdout[-4000:]); sys.stderr.write(r.stderr[-4000:])
     assert r.returncode == 0
+
+
+@pytest.mark.parametrize("name,sw", [("plate_varh", 0), ("plate_dg0", 1)])
+def test_two_gpu_time_stepping_matches_oracle(built_lib, name, sw):
+    """SURVEY 8 f1 on 2 GPUs: history, energies, time adjoint and thickness gradient (tests/dist_gpu_dyn_worker.py)."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29534", os.path.join(ROOT, "tests", "dist_gpu_dyn_worker.py"), name, str(sw)]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(r.stdout[-4000:]); sys.stderr.write(r.stderr[-4000:])
+    assert r.returncode == 0
