@@ -98,6 +98,14 @@ SIGNATURES = {
     "femo_dyn_total_strain_energy_grad": [_P, C.c_int, _P, C.c_int],
     "femo_dyn_mass_apply": [_P, _P, _P, C.c_int],
     "femo_dyn_info": [_P, _D, _D, C.POINTER(C.c_int)],
+    "femo_hex_setup": [_P, C.c_int64, _P, C.c_int64, _P, C.c_int, C.c_double, C.c_double, C.c_double],
+    "femo_hex_set_input": [_P, C.c_int, _P, C.c_int64, C.c_int],
+    "femo_hex_get_input": [_P, C.c_int, _P, C.c_int64, C.c_int],
+    "femo_hex_dRdf_T_apply": [_P, C.c_int, _P, _P, C.c_int],
+    "femo_hex_dRdf_apply": [_P, C.c_int, _P, _P, C.c_int],
+    "femo_hex_output": [_P, C.c_int, _D],
+    "femo_hex_output_grad": [_P, C.c_int, C.c_int, _P, C.c_int],
+    "femo_hex_get_mesh": [_P, _P, _P],
     "femo_launch_count": [_P, C.POINTER(C.c_int64)],
     "femo_last_timings": [_P, _D],
     "femo_pcg_fixed": [_P, C.c_int, _D],

@@ -113,6 +113,11 @@ int copy_out(femo_ctx* c, double* dst, const double* src, int64_t n, int on_devi
 #define NEED_SETUP(c, name) \
   if (!(c) || !(c)->setup_done) return femo_fail(std::string(name) + ": context not set up (femo_mesh_set + femo_shell_setup)")
 
+// entry points that read shell data refuse the solid contexts of hex.cu
+#define NEED_SHELL(c, name) \
+  NEED_SETUP(c, name);      \
+  if ((c)->kind != 0) return femo_fail(std::string(name) + ": RM-shell entry point called on a hexahedral-solid context (use femo_hex_*)")
+
 }  // namespace
 
 extern "C" {
@@ -151,7 +156,8 @@ int femo_ctx_destroy(femo_ctx* c) {
                   c->nc_adj, c->rec, c->bcmask, c->bcbits, c->colbc, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
                   c->pen_val, c->pen_dest_col, c->tab4, c->cell_tags, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
                   c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf, c->it_pack, c->it_dest, c->chunk_ptr, c->halo_ptr,
-                  c->halo_cells, c->tpos, c->tabm, c->vals_K, c->mvals, c->mass_me};
+                  c->halo_cells, c->tpos, c->tabm, c->vals_K, c->mvals, c->mass_me, c->hx_cells, c->hx_geo, c->hx_rho,
+                  c->hx_scale, c->hx_vol, c->hx_f, c->hx_cellvec};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
@@ -167,6 +173,7 @@ int femo_set_stream(femo_ctx* c, void* s) {
 
 int femo_mesh_set(femo_ctx* c, int64_t n_nodes, const double* xyz, int64_t n_cells, int npc, const int32_t* conn) {
   if (!c) return femo_fail("null context");
+  if (c->kind != 0) return femo_fail("femo_mesh_set: this context holds a hexahedral solid (femo_hex_setup)");
   if (npc == 3) return femo_fail("femo_mesh_set: triangles (P2xP1) are not implemented; quadrilaterals only");
   if (npc != 4) return femo_fail("femo_mesh_set: nodes_per_cell must be 4");
   if (n_nodes <= 0 || n_cells <= 0 || !xyz || !conn) return femo_fail("femo_mesh_set: empty mesh");
@@ -288,14 +295,14 @@ int femo_set_strong_bc(femo_ctx* c, int64_t n, const int32_t* dofs) {
 }
 
 int femo_set_penalty_bc(femo_ctx* c, int64_t n_nodes, const uint8_t* von) {
-  NEED_SETUP(c, "femo_set_penalty_bc");
+  NEED_SHELL(c, "femo_set_penalty_bc");
   if (n_nodes != c->nn) return femo_fail("femo_set_penalty_bc: vertex mask must have n_nodes entries");
   DevGuard g(c->device);
   return penalty_build(c, von);
 }
 
 int femo_set_input(femo_ctx* c, int which, const double* data, int64_t n, int on_device) {
-  NEED_SETUP(c, "femo_set_input");
+  NEED_SHELL(c, "femo_set_input");
   DevGuard g(c->device);
   int64_t want = 0;
   double** slot = input_slot(c, which, &want);
@@ -321,7 +328,7 @@ int femo_set_input(femo_ctx* c, int which, const double* data, int64_t n, int on
 }
 
 int femo_get_input(femo_ctx* c, int which, double* out, int64_t n, int on_device) {
-  NEED_SETUP(c, "femo_get_input");
+  NEED_SHELL(c, "femo_get_input");
   DevGuard g(c->device);
   int64_t want = 0;
   double** slot = input_slot(c, which, &want);
@@ -450,7 +457,7 @@ int femo_solve_forward(femo_ctx* c, const double* rhs, double* du, double rtol, 
 }
 
 int femo_dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out, int on_device) {
-  NEED_SETUP(c, "femo_dRdf_T_apply");
+  NEED_SHELL(c, "femo_dRdf_T_apply");
   DevGuard g(c->device);
   int64_t n = 0;
   if (!input_slot(c, arg, &n)) return femo_fail("femo_dRdf_T_apply: unknown argument");
@@ -460,7 +467,7 @@ int femo_dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out, int 
 }
 
 int femo_dRdf_apply(femo_ctx* c, int arg, const double* df, double* out, int on_device) {
-  NEED_SETUP(c, "femo_dRdf_apply");
+  NEED_SHELL(c, "femo_dRdf_apply");
   DevGuard g(c->device);
   int64_t n = 0;
   if (!input_slot(c, arg, &n)) return femo_fail("femo_dRdf_apply: unknown argument");
@@ -470,13 +477,13 @@ int femo_dRdf_apply(femo_ctx* c, int arg, const double* df, double* out, int on_
 }
 
 int femo_output(femo_ctx* c, int which, double* value) {
-  NEED_SETUP(c, "femo_output");
+  NEED_SHELL(c, "femo_output");
   DevGuard g(c->device);
   return out_scalar(c, which, value);
 }
 
 int femo_output_grad(femo_ctx* c, int which, int arg, double* gout, int on_device) {
-  NEED_SETUP(c, "femo_output_grad");
+  NEED_SHELL(c, "femo_output_grad");
   DevGuard g(c->device);
   int64_t n = c->ndof;
   if (arg != FEMO_ARG_STATE && !input_slot(c, arg, &n)) return femo_fail("femo_output_grad: unknown argument");
@@ -491,7 +498,7 @@ int femo_set_stress_params(femo_ctx* c, double m, double rho) {
 }
 
 int femo_set_cell_tags(femo_ctx* c, int64_t n, const int32_t* tags) {
-  NEED_SETUP(c, "femo_set_cell_tags");
+  NEED_SHELL(c, "femo_set_cell_tags");
   if (n != c->nc) return femo_fail("femo_set_cell_tags: need one tag per cell");
   DevGuard g(c->device);
   TRY(dev_alloc(&c->cell_tags, (size_t)n));
@@ -501,13 +508,13 @@ int femo_set_cell_tags(femo_ctx* c, int64_t n, const int32_t* tags) {
 }
 
 int femo_pnorm_stress(femo_ctx* c, int tag, double* value) {
-  NEED_SETUP(c, "femo_pnorm_stress");
+  NEED_SHELL(c, "femo_pnorm_stress");
   DevGuard g(c->device);
   return pnorm_value(c, tag, value);
 }
 
 int femo_pnorm_stress_grad(femo_ctx* c, int tag, int arg, double* gout, int on_device) {
-  NEED_SETUP(c, "femo_pnorm_stress_grad");
+  NEED_SHELL(c, "femo_pnorm_stress_grad");
   DevGuard g(c->device);
   int64_t n = c->ndof;
   if (arg != FEMO_ARG_STATE && !input_slot(c, arg, &n)) return femo_fail("femo_pnorm_stress_grad: unknown argument");
@@ -516,7 +523,7 @@ int femo_pnorm_stress_grad(femo_ctx* c, int tag, int arg, double* gout, int on_d
 }
 
 int femo_stress_field(femo_ctx* c, int surface, double* out, int on_device) {
-  NEED_SETUP(c, "femo_stress_field");
+  NEED_SHELL(c, "femo_stress_field");
   if (surface < 0 || surface > 2) return femo_fail("femo_stress_field: surface must be 0 (Top), 1 (Mid) or 2 (Bot)");
   DevGuard g(c->device);
   double* t = nullptr;

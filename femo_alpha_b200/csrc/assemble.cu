@@ -662,6 +662,7 @@ int assemble_stiffness(femo_ctx* c) {
 }
 
 int assemble_load(femo_ctx* c, double* F) {
+  if (c->kind == 1) return hex_load(c, F);
   const double* uh = c->uhat_zero ? nullptr : c->uhat;
   CUDA_TRY(cudaMemsetAsync(F, 0, sizeof(double) * c->ndof, c->stream));
   k_load_cells<<<(unsigned)cdiv(c->nc, 128), 128, 0, c->stream>>>(c->xyz, c->cv, uh, c->f, c->tab, c->nq, c->ewp, c->nc, c->cellbuf);

@@ -250,6 +250,7 @@ int dyn_energies(femo_dyn* d) {
 
 // assembly entry point of every solver: K, or A while the context is in dynamic mode
 int assemble_jacobian(femo_ctx* c) {
+  if (c->kind == 1) return hex_assemble(c);
   if (c->dyn_on) return dyn_assemble(c);
   return assemble_stiffness(c);
 }
@@ -258,6 +259,7 @@ extern "C" {
 
 int femo_dyn_create(femo_ctx* c, double dt, int n_steps, int add_self_weight, double g_factor, femo_dyn** out) {
   if (!c || !c->setup_done || !out) return femo_fail("femo_dyn_create: context not set up");
+  if (c->kind != 0) return femo_fail("femo_dyn_create: RM-shell contexts only");
   if (!(dt > 0) || n_steps < 1) return femo_fail("femo_dyn_create: need dt > 0 and n_steps >= 1");
   DevGuard g(c->device);
   TRY(dyn_enable(c, dt));

@@ -173,6 +173,18 @@ struct femo_ctx {
   double dyn_dt = 0.0;
   double *vals_K = nullptr, *mvals = nullptr, *mass_me = nullptr;
   Tables* tabm = nullptr;       // 4x4 rule of the mass form
+  // generic 3-D forms on trilinear hexahedra (hex.cu): kind 1 contexts carry no shell data;
+  // the BSR pattern, BC masks, Krylov vectors and the block-Jacobi PCG above are shared (nn = 0: every node is a
+  // 3x3 block node of the `dinv3` kind)
+  int kind = 0;                 // 0 RM shell, 1 hexahedral solid
+  int hx_form = 1;              // 1 linear elasticity, 0 vector Poisson
+  double hx_c1 = 0, hx_c2 = 0, hx_p = 3.0;   // (lam, mu) or (kappa, -); SIMP exponent
+  int64_t hx_nn = 0;            // mesh nodes (= nb)
+  int32_t* hx_cells = nullptr;  // nc*8, VTK_HEXAHEDRON order
+  double *hx_geo = nullptr;     // nc*8*10 inverse Jacobians and weights
+  double *hx_rho = nullptr, *hx_scale = nullptr, *hx_vol = nullptr;   // nc: density, rho^p, cell volume
+  double *hx_f = nullptr;       // nn*3 nodal body force
+  double *hx_cellvec = nullptr; // nc*24 element vectors
 };
 
 // ---- host-side helpers (context.cu) ---------------------------------------
@@ -200,6 +212,8 @@ int asm_plan_build(femo_ctx* c);                                          // top
 int tile_plan_setup(femo_ctx* c);                                         // assemble_tiles.cu
 void tile_plan_free(femo_ctx* c);                                         // assemble_tiles.cu
 int assemble_jacobian_tiles(femo_ctx* c, const double* uhat);             // assemble_tiles.cu (records + assembly)
+int hex_assemble(femo_ctx* c);                                            // hex.cu: K(rho) -> c->vals
+int hex_load(femo_ctx* c, double* F);                                     // hex.cu: F = M f
 int assemble_stiffness(femo_ctx* c);                                      // assemble.cu: K -> c->vals
 int assemble_jacobian(femo_ctx* c);                                       // dynamic.cu: K, or A_eff while c->dyn_on
 int assemble_load(femo_ctx* c, double* F_dev);                            // assemble.cu

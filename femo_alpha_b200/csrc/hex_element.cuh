@@ -1,0 +1,186 @@
+// Trilinear hexahedron (Q1, 2x2x2 Gauss) element mathematics of the generic 3-D forms (SURVEY 8 f4 / BASELINE config 5):
+// per-thread bodies shared by the kernels of hex.cu and by the host harness tests/hex_host.cu (nvcc compiles them for
+// both sides).  The reference has no in-tree form for this configuration -- its generic FEA takes any UFL form
+// (femo_alpha/fea/fea_dolfinx.py:71-116); the two forms here are the ones SURVEY 8d names for config 5:
+//   form 1  linear elasticity   a(u, v) = int  s_e ( lam div u div v + 2 mu eps(u) : eps(v) ) dx
+//   form 0  vector Poisson      a(u, v) = int  s_e  kappa grad u : grad v dx       (three independent components)
+// with the SIMP cell factor s_e = rho_e^p and the load  l(v) = int f . v dx  of a nodal (Q1) field f.
+// Node order of a cell: VTK_HEXAHEDRON (bottom face counter-clockwise, then the top face).
+#pragma once
+#include <cstdint>
+
+#ifndef FEMO_HD
+#define FEMO_HD __host__ __device__ __forceinline__
+#endif
+
+namespace femo_hex {
+
+constexpr int GEO = 10;          // per (cell, point): inverse Jacobian (9, [j][i] = d xi_j / d x_i) and weight * det J
+
+// reference values at Gauss point q (bit 0/1/2 of q = sign of xi/eta/zeta) of shape function a
+FEMO_HD void ref_shape(int a, int q, double* N, double dN[3]) {
+  const double g = 0.57735026918962576451;
+  const double sx = ((a + 1) & 2) ? 1.0 : -1.0;      // a = 1, 2, 5, 6
+  const double sy = (a & 2) ? 1.0 : -1.0;            // a = 2, 3, 6, 7
+  const double sz = (a & 4) ? 1.0 : -1.0;            // a = 4 .. 7
+  const double fx = 1.0 + sx * ((q & 1) ? g : -g);
+  const double fy = 1.0 + sy * ((q & 2) ? g : -g);
+  const double fz = 1.0 + sz * ((q & 4) ? g : -g);
+  *N = 0.125 * fx * fy * fz;
+  dN[0] = 0.125 * sx * fy * fz;
+  dN[1] = 0.125 * fx * sy * fz;
+  dN[2] = 0.125 * fx * fy * sz;
+}
+
+// geometry record of (cell, q); returns det J
+FEMO_HD double geom_qp(const double* __restrict__ xyz, const int32_t* __restrict__ cn, int q, double* __restrict__ rec) {
+  double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};         // J[i][j] = d x_i / d xi_j
+  for (int a = 0; a < 8; ++a) {
+    double N, dN[3];
+    ref_shape(a, q, &N, dN);
+    const double* x = xyz + 3 * (int64_t)cn[a];
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) J[3 * i + j] += x[i] * dN[j];
+  }
+  const double c00 = J[4] * J[8] - J[5] * J[7], c01 = J[5] * J[6] - J[3] * J[8], c02 = J[3] * J[7] - J[4] * J[6];
+  const double det = J[0] * c00 + J[1] * c01 + J[2] * c02;
+  const double id = 1.0 / det;
+  // inverse = adj / det, stored as rec[3 j + i] = d xi_j / d x_i
+  rec[0] = c00 * id;                         rec[1] = (J[2] * J[7] - J[1] * J[8]) * id; rec[2] = (J[1] * J[5] - J[2] * J[4]) * id;
+  rec[3] = c01 * id;                         rec[4] = (J[0] * J[8] - J[2] * J[6]) * id; rec[5] = (J[2] * J[3] - J[0] * J[5]) * id;
+  rec[6] = c02 * id;                         rec[7] = (J[1] * J[6] - J[0] * J[7]) * id; rec[8] = (J[0] * J[4] - J[1] * J[3]) * id;
+  rec[9] = det;                              // Gauss weights are 1
+  return det;
+}
+
+// physical gradient of shape function a at the point of `rec`
+FEMO_HD void phys_grad(const double* __restrict__ rec, int a, int q, double* N, double g[3]) {
+  double dN[3];
+  ref_shape(a, q, N, dN);
+  for (int i = 0; i < 3; ++i) g[i] = rec[i] * dN[0] + rec[3 + i] * dN[1] + rec[6 + i] * dN[2];
+}
+
+// 3x3 block (row node i, column node j) of the stiffness matrix: contributions of the cells around i that hold j, in
+// adjacency (= cell-ascending) order -> deterministic
+FEMO_HD void block_body(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
+                        const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr,
+                        const int32_t* __restrict__ nc_adj, int64_t i, int32_t j, double B[9]) {
+  for (int k = 0; k < 9; ++k) B[k] = 0.0;
+  for (int32_t e = nc_ptr[i]; e < nc_ptr[i + 1]; ++e) {
+    const int32_t ca = nc_adj[e];
+    const int64_t cell = ca >> 3;
+    const int a = ca & 7;
+    const int32_t* cn = cells + 8 * cell;
+    int b = -1;
+    for (int k = 0; k < 8; ++k) if (cn[k] == j) b = k;
+    if (b < 0) continue;
+    const double s = scale[cell];
+    for (int q = 0; q < 8; ++q) {
+      const double* rec = geo + (cell * 8 + q) * GEO;
+      double Na, Nb, ga[3], gb[3];
+      phys_grad(rec, a, q, &Na, ga);
+      phys_grad(rec, b, q, &Nb, gb);
+      const double w = s * rec[9];
+      const double d = ga[0] * gb[0] + ga[1] * gb[1] + ga[2] * gb[2];
+      if (form == 1) {
+        for (int r = 0; r < 3; ++r)
+          for (int c = 0; c < 3; ++c) B[3 * r + c] += w * (c1 * ga[r] * gb[c] + c2 * gb[r] * ga[c]);
+        B[0] += w * c2 * d; B[4] += w * c2 * d; B[8] += w * c2 * d;
+      } else {
+        B[0] += w * c1 * d; B[4] += w * c1 * d; B[8] += w * c1 * d;
+      }
+    }
+  }
+}
+
+// displacement gradient G[i][k] = sum_a u_a[i] d N_a / d x_k of one cell at point q
+FEMO_HD void cell_grad(const double* __restrict__ rec, const int32_t* __restrict__ cn, const double* __restrict__ u, int q,
+                       double G[9]) {
+  for (int k = 0; k < 9; ++k) G[k] = 0.0;
+  for (int a = 0; a < 8; ++a) {
+    double N, g[3];
+    phys_grad(rec, a, q, &N, g);
+    const double* ua = u + 3 * (int64_t)cn[a];
+    for (int i = 0; i < 3; ++i)
+      for (int k = 0; k < 3; ++k) G[3 * i + k] += ua[i] * g[k];
+  }
+}
+
+// unit-density "stress" of the form: S = lam tr(G) I + mu (G + G^T)   or   kappa G
+FEMO_HD void stress0(int form, double c1, double c2, const double G[9], double S[9]) {
+  if (form == 1) {
+    const double tr = c1 * (G[0] + G[4] + G[8]);
+    for (int i = 0; i < 3; ++i)
+      for (int k = 0; k < 3; ++k) S[3 * i + k] = c2 * (G[3 * i + k] + G[3 * k + i]) + ((i == k) ? tr : 0.0);
+  } else {
+    for (int k = 0; k < 9; ++k) S[k] = c1 * G[k];
+  }
+}
+
+// a0_e(lam, u) = int_e S0(u) : grad(lam) dx   (unit density)
+FEMO_HD double cell_energy(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
+                           int64_t cell, const double* __restrict__ u, const double* __restrict__ lm) {
+  const int32_t* cn = cells + 8 * cell;
+  double acc = 0.0;
+  for (int q = 0; q < 8; ++q) {
+    const double* rec = geo + (cell * 8 + q) * GEO;
+    double G[9], L[9], S[9];
+    cell_grad(rec, cn, u, q, G);
+    cell_grad(rec, cn, lm, q, L);
+    stress0(form, c1, c2, G, S);
+    double s = 0.0;
+    for (int k = 0; k < 9; ++k) s += S[k] * L[k];
+    acc += rec[9] * s;
+  }
+  return acc;
+}
+
+// element vector  ye[3 a + i] = coef * int_e S0(u)[i][:] . grad N_a dx  (= coef * K0_e u_e)
+FEMO_HD void cell_apply(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
+                        int64_t cell, const double* __restrict__ u, double coef, double* __restrict__ ye) {
+  const int32_t* cn = cells + 8 * cell;
+  for (int k = 0; k < 24; ++k) ye[k] = 0.0;
+  for (int q = 0; q < 8; ++q) {
+    const double* rec = geo + (cell * 8 + q) * GEO;
+    double G[9], S[9];
+    cell_grad(rec, cn, u, q, G);
+    stress0(form, c1, c2, G, S);
+    const double w = coef * rec[9];
+    for (int a = 0; a < 8; ++a) {
+      double N, g[3];
+      phys_grad(rec, a, q, &N, g);
+      for (int i = 0; i < 3; ++i) ye[3 * a + i] += w * (S[3 * i] * g[0] + S[3 * i + 1] * g[1] + S[3 * i + 2] * g[2]);
+    }
+  }
+}
+
+// element vector of the consistent mass product  ye[3 a + i] = coef * int_e N_a (sum_b N_b f_b[i]) dx
+FEMO_HD void cell_mass_apply(const double* __restrict__ geo, const int32_t* __restrict__ cells, int64_t cell,
+                             const double* __restrict__ f, double coef, double* __restrict__ ye) {
+  const int32_t* cn = cells + 8 * cell;
+  for (int k = 0; k < 24; ++k) ye[k] = 0.0;
+  for (int q = 0; q < 8; ++q) {
+    const double* rec = geo + (cell * 8 + q) * GEO;
+    double N[8], dN[3], fq[3] = {0, 0, 0};
+    for (int a = 0; a < 8; ++a) {
+      ref_shape(a, q, &N[a], dN);
+      const double* fa = f + 3 * (int64_t)cn[a];
+      for (int i = 0; i < 3; ++i) fq[i] += N[a] * fa[i];
+    }
+    const double w = coef * rec[9];
+    for (int a = 0; a < 8; ++a)
+      for (int i = 0; i < 3; ++i) ye[3 * a + i] += w * N[a] * fq[i];
+  }
+}
+
+// nodal gather of element vectors (adjacency order = cell-ascending): deterministic, no atomics
+FEMO_HD void node_gather(const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
+                         const double* __restrict__ cellvec, int64_t i, double out[3]) {
+  out[0] = out[1] = out[2] = 0.0;
+  for (int32_t e = nc_ptr[i]; e < nc_ptr[i + 1]; ++e) {
+    const double* v = cellvec + 3 * (int64_t)nc_adj[e];
+    out[0] += v[0]; out[1] += v[1]; out[2] += v[2];
+  }
+}
+
+}  // namespace femo_hex

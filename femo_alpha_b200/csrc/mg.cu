@@ -310,6 +310,7 @@ int femo_mg_create(int n_levels, femo_ctx** ctxs, femo_mg** out) {
   m->L.resize(n_levels);
   for (int l = 0; l < n_levels; ++l) {
     if (!ctxs[l] || !ctxs[l]->setup_done) { delete m; return femo_fail("femo_mg_create: level context not set up"); }
+    if (ctxs[l]->kind != 0) { delete m; return femo_fail("femo_mg_create: RM-shell contexts only"); }
     if (ctxs[l]->world > 1) { delete m; return femo_fail("femo_mg_create: multigrid levels are single-GPU contexts"); }
     if (ctxs[l]->device != ctxs[0]->device) { delete m; return femo_fail("femo_mg_create: levels must share one device"); }
     m->L[l].c = ctxs[l];

@@ -33,7 +33,7 @@ class FunctionSpace:
         return self, np.arange(self.size)
 
     def tabulate_dof_coordinates(self):
-        if self.kind == "W":
+        if self.kind in ("W", "W3"):
             return np.repeat(self.device.block_coords(), 3, axis=0)
         raise NotImplementedError
 
@@ -175,6 +175,9 @@ def locate_dofs_geometrical(V, marker):
     """dolfinx.fem.locate_dofs_geometrical on W.sub(0) / W.sub(1) (rm_shell_model.py:168-173):
     dofs whose coordinates satisfy `marker(x)` (x has shape (3, n))."""
     sub = V[0] if isinstance(V, (tuple, list)) else V
+    if isinstance(sub, FunctionSpace) and sub.kind == "W3":       # solid forms (fea/named_forms.py): 3 dofs per node
+        blocks = np.nonzero(np.asarray(marker(sub.device.block_coords().T)).astype(bool))[0]
+        return np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel()).astype(np.int32)
     if not isinstance(sub, _SubSpace):
         raise ValueError("locate_dofs_geometrical expects W.sub(i) (optionally with its collapsed space)")
     dev = sub.parent.device

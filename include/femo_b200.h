@@ -246,6 +246,32 @@ int femo_dyn_mass_apply(femo_dyn* d, const double* x, double* y, int on_device);
 /* device time of the last femo_dyn_solve / femo_dyn_solve_adjoint (ms) and the solver in use (1 dense, 2 PCG, 3 MG) */
 int femo_dyn_info(femo_dyn* d, double* ms_forward, double* ms_adjoint, int* solver);
 
+/* ---- generic 3-D forms on trilinear hexahedra (BASELINE config 5) --------------------------------
+ * Replaces, for the named forms below, what the reference's generic FEA does with an arbitrary UFL form
+ * (femo_alpha/fea/fea_dolfinx.py:71-95 add_state / add_output, :159-203 solve / solveLinearBwd;
+ * femo_alpha/fea/utils_dolfinx.py:194-221 assembleVector / assembleMatrix / assembleSystem):
+ *   form 1  linear elasticity   R(u; rho, f) = K(rho) u - M f,  K_e = rho_e^p K0_e(E0, nu)   (SIMP)
+ *   form 0  vector Poisson      the same with K0_e = kappa int grad N_a . grad N_b I3 (kappa = E0)
+ * Q1 hexahedra (VTK_HEXAHEDRON node order), 2x2x2 Gauss; state = 3 dofs per node, dof = 3 node + component.
+ * A context set up with femo_hex_setup is a "solid" context: femo_set_strong_bc, femo_set_state / femo_get_state,
+ * femo_assemble_jacobian / _load / _residual, femo_jacobian_apply, femo_get_bsr, femo_get_sizes, femo_solve_state /
+ * _adjoint / _forward, femo_pcg_fixed, femo_launch_count and femo_last_timings work on it unchanged; the RM-shell
+ * entry points (inputs, partials, outputs, penalty BC, dist, mg, dyn) refuse it. */
+int femo_hex_setup(femo_ctx* ctx, int64_t n_nodes, const double* xyz, int64_t n_cells, const int32_t* conn /* n_cells*8 */,
+                   int form, double E0, double nu, double simp_p);
+/* which: 0 cell density rho (n_cells values, or 1 host value broadcast), 1 nodal body force f (3 n_nodes) */
+int femo_hex_set_input(femo_ctx* ctx, int which, const double* data, int64_t n, int on_device);
+int femo_hex_get_input(femo_ctx* ctx, int which, double* out, int64_t n, int on_device);
+/* matrix-free partials at the context's state (state_operation.py:163-171,183-184 with the matrices of :282-286):
+ * arg 0: (dR/drho)^T lam = p rho_e^(p-1) lam_e^T K0_e u_e per cell,  (dR/drho) drho (3 n_nodes);  arg 1: -/+ M */
+int femo_hex_dRdf_T_apply(femo_ctx* ctx, int arg, const double* lam, double* out, int on_device);
+int femo_hex_dRdf_apply(femo_ctx* ctx, int arg, const double* df, double* out, int on_device);
+/* outputs (output_operation.py:51-69): which 0 compliance int f.u dx, 1 volume sum rho_e |e|;
+ * gradients w.r.t. arg 0 (density), 1 (body force) or FEMO_ARG_STATE */
+int femo_hex_output(femo_ctx* ctx, int which, double* value);
+int femo_hex_output_grad(femo_ctx* ctx, int which, int arg, double* grad, int on_device);
+int femo_hex_get_mesh(femo_ctx* ctx, double* xyz /* 3 n_nodes or NULL */, int32_t* conn /* 8 n_cells or NULL */);
+
 /* ---- instrumentation ---------------------------------------------------------------- */
 /* number of kernels this context has launched so far */
 int femo_launch_count(femo_ctx* ctx, int64_t* n);

@@ -5,6 +5,7 @@
 #   bench   bench.py (ours) + bench.py --impl reference
 #   dyn     config-4 timings (scripts/dyn_bench.py --large)
 #   ncu     launch list of a short bench run and of a short dynamic run (per-launch durations, no clock control)
+#   hex     config-5 solid forms: parity tests + 160^3 assembly / PCG timings (scripts/hex_bench.py)
 #   distdyn 2-GPU parity of the time-stepped path only (needs `gpurun --gpus 2`)
 #   dist    2-GPU parity test + 2-GPU bench line (needs `gpurun --gpus 2`)
 set -u
@@ -29,6 +30,9 @@ for sec in "$@"; do
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29544 bench.py --gpus 2 --steps 10 --warmup 3 --krylov-iters 50 > gpurun_out/${T}_bench_2gpu.json 2> gpurun_out/${T}_bench_2gpu.err; echo "bench 2gpu rc=$?"; cat gpurun_out/${T}_bench_2gpu.json; tail -n 3 gpurun_out/${T}_bench_2gpu.err ;;
     distdyn)
       timeout 600 python -m pytest tests/test_gpu_dist.py -m gpu -q --tb=short -s -k time_stepping > gpurun_out/${T}_pytest_gpu_distdyn.log 2>&1; echo "pytest distdyn rc=$?"; grep -E "^rank|passed|failed|Error|error" gpurun_out/${T}_pytest_gpu_distdyn.log | tail -n 12 ;;
+    hex)
+      timeout 600 python -m pytest tests/test_gpu_hex.py -m gpu -q --tb=short > gpurun_out/${T}_pytest_gpu_hex.log 2>&1; echo "pytest hex rc=$?"; tail -n 25 gpurun_out/${T}_pytest_gpu_hex.log
+      timeout 600 python scripts/hex_bench.py --n ${HEX_N:-160} --out gpurun_out/${T}_hex_bench.json > gpurun_out/${T}_hex_bench.log 2>&1; echo "hex bench rc=$?"; tail -n 5 gpurun_out/${T}_hex_bench.log ;;
     *) echo "unknown section $sec" ;;
   esac
 done

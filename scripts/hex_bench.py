@@ -1,0 +1,72 @@
+"""BASELINE config 5: unit cube, n^3 trilinear hexahedra, linear elasticity with a cell-wise SIMP density
+rho_e in [0.01, 1] (seed 20261104).  Times the Jacobian assembly (k_hex_assemble, CUDA events inside the library) and the
+block-Jacobi PCG iteration of the shared solver on one B200; prints one JSON line.
+
+    python scripts/hex_bench.py [--n 160] [--reps 5] [--krylov-iters 50] [--out FILE]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=160)
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--krylov-iters", type=int, default=50)
+    ap.add_argument("--form", default="elasticity")
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+    from femo_alpha_b200.solid_device import SolidDevice, box_hexes
+    n = a.n
+    t0 = time.time()
+    nodes, cells = box_hexes(n, n, n)
+    t1 = time.time()
+    d = SolidDevice(nodes, cells, form=a.form, E0=1.0, nu=0.3, simp_p=3.0)
+    t2 = time.time()
+    rng = np.random.default_rng(20261104)
+    f = np.zeros((d.nb, 3)); f[:, 2] = -1.0
+    d.set_input("body_force", f)
+    base = np.nonzero(nodes[:, 0] < 1e-12)[0]
+    d.set_strong_bc((3 * base[:, None] + np.arange(3)).ravel())
+    ms = []
+    for r in range(a.reps + 2):
+        d.set_input("density", rng.uniform(0.01, 1.0, d.nc))       # invalidates the operator
+        d.assemble_jacobian()
+        ms.append(d.last_timings()["assemble_ms"])
+    ms = ms[2:]
+    asm = float(np.mean(ms))
+    l0 = d.launch_count()
+    tot = d.pcg_fixed(a.krylov_iters)
+    launches_pcg = d.launch_count() - l0
+    # algorithmic bytes per launch: every BSR block written once; per cell 8 geometry records, density, connectivity
+    bytes_alg = 72.0 * d.nnzb + d.nc * (8 * 80 + 8 + 32)
+    peak = None
+    try:
+        peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
+        peak = float(peak.get("hbm_gbs") or peak.get("hbm_gbps") or 0) or None
+    except Exception:
+        pass
+    line = dict(metric="3-D elasticity Jacobian assembly throughput (config 5)", value=d.ndof / asm / 1e6, unit="GDOF/s",
+                config=dict(workload="unit cube %d^3 Q1 hexahedra, %s, SIMP rho^3, seed 20261104" % (n, a.form), n_dof=int(d.ndof),
+                            n_cells=int(d.nc), nnz_blocks=int(d.nnzb)),
+                assemble_ms=asm, assemble_ms_all=ms, pcg_ms_per_iter=tot / a.krylov_iters, pcg_launches=int(launches_pcg),
+                mesh_s=t1 - t0, setup_s=t2 - t1,
+                roofline=dict(bound="hbm", achieved=bytes_alg / asm / 1e6, peak=peak, unit="GB/s",
+                              frac=(bytes_alg / asm / 1e6 / peak) if peak else None, traffic=None),
+                dtype="f64", data="synthetic")
+    s = json.dumps(line)
+    print(s)
+    if a.out:
+        open(a.out, "w").write(s + "\n")
+    d.close()
+
+
+if __name__ == "__main__":
+    main()

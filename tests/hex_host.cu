@@ -1,0 +1,89 @@
+// CPU harness around femo_alpha_b200/csrc/hex_element.cuh for tests/test_hex_host.py: the per-thread bodies of the
+// kernels of hex.cu (k_hex_geom, k_hex_assemble, k_hex_cellvec, k_hex_gather, k_hex_energy) run in host loops with the
+// same index arithmetic -- compiled by nvcc into a shared object, no GPU needed.
+#include <cstdint>
+#include <cmath>
+#include <vector>
+
+#include "../femo_alpha_b200/csrc/hex_element.cuh"
+
+using namespace femo_hex;
+
+extern "C" {
+
+// geo (nc*8*10), vol (nc); returns the number of non-positive Jacobians
+int hex_host_geom(int64_t nc, const double* xyz, const int32_t* cells, double* geo, double* vol) {
+  int bad = 0;
+  for (int64_t cell = 0; cell < nc; ++cell) {
+    double v = 0;
+    for (int q = 0; q < 8; ++q) {
+      const double det = geom_qp(xyz, cells + 8 * cell, q, geo + (cell * 8 + q) * GEO);
+      if (!(det > 0.0)) ++bad;
+      v += det;
+    }
+    vol[cell] = v;
+  }
+  return bad;
+}
+
+// the warp-per-row loop of k_hex_assemble, lane by lane
+int hex_host_assemble(int form, double c1, double c2, double p, int64_t nb, const double* geo, const int32_t* cells,
+                      const double* rho, int64_t nc, const int32_t* nc_ptr, const int32_t* nc_adj, const int32_t* rowptr,
+                      const int32_t* colidx, double* vals) {
+  std::vector<double> scale(nc);
+  for (int64_t e = 0; e < nc; ++e) scale[e] = pow(rho[e], p);
+  for (int64_t i = 0; i < nb; ++i)
+    for (int lane = 0; lane < 32; ++lane)
+      for (int32_t k = rowptr[i] + lane; k < rowptr[i + 1]; k += 32) {
+        double B[9];
+        block_body(form, c1, c2, geo, cells, scale.data(), nc_ptr, nc_adj, i, colidx[k], B);
+        for (int e = 0; e < 9; ++e) vals[(int64_t)k * 9 + e] = B[e];
+      }
+  return 0;
+}
+
+// k_hex_cellvec + k_hex_gather
+int hex_host_cellvec_gather(int mode, int form, double c1, double c2, int64_t nb, int64_t nc, const double* geo,
+                            const int32_t* cells, const double* x, const double* cellcoef, double coef, const int32_t* nc_ptr,
+                            const int32_t* nc_adj, double* out) {
+  std::vector<double> cellvec((size_t)nc * 24);
+  for (int64_t cell = 0; cell < nc; ++cell) {
+    const double cf = coef * (cellcoef ? cellcoef[cell] : 1.0);
+    if (mode == 0) cell_mass_apply(geo, cells, cell, x, cf, cellvec.data() + cell * 24);
+    else cell_apply(form, c1, c2, geo, cells, cell, x, cf, cellvec.data() + cell * 24);
+  }
+  for (int64_t i = 0; i < nb; ++i) node_gather(nc_ptr, nc_adj, cellvec.data(), i, out + 3 * i);
+  return 0;
+}
+
+// k_hex_energy
+int hex_host_energy(int form, double c1, double c2, double p, int64_t nc, const double* geo, const int32_t* cells, const double* u,
+                    const double* lm, const double* rho, double* out) {
+  for (int64_t cell = 0; cell < nc; ++cell)
+    out[cell] = p * pow(rho[cell], p - 1.0) * cell_energy(form, c1, c2, geo, cells, cell, u, lm);
+  return 0;
+}
+
+}  // extern "C"
+
+#include "../femo_alpha_b200/csrc/hex_pattern.hpp"
+
+extern "C" {
+
+// pattern of femo_hex_setup; call once with null outputs for the sizes (returns nnzb), then with buffers
+int64_t hex_host_pattern(int64_t nb, int64_t nc, const int32_t* cells, int32_t* nc_ptr, int32_t* nc_adj, int32_t* rowptr,
+                         int32_t* colidx, int32_t* diag) {
+  Pattern P;
+  const int64_t r = build_pattern(nb, nc, cells, P);
+  if (r != 0) return -r;
+  if (nc_ptr) {
+    std::copy(P.nc_ptr.begin(), P.nc_ptr.end(), nc_ptr);
+    std::copy(P.nc_adj.begin(), P.nc_adj.end(), nc_adj);
+    std::copy(P.rowptr.begin(), P.rowptr.end(), rowptr);
+    std::copy(P.colidx.begin(), P.colidx.end(), colidx);
+    std::copy(P.diag.begin(), P.diag.end(), diag);
+  }
+  return (int64_t)P.colidx.size();
+}
+
+}  // extern "C"
