@@ -47,21 +47,47 @@ __global__ void k_hex_scale(const double* __restrict__ rho, double p, int64_t nc
   if (i < nc) scale[i] = pow(rho[i], p);
 }
 
-// 32 lanes per row node; lane l owns blocks rowptr[i] + l, + 32, ...
-__global__ void __launch_bounds__(256)
+// one warp per row node: stage HEX_PASS work items (cell, local column) at a time in shared memory, two per lane, then
+// the lanes that own the destination blocks collect them (hex_element.cuh: row_item / row_collect)
+constexpr int HEX_WARPS = 8;
+__global__ void __launch_bounds__(32 * HEX_WARPS)
 k_hex_assemble(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
                const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int64_t nb,
                double* __restrict__ vals) {
-  const int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (i >= nb) return;
-  for (int32_t k = rowptr[i] + lane; k < rowptr[i + 1]; k += 32) {
-    double B[9];
-    block_body(form, c1, c2, geo, cells, scale, nc_ptr, nc_adj, i, colidx[k], B);
-    double* out = vals + (int64_t)k * 9;
+  __shared__ double s_val[HEX_WARPS][HEX_PASS * 9];
+  __shared__ int32_t s_col[HEX_WARPS][HEX_PASS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t i = blockIdx.x * (int64_t)HEX_WARPS + warp;
+  if (i >= nb) return;                                   // whole warps leave together
+  const int n_items = 8 * (nc_ptr[i + 1] - nc_ptr[i]);
+  for (int t0 = 0; t0 < n_items; t0 += HEX_PASS) {
+    const int n_staged = min(HEX_PASS, n_items - t0);
 #pragma unroll
-    for (int e = 0; e < 9; ++e) out[e] = B[e];
+    for (int h = 0; h < HEX_PASS / 32; ++h) {
+      const int t = lane + 32 * h;
+      double B[9];
+      int32_t col;
+      if (t < n_staged && row_item(form, c1, c2, geo, cells, scale, nc_ptr, nc_adj, i, t0 + t, B, &col)) {
+        s_col[warp][t] = col;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) s_val[warp][9 * t + k] = B[k];
+      }
+    }
+    __syncwarp();
+    for (int32_t k = rowptr[i] + lane; k < rowptr[i + 1]; k += 32) {
+      double acc[9];
+      row_collect(s_val[warp], s_col[warp], n_staged, colidx[k], acc);
+      double* out = vals + (int64_t)k * 9;
+      if (t0 == 0) {
+#pragma unroll
+        for (int e = 0; e < 9; ++e) out[e] = acc[e];
+      } else {
+#pragma unroll
+        for (int e = 0; e < 9; ++e) out[e] += acc[e];
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -135,7 +161,7 @@ int hex_assemble(femo_ctx* c) {
   cudaEventRecord(c->ev0, c->stream);
   k_hex_scale<<<(unsigned)cdiv(c->nc, 256), 256, 0, c->stream>>>(c->hx_rho, c->hx_p, c->nc, c->hx_scale);
   TRY(check_launch(c, "k_hex_scale"));
-  k_hex_assemble<<<(unsigned)cdiv(c->nb * 32, 256), 256, 0, c->stream>>>(c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo, c->hx_cells,
+  k_hex_assemble<<<(unsigned)cdiv(c->nb, HEX_WARPS), 32 * HEX_WARPS, 0, c->stream>>>(c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo, c->hx_cells,
                                                                        c->hx_scale, c->nc_ptr, c->nc_adj, c->rowptr, c->colidx,
                                                                        c->nb, c->vals);
   TRY(check_launch(c, "k_hex_assemble"));

@@ -60,37 +60,53 @@ FEMO_HD void phys_grad(const double* __restrict__ rec, int a, int q, double* N, 
   for (int i = 0; i < 3; ++i) g[i] = rec[i] * dN[0] + rec[3 + i] * dN[1] + rec[6 + i] * dN[2];
 }
 
-// 3x3 block (row node i, column node j) of the stiffness matrix: contributions of the cells around i that hold j, in
-// adjacency (= cell-ascending) order -> deterministic
-FEMO_HD void block_body(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
-                        const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr,
-                        const int32_t* __restrict__ nc_adj, int64_t i, int32_t j, double B[9]) {
+// contribution of one cell to the 3x3 block (row = local node a, column = local node b), SIMP factor s included
+FEMO_HD void item_body(int form, double c1, double c2, const double* __restrict__ geo, int64_t cell, double s, int a, int b,
+                       double B[9]) {
   for (int k = 0; k < 9; ++k) B[k] = 0.0;
-  for (int32_t e = nc_ptr[i]; e < nc_ptr[i + 1]; ++e) {
-    const int32_t ca = nc_adj[e];
-    const int64_t cell = ca >> 3;
-    const int a = ca & 7;
-    const int32_t* cn = cells + 8 * cell;
-    int b = -1;
-    for (int k = 0; k < 8; ++k) if (cn[k] == j) b = k;
-    if (b < 0) continue;
-    const double s = scale[cell];
-    for (int q = 0; q < 8; ++q) {
-      const double* rec = geo + (cell * 8 + q) * GEO;
-      double Na, Nb, ga[3], gb[3];
-      phys_grad(rec, a, q, &Na, ga);
-      phys_grad(rec, b, q, &Nb, gb);
-      const double w = s * rec[9];
-      const double d = ga[0] * gb[0] + ga[1] * gb[1] + ga[2] * gb[2];
-      if (form == 1) {
-        for (int r = 0; r < 3; ++r)
-          for (int c = 0; c < 3; ++c) B[3 * r + c] += w * (c1 * ga[r] * gb[c] + c2 * gb[r] * ga[c]);
-        B[0] += w * c2 * d; B[4] += w * c2 * d; B[8] += w * c2 * d;
-      } else {
-        B[0] += w * c1 * d; B[4] += w * c1 * d; B[8] += w * c1 * d;
-      }
+  for (int q = 0; q < 8; ++q) {
+    const double* rec = geo + (cell * 8 + q) * GEO;
+    double Na, Nb, ga[3], gb[3];
+    phys_grad(rec, a, q, &Na, ga);
+    phys_grad(rec, b, q, &Nb, gb);
+    const double w = s * rec[9];
+    const double d = ga[0] * gb[0] + ga[1] * gb[1] + ga[2] * gb[2];
+    if (form == 1) {
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) B[3 * r + c] += w * (c1 * ga[r] * gb[c] + c2 * gb[r] * ga[c]);
+      B[0] += w * c2 * d; B[4] += w * c2 * d; B[8] += w * c2 * d;
+    } else {
+      B[0] += w * c1 * d; B[4] += w * c1 * d; B[8] += w * c1 * d;
     }
   }
+}
+
+// Row assembly, the algorithm of k_hex_assemble (one warp per row node i): the 8 n_cells(i) work items (cell around i,
+// local column b) are evaluated HEX_PASS at a time, one or two per lane, into a staging area; then the lane that owns a
+// destination block sums the staged items of its column in item (= cell-ascending) order.  Deterministic, no atomics.
+constexpr int HEX_PASS = 64;
+
+// item t of row i -> staged block and column; returns false past the end
+FEMO_HD bool row_item(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
+                      const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
+                      int64_t i, int t, double B[9], int32_t* col) {
+  const int32_t e = nc_ptr[i] + (t >> 3);
+  if (e >= nc_ptr[i + 1]) return false;
+  const int32_t ca = nc_adj[e];
+  const int64_t cell = ca >> 3;
+  const int b = t & 7;
+  *col = cells[8 * cell + b];
+  item_body(form, c1, c2, geo, cell, scale[cell], ca & 7, b, B);
+  return true;
+}
+
+// sum of the staged items [0, n_staged) whose column is `col`
+FEMO_HD void row_collect(const double* __restrict__ s_val, const int32_t* __restrict__ s_col, int n_staged, int32_t col,
+                         double acc[9]) {
+  for (int k = 0; k < 9; ++k) acc[k] = 0.0;
+  for (int t = 0; t < n_staged; ++t)
+    if (s_col[t] == col)
+      for (int k = 0; k < 9; ++k) acc[k] += s_val[9 * t + k];
 }
 
 // displacement gradient G[i][k] = sum_a u_a[i] d N_a / d x_k of one cell at point q

@@ -119,7 +119,7 @@ class SolidDevice(ShellDevice):
     # ---- bench helpers ------------------------------------------------------------------------------------------------------------
     def last_timings(self):
         ms = np.zeros(4)
-        L.check(self.lib.femo_last_timings(self._ctx, L.ptr(ms)))
+        L.check(self.lib.femo_last_timings(self._ctx, ms.ctypes.data_as(C.POINTER(C.c_double))))
         return dict(assemble_ms=ms[1], solve_ms=ms[2], iter_ms=ms[3])
 
     def pcg_fixed(self, n_iter):

@@ -2,6 +2,7 @@
 // kernels of hex.cu (k_hex_geom, k_hex_assemble, k_hex_cellvec, k_hex_gather, k_hex_energy) run in host loops with the
 // same index arithmetic -- compiled by nvcc into a shared object, no GPU needed.
 #include <cstdint>
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -26,19 +27,39 @@ int hex_host_geom(int64_t nc, const double* xyz, const int32_t* cells, double* g
   return bad;
 }
 
-// the warp-per-row loop of k_hex_assemble, lane by lane
+// the warp-per-row algorithm of k_hex_assemble: passes of HEX_PASS staged items, then the destination lanes collect
 int hex_host_assemble(int form, double c1, double c2, double p, int64_t nb, const double* geo, const int32_t* cells,
                       const double* rho, int64_t nc, const int32_t* nc_ptr, const int32_t* nc_adj, const int32_t* rowptr,
                       const int32_t* colidx, double* vals) {
   std::vector<double> scale(nc);
   for (int64_t e = 0; e < nc; ++e) scale[e] = pow(rho[e], p);
-  for (int64_t i = 0; i < nb; ++i)
-    for (int lane = 0; lane < 32; ++lane)
-      for (int32_t k = rowptr[i] + lane; k < rowptr[i + 1]; k += 32) {
-        double B[9];
-        block_body(form, c1, c2, geo, cells, scale.data(), nc_ptr, nc_adj, i, colidx[k], B);
-        for (int e = 0; e < 9; ++e) vals[(int64_t)k * 9 + e] = B[e];
-      }
+  double s_val[HEX_PASS * 9];
+  int32_t s_col[HEX_PASS];
+  for (int64_t i = 0; i < nb; ++i) {
+    const int n_items = 8 * (nc_ptr[i + 1] - nc_ptr[i]);
+    for (int t0 = 0; t0 < n_items; t0 += HEX_PASS) {
+      const int n_staged = std::min(HEX_PASS, n_items - t0);
+      for (int h = 0; h < HEX_PASS / 32; ++h)
+        for (int lane = 0; lane < 32; ++lane) {
+          const int t = lane + 32 * h;
+          double B[9];
+          int32_t col;
+          if (t < n_staged && row_item(form, c1, c2, geo, cells, scale.data(), nc_ptr, nc_adj, i, t0 + t, B, &col)) {
+            s_col[t] = col;
+            for (int k = 0; k < 9; ++k) s_val[9 * t + k] = B[k];
+          }
+        }
+      for (int lane = 0; lane < 32; ++lane)
+        for (int32_t k = rowptr[i] + lane; k < rowptr[i + 1]; k += 32) {
+          double acc[9];
+          row_collect(s_val, s_col, n_staged, colidx[k], acc);
+          for (int e = 0; e < 9; ++e) {
+            if (t0 == 0) vals[(int64_t)k * 9 + e] = acc[e];
+            else vals[(int64_t)k * 9 + e] += acc[e];
+          }
+        }
+    }
+  }
   return 0;
 }
 

@@ -96,6 +96,16 @@ def test_unstructured_valence_and_errors(built_lib):
     d.set_input("density", o.rho)
     K = o.stiffness()
     assert abs(d.get_csr() - K).max() < 1e-12 * abs(K).max()
+    # ten cells around one edge: 80 work items on the axis rows -> two staging passes of k_hex_assemble
+    from tests.test_hex_host import fan_mesh
+    n2, c2 = fan_mesh(10)
+    o2 = HexOracle(n2, c2, E0=2.0, nu=0.2)
+    o2.set_inputs(density=np.linspace(0.2, 1.0, o2.nc))
+    d2 = SolidDevice(n2, c2, E0=2.0, nu=0.2)
+    d2.set_input("density", o2.rho)
+    K2 = o2.stiffness()
+    assert abs(d2.get_csr() - K2).max() < 1e-12 * abs(K2).max()
+    d2.close()
     # RM-shell entry points refuse a solid context; wrong sizes and inverted cells are reported
     from femo_alpha_b200 import _lib as L
     import ctypes as C

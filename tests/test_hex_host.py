@@ -138,3 +138,26 @@ def test_unstructured_valence(host_lib):
     h = Host(host_lib, o)
     K = o.stiffness()
     assert abs(h.matrix() - K).max() < 1e-12 * abs(K).max()
+
+
+def fan_mesh(n_sectors=10):
+    """n hexahedra around one edge (extruded kites): the axis nodes see 8 n > 64 work items -> several staging passes."""
+    th = 2 * np.pi * np.arange(n_sectors) / n_sectors
+    ring = np.stack([np.cos(th), np.sin(th)], 1)
+    outer = 1.8 * np.stack([np.cos(th + np.pi / n_sectors), np.sin(th + np.pi / n_sectors)], 1)
+    pts2 = np.vstack([[0, 0], ring, outer])
+    m = len(pts2)
+    nodes = np.vstack([np.c_[pts2, np.zeros(m)], np.c_[pts2, np.full(m, 0.7)]])
+    quads = [[0, 1 + k, 1 + n_sectors + k, 1 + (k + 1) % n_sectors] for k in range(n_sectors)]
+    cells = np.array([q + [v + m for v in q] for q in quads], dtype=np.int32)
+    return nodes, cells
+
+
+def test_high_valence_rows_take_several_passes(host_lib):
+    nodes, cells = fan_mesh(10)
+    o = HexOracle(nodes, cells, E0=2.0, nu=0.2)
+    o.set_inputs(density=np.linspace(0.2, 1.0, o.nc))
+    h = Host(host_lib, o)
+    assert (h.nc_ptr[1] - h.nc_ptr[0]) * 8 == 80
+    K = o.stiffness()
+    assert abs(h.matrix() - K).max() < 1e-12 * abs(K).max()
