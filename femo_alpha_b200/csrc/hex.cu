@@ -47,47 +47,80 @@ __global__ void k_hex_scale(const double* __restrict__ rho, double p, int64_t nc
   if (i < nc) scale[i] = pow(rho[i], p);
 }
 
-// one warp per row node: stage HEX_PASS work items (cell, local column) at a time in shared memory, two per lane, then
-// the lanes that own the destination blocks collect them (hex_element.cuh: row_item / row_collect)
-constexpr int HEX_WARPS = 8;
+// One warp per row node i.  Per pass of up to 8 cells around i (HEX_PASS = 64 work items, hex_element.cuh):
+//   1. the cells' geometry records (8 x 80 doubles) are copied to shared memory with coalesced loads (row stride 81
+//      doubles: the 8 cells of a request fall into different banks);
+//   2. lane l evaluates the item pair (2 l, 2 l + 1) = two columns of cell l / 4 (item_pair_body);
+//   3. the blocks are staged component-major in the same shared region, and the lanes that own the destination blocks of
+//      the row collect the items of their column in cell-ascending order (row_collect);
+//   4. the row's blocks leave through a shared transpose as contiguous 256-byte stores.
+// Deterministic, no atomics.  Rows with more than 8 cells take further passes (read-modify-write of their own blocks),
+// rows with more than 32 blocks further destination chunks.
+static_assert(HEX_PASS == 64, "k_hex_assemble stages one item pair per lane");
+constexpr int HEX_WARPS = 4;
+constexpr int HEX_GSTRIDE = 8 * GEO + 1;
+constexpr int HEX_REGION = 8 * HEX_GSTRIDE;              // >= 9 * HEX_PASS
 __global__ void __launch_bounds__(32 * HEX_WARPS)
 k_hex_assemble(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
                const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int64_t nb,
                double* __restrict__ vals) {
-  __shared__ double s_val[HEX_WARPS][HEX_PASS * 9];
-  __shared__ int32_t s_col[HEX_WARPS][HEX_PASS];
+  __shared__ double s_reg[HEX_WARPS][HEX_REGION];        // geometry records, then the staged blocks
+  __shared__ double s_out[HEX_WARPS][32 * 9];
+  __shared__ __align__(16) int32_t s_col[HEX_WARPS][HEX_PASS];
+  const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t i = blockIdx.x * (int64_t)HEX_WARPS + warp;
   if (i >= nb) return;                                   // whole warps leave together
-  const int n_items = 8 * (nc_ptr[i + 1] - nc_ptr[i]);
-  for (int t0 = 0; t0 < n_items; t0 += HEX_PASS) {
-    const int n_staged = min(HEX_PASS, n_items - t0);
-#pragma unroll
-    for (int h = 0; h < HEX_PASS / 32; ++h) {
-      const int t = lane + 32 * h;
-      double B[9];
-      int32_t col;
-      if (t < n_staged && row_item(form, c1, c2, geo, cells, scale, nc_ptr, nc_adj, i, t0 + t, B, &col)) {
-        s_col[warp][t] = col;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) s_val[warp][9 * t + k] = B[k];
-      }
+  double* reg = s_reg[warp];
+  const int32_t e0 = nc_ptr[i], n_cells_i = nc_ptr[i + 1] - e0;
+  const int32_t r0 = rowptr[i], n_row = rowptr[i + 1] - r0;
+  for (int c0 = 0; c0 < n_cells_i; c0 += 8) {
+    const int n_pass = min(8, n_cells_i - c0);           // cells of this pass
+    const int32_t my_ca = (lane < n_pass) ? nc_adj[e0 + c0 + lane] : 0;
+    // 1. geometry records -> shared memory
+    for (int base = 0; base < n_pass * 8 * GEO; base += 32) {
+      const int idx = base + lane;
+      const int cl = min(idx / (8 * GEO), 7);
+      const int32_t ca = __shfl_sync(FULL, my_ca, cl);
+      if (idx < n_pass * 8 * GEO) reg[cl * HEX_GSTRIDE + (idx - cl * 8 * GEO)] = geo[(int64_t)(ca >> 3) * (8 * GEO) + (idx - cl * 8 * GEO)];
     }
     __syncwarp();
-    for (int32_t k = rowptr[i] + lane; k < rowptr[i + 1]; k += 32) {
-      double acc[9];
-      row_collect(s_val[warp], s_col[warp], n_staged, colidx[k], acc);
-      double* out = vals + (int64_t)k * 9;
-      if (t0 == 0) {
+    // 2. item pair of this lane
+    const int cl = lane >> 2, b = 2 * (lane & 3);
+    const int32_t ca = __shfl_sync(FULL, my_ca, cl);
+    double B0[9], B1[9];
+    int32_t col0 = -1, col1 = -1;
+    if (cl < n_pass) {
+      const int64_t cell = ca >> 3;
+      const int2 cc = *reinterpret_cast<const int2*>(cells + 8 * cell + b);
+      col0 = cc.x; col1 = cc.y;
+      item_pair_body(form, c1, c2, reg + cl * HEX_GSTRIDE, scale[cell], ca & 7, b, B0, B1);
+    }
+    __syncwarp();                                        // every lane is done with the records
+    // 3. stage and collect
+    const int n_staged = 8 * n_pass;
+    if (cl < n_pass) {
+      *reinterpret_cast<int2*>(&s_col[warp][2 * lane]) = make_int2(col0, col1);
 #pragma unroll
-        for (int e = 0; e < 9; ++e) out[e] = acc[e];
-      } else {
-#pragma unroll
-        for (int e = 0; e < 9; ++e) out[e] += acc[e];
-      }
+      for (int k = 0; k < 9; ++k) *reinterpret_cast<double2*>(&reg[k * HEX_PASS + 2 * lane]) = make_double2(B0[k], B1[k]);
     }
     __syncwarp();
+    for (int k0 = 0; k0 < n_row; k0 += 32) {
+      const int n_dst = min(32, n_row - k0);
+      if (lane < n_dst) {
+        double acc[9];
+        row_collect(reg, s_col[warp], n_staged, colidx[r0 + k0 + lane], acc);
+#pragma unroll
+        for (int e = 0; e < 9; ++e) s_out[warp][9 * lane + e] = acc[e];
+      }
+      __syncwarp();
+      // 4. contiguous stores of the row's blocks
+      double* out = vals + (int64_t)(r0 + k0) * 9;
+      if (c0 == 0) for (int idx = lane; idx < 9 * n_dst; idx += 32) out[idx] = s_out[warp][idx];
+      else for (int idx = lane; idx < 9 * n_dst; idx += 32) out[idx] += s_out[warp][idx];
+      __syncwarp();
+    }
   }
 }
 

@@ -60,53 +60,92 @@ FEMO_HD void phys_grad(const double* __restrict__ rec, int a, int q, double* N, 
   for (int i = 0; i < 3; ++i) g[i] = rec[i] * dN[0] + rec[3 + i] * dN[1] + rec[6 + i] * dN[2];
 }
 
-// contribution of one cell to the 3x3 block (row = local node a, column = local node b), SIMP factor s included
-FEMO_HD void item_body(int form, double c1, double c2, const double* __restrict__ geo, int64_t cell, double s, int a, int b,
-                       double B[9]) {
-  for (int k = 0; k < 9; ++k) B[k] = 0.0;
-  for (int q = 0; q < 8; ++q) {
-    const double* rec = geo + (cell * 8 + q) * GEO;
-    double Na, Nb, ga[3], gb[3];
-    phys_grad(rec, a, q, &Na, ga);
-    phys_grad(rec, b, q, &Nb, gb);
-    const double w = s * rec[9];
-    const double d = ga[0] * gb[0] + ga[1] * gb[1] + ga[2] * gb[2];
-    if (form == 1) {
-      for (int r = 0; r < 3; ++r)
-        for (int c = 0; c < 3; ++c) B[3 * r + c] += w * (c1 * ga[r] * gb[c] + c2 * gb[r] * ga[c]);
-      B[0] += w * c2 * d; B[4] += w * c2 * d; B[8] += w * c2 * d;
-    } else {
-      B[0] += w * c1 * d; B[4] += w * c1 * d; B[8] += w * c1 * d;
-    }
+// block of the form from the moment matrix M = sum_q w g_a (x) g_b:  lam M + mu M^T + mu tr(M) I   or   kappa tr(M) I
+FEMO_HD void block_from_moments(int form, double c1, double c2, double s, const double M[9], double B[9]) {
+  const double tr = M[0] + M[4] + M[8];
+  if (form == 1) {
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) B[3 * r + c] = s * (c1 * M[3 * r + c] + c2 * M[3 * c + r] + ((r == c) ? c2 * tr : 0.0));
+  } else {
+    for (int k = 0; k < 9; ++k) B[k] = 0.0;
+    B[0] = B[4] = B[8] = s * c1 * tr;
   }
 }
 
+// contributions of one cell to the two 3x3 blocks (row = local node a, columns = local nodes b and b + 1), SIMP factor
+// s included: the geometry record and the row gradient are shared by the pair.  `cg` = the 8 records of the cell
+// (global memory, or the copy k_hex_assemble stages in shared memory)
+FEMO_HD void item_pair_body(int form, double c1, double c2, const double* __restrict__ cg, double s, int a, int b,
+                            double B0[9], double B1[9]) {
+  double M0[9], M1[9];
+  for (int k = 0; k < 9; ++k) { M0[k] = 0.0; M1[k] = 0.0; }
+  for (int q = 0; q < 8; ++q) {
+    const double* rec = cg + q * GEO;
+    double N, ga[3], g0[3], g1[3];
+    phys_grad(rec, a, q, &N, ga);
+    phys_grad(rec, b, q, &N, g0);
+    phys_grad(rec, b + 1, q, &N, g1);
+    const double w = rec[9];
+    for (int r = 0; r < 3; ++r) {
+      const double wg = w * ga[r];
+      for (int c = 0; c < 3; ++c) { M0[3 * r + c] += wg * g0[c]; M1[3 * r + c] += wg * g1[c]; }
+    }
+  }
+  block_from_moments(form, c1, c2, s, M0, B0);
+  block_from_moments(form, c1, c2, s, M1, B1);
+}
+
 // Row assembly, the algorithm of k_hex_assemble (one warp per row node i): the 8 n_cells(i) work items (cell around i,
-// local column b) are evaluated HEX_PASS at a time, one or two per lane, into a staging area; then the lane that owns a
+// local column b), item t = 8 (cell position in the adjacency of i) + b, are evaluated HEX_PASS at a time -- lane l takes
+// the pair (2 l, 2 l + 1) of the pass, two columns of one cell -- into a staging area; then the lane that owns a
 // destination block sums the staged items of its column in item (= cell-ascending) order.  Deterministic, no atomics.
 constexpr int HEX_PASS = 64;
 
-// item t of row i -> staged block and column; returns false past the end
-FEMO_HD bool row_item(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
-                      const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
-                      int64_t i, int t, double B[9], int32_t* col) {
+// items t, t + 1 (t even) of row i -> staged blocks and columns; returns false past the end
+FEMO_HD bool row_item_pair(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
+                           const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr,
+                           const int32_t* __restrict__ nc_adj, int64_t i, int t, double B0[9], double B1[9], int32_t col[2]) {
   const int32_t e = nc_ptr[i] + (t >> 3);
   if (e >= nc_ptr[i + 1]) return false;
   const int32_t ca = nc_adj[e];
   const int64_t cell = ca >> 3;
   const int b = t & 7;
-  *col = cells[8 * cell + b];
-  item_body(form, c1, c2, geo, cell, scale[cell], ca & 7, b, B);
+  col[0] = cells[8 * cell + b];
+  col[1] = cells[8 * cell + b + 1];
+  item_pair_body(form, c1, c2, geo + cell * 8 * GEO, scale[cell], ca & 7, b, B0, B1);
   return true;
 }
 
-// sum of the staged items [0, n_staged) whose column is `col`
+// sum of the staged items [0, n_staged) whose column is `col`, in ascending item order; staging is component-major:
+// s_val[k * HEX_PASS + t].  Two phases so that a warp does not run the 9-term body once per item with a single lane
+// active: (1) a 64-bit match mask, every lane busy; (2) a loop over the set bits (1, 2, 4 or 8 on a structured mesh).
+// s_col must hold HEX_PASS readable entries (16-byte aligned on the device); entries past n_staged are ignored.
 FEMO_HD void row_collect(const double* __restrict__ s_val, const int32_t* __restrict__ s_col, int n_staged, int32_t col,
                          double acc[9]) {
+  unsigned long long m = 0ull;
+#ifdef __CUDA_ARCH__
+  const int4* c4 = reinterpret_cast<const int4*>(s_col);
+#pragma unroll
+  for (int j = 0; j < HEX_PASS / 4; ++j) {
+    const int4 v = c4[j];
+    const unsigned long long bits = (unsigned long long)((v.x == col) | ((v.y == col) << 1) | ((v.z == col) << 2) | ((v.w == col) << 3));
+    m |= bits << (4 * j);
+  }
+#else
+  for (int t = 0; t < HEX_PASS; ++t) m |= (unsigned long long)(s_col[t] == col) << t;
+#endif
+  if (n_staged < HEX_PASS) m &= (1ull << n_staged) - 1ull;
   for (int k = 0; k < 9; ++k) acc[k] = 0.0;
-  for (int t = 0; t < n_staged; ++t)
-    if (s_col[t] == col)
-      for (int k = 0; k < 9; ++k) acc[k] += s_val[9 * t + k];
+  while (m) {
+#ifdef __CUDA_ARCH__
+    const int t = __ffsll((long long)m) - 1;
+#else
+    int t = 0;
+    while (!((m >> t) & 1ull)) ++t;
+#endif
+    m &= m - 1ull;
+    for (int k = 0; k < 9; ++k) acc[k] += s_val[k * HEX_PASS + t];
+  }
 }
 
 // displacement gradient G[i][k] = sum_a u_a[i] d N_a / d x_k of one cell at point q

@@ -34,21 +34,20 @@ int hex_host_assemble(int form, double c1, double c2, double p, int64_t nb, cons
   std::vector<double> scale(nc);
   for (int64_t e = 0; e < nc; ++e) scale[e] = pow(rho[e], p);
   double s_val[HEX_PASS * 9];
-  int32_t s_col[HEX_PASS];
+  int32_t s_col[HEX_PASS] = {0};
   for (int64_t i = 0; i < nb; ++i) {
     const int n_items = 8 * (nc_ptr[i + 1] - nc_ptr[i]);
     for (int t0 = 0; t0 < n_items; t0 += HEX_PASS) {
       const int n_staged = std::min(HEX_PASS, n_items - t0);
-      for (int h = 0; h < HEX_PASS / 32; ++h)
-        for (int lane = 0; lane < 32; ++lane) {
-          const int t = lane + 32 * h;
-          double B[9];
-          int32_t col;
-          if (t < n_staged && row_item(form, c1, c2, geo, cells, scale.data(), nc_ptr, nc_adj, i, t0 + t, B, &col)) {
-            s_col[t] = col;
-            for (int k = 0; k < 9; ++k) s_val[9 * t + k] = B[k];
-          }
+      for (int lane = 0; lane < 32; ++lane) {
+        const int t = 2 * lane;
+        double B0[9], B1[9];
+        int32_t col[2];
+        if (t < n_staged && row_item_pair(form, c1, c2, geo, cells, scale.data(), nc_ptr, nc_adj, i, t0 + t, B0, B1, col)) {
+          s_col[t] = col[0]; s_col[t + 1] = col[1];
+          for (int k = 0; k < 9; ++k) { s_val[k * HEX_PASS + t] = B0[k]; s_val[k * HEX_PASS + t + 1] = B1[k]; }
         }
+      }
       for (int lane = 0; lane < 32; ++lane)
         for (int32_t k = rowptr[i] + lane; k < rowptr[i + 1]; k += 32) {
           double acc[9];
