@@ -48,8 +48,8 @@ __global__ void k_hex_scale(const double* __restrict__ rho, double p, int64_t nc
 }
 
 // One warp per row node i.  Per pass of up to 8 cells around i (HEX_PASS = 64 work items, hex_element.cuh):
-//   1. the cells' geometry records (8 x 80 doubles) are copied to shared memory with coalesced loads (row stride 81
-//      doubles: the 8 cells of a request fall into different banks);
+//   1. the cells' geometry records (8 x 80 doubles) are copied to shared memory with cp.async (row stride 82
+//      doubles: 16-byte aligned, and the 8 cells of a request fall into different banks);
 //   2. lane l evaluates the item pair (2 l, 2 l + 1) = two columns of cell l / 4 (item_pair_body);
 //   3. the blocks are staged component-major in the same shared region, and the lanes that own the destination blocks of
 //      the row collect the items of their column in cell-ascending order (row_collect);
@@ -58,14 +58,14 @@ __global__ void k_hex_scale(const double* __restrict__ rho, double p, int64_t nc
 // rows with more than 32 blocks further destination chunks.
 static_assert(HEX_PASS == 64, "k_hex_assemble stages one item pair per lane");
 constexpr int HEX_WARPS = 4;
-constexpr int HEX_GSTRIDE = 8 * GEO + 1;
+constexpr int HEX_GSTRIDE = 8 * GEO + 2;                 // 16-byte aligned rows, 4 banks apart
 constexpr int HEX_REGION = 8 * HEX_GSTRIDE;              // >= 9 * HEX_PASS
-__global__ void __launch_bounds__(32 * HEX_WARPS)
+__global__ void __launch_bounds__(32 * HEX_WARPS, 5)
 k_hex_assemble(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
                const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int64_t nb,
                double* __restrict__ vals) {
-  __shared__ double s_reg[HEX_WARPS][HEX_REGION];        // geometry records, then the staged blocks
+  __shared__ __align__(16) double s_reg[HEX_WARPS][HEX_REGION];        // geometry records, then the staged blocks
   __shared__ double s_out[HEX_WARPS][32 * 9];
   __shared__ __align__(16) int32_t s_col[HEX_WARPS][HEX_PASS];
   const unsigned FULL = 0xffffffffu;
@@ -78,13 +78,22 @@ k_hex_assemble(int form, double c1, double c2, const double* __restrict__ geo, c
   for (int c0 = 0; c0 < n_cells_i; c0 += 8) {
     const int n_pass = min(8, n_cells_i - c0);           // cells of this pass
     const int32_t my_ca = (lane < n_pass) ? nc_adj[e0 + c0 + lane] : 0;
-    // 1. geometry records -> shared memory
-    for (int base = 0; base < n_pass * 8 * GEO; base += 32) {
-      const int idx = base + lane;
-      const int cl = min(idx / (8 * GEO), 7);
+    // 1. geometry records -> shared memory: 8 cells x 40 chunks of 16 bytes, ten asynchronous copies per lane in flight
+    //    at once (a load -> store loop exposes the full memory latency ten times: 37 % of the stall samples in
+    //    profiles/r01t_hex_asm_*.csv)
+#pragma unroll
+    for (int j = 0; j < (8 * 8 * GEO / 2) / 32; ++j) {
+      const int idx = j * 32 + lane;
+      const int cl = idx / (8 * GEO / 2), ch = idx - cl * (8 * GEO / 2);
       const int32_t ca = __shfl_sync(FULL, my_ca, cl);
-      if (idx < n_pass * 8 * GEO) reg[cl * HEX_GSTRIDE + (idx - cl * 8 * GEO)] = geo[(int64_t)(ca >> 3) * (8 * GEO) + (idx - cl * 8 * GEO)];
+      if (cl < n_pass) {
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(reg + cl * HEX_GSTRIDE + 2 * ch);
+        const double* src = geo + (int64_t)(ca >> 3) * (8 * GEO) + 2 * ch;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+      }
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     // 2. item pair of this lane
     const int cl = lane >> 2, b = 2 * (lane & 3);
