@@ -211,6 +211,16 @@ def dynamic_metric():
         return {"error": "%s: %s" % (type(e).__name__, e)}
 
 
+def solid_metric():
+    """BASELINE config 5 (generic 3-D form): unit cube, 160^3 Q1 hexahedra, SIMP elasticity -- Jacobian assembly and
+    PCG iteration times (scripts/hex_bench.py)."""
+    try:
+        from scripts.hex_bench import run
+        return run(160, 3, 20)
+    except Exception as e:                      # reported, never hidden
+        return {"error": "%s: %s" % (type(e).__name__, e)}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -326,10 +336,11 @@ def run_ours(args, rank, world, local_rank):
     barrier()
 
     mg = None
-    dyn = None
+    dyn = solid = None
     if world == 1 and not args.no_mg:
         mg = mg_solve_metric(n, local_rank)
         dyn = dynamic_metric()
+        solid = solid_metric()
 
     if rank != 0:
         if world > 1:
@@ -374,6 +385,7 @@ def run_ours(args, rank, world, local_rank):
                   "converged": False, "note": "fixed iteration count; N>1: one coupled system, NCCL halo exchange + 2 all-reduces per iteration",
                   "multigrid": mg},
         "dynamic": dyn,
+        "solid": solid,
         "cpu_baseline": cpu,
     }
     print(json.dumps(out))

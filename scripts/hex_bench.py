@@ -15,20 +15,12 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=160)
-    ap.add_argument("--reps", type=int, default=5)
-    ap.add_argument("--krylov-iters", type=int, default=50)
-    ap.add_argument("--form", default="elasticity")
-    ap.add_argument("--out", default=None)
-    a = ap.parse_args()
+def run(n=160, reps=5, krylov_iters=50, form="elasticity"):
     from femo_alpha_b200.solid_device import SolidDevice, box_hexes
-    n = a.n
     t0 = time.time()
     nodes, cells = box_hexes(n, n, n)
     t1 = time.time()
-    d = SolidDevice(nodes, cells, form=a.form, E0=1.0, nu=0.3, simp_p=3.0)
+    d = SolidDevice(nodes, cells, form=form, E0=1.0, nu=0.3, simp_p=3.0)
     t2 = time.time()
     rng = np.random.default_rng(20261104)
     f = np.zeros((d.nb, 3)); f[:, 2] = -1.0
@@ -36,14 +28,14 @@ def main():
     base = np.nonzero(nodes[:, 0] < 1e-12)[0]
     d.set_strong_bc((3 * base[:, None] + np.arange(3)).ravel())
     ms = []
-    for r in range(a.reps + 2):
+    for r in range(reps + 2):
         d.set_input("density", rng.uniform(0.01, 1.0, d.nc))       # invalidates the operator
         d.assemble_jacobian()
         ms.append(d.last_timings()["assemble_ms"])
     ms = ms[2:]
     asm = float(np.mean(ms))
     l0 = d.launch_count()
-    tot = d.pcg_fixed(a.krylov_iters)
+    tot = d.pcg_fixed(krylov_iters)
     launches_pcg = d.launch_count() - l0
     # algorithmic bytes per launch: every BSR block written once; per cell 8 geometry records, density, connectivity
     bytes_alg = 72.0 * d.nnzb + d.nc * (8 * 80 + 8 + 32)
@@ -54,18 +46,29 @@ def main():
     except Exception:
         pass
     line = dict(metric="3-D elasticity Jacobian assembly throughput (config 5)", value=d.ndof / asm / 1e6, unit="GDOF/s",
-                config=dict(workload="unit cube %d^3 Q1 hexahedra, %s, SIMP rho^3, seed 20261104" % (n, a.form), n_dof=int(d.ndof),
+                config=dict(workload="unit cube %d^3 Q1 hexahedra, %s, SIMP rho^3, seed 20261104" % (n, form), n_dof=int(d.ndof),
                             n_cells=int(d.nc), nnz_blocks=int(d.nnzb)),
-                assemble_ms=asm, assemble_ms_all=ms, pcg_ms_per_iter=tot / a.krylov_iters, pcg_launches=int(launches_pcg),
+                assemble_ms=asm, assemble_ms_all=ms, pcg_ms_per_iter=tot / krylov_iters, pcg_launches=int(launches_pcg),
                 mesh_s=t1 - t0, setup_s=t2 - t1,
-                roofline=dict(bound="hbm", achieved=bytes_alg / asm / 1e6, peak=peak, unit="GB/s",
+                roofline=dict(kernel="k_hex_assemble", bound="hbm", achieved=bytes_alg / asm / 1e6, peak=peak, unit="GB/s",
                               frac=(bytes_alg / asm / 1e6 / peak) if peak else None, traffic=None),
                 dtype="f64", data="synthetic")
-    s = json.dumps(line)
+    d.close()
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=160)
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--krylov-iters", type=int, default=50)
+    ap.add_argument("--form", default="elasticity")
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+    s = json.dumps(run(a.n, a.reps, a.krylov_iters, a.form))
     print(s)
     if a.out:
         open(a.out, "w").write(s + "\n")
-    d.close()
 
 
 if __name__ == "__main__":
