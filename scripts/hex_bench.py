@@ -15,7 +15,21 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def run(n=160, reps=5, krylov_iters=50, form="elasticity"):
+def cpu_baseline(form="elasticity", n=24):
+    """The oracle's assembly (numpy einsum element matrices + scipy CSR scatter, oracle/hex_ref.py) on a bounded sample
+    of the same workload -- a reported baseline, one host core."""
+    from oracle.hex_ref import HexOracle, box_mesh
+    nodes, cells = box_mesh(n, n, n)
+    o = HexOracle(nodes, cells, form=form, E0=1.0, nu=0.3, simp_p=3.0)
+    o.set_inputs(density=np.random.default_rng(20261104).uniform(0.01, 1.0, o.nc))
+    ts = []
+    for _ in range(2):
+        t = time.time(); o.stiffness(); ts.append(time.time() - t)
+    return dict(value=o.ndof / min(ts) / 1e9, unit="GDOF/s", cores=1, kind="port",
+                sample="%d^3-cell cube of the same form (%d DOF), best of 2 assemblies, %.2f s" % (n, o.ndof, min(ts)))
+
+
+def run(n=160, reps=5, krylov_iters=50, form="elasticity", with_cpu=True):
     from femo_alpha_b200.solid_device import SolidDevice, box_hexes
     t0 = time.time()
     nodes, cells = box_hexes(n, n, n)
@@ -54,6 +68,11 @@ def run(n=160, reps=5, krylov_iters=50, form="elasticity"):
                               frac=(bytes_alg / asm / 1e6 / peak) if peak else None, traffic=None),
                 dtype="f64", data="synthetic")
     d.close()
+    if with_cpu:
+        try:
+            line["cpu_baseline"] = cpu_baseline(form)
+        except Exception as e:
+            line["cpu_baseline"] = {"error": "%s: %s" % (type(e).__name__, e)}
     return line
 
 
