@@ -143,7 +143,6 @@ int femo_dist_setup(femo_ctx* c, int rank, int world, int n_nbr, const int32_t* 
                     const int32_t* send_blocks, const int32_t* recv_off, const int32_t* recv_blocks,
                     const uint8_t* own_block, int64_t n_owned_cells) {
   if (!c || !c->setup_done) return femo_fail("femo_dist_setup: context not set up");
-  if (c->kind != 0) return femo_fail("femo_dist_setup: hexahedral-solid contexts are single-GPU");
   if (world < 1 || rank < 0 || rank >= world) return femo_fail("femo_dist_setup: bad rank / world");
   if (n_owned_cells < 0 || n_owned_cells > c->nc) return femo_fail("femo_dist_setup: bad owned-cell count");
   DevGuard2 g(c->device);

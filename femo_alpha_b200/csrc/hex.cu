@@ -4,7 +4,9 @@
 // of named forms (hex_element.cuh) is assembled into the BSR 3x3 matrix of a `kind = 1` femo_ctx, so that
 // femo_set_strong_bc, femo_assemble_jacobian, femo_jacobian_apply, femo_get_bsr, femo_assemble_residual,
 // femo_solve_state / _adjoint / _forward, femo_pcg_fixed, femo_set_state / femo_get_state work on it unchanged
-// (k_spmv<8,6> and the fused block-Jacobi PCG of solver.cu).
+// (k_spmv<8,6> and the fused block-Jacobi PCG of solver.cu) -- and so does femo_dist_setup / femo_dist_init: with the
+// owner mask and halo lists of femo_alpha_b200/partition.py (build_local_part_hex) the solves run over NCCL like the
+// shell's (owner-computes assembly with one ghost-cell layer, no collective in assembly).
 //
 // Assembly is destination-driven: one thread per BSR block (32 lanes per row node) sums the contributions of the cells
 // around the row node that also hold the column node, in cell-ascending order -- no atomics, no intermediate element
@@ -381,7 +383,15 @@ int femo_hex_output(femo_ctx* c, int which, double* val) {
     TRY(hex_load(c, c->tmp));
     return dev_dot(c, c->tmp, c->w, c->ndof, val);
   }
-  if (which == 1) return dev_dot(c, c->hx_rho, c->hx_vol, c->nc, val);
+  if (which == 1) {
+    // multi-GPU: every cell is counted by the rank that owns it (owned cells come first), then summed over ranks
+    const int64_t ncs = c->world > 1 ? c->nc_owned : c->nc;
+    TRY(dev_dot_async(c, c->hx_rho, c->hx_vol, ncs, c->scal + 9));
+    if (c->world > 1) TRY(dist_allreduce_sum(c, c->scal + 9, 1));
+    CUDA_TRY(cudaMemcpyAsync(val, c->scal + 9, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+  }
   return femo_fail("femo_hex_output: unknown output");
 }
 

@@ -185,3 +185,52 @@ def halo_arrays(lp: LocalPart):
     r = np.concatenate([lp.recv_blocks[q] for q in lp.neighbors]) if lp.neighbors else np.zeros(0, np.int32)
     return (nbr, np.asarray(s_off, dtype=np.int32), np.ascontiguousarray(s, dtype=np.int32),
             np.asarray(r_off, dtype=np.int32), np.ascontiguousarray(r, dtype=np.int32))
+
+
+# ---- hexahedral solids (csrc/hex.cu, SURVEY 8 f4 on N GPUs): block nodes = mesh nodes ------------------------------------
+def build_local_part_hex(nodes: np.ndarray, hexes: np.ndarray, part: np.ndarray, rank: int, world: int) -> LocalPart:
+    """Local mesh of ``rank`` for a hexahedral solid, halo lists included (the library numbers the block nodes of a solid
+    context like the mesh nodes, so no attach_blocks step is needed).  Same rules as for the shell: a node is owned by
+    the lowest part among its cells; a rank keeps every cell that holds a node it owns (owned cells first)."""
+    nodes = np.asarray(nodes, dtype=np.float64)
+    hexes = np.asarray(hexes).astype(np.int64)
+    part = np.asarray(part, dtype=np.int32)
+    nv, npc = nodes.shape[0], hexes.shape[1]
+    v_owner = np.full(nv, world, dtype=np.int32)
+    np.minimum.at(v_owner, hexes.ravel(), np.repeat(part, npc))
+    own = v_owner[hexes]                                            # (nc, 8) owner of every cell node
+    needed = (own == rank).any(axis=1)
+    owned = part == rank
+    assert not (owned & ~needed).any()
+    loc_cells = np.concatenate([np.nonzero(owned)[0], np.nonzero(needed & ~owned)[0]])
+    vglob = np.unique(hexes[loc_cells].ravel())
+    remap = np.full(nv, -1, dtype=np.int64)
+    remap[vglob] = np.arange(vglob.size)
+    lp = LocalPart(rank=rank, world=world, nodes=np.ascontiguousarray(nodes[vglob]),
+                   quads=np.ascontiguousarray(remap[hexes[loc_cells]].astype(np.int32)),
+                   vertex_global=vglob, cell_global=loc_cells, n_owned_cells=int(owned.sum()),
+                   own9=own[loc_cells], gkey9=hexes[loc_cells],
+                   n_global_vertices=nv, n_global_cells=hexes.shape[0], n_global_edges=0)
+    lp.block_owner = v_owner[vglob].astype(np.int32)
+    lp.block_gkey = vglob.astype(np.int64)
+    # receive side: my ghost nodes grouped by owner; vglob is ascending, so local order = key order
+    recv = {}
+    ghosts = np.nonzero(lp.block_owner != rank)[0]
+    for q in np.unique(lp.block_owner[ghosts]):
+        recv[int(q)] = ghosts[lp.block_owner[ghosts] == q].astype(np.int32)
+    # send side: nodes I own inside cells that rank q keeps (q owns another node of the same cell)
+    mine = own == rank
+    cells_with_mine = mine.any(axis=1)
+    send = {}
+    for q in np.unique(own[cells_with_mine]):
+        if q == rank:
+            continue
+        cells_q = cells_with_mine & (own == q).any(axis=1)
+        keys = np.unique(hexes[cells_q][mine[cells_q]])
+        send[int(q)] = remap[keys].astype(np.int32)
+    lp.send_blocks, lp.recv_blocks = send, recv
+    lp.neighbors = sorted(set(send) | set(recv))
+    for q in lp.neighbors:
+        send.setdefault(q, np.zeros(0, dtype=np.int32))
+        recv.setdefault(q, np.zeros(0, dtype=np.int32))
+    return lp

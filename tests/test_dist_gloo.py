@@ -67,3 +67,38 @@ def test_rcb_partition_is_balanced_and_covers():
         part = partition_cells_rcb(c, world)
         cnt = np.bincount(part, minlength=world)
         assert cnt.sum() == 1000 and cnt.min() >= 1000 // world - 1 and cnt.max() <= 1000 // world + 2
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_distributed_hexahedral_solid_matches_global_solve(tmp_path, world):
+    """build_local_part_hex (SURVEY 8 f4 on N GPUs): state, compliance, volume and the density gradient of the
+    compliance of a distorted 6x4x3 box against the oracle's global solve."""
+    from oracle.hex_ref import HexOracle
+    from tests.dist_hex_worker import problem
+    port = _free_port()
+    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "dist_hex_worker.py"), str(r), str(world),
+                               str(port), str(tmp_path)], cwd=ROOT) for r in range(world)]
+    for pr in procs:
+        assert pr.wait(timeout=600) == 0
+    nodes, cells, rho, f = problem()
+    o = HexOracle(nodes, cells, E0=4.0, nu=0.3)
+    o.set_inputs(density=rho, body_force=f)
+    base = np.nonzero(nodes[:, 0] < 1e-12)[0]
+    o.set_strong_bc((3 * base[:, None] + np.arange(3)).ravel())
+    u = o.solve()
+    g = o.total_dcompliance_drho()
+    seen = np.zeros(o.nn, dtype=int); cells_seen = np.zeros(o.nc, dtype=int)
+    tot_send = tot_recv = 0
+    for r in range(world):
+        d = np.load(os.path.join(tmp_path, "hex_rank%d.npz" % r))
+        x = d["x"].reshape(-1, 3)
+        assert np.abs(x - u.reshape(-1, 3)[d["gkey"]]).max() <= 1e-8 * np.abs(u).max()      # owned and ghost entries
+        assert np.isclose(float(d["compliance"]), o.compliance(u), rtol=1e-9)
+        assert np.isclose(float(d["volume"]), o.volume(), rtol=1e-12)
+        n_own = int(d["n_owned_cells"])
+        assert np.abs(d["g_own"] - g[d["cell_global"][:n_own]]).max() <= 1e-8 * np.abs(g).max()
+        seen[d["gkey"][d["owner"] == r]] += 1
+        cells_seen[d["cell_global"][:n_own]] += 1
+        tot_send += int(d["send"]); tot_recv += int(d["recv"])
+    assert (seen == 1).all() and (cells_seen == 1).all()
+    assert tot_send == tot_recv and tot_send > 0

@@ -37,3 +37,16 @@ def test_two_gpu_time_stepping_matches_oracle(built_lib, name, sw):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     sys.stdout.write(r.stdout[-4000:]); sys.stderr.write(r.stderr[-4000:])
     assert r.returncode == 0
+
+
+@pytest.mark.parametrize("n", [2, 3])
+def test_multi_gpu_hexahedral_solid_matches_oracle(built_lib, n):
+    """SURVEY 8 f4 on N GPUs (DistributedSolid): state, compliance, volume, adjoint density gradient
+    (tests/dist_gpu_hex_worker.py).  Not yet run on hardware in round 1."""
+    if _ngpu() < n:
+        pytest.skip("needs %d GPUs" % n)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr",
+           "127.0.0.1", "--master-port", "29535", os.path.join(ROOT, "tests", "dist_gpu_hex_worker.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(r.stdout[-4000:]); sys.stderr.write(r.stderr[-4000:])
+    assert r.returncode == 0
