@@ -374,5 +374,5 @@ def computeMatVecProductBwd(A, R):
 
 
 # ---- mesh readers (utils_dolfinx.py:34-50,88-142,653-668): host side, femo_alpha_b200/mesh_io.py --------------------
-from ..mesh_io import readFEAMesh, import_mesh, writeFEAMesh, read_msh, readMshShellMesh   # noqa: E402,F401
+from ..mesh_io import readFEAMesh, import_mesh, writeFEAMesh, read_msh, readMshShellMesh, readMshSolidMesh   # noqa: E402,F401
 from ..mesh import reconstructFEAMesh, createRectangleMesh, createUnitSquareMesh          # noqa: E402,F401

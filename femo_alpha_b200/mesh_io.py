@@ -22,7 +22,7 @@ import numpy as np
 
 from .mesh import ShellMesh
 
-_XDMF_CELLS = {"quadrilateral": 4, "quad": 4, "triangle": 3, "polyline": 2, "line": 2, "polyvertex": 1}
+_XDMF_CELLS = {"quadrilateral": 4, "quad": 4, "triangle": 3, "polyline": 2, "line": 2, "polyvertex": 1, "hexahedron": 8}
 
 
 def _check_not_lfs_stub(path):
@@ -88,6 +88,9 @@ def readFEAMesh(meshFile, format='HDF'):
     if format not in ('HDF', 'XML'):
         raise ValueError("Invalid mesh file type. Must be 'HDF' or 'XML'")
     x, conn, ttype, _ = _read_xdmf_grid(meshFile, "Grid")
+    if conn.shape[1] == 8:                  # hexahedral solid for the named 3-D forms (fea/named_forms.py); XDMF = VTK order
+        from .fea.named_forms import SolidMesh
+        return SolidMesh(x, conn)
     if conn.shape[1] not in (3, 4):
         raise ValueError('Invalid cell shape--should be either triangular or quadrilateral')
     return ShellMesh(x, conn)
@@ -97,7 +100,7 @@ def writeFEAMesh(meshFile, nodes, connectivity, cell_data=None):
     """Self-contained ASCII XDMF ('XML' format of readFEAMesh), the layout meshio writes."""
     nodes = np.asarray(nodes, dtype=np.float64)
     conn = np.asarray(connectivity, dtype=np.int64)
-    ttype = {4: "Quadrilateral", 3: "Triangle", 2: "Polyline"}[conn.shape[1]]
+    ttype = {8: "Hexahedron", 4: "Quadrilateral", 3: "Triangle", 2: "Polyline"}[conn.shape[1]]
     root = ET.Element("Xdmf", Version="3.0")
     dom = ET.SubElement(root, "Domain")
     grid = ET.SubElement(dom, "Grid", Name="Grid", GridType="Uniform")
@@ -158,11 +161,11 @@ def import_mesh(prefix='mesh', subdomains=False, dim=2, directory='.'):
 
 
 # ---- Gmsh .msh (ASCII 2.2 and 4.1) ---------------------------------------------------------------------------------
-_GMSH_NODES = {1: 2, 2: 3, 3: 4, 15: 1}       # line, triangle, quadrangle, point
+_GMSH_NODES = {1: 2, 2: 3, 3: 4, 5: 8, 15: 1}       # line, triangle, quadrangle, hexahedron (VTK node order), point
 
 
 def read_msh(path):
-    """Gmsh ASCII mesh -> dict(nodes (n,3), quads, triangles, lines, quad_tags, triangle_tags, line_tags,
+    """Gmsh ASCII mesh -> dict(nodes (n,3), quads, triangles, lines, hexes, quad_tags, triangle_tags, line_tags, hex_tags,
     physical_names {name: (dim, tag)}).  Tags are the physical tags (first tag of 2.2, entity -> physical map of 4.1)."""
     _check_not_lfs_stub(path)
     with open(path, "r") as f:
@@ -189,7 +192,7 @@ def read_msh(path):
         p = ln.split(None, 2)
         if len(p) == 3:
             names[p[2].strip().strip('"')] = (int(p[0]), int(p[1]))
-    cells = {2: ([], []), 3: ([], []), 4: ([], [])}       # nodes-per-cell -> (connectivity, tag)
+    cells = {2: ([], []), 3: ([], []), 4: ([], []), 8: ([], [])}       # nodes-per-cell -> (connectivity, tag)
     if ver.startswith("2"):
         nn = int(sections["Nodes"][0])
         ids = np.empty(nn, dtype=np.int64); xyz = np.empty((nn, 3))
@@ -210,7 +213,7 @@ def read_msh(path):
         if E:
             npnt, ncur, nsur, nvol = [int(v) for v in E[0].split()]
             row = 1 + npnt
-            for d, cnt in ((1, ncur), (2, nsur)):
+            for d, cnt in ((1, ncur), (2, nsur), (3, nvol)):
                 for ln in E[row:row + cnt]:
                     p = ln.split()
                     nphys = int(p[7])
@@ -243,9 +246,9 @@ def read_msh(path):
     lookup = np.full(ids.max() + 1, -1, dtype=np.int64)
     lookup[ids] = np.arange(ids.size)
     out = dict(nodes=xyz, physical_names=names)
-    for npc, key in ((4, "quad"), (3, "triangle"), (2, "line")):
+    for npc, key in ((8, "hex"), (4, "quad"), (3, "triangle"), (2, "line")):
         c = np.array(cells[npc][0], dtype=np.int64).reshape(-1, npc)
-        out[key + "s"] = lookup[c] if c.size else c
+        out[key + ("es" if key == "hex" else "s")] = lookup[c] if c.size else c
         out[key + "_tags"] = np.array(cells[npc][1], dtype=np.int64)
     return out
 
@@ -264,4 +267,20 @@ def readMshShellMesh(path):
     remap[used] = np.arange(used.size)
     mesh = ShellMesh(m["nodes"][used], remap[quads])
     tags = MeshTags(2, np.arange(quads.shape[0]), m["quad_tags"])
+    return mesh, tags.as_dict(), m["physical_names"]
+
+
+def readMshSolidMesh(path):
+    """Hexahedral solid mesh + {physical tag: cell indices} + physical names from a Gmsh file, for the named 3-D forms
+    (fea/named_forms.py: build_fea).  Nodes not used by any hexahedron are dropped."""
+    from .fea.named_forms import SolidMesh
+    m = read_msh(path)
+    hexes = m["hexes"]
+    if hexes.size == 0:
+        raise ValueError("%s holds no hexahedra" % path)
+    used = np.unique(hexes)
+    remap = np.full(m["nodes"].shape[0], -1, dtype=np.int64)
+    remap[used] = np.arange(used.size)
+    mesh = SolidMesh(m["nodes"][used], remap[hexes])
+    tags = MeshTags(3, np.arange(hexes.shape[0]), m["hex_tags"])
     return mesh, tags.as_dict(), m["physical_names"]

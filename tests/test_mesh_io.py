@@ -134,3 +134,62 @@ def test_reference_wing_msh_is_an_lfs_pointer():
         pytest.skip("reference checkout not present")
     with pytest.raises(IOError, match="git-LFS"):
         IO.read_msh(ref)
+
+
+# ---- hexahedral solids (named 3-D forms) ---------------------------------------------------------------------
+def _two_hexes():
+    nodes = np.array([[x, y, z] for z in (0.0, 1.0) for y in (0.0, 1.0) for x in (0.0, 1.0, 2.0)], dtype=float)
+    # node id = x + 3 y + 6 z ; VTK_HEXAHEDRON order
+    cells = np.array([[0, 1, 4, 3, 6, 7, 10, 9], [1, 2, 5, 4, 7, 8, 11, 10]])
+    return nodes, cells
+
+
+def test_xdmf_hexahedron_round_trip(tmp_path):
+    from femo_alpha_b200.fea.named_forms import SolidMesh
+    nodes, cells = _two_hexes()
+    p = str(tmp_path / "block.xdmf")
+    IO.writeFEAMesh(p, nodes, cells)
+    mesh = IO.readFEAMesh(p, 'XML')
+    assert isinstance(mesh, SolidMesh)
+    assert np.array_equal(mesh.cells, cells) and np.allclose(mesh.geometry.x, nodes)
+    assert mesh.topology.dim == 3 and mesh.topology.index_map(3).size_local == 2 and mesh.topology.index_map(0).size_local == 12
+    assert mesh.ufl_cell().cellname() == "hexahedron"
+
+
+def _msh22_hex():
+    nodes, cells = _two_hexes()
+    lines = ["$MeshFormat", "2.2 0 8", "$EndMeshFormat", "$PhysicalNames", "2", '3 7 "core"', '3 8 "shell"', "$EndPhysicalNames",
+             "$Nodes", str(len(nodes) + 1)]
+    lines += ["%d %r %r %r" % (i + 1, *map(float, nodes[i])) for i in range(len(nodes))] + ["40 9 9 9", "$EndNodes", "$Elements", "3"]
+    lines += ["1 5 2 7 1 " + " ".join(str(v + 1) for v in cells[0]), "2 5 2 8 2 " + " ".join(str(v + 1) for v in cells[1]),
+              "3 15 2 0 1 40", "$EndElements", ""]
+    return "\n".join(lines)
+
+
+def _msh41_hex():
+    nodes, cells = _two_hexes()
+    lines = ["$MeshFormat", "4.1 0 8", "$EndMeshFormat", "$PhysicalNames", "1", '3 8 "shell"', "$EndPhysicalNames",
+             "$Entities", "0 0 0 2", "1 0 0 0 1 1 1 1 7 0", "2 1 0 0 2 1 1 1 8 0", "$EndEntities",
+             "$Nodes", "1 12 1 12", "3 1 0 12"] + [str(i + 1) for i in range(12)]
+    lines += ["%r %r %r" % tuple(map(float, nodes[i])) for i in range(12)] + ["$EndNodes", "$Elements", "2 2 1 2", "3 1 5 1",
+              "1 " + " ".join(str(v + 1) for v in cells[0]), "3 2 5 1", "2 " + " ".join(str(v + 1) for v in cells[1]),
+              "$EndElements", ""]
+    return "\n".join(lines)
+
+
+@pytest.mark.parametrize("text", [_msh22_hex(), _msh41_hex()], ids=["msh22", "msh41"])
+def test_gmsh_hexahedra(tmp_path, text):
+    nodes, cells = _two_hexes()
+    p = tmp_path / "block.msh"
+    p.write_text(text)
+    mesh, tags, names = IO.readMshSolidMesh(str(p))
+    assert mesh.geometry.x.shape == (12, 3) and np.allclose(mesh.geometry.x, nodes)      # the stray point is dropped
+    assert np.array_equal(mesh.cells, cells)
+    assert np.array_equal(tags[7], [0]) and np.array_equal(tags[8], [1])
+    assert names["shell"] == (3, 8)
+    with pytest.raises(ValueError):
+        q = tmp_path / "wing.msh"; q.write_text(MSH22)
+        IO.readMshSolidMesh(str(q))
+    # the mesh feeds the oracle of the named forms: positive Jacobians, volume 2
+    from oracle.hex_ref import HexOracle
+    assert np.isclose(HexOracle(mesh.geometry.x, mesh.cells).vol.sum(), 2.0)
