@@ -6,6 +6,8 @@
 #   dyn     config-4 timings (scripts/dyn_bench.py --large)
 #   ncu     launch list of a short bench run and of a short dynamic run (per-launch durations, no clock control)
 #   hex     config-5 solid forms: parity tests + 160^3 assembly / PCG timings (scripts/hex_bench.py)
+#   ncuhex  ncu --set full of one k_hex_assemble launch -> gpurun_out/${TAG}_hex_asm.ncu-rep
+#   disthex N-GPU parity of the hexahedral solids (needs `gpurun --gpus 2` or more; first run pending)
 #   distdyn 2-GPU parity of the time-stepped path only (needs `gpurun --gpus 2`)
 #   dist    2-GPU parity test + 2-GPU bench line (needs `gpurun --gpus 2`)
 set -u
@@ -33,6 +35,11 @@ for sec in "$@"; do
     hex)
       timeout 600 python -m pytest tests/test_gpu_hex.py -m gpu -q --tb=short > gpurun_out/${T}_pytest_gpu_hex.log 2>&1; echo "pytest hex rc=$?"; tail -n 25 gpurun_out/${T}_pytest_gpu_hex.log
       timeout 600 python scripts/hex_bench.py --n ${HEX_N:-160} --out gpurun_out/${T}_hex_bench.json > gpurun_out/${T}_hex_bench.log 2>&1; echo "hex bench rc=$?"; tail -n 5 gpurun_out/${T}_hex_bench.log ;;
+    ncuhex)
+      # full ncu capture of one k_hex_assemble launch (read here with `ncu -i ... --page raw|source --csv`)
+      timeout 300 ncu --set full --clock-control none --import-source on -k regex:k_hex_assemble -s 2 -c 1 -f -o gpurun_out/${T}_hex_asm python scripts/hex_bench.py --n ${HEX_N:-160} --reps 1 > gpurun_out/${T}_ncu_hex.log 2>&1; echo "ncu hex rc=$?" ;;
+    disthex)
+      timeout 600 python -m pytest tests/test_gpu_dist.py -m gpu -q --tb=short -s -k hexahedral > gpurun_out/${T}_pytest_gpu_disthex.log 2>&1; echo "pytest disthex rc=$?"; grep -E "^rank|passed|failed|xfailed|xpassed|Error|error" gpurun_out/${T}_pytest_gpu_disthex.log | tail -n 12 ;;
     *) echo "unknown section $sec" ;;
   esac
 done
