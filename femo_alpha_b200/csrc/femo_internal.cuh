@@ -182,6 +182,7 @@ struct femo_ctx {
   int64_t hx_nn = 0;            // mesh nodes (= nb)
   int32_t* hx_cells = nullptr;  // nc*8, VTK_HEXAHEDRON order
   double *hx_geo = nullptr;     // nc*8*10 inverse Jacobians and weights
+  double *hx_geo2 = nullptr;    // nc*8*26 gradient records (only with FEMO_HEX_GRAD=1: k_hex_assemble_g)
   double *hx_rho = nullptr, *hx_scale = nullptr, *hx_vol = nullptr;   // nc: density, rho^p, cell volume
   double *hx_f = nullptr;       // nn*3 nodal body force
   double *hx_cellvec = nullptr; // nc*24 element vectors

@@ -15,6 +15,7 @@
 // block (warp-uniform addresses, served by L1/L2).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "femo_internal.cuh"
@@ -135,6 +136,86 @@ k_hex_assemble(int form, double c1, double c2, const double* __restrict__ geo, c
   }
 }
 
+// ---- gradient-record variant (FEMO_HEX_GRAD=1 at femo_hex_setup; NOT YET MEASURED: written after the round-1 GPU budget
+// was spent, its element maths is covered by the CPU harness, its launch by tests/test_gpu_hex.py::test_gradient_records) ----
+__global__ void k_hex_geom2(const double* __restrict__ geo, int64_t n_rec, double* __restrict__ geo2) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;       // r = cell * 8 + q
+  if (r < n_rec) geom2_qp(geo + r * GEO, (int)(r & 7), geo2 + r * GEO2);
+}
+
+// Same row algorithm as k_hex_assemble with one item per lane and sub-passes of 4 cells: the 4 x 208 doubles of gradient
+// records are staged with cp.async (13 chunks of 16 bytes per lane), lane l evaluates item (cell l / 8, column l % 8), the
+// blocks of up to two sub-passes (64 items) are staged, then collected and stored as in k_hex_assemble.
+constexpr int HEXG_WARPS = 3;
+constexpr int HEXG_CSTRIDE = 8 * GEO2 + 2;               // 210 doubles: 16-byte aligned, cells 4 banks apart
+__global__ void __launch_bounds__(32 * HEXG_WARPS)
+k_hex_assemble_g(int form, double c1, double c2, const double* __restrict__ geo2, const int32_t* __restrict__ cells,
+                 const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
+                 const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int64_t nb,
+                 double* __restrict__ vals) {
+  __shared__ __align__(16) double s_geo[HEXG_WARPS][4 * HEXG_CSTRIDE];
+  __shared__ __align__(16) double s_stg[HEXG_WARPS][9 * HEX_PASS];
+  __shared__ double s_out[HEXG_WARPS][32 * 9];
+  __shared__ __align__(16) int32_t s_col[HEXG_WARPS][HEX_PASS];
+  const unsigned FULL = 0xffffffffu;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t i = blockIdx.x * (int64_t)HEXG_WARPS + warp;
+  if (i >= nb) return;
+  double* reg = s_geo[warp];
+  double* stg = s_stg[warp];
+  const int32_t e0 = nc_ptr[i], n_cells_i = nc_ptr[i + 1] - e0;
+  const int32_t r0 = rowptr[i], n_row = rowptr[i + 1] - r0;
+  constexpr int CH = 8 * GEO2 / 2;                       // 16-byte chunks per cell
+  for (int c0 = 0; c0 < n_cells_i; c0 += 8) {
+    const int n_chunk = min(8, n_cells_i - c0);          // cells of this chunk (two sub-passes of 4)
+    for (int h = 0; h < 2 && 4 * h < n_chunk; ++h) {
+      const int n_pass = min(4, n_chunk - 4 * h);
+      const int32_t my_ca = (lane < n_pass) ? nc_adj[e0 + c0 + 4 * h + lane] : 0;
+#pragma unroll
+      for (int j = 0; j < (4 * CH) / 32; ++j) {
+        const int idx = j * 32 + lane;
+        const int cl = idx / CH, ch = idx - cl * CH;
+        const int32_t ca = __shfl_sync(FULL, my_ca, cl);
+        if (cl < n_pass) {
+          const unsigned dst = (unsigned)__cvta_generic_to_shared(reg + cl * HEXG_CSTRIDE + 2 * ch);
+          const double* src = geo2 + (int64_t)(ca >> 3) * (8 * GEO2) + 2 * ch;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+      const int cl = lane >> 3, b = lane & 7;
+      const int32_t ca = __shfl_sync(FULL, my_ca, cl);
+      if (cl < n_pass) {
+        const int64_t cell = ca >> 3;
+        double B[9];
+        item_body_g(form, c1, c2, reg + cl * HEXG_CSTRIDE, scale[cell], ca & 7, b, B);
+        const int t = 32 * h + lane;                     // = 8 * (cell position in the chunk) + b
+        s_col[warp][t] = cells[8 * cell + b];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) stg[k * HEX_PASS + t] = B[k];
+      }
+      __syncwarp();                                      // records free for the next sub-pass, staging visible
+    }
+    const int n_staged = 8 * n_chunk;
+    for (int k0 = 0; k0 < n_row; k0 += 32) {
+      const int n_dst = min(32, n_row - k0);
+      if (lane < n_dst) {
+        double acc[9];
+        row_collect(stg, s_col[warp], n_staged, colidx[r0 + k0 + lane], acc);
+#pragma unroll
+        for (int e = 0; e < 9; ++e) s_out[warp][9 * lane + e] = acc[e];
+      }
+      __syncwarp();
+      double* out = vals + (int64_t)(r0 + k0) * 9;
+      if (c0 == 0) for (int idx = lane; idx < 9 * n_dst; idx += 32) out[idx] = s_out[warp][idx];
+      else for (int idx = lane; idx < 9 * n_dst; idx += 32) out[idx] += s_out[warp][idx];
+      __syncwarp();
+    }
+  }
+}
+
 // mode 0: consistent mass product coef * M_e x_e;  mode 1: cellcoef[e] * coef * K0_e x_e
 __global__ void k_hex_cellvec(int mode, int form, double c1, double c2, const double* __restrict__ geo,
                               const int32_t* __restrict__ cells, const double* __restrict__ x,
@@ -205,9 +286,14 @@ int hex_assemble(femo_ctx* c) {
   cudaEventRecord(c->ev0, c->stream);
   k_hex_scale<<<(unsigned)cdiv(c->nc, 256), 256, 0, c->stream>>>(c->hx_rho, c->hx_p, c->nc, c->hx_scale);
   TRY(check_launch(c, "k_hex_scale"));
-  k_hex_assemble<<<(unsigned)cdiv(c->nb, HEX_WARPS), 32 * HEX_WARPS, 0, c->stream>>>(c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo, c->hx_cells,
-                                                                       c->hx_scale, c->nc_ptr, c->nc_adj, c->rowptr, c->colidx,
-                                                                       c->nb, c->vals);
+  if (c->hx_geo2)
+    k_hex_assemble_g<<<(unsigned)cdiv(c->nb, HEXG_WARPS), 32 * HEXG_WARPS, 0, c->stream>>>(
+        c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo2, c->hx_cells, c->hx_scale, c->nc_ptr, c->nc_adj, c->rowptr, c->colidx, c->nb,
+        c->vals);
+  else
+    k_hex_assemble<<<(unsigned)cdiv(c->nb, HEX_WARPS), 32 * HEX_WARPS, 0, c->stream>>>(
+        c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo, c->hx_cells, c->hx_scale, c->nc_ptr, c->nc_adj, c->rowptr, c->colidx, c->nb,
+        c->vals);
   TRY(check_launch(c, "k_hex_assemble"));
   cudaEventRecord(c->ev1, c->stream);
   CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -299,6 +385,13 @@ int femo_hex_setup(femo_ctx* c, int64_t n_nodes, const double* xyz, int64_t n_ce
   k_hex_geom<<<(unsigned)cdiv(n_cells, 128), 128, 0, c->stream>>>(c->xyz, c->hx_cells, n_cells, c->hx_geo, c->hx_vol, bad);
   TRY(check_launch(c, "k_hex_geom"));
   c->launches += 4;
+  const char* genv = getenv("FEMO_HEX_GRAD");
+  if (genv && genv[0] == '1') {                            // gradient records for k_hex_assemble_g
+    TRY(dev_alloc(&c->hx_geo2, (size_t)n_cells * 8 * GEO2));
+    k_hex_geom2<<<(unsigned)cdiv(n_cells * 8, 256), 256, 0, c->stream>>>(c->hx_geo, n_cells * 8, c->hx_geo2);
+    TRY(check_launch(c, "k_hex_geom2"));
+    c->launches += 1;
+  }
   int hbad = 0;
   CUDA_TRY(cudaMemcpyAsync(&hbad, bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));

@@ -95,6 +95,36 @@ FEMO_HD void item_pair_body(int form, double c1, double c2, const double* __rest
   block_from_moments(form, c1, c2, s, M1, B1);
 }
 
+// ---- variant with gradient records (FEMO_HEX_GRAD=1, k_hex_assemble_g): per (cell, point) the physical gradients of the
+// 8 shape functions and weight * det J, so that an item costs 7 loads and 12 fp64 instructions per point instead of three
+// inverse-Jacobian products.  2.6x the record memory of the default path.
+constexpr int GEO2 = 26;         // 8 x 3 gradients, weight * det J, one pad (16-byte multiples)
+
+FEMO_HD void geom2_qp(const double* __restrict__ rec, int q, double* __restrict__ rec2) {
+  for (int a = 0; a < 8; ++a) {
+    double N, g[3];
+    phys_grad(rec, a, q, &N, g);
+    rec2[3 * a] = g[0]; rec2[3 * a + 1] = g[1]; rec2[3 * a + 2] = g[2];
+  }
+  rec2[24] = rec[9];
+  rec2[25] = 0.0;
+}
+
+// contribution of one cell to the block (row = local node a, column = local node b); `cg` = the 8 gradient records of the cell
+FEMO_HD void item_body_g(int form, double c1, double c2, const double* __restrict__ cg, double s, int a, int b, double B[9]) {
+  double M[9];
+  for (int k = 0; k < 9; ++k) M[k] = 0.0;
+  for (int q = 0; q < 8; ++q) {
+    const double* rec = cg + q * GEO2;
+    const double w = rec[24];
+    for (int r = 0; r < 3; ++r) {
+      const double wg = w * rec[3 * a + r];
+      for (int c = 0; c < 3; ++c) M[3 * r + c] += wg * rec[3 * b + c];
+    }
+  }
+  block_from_moments(form, c1, c2, s, M, B);
+}
+
 // Row assembly, the algorithm of k_hex_assemble (one warp per row node i): the 8 n_cells(i) work items (cell around i,
 // local column b), item t = 8 (cell position in the adjacency of i) + b, are evaluated HEX_PASS at a time -- lane l takes
 // the pair (2 l, 2 l + 1) of the pass, two columns of one cell -- into a staging area; then the lane that owns a

@@ -63,8 +63,8 @@ def run(n=160, reps=5, krylov_iters=50, form="elasticity", with_cpu=True):
                 config=dict(workload="unit cube %d^3 Q1 hexahedra, %s, SIMP rho^3, seed 20261104" % (n, form), n_dof=int(d.ndof),
                             n_cells=int(d.nc), nnz_blocks=int(d.nnzb)),
                 assemble_ms=asm, assemble_ms_all=ms, pcg_ms_per_iter=tot / krylov_iters, pcg_launches=int(launches_pcg),
-                mesh_s=t1 - t0, setup_s=t2 - t1,
-                roofline=dict(kernel="k_hex_assemble", bound="hbm", achieved=bytes_alg / asm / 1e6, peak=peak, unit="GB/s",
+                mesh_s=t1 - t0, setup_s=t2 - t1, gradient_records=os.environ.get("FEMO_HEX_GRAD", "0") == "1",
+                roofline=dict(kernel="k_hex_assemble_g" if os.environ.get("FEMO_HEX_GRAD", "0") == "1" else "k_hex_assemble", bound="hbm", achieved=bytes_alg / asm / 1e6, peak=peak, unit="GB/s",
                               frac=(bytes_alg / asm / 1e6 / peak) if peak else None, traffic=None),
                 dtype="f64", data="synthetic")
     d.close()

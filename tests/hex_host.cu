@@ -107,3 +107,48 @@ int64_t hex_host_pattern(int64_t nb, int64_t nc, const int32_t* cells, int32_t* 
 }
 
 }  // extern "C"
+
+extern "C" {
+
+// k_hex_geom2 + k_hex_assemble_g (FEMO_HEX_GRAD=1): sub-passes of 4 cells, one item per lane, two sub-passes staged per collect
+int hex_host_assemble_g(int form, double c1, double c2, double p, int64_t nb, const double* geo, const int32_t* cells,
+                        const double* rho, int64_t nc, const int32_t* nc_ptr, const int32_t* nc_adj, const int32_t* rowptr,
+                        const int32_t* colidx, double* vals) {
+  std::vector<double> scale(nc), geo2((size_t)nc * 8 * GEO2);
+  for (int64_t e = 0; e < nc; ++e) scale[e] = pow(rho[e], p);
+  for (int64_t r = 0; r < nc * 8; ++r) geom2_qp(geo + r * GEO, (int)(r & 7), geo2.data() + r * GEO2);
+  double stg[HEX_PASS * 9];
+  int32_t s_col[HEX_PASS] = {0};
+  for (int64_t i = 0; i < nb; ++i) {
+    const int32_t e0 = nc_ptr[i], n_cells_i = nc_ptr[i + 1] - e0;
+    for (int c0 = 0; c0 < n_cells_i; c0 += 8) {
+      const int n_chunk = std::min(8, n_cells_i - c0);
+      for (int h = 0; h < 2 && 4 * h < n_chunk; ++h) {
+        const int n_pass = std::min(4, n_chunk - 4 * h);
+        for (int lane = 0; lane < 32; ++lane) {
+          const int cl = lane >> 3, b = lane & 7;
+          if (cl >= n_pass) continue;
+          const int32_t ca = nc_adj[e0 + c0 + 4 * h + cl];
+          const int64_t cell = ca >> 3;
+          double B[9];
+          item_body_g(form, c1, c2, geo2.data() + cell * 8 * GEO2, scale[cell], ca & 7, b, B);
+          const int t = 32 * h + lane;
+          s_col[t] = cells[8 * cell + b];
+          for (int k = 0; k < 9; ++k) stg[k * HEX_PASS + t] = B[k];
+        }
+      }
+      const int n_staged = 8 * n_chunk;
+      for (int32_t k = rowptr[i]; k < rowptr[i + 1]; ++k) {
+        double acc[9];
+        row_collect(stg, s_col, n_staged, colidx[k], acc);
+        for (int e = 0; e < 9; ++e) {
+          if (c0 == 0) vals[(int64_t)k * 9 + e] = acc[e];
+          else vals[(int64_t)k * 9 + e] += acc[e];
+        }
+      }
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -181,3 +181,27 @@ def test_generic_fea_operations_on_the_device(built_lib):
     assert rep[out.compliance, g.body_force]["relative_error"] < 1e-5
     assert rep[out.volume, g.density]["relative_error"] < 1e-7
     fea.device.close()
+
+
+@pytest.mark.xfail(strict=False, reason="k_hex_assemble_g was written after the round-1 GPU budget was spent: not yet run on hardware "
+                                        "(its element maths and index arithmetic are covered by tests/test_hex_host.py)")
+@pytest.mark.parametrize("form", ["elasticity", "vector_poisson"])
+def test_gradient_records(built_lib, form, monkeypatch):
+    """FEMO_HEX_GRAD=1: assembly from per-point gradient records (k_hex_geom2 + k_hex_assemble_g) gives the same matrix,
+    on the box and on the ten-cell fan."""
+    from oracle.hex_ref import HexOracle
+    from femo_alpha_b200.solid_device import SolidDevice
+    from tests.test_hex_host import fan_mesh
+    monkeypatch.setenv("FEMO_HEX_GRAD", "1")
+    o, d, rng = _pair(built_lib, form)
+    K = o.stiffness()
+    assert abs(d.get_csr() - K).max() < 1e-12 * abs(K).max()
+    d.close()
+    nodes, cells = fan_mesh(10)
+    o = HexOracle(nodes, cells, form=form, E0=2.0, nu=0.2)
+    o.set_inputs(density=np.linspace(0.2, 1.0, o.nc))
+    d = SolidDevice(nodes, cells, form=form, E0=2.0, nu=0.2)
+    d.set_input("density", o.rho)
+    K = o.stiffness()
+    assert abs(d.get_csr() - K).max() < 1e-12 * abs(K).max()
+    d.close()

@@ -54,11 +54,12 @@ class Host:
         assert lib.hex_host_geom(I64(nc), _p(self.xyz), _p(self.cells), _p(self.geo), _p(self.vol)) == 0
         self.form = 1 if o.form == "elasticity" else 0
 
-    def matrix(self):
+    def matrix(self, gradient_records=False):
         o = self.o
         vals = np.zeros(self.colidx.size * 9)
         rho = np.ascontiguousarray(o.rho)
-        assert self.lib.hex_host_assemble(self.form, F64(o.c1), F64(o.c2), F64(o.p), I64(o.nn), _p(self.geo), _p(self.cells),
+        fn = self.lib.hex_host_assemble_g if gradient_records else self.lib.hex_host_assemble
+        assert fn(self.form, F64(o.c1), F64(o.c2), F64(o.p), I64(o.nn), _p(self.geo), _p(self.cells),
                                           _p(rho), I64(o.nc), _p(self.nc_ptr), _p(self.nc_adj), _p(self.rowptr),
                                           _p(self.colidx), _p(vals)) == 0
         return sp.bsr_matrix((vals.reshape(-1, 3, 3), self.colidx, self.rowptr), shape=(o.ndof, o.ndof)).tocsr()
@@ -161,3 +162,17 @@ def test_high_valence_rows_take_several_passes(host_lib):
     assert (h.nc_ptr[1] - h.nc_ptr[0]) * 8 == 80
     K = o.stiffness()
     assert abs(h.matrix() - K).max() < 1e-12 * abs(K).max()
+
+
+@pytest.mark.parametrize("form", ["elasticity", "vector_poisson"])
+def test_gradient_record_variant(host_lib, form):
+    """FEMO_HEX_GRAD=1 (k_hex_geom2 + k_hex_assemble_g): same matrix from the gradient records, on a box, on the
+    valence-3 column and on the ten-cell fan (two chunks of sub-passes)."""
+    o, rng = problem(form)
+    K = o.stiffness()
+    assert abs(Host(host_lib, o).matrix(gradient_records=True) - K).max() < 1e-12 * abs(K).max()
+    nodes, cells = fan_mesh(10)
+    o = HexOracle(nodes, cells, form=form, E0=2.0, nu=0.2)
+    o.set_inputs(density=np.linspace(0.2, 1.0, o.nc))
+    K = o.stiffness()
+    assert abs(Host(host_lib, o).matrix(gradient_records=True) - K).max() < 1e-12 * abs(K).max()
