@@ -185,23 +185,16 @@ def test_generic_fea_operations_on_the_device(built_lib):
 
 @pytest.mark.xfail(strict=False, reason="k_hex_assemble_g was written after the round-1 GPU budget was spent: not yet run on hardware "
                                         "(its element maths and index arithmetic are covered by tests/test_hex_host.py)")
-@pytest.mark.parametrize("form", ["elasticity", "vector_poisson"])
-def test_gradient_records(built_lib, form, monkeypatch):
-    """FEMO_HEX_GRAD=1: assembly from per-point gradient records (k_hex_geom2 + k_hex_assemble_g) gives the same matrix,
-    on the box and on the ten-cell fan."""
-    from oracle.hex_ref import HexOracle
-    from femo_alpha_b200.solid_device import SolidDevice
-    from tests.test_hex_host import fan_mesh
-    monkeypatch.setenv("FEMO_HEX_GRAD", "1")
-    o, d, rng = _pair(built_lib, form)
-    K = o.stiffness()
-    assert abs(d.get_csr() - K).max() < 1e-12 * abs(K).max()
-    d.close()
-    nodes, cells = fan_mesh(10)
-    o = HexOracle(nodes, cells, form=form, E0=2.0, nu=0.2)
-    o.set_inputs(density=np.linspace(0.2, 1.0, o.nc))
-    d = SolidDevice(nodes, cells, form=form, E0=2.0, nu=0.2)
-    d.set_input("density", o.rho)
-    K = o.stiffness()
-    assert abs(d.get_csr() - K).max() < 1e-12 * abs(K).max()
-    d.close()
+def test_gradient_records(built_lib):
+    """FEMO_HEX_GRAD=1: assembly from per-point gradient records (k_hex_geom2 + k_hex_assemble_g) gives the same matrix.
+    Runs in its own process (tests/hex_grad_worker.py) so that a fault in the unproven kernel cannot poison the CUDA
+    context of the rest of the suite."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, FEMO_HEX_GRAD="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "hex_grad_worker.py")], cwd=root, env=env, capture_output=True,
+                       text=True, timeout=600)
+    sys.stdout.write(r.stdout[-3000:]); sys.stderr.write(r.stderr[-3000:])
+    assert r.returncode == 0
