@@ -156,7 +156,8 @@ int femo_ctx_destroy(femo_ctx* c) {
                   c->nc_adj, c->rec, c->bcmask, c->bcbits, c->colbc, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
                   c->pen_val, c->pen_dest_col, c->tab4, c->cell_tags, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
                   c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf, c->it_pack, c->it_dest, c->chunk_ptr, c->halo_ptr,
-                  c->halo_cells, c->tpos, c->tabm, c->vals_K, c->mvals, c->mass_me, c->hx_cells, c->hx_geo, c->hx_geo2, c->hx_rho,
+                  c->halo_cells, c->tpos, c->tabm, c->vals_K, c->mvals, c->mass_me, c->hx_cells, c->hx_geo, c->hx_geo2, c->hx_rho, c->pen_vkey, c->pen_vptr, c->pen_vadj, c->pen_bkey, c->pen_bptr,
+                  c->pen_badj, c->pen_buf,
                   c->hx_scale, c->hx_vol, c->hx_f, c->hx_cellvec};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->ev0) cudaEventDestroy(c->ev0);

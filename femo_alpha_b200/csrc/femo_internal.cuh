@@ -142,6 +142,11 @@ struct femo_ctx {
   int64_t n_pen_rows = 0;
   int32_t* pen_row = nullptr;        // n_pen_rows: row block
   int32_t* pen_row_ptr = nullptr;    // n_pen_rows+1 -> into destinations
+  // shape derivative of the penalty terms (penalty_shape.cu): pairs grouped by vertex and by trace block node
+  int64_t n_pen_vkey = 0, n_pen_bkey = 0;
+  int32_t *pen_vkey = nullptr, *pen_vptr = nullptr, *pen_vadj = nullptr;   // vertex -> entries pair*4 + local vertex
+  int32_t *pen_bkey = nullptr, *pen_bptr = nullptr, *pen_badj = nullptr;   // block node -> entries pair*5 + trace index
+  double* pen_buf = nullptr;         // n_pen*15 per-pair results
   // multi-GPU (one process per GPU): owner mask, halo lists, NCCL communicator (dist.cu)
   int world = 1, rank = 0;
   void* nccl_comm = nullptr;
@@ -213,6 +218,8 @@ int asm_plan_build(femo_ctx* c);                                          // top
 int tile_plan_setup(femo_ctx* c);                                         // assemble_tiles.cu
 void tile_plan_free(femo_ctx* c);                                         // assemble_tiles.cu
 int assemble_jacobian_tiles(femo_ctx* c, const double* uhat);             // assemble_tiles.cu (records + assembly)
+int penalty_shape_T(femo_ctx* c, const double* lam, double* out_nn3);      // penalty_shape.cu: out += (dR_pen/duhat)^T lam
+int penalty_shape_fwd(femo_ctx* c, const double* duhat, double* out_ndof); // penalty_shape.cu: out += (dR_pen/duhat) duhat
 int hex_assemble(femo_ctx* c);                                            // hex.cu: K(rho) -> c->vals
 int hex_load(femo_ctx* c, double* F);                                     // hex.cu: F = M f
 int assemble_stiffness(femo_ctx* c);                                      // assemble.cu: K -> c->vals

@@ -571,10 +571,11 @@ static int gather_vertices3(femo_ctx* c, double* out) {
 int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out) {
   CellArgs A = base_args(c);
   A.vec_l = lam;
-  if (arg == FEMO_UHAT) {                       // shape partial; strong-BC residual (no penalty terms)
+  if (arg == FEMO_UHAT) {                       // shape partial: cell terms, then the penalty-BC facet terms
     A.mode = 1;
     TRY(run_cell_op<OP_SHAPE_T>(c, A));
-    return gather_vertices3(c, out);
+    TRY(gather_vertices3(c, out));
+    return penalty_shape_T(c, lam, out);
   }
   if (arg == FEMO_F_SOLID) {
     TRY(run_cell_op<OP_F_T>(c, A));
@@ -595,7 +596,8 @@ int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out) {
   A.vec_l = df;
   if (arg == FEMO_UHAT) {
     TRY(run_cell_op<OP_SHAPE_FWD>(c, A));
-    return gather_dofs(c, out, true);
+    TRY(gather_dofs(c, out, true));
+    return penalty_shape_fwd(c, df, out);
   }
   if (arg == FEMO_F_SOLID) {
     TRY(run_cell_op<OP_F_FWD>(c, A));

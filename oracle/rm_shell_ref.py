@@ -412,13 +412,13 @@ class RMShellOracle:
             va, vb = LOCAL_EDGES[le]
             tvec = xv[:, vb] - xv[:, va]
             L = np.linalg.norm(tvec, axis=1)
-            Me = np.zeros((cells.size, 5, 5))     # trace nodes: q2(va), q2(mid), q2(vb), q1(va), q1(vb)
+            Me = np.zeros((cells.size, 5, 5), dtype=uh.dtype)   # trace nodes: q2(va), q2(mid), q2(vb), q1(va), q1(vb)
             for s, ws in zip(gx, gw):
                 X0, X1 = edge_point(le, s)
                 g = qp_geometry(xv, uh, X0, X1)
                 Nf = np.cross(tvec / L[:, None], g.E2)          # in-surface facet normal (sign irrelevant)
                 nanson = g.Ju[:, None] * np.einsum("cji,cj->ci", g.Finv, Nf)
-                sc = np.linalg.norm(nanson, axis=1)
+                sc = np.sqrt(np.einsum("ci,ci->c", nanson, nanson))   # analytic in uhat (complex-step, oracle/shape_ref.py)
                 l2, _ = lag2(s)
                 tr = np.array([l2[0], l2[1], l2[2], 1 - s, s])
                 # Q2/Q1 traces never couple (u-u and theta-theta only: inner(w, dw))

@@ -125,3 +125,34 @@ def dpnorm_duhat(o, w, m=1e-6, rho=100, cells=None):
     for X0, X1, wq in o.qp:
         area += np.sum(mask * wq * qp_geometry(xv, np.zeros_like(xv), X0, X1).detJ)
     return _vertex_gradient(o, lambda uh: _cell_pnorm(o, w, uh, m, rho, cells)) / area
+
+
+# ---- penalty-BC facet terms (linear_shell_model.py:323-333): Nanson's factor |J F^-T N| depends on uhat -----------------
+def penalty_residual_at(o, w, uhat):
+    """R_pen(w; uhat) = P(uhat) w with the oracle's own penalty matrix, uhat real or complex."""
+    saved = o.uhat
+    try:
+        o.uhat = np.asarray(uhat).ravel()
+        return o.penalty_matrix() @ w
+    finally:
+        o.uhat = saved
+
+
+def dRpen_duhat_apply(o, w, duhat):
+    """(dR_pen/duhat) duhat  (n_dof), complex step."""
+    uh = o.uhat.astype(complex) + 1j * EPS * np.asarray(duhat, dtype=np.float64)
+    return penalty_residual_at(o, w, uh).imag / EPS
+
+
+def dRpen_duhat_T_apply(o, w, lam):
+    """(dR_pen/duhat)^T lam  (3 nn): one complex step per uhat entry of the cells that carry a penalised edge."""
+    t = o.topo
+    sel = np.zeros(t.ne, dtype=bool); sel[o.pen_edges] = True
+    verts = np.unique(t.cv[sel[t.ce].any(axis=1)])
+    g = np.zeros(3 * t.nn)
+    for v in verts:
+        for i in range(3):
+            uh = o.uhat.astype(complex)
+            uh[3 * v + i] += 1j * EPS
+            g[3 * v + i] = lam @ (penalty_residual_at(o, w, uh).imag / EPS)
+    return g

@@ -80,3 +80,35 @@ int shape_host(int op, int m, int64_t nc, const double* xv, const double* uh, co
 }
 
 }  // extern "C"
+
+#include "../femo_alpha_b200/csrc/penalty_shape.cuh"
+
+extern "C" {
+
+// penalty-BC facet terms, one (edge, cell) pair per row: xv, uh (np,4,3); le (np) local edge; hE (np); we, lam (np,5,3)
+// trace-node values; duh (np,4,3).  op 0: (dR_pen/duhat)^T lam -> out (np,12); 1: (dR_pen/duhat) duhat -> out (np,15);
+// 2: the 5x5 trace matrix of the forward penalty (what k_penalty_me computes) -> out (np,25)
+int penalty_shape_host(int op, int64_t np_, const double* xv, const double* uh, const int32_t* le, const double* hE,
+                       const double* we, const double* lam, const double* duh, double* out) {
+  for (int64_t p = 0; p < np_; ++p) {
+    V3 x[4], u[4], d[4];
+    for (int v = 0; v < 4; ++v) {
+      x[v] = ldv3(xv + (p * 4 + v) * 3); u[v] = ldv3(uh + (p * 4 + v) * 3); d[v] = ldv3(duh + (p * 4 + v) * 3);
+    }
+    if (op == 0) penalty_shape_T_pair(x, u, le[p], hE[p], we + p * 15, lam + p * 15, out + p * 12);
+    else if (op == 1) penalty_shape_fwd_pair(x, u, le[p], hE[p], we + p * 15, d, out + p * 15);
+    else {
+      for (int i = 0; i < 25; ++i) out[p * 25 + i] = 0.0;
+      for (int k = 0; k < 3; ++k) {
+        PenQp q;
+        penalty_qp(x, u, le[p], k, hE[p], q);
+        for (int i = 0; i < 5; ++i)
+          for (int j = 0; j < 5; ++j)
+            if ((i < 3) == (j < 3)) out[p * 25 + i * 5 + j] += q.coef * q.sc * q.tr[i] * q.tr[j];
+      }
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

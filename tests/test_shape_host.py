@@ -21,7 +21,7 @@ def host_lib():
     out = os.path.join(HERE, "_build", "libshape_host.so")
     os.makedirs(os.path.dirname(out), exist_ok=True)
     src = os.path.join(HERE, "shape_host.cu")
-    deps = [src] + [os.path.join(CSRC, f) for f in ("shape_partials.cuh", "femo_internal.cuh", "tables.hpp")]
+    deps = [src] + [os.path.join(CSRC, f) for f in ("shape_partials.cuh", "femo_internal.cuh", "tables.hpp", "penalty_shape.cuh")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
         nvcc = "/usr/local/cuda/bin/nvcc" if os.path.exists("/usr/local/cuda/bin/nvcc") else "nvcc"
         subprocess.run([nvcc, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC",
@@ -91,3 +91,59 @@ def test_complex_step_oracle_against_finite_differences():
     assert rel(S.dRduhat_apply(o, w, du), fd) < 1e-8
     lam = rng.standard_normal(o.topo.ndof)
     assert np.isclose(lam @ S.dRduhat_apply(o, w, du), S.dRduhat_T_apply(o, w, lam) @ du, rtol=1e-12)
+
+
+# ---- penalty-BC facet terms: shape derivative of Nanson's factor (csrc/penalty_shape.cuh) ---------------------------------
+LOCAL_EDGES = np.array([(0, 1), (0, 2), (1, 3), (2, 3)])
+EDGE_Q2 = np.array([(0, 4, 1), (0, 5, 2), (1, 6, 3), (2, 7, 3)])
+
+
+def penalty_pairs(o):
+    """(cell, local edge) pairs of the penalised edges and the dof triples of their 5 trace nodes -- penalty_build's lists"""
+    t = o.topo
+    sel = np.zeros(t.ne, dtype=bool); sel[o.pen_edges] = True
+    cells, les = np.nonzero(sel[t.ce])
+    blocks = np.stack([t.cell_blocks[cells, EDGE_Q2[les, 0]], t.cell_blocks[cells, EDGE_Q2[les, 1]],
+                       t.cell_blocks[cells, EDGE_Q2[les, 2]], t.cell_blocks[cells, 9 + LOCAL_EDGES[les, 0]],
+                       t.cell_blocks[cells, 9 + LOCAL_EDGES[les, 1]]], 1)
+    dofs = (3 * blocks[:, :, None] + np.arange(3)).reshape(len(cells), 15)
+    return cells, les.astype(np.int32), blocks, dofs
+
+
+def run_penalty(lib, o, op, w, lam=None, duhat=None):
+    t = o.topo
+    cells, les, blocks, dofs = penalty_pairs(o)
+    n = len(cells)
+    xv = np.ascontiguousarray(t.x[t.cv[cells]]); uh = np.ascontiguousarray(o.uhat.reshape(-1, 3)[t.cv[cells]])
+    du = np.ascontiguousarray((np.zeros(3 * t.nn) if duhat is None else duhat).reshape(-1, 3)[t.cv[cells]])
+    we = np.ascontiguousarray(w[dofs]); le_ = np.ascontiguousarray((w if lam is None else lam)[dofs])
+    out = np.zeros((n, {0: 12, 1: 15, 2: 25}[op]))
+    assert lib.penalty_shape_host(op, ctypes.c_int64(n), _p(xv), _p(uh), _p(les), _p(np.ascontiguousarray(o.hE[cells])), _p(we),
+                                  _p(le_), _p(du), _p(out)) == 0
+    if op == 0:
+        g = np.zeros((t.nn, 3)); np.add.at(g, t.cv[cells].ravel(), out.reshape(-1, 3))
+        return g.ravel()
+    if op == 1:
+        r = np.zeros(t.ndof); np.add.at(r, dofs.ravel(), out.ravel())
+        return r
+    return out, blocks
+
+
+@pytest.mark.parametrize("name", ["plate_4x20", "warped", "skew_planar"])
+def test_penalty_shape_derivative_against_complex_step(host_lib, name):
+    p = make_problem(name)
+    o = oracle_for(p, penalty=True)
+    rng = np.random.default_rng(2)
+    if p["uhat"] is None:
+        o.set_inputs(uhat=0.05 * rng.standard_normal(3 * o.topo.nn))
+    n = o.topo.ndof
+    w, lam, du = rng.standard_normal(n), rng.standard_normal(n), rng.standard_normal(3 * o.topo.nn)
+    # the forward trace matrices reproduce the oracle's penalty matrix
+    Me, blocks = run_penalty(host_lib, o, 2, w)
+    import scipy.sparse as sp
+    rows = np.repeat(blocks, 5, axis=1).ravel(); cols = np.tile(blocks, (1, 5)).ravel()
+    Pb = sp.coo_matrix((Me.ravel(), (rows, cols)), shape=(o.topo.nb, o.topo.nb)).tocsr()
+    P = o.penalty_matrix()
+    assert abs(sp.kron(Pb, sp.identity(3)).tocsr() - P).max() < 1e-12 * abs(P).max()
+    assert rel(run_penalty(host_lib, o, 1, w, duhat=du), S.dRpen_duhat_apply(o, w, du)) < 1e-11
+    assert rel(run_penalty(host_lib, o, 0, w, lam), S.dRpen_duhat_T_apply(o, w, lam)) < 1e-11
