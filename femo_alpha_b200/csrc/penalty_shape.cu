@@ -3,6 +3,9 @@
 // values of its pairs in ascending pair order (lists built by penalty_build) -- deterministic, no atomics.
 // NOT YET RUN ON HARDWARE (written after the round-1 GPU budget was spent); the element maths is covered on the CPU by
 // tests/test_shape_host.py against the complex-step oracle, the launch by tests/test_gpu_shape.py::test_penalty_shape.
+#include <map>
+#include <vector>
+
 #include "penalty_shape.cuh"
 
 namespace {
@@ -69,8 +72,46 @@ __global__ void k_penalty_shape_gather(const int32_t* __restrict__ key, const in
   o[0] += s0; o[1] += s1; o[2] += s2;
 }
 
+// pairs grouped by vertex and by trace block node (ascending pair order inside a group), built on first use from the
+// lists of penalty_build (which frees them whenever the penalised edges change)
+int ensure_lists(femo_ctx* c) {
+  if (c->pen_buf) return 0;
+  const int LE[4][2] = {{0, 1}, {0, 2}, {1, 3}, {2, 3}};
+  const int EQ2[4][3] = {{0, 4, 1}, {0, 5, 2}, {1, 6, 3}, {2, 7, 3}};
+  std::vector<int32_t> pen((size_t)c->n_pen), cv((size_t)c->nc * 4), cb((size_t)c->nc * 13);
+  CUDA_TRY(cudaMemcpy(pen.data(), c->pen_cell, sizeof(int32_t) * pen.size(), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(cv.data(), c->cv, sizeof(int32_t) * cv.size(), cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemcpy(cb.data(), c->cell_blocks, sizeof(int32_t) * cb.size(), cudaMemcpyDeviceToHost));
+  auto group = [&](int per, auto key_of, int32_t** dkey, int32_t** dptr, int32_t** dadj, int64_t* nkey) -> int {
+    std::map<int32_t, std::vector<int32_t>> g;
+    for (size_t p = 0; p < pen.size(); ++p)
+      for (int i = 0; i < per; ++i) g[key_of(p, i)].push_back((int32_t)(p * per + i));
+    std::vector<int32_t> key, ptr(1, 0), adj;
+    for (auto& kv : g) {
+      key.push_back(kv.first);
+      adj.insert(adj.end(), kv.second.begin(), kv.second.end());
+      ptr.push_back((int32_t)adj.size());
+    }
+    *nkey = (int64_t)key.size();
+    TRY(dev_alloc(dkey, key.size())); TRY(dev_alloc(dptr, ptr.size())); TRY(dev_alloc(dadj, adj.size()));
+    CUDA_TRY(cudaMemcpy(*dkey, key.data(), sizeof(int32_t) * key.size(), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(*dptr, ptr.data(), sizeof(int32_t) * ptr.size(), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(*dadj, adj.data(), sizeof(int32_t) * adj.size(), cudaMemcpyHostToDevice));
+    return 0;
+  };
+  TRY(group(4, [&](size_t p, int v) { return cv[4 * (int64_t)(pen[p] >> 2) + v]; }, &c->pen_vkey, &c->pen_vptr, &c->pen_vadj,
+            &c->n_pen_vkey));
+  TRY(group(5, [&](size_t p, int i) {
+        const int64_t cell = pen[p] >> 2; const int le = pen[p] & 3;
+        return i < 3 ? cb[13 * cell + EQ2[le][i]] : cb[13 * cell + 9 + LE[le][i - 3]];
+      }, &c->pen_bkey, &c->pen_bptr, &c->pen_badj, &c->n_pen_bkey));
+  TRY(dev_alloc(&c->pen_buf, pen.size() * 15));
+  return 0;
+}
+
 int run(femo_ctx* c, int mode, const double* x, double* out) {
   if (c->n_pen == 0) return 0;
+  TRY(ensure_lists(c));
   const double* uh = c->uhat_zero ? nullptr : c->uhat;
   k_penalty_shape_pairs<<<(unsigned)cdiv(c->n_pen, 128), 128, 0, c->stream>>>(mode, c->xyz, c->cv, uh, c->hE, c->cell_blocks,
                                                                             c->pen_cell, c->n_pen, c->w, x, c->pen_buf);

@@ -383,34 +383,6 @@ int penalty_build(femo_ctx* c, const uint8_t* von) {
   c->n_pen_dest = 0; c->n_pen_rows = 0; c->n_pen_vkey = 0; c->n_pen_bkey = 0;
   c->jac_valid = false; c->prec_valid = false;
   if (c->n_pen == 0) return 0;
-  {
-    // pairs grouped by vertex and by trace block node (ascending pair order inside a group): the deterministic gathers
-    // of the penalty shape derivative (penalty_shape.cu)
-    auto group = [&](int per, auto key_of, int32_t** dkey, int32_t** dptr, int32_t** dadj, int64_t* nkey) -> int {
-      std::map<int32_t, std::vector<int32_t>> g;
-      for (size_t p = 0; p < pen.size(); ++p)
-        for (int i = 0; i < per; ++i) g[key_of(p, i)].push_back((int32_t)(p * per + i));
-      std::vector<int32_t> key, ptr(1, 0), adj;
-      for (auto& kv : g) {
-        key.push_back(kv.first);
-        adj.insert(adj.end(), kv.second.begin(), kv.second.end());
-        ptr.push_back((int32_t)adj.size());
-      }
-      *nkey = (int64_t)key.size();
-      TRY(dev_alloc(dkey, key.size())); TRY(dev_alloc(dptr, ptr.size())); TRY(dev_alloc(dadj, adj.size()));
-      CUDA_TRY(cudaMemcpy(*dkey, key.data(), sizeof(int32_t) * key.size(), cudaMemcpyHostToDevice));
-      CUDA_TRY(cudaMemcpy(*dptr, ptr.data(), sizeof(int32_t) * ptr.size(), cudaMemcpyHostToDevice));
-      CUDA_TRY(cudaMemcpy(*dadj, adj.data(), sizeof(int32_t) * adj.size(), cudaMemcpyHostToDevice));
-      return 0;
-    };
-    TRY(group(4, [&](size_t p, int v) { return cv[4 * (int64_t)(pen[p] >> 2) + v]; }, &c->pen_vkey, &c->pen_vptr, &c->pen_vadj,
-              &c->n_pen_vkey));
-    TRY(group(5, [&](size_t p, int i) {
-          const int64_t cell = pen[p] >> 2; const int le = pen[p] & 3;
-          return i < 3 ? cb[13 * cell + EQ2[le][i]] : cb[13 * cell + 9 + LE[le][i - 3]];
-        }, &c->pen_bkey, &c->pen_bptr, &c->pen_badj, &c->n_pen_bkey));
-    TRY(dev_alloc(&c->pen_buf, pen.size() * 15));
-  }
   // destinations: (row block, col block) -> list of sources (pair*25 + i*5 + j); u-u (3x3) and th-th (2x2) traces
   std::map<std::pair<int32_t, int32_t>, std::vector<int32_t>> dst;
   for (size_t p = 0; p < pen.size(); ++p) {
