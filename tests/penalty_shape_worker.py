@@ -10,6 +10,7 @@ sys.path.insert(0, ROOT)
 
 
 def main():
+    assert os.environ.get("FEMO_PENALTY_SHAPE") == "1"
     from oracle import shape_ref as S
     from tests.problems import make_problem, oracle_for, device_for
     worst = 0.0

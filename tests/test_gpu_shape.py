@@ -66,6 +66,6 @@ def test_penalty_shape(built_lib):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, os.path.join(root, "tests", "penalty_shape_worker.py")], cwd=root, capture_output=True,
-                       text=True, timeout=900)
+                       text=True, timeout=900, env=dict(os.environ, FEMO_PENALTY_SHAPE="1"))
     sys.stdout.write(r.stdout[-3000:]); sys.stderr.write(r.stderr[-3000:])
     assert r.returncode == 0
