@@ -477,10 +477,10 @@ int femo_hex_output(femo_ctx* c, int which, double* val) {
     return dev_dot(c, c->tmp, c->w, c->ndof, val);
   }
   if (which == 1) {
+    if (c->world == 1) return dev_dot(c, c->hx_rho, c->hx_vol, c->nc, val);
     // multi-GPU: every cell is counted by the rank that owns it (owned cells come first), then summed over ranks
-    const int64_t ncs = c->world > 1 ? c->nc_owned : c->nc;
-    TRY(dev_dot_async(c, c->hx_rho, c->hx_vol, ncs, c->scal + 9));
-    if (c->world > 1) TRY(dist_allreduce_sum(c, c->scal + 9, 1));
+    TRY(dev_dot_async(c, c->hx_rho, c->hx_vol, c->nc_owned, c->scal + 9));
+    TRY(dist_allreduce_sum(c, c->scal + 9, 1));
     CUDA_TRY(cudaMemcpyAsync(val, c->scal + 9, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     return 0;
