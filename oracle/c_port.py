@@ -70,3 +70,57 @@ class CsrAssembler:
     def matrix(self):
         import scipy.sparse as sp
         return sp.csr_matrix((self.vals, self.indices, self.indptr), shape=(self.topo.ndof,) * 2)
+
+
+# ---- oracle/hex_c.c: generic 3-D forms on hexahedra (config 5) -----------------------------------------------------------
+_HEX_SO = os.path.join(_HERE, "libhex_c.so")
+_hexlib = None
+
+
+def build_hex():
+    src = os.path.join(_HERE, "hex_c.c")
+    if not os.path.exists(_HEX_SO) or os.path.getmtime(src) > os.path.getmtime(_HEX_SO):
+        subprocess.check_call(["gcc", "-O3", "-march=x86-64-v3", "-fopenmp", "-fPIC", "-std=gnu11", "-shared",
+                               "-o", _HEX_SO, src, "-lm"])
+    return _HEX_SO
+
+
+def hexlib():
+    global _hexlib
+    if _hexlib is None:
+        _hexlib = C.CDLL(build_hex())
+    return _hexlib
+
+
+class HexCsrAssembler:
+    """Pattern + element -> CSR map of a HexOracle built once (as dolfinx does in create_matrix); `assemble` is the
+    timed part (hexc_assemble_csr, OpenMP over the cells)."""
+
+    def __init__(self, o):
+        self.o = o
+        ed = (3 * o.cells[:, :, None] + np.arange(3)[None, None, :]).reshape(o.nc, 24)
+        rows = np.repeat(ed, 24, axis=1).ravel()
+        cols = np.tile(ed, (1, 24)).ravel()
+        n = o.ndof
+        ukey, inv = np.unique(rows.astype(np.int64) * n + cols, return_inverse=True)
+        self.emap = np.ascontiguousarray(inv.astype(np.int64))
+        self.nnz = ukey.size
+        self.indices = np.ascontiguousarray((ukey % n).astype(np.int32))
+        self.indptr = np.zeros(n + 1, dtype=np.int64)
+        np.add.at(self.indptr, (ukey // n) + 1, 1)
+        self.indptr = np.cumsum(self.indptr)
+        self.vals = np.zeros(self.nnz)
+        self.xyz = np.ascontiguousarray(o.x)
+        self.cells = np.ascontiguousarray(o.cells, dtype=np.int32)
+
+    def assemble(self):
+        o = self.o
+        rho = np.ascontiguousarray(o.rho)
+        hexlib().hexc_assemble_csr(C.c_int64(o.nc), _p(self.xyz), _p(self.cells), _p(rho), C.c_double(o.p),
+                                   C.c_int(1 if o.form == "elasticity" else 0), C.c_double(o.c1), C.c_double(o.c2),
+                                   _p(self.emap), C.c_int64(self.nnz), _p(self.vals))
+        return self.vals
+
+    def matrix(self):
+        import scipy.sparse as sp
+        return sp.csr_matrix((self.assemble().copy(), self.indices, self.indptr), shape=(self.o.ndof, self.o.ndof))

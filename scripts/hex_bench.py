@@ -15,18 +15,24 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def cpu_baseline(form="elasticity", n=24):
-    """The oracle's assembly (numpy einsum element matrices + scipy CSR scatter, oracle/hex_ref.py) on a bounded sample
-    of the same workload -- a reported baseline, one host core."""
+def cpu_baseline(form="elasticity", n=40):
+    """oracle/hex_c.c (C + OpenMP: dense element matrices added into a pre-patterned CSR matrix, what dolfinx + PETSc do
+    for the reference's generic FEA) on a bounded sample of the same workload, all host threads."""
+    from oracle.c_port import HexCsrAssembler
     from oracle.hex_ref import HexOracle, box_mesh
     nodes, cells = box_mesh(n, n, n)
-    o = HexOracle(nodes, cells, form=form, E0=1.0, nu=0.3, simp_p=3.0)
-    o.set_inputs(density=np.random.default_rng(20261104).uniform(0.01, 1.0, o.nc))
+    o = HexOracle.__new__(HexOracle)                     # inputs only: the NumPy geometry tables are not needed here
+    o.x, o.cells, o.nn, o.nc, o.ndof, o.form, o.p = nodes, cells.astype(np.int64), len(nodes), len(cells), 3 * len(nodes), form, 3.0
+    E0, nu = 1.0, 0.3
+    o.c1, o.c2 = (E0 * nu / ((1 + nu) * (1 - 2 * nu)), E0 / (2 * (1 + nu))) if form == "elasticity" else (E0, 0.0)
+    o.rho = np.random.default_rng(20261104).uniform(0.01, 1.0, o.nc)
+    asm = HexCsrAssembler(o)
     ts = []
-    for _ in range(2):
-        t = time.time(); o.stiffness(); ts.append(time.time() - t)
-    return dict(value=o.ndof / min(ts) / 1e9, unit="GDOF/s", cores=1, kind="port",
-                sample="%d^3-cell cube of the same form (%d DOF), best of 2 assemblies, %.2f s" % (n, o.ndof, min(ts)))
+    for _ in range(4):
+        t = time.time(); asm.assemble(); ts.append(time.time() - t)
+    best = min(ts[1:])
+    return dict(value=o.ndof / best / 1e9, unit="GDOF/s", cores=len(os.sched_getaffinity(0)), kind="port",
+                sample="%d^3-cell cube of the same form (%d DOF), best of 3 assemblies after one warm-up, %.3f s" % (n, o.ndof, best))
 
 
 def run(n=160, reps=5, krylov_iters=50, form="elasticity", with_cpu=True):

@@ -103,3 +103,15 @@ def test_golden_fixtures_are_reproduced(form):
         assert np.abs(d[k] - g[k]).max() <= 1e-12 * np.abs(g[k]).max(), k
     assert np.array_equal(d["K_indices"], g["K_indices"]) and np.array_equal(d["cells"], g["cells"])
     assert np.isclose(d["compliance"], float(g["compliance"]), rtol=1e-12) and np.isclose(d["volume"], float(g["volume"]), rtol=1e-14)
+
+
+@pytest.mark.parametrize("form", ["elasticity", "vector_poisson"])
+def test_c_port_matches_the_numpy_oracle(form):
+    """oracle/hex_c.c (the timed CPU baseline of scripts/hex_bench.py) against oracle/hex_ref.py"""
+    from oracle.c_port import HexCsrAssembler
+    nodes, cells = box_mesh(4, 3, 5, distort=0.25, seed=6)
+    o = HexOracle(nodes, cells, form=form, E0=3.0, nu=0.25)
+    o.set_inputs(density=np.random.default_rng(0).uniform(0.05, 1.0, o.nc))
+    K = o.stiffness()
+    Kc = HexCsrAssembler(o).matrix()
+    assert abs(Kc - K).max() < 1e-13 * abs(K).max()
