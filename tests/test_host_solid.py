@@ -156,3 +156,36 @@ def test_operations_and_totals(solid):
     assert rep[out.compliance, g.density]["relative_error"] < 1e-5
     assert rep[out.compliance, g.body_force]["relative_error"] < 1e-5
     assert rep[out.volume, g.density]["relative_error"] < 1e-7
+
+
+def test_field_output_operation_protocol(solid):
+    """OutputFieldOperation (output_operation.py:72-128 of the reference): shape from the registry, projection on compute,
+    recorder hook, no derivatives."""
+    NF, mesh, fea, fn = solid
+    from femo_alpha_b200 import csdl_shim as csdl
+    from femo_alpha_b200.csdl_alpha_opt.output_operation import OutputFieldOperation, OutputOperation
+    from femo_alpha_b200.fea.utils_dolfinx import FunctionSpace
+
+    class CellField:
+        kind = "field"
+
+        def field_space(self, spec):
+            return FunctionSpace(mesh, "DG0", fea.nel, fea.device, "cell_density")
+
+        def project(self):
+            return 2.0 * fea.device.o.rho
+
+    fea.add_field_output("twice_density", CellField(), ["density"], record=True)
+    written = []
+    fea.outputs_field_dict["twice_density"]["recorder"] = type("R", (), {"write_function": lambda self, f, t: written.append(t)})()
+    rec = csdl.Recorder(inline=True); rec.start()
+    g = csdl.VariableGroup()
+    rho = np.linspace(0.2, 1.0, fea.nel)
+    g.density = csdl.Variable(value=rho, name="density")
+    out = OutputFieldOperation(fea, ["density"], "twice_density").evaluate(g)
+    rec.stop()
+    assert out.value.shape == (fea.nel,) and np.allclose(out.value, 2.0 * rho) and len(written) == 1
+    with pytest.raises(ValueError):
+        OutputOperation(fea, ["density", "body_force"], "volume").evaluate(g)       # body_force missing from the group
+    with pytest.raises(KeyError):
+        OutputFieldOperation(fea, ["density"], "no_such_field")
