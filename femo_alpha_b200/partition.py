@@ -197,7 +197,8 @@ def build_local_part_hex(nodes: np.ndarray, hexes: np.ndarray, part: np.ndarray,
     part = np.asarray(part, dtype=np.int32)
     nv, npc = nodes.shape[0], hexes.shape[1]
     v_owner = np.full(nv, world, dtype=np.int32)
-    np.minimum.at(v_owner, hexes.ravel(), np.repeat(part, npc))
+    for r in range(world - 1, -1, -1):                              # lowest part written last = minimum over the cells
+        v_owner[hexes[part == r].ravel()] = r
     own = v_owner[hexes]                                            # (nc, 8) owner of every cell node
     needed = (own == rank).any(axis=1)
     owned = part == rank

@@ -7,6 +7,7 @@
 #   ncu     launch list of a short bench run and of a short dynamic run (per-launch durations, no clock control)
 #   hex     config-5 solid forms: parity tests + 160^3 assembly / PCG timings (scripts/hex_bench.py)
 #   ncuhex  ncu --set full of one k_hex_assemble launch -> gpurun_out/${TAG}_hex_asm.ncu-rep
+#   hexscale weak scaling of config 5 on NGPU GPUs (scripts/hex_bench_dist.py; first run pending)
 #   disthex N-GPU parity of the hexahedral solids (needs `gpurun --gpus 2` or more; first run pending)
 #   distdyn 2-GPU parity of the time-stepped path only (needs `gpurun --gpus 2`)
 #   dist    2-GPU parity test + 2-GPU bench line (needs `gpurun --gpus 2`)
@@ -40,6 +41,9 @@ for sec in "$@"; do
       timeout 300 ncu --set full --clock-control none --import-source on -k regex:k_hex_assemble -s 2 -c 1 -f -o gpurun_out/${T}_hex_asm python scripts/hex_bench.py --n ${HEX_N:-160} --reps 1 > gpurun_out/${T}_ncu_hex.log 2>&1; echo "ncu hex rc=$?" ;;
     disthex)
       timeout 600 python -m pytest tests/test_gpu_dist.py -m gpu -q --tb=short -s -k hexahedral > gpurun_out/${T}_pytest_gpu_disthex.log 2>&1; echo "pytest disthex rc=$?"; grep -E "^rank|passed|failed|xfailed|xpassed|Error|error" gpurun_out/${T}_pytest_gpu_disthex.log | tail -n 12 ;;
+    hexscale)
+      # weak scaling of config 5 (needs `gpurun --gpus N`, N = NGPU)
+      timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node ${NGPU:-2} --master-addr 127.0.0.1 --master-port 29561 scripts/hex_bench_dist.py --n ${HEX_N:-128} --out gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.json > gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.log 2>&1; echo "hex scale rc=$?"; tail -n 4 gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.log ;;
     *) echo "unknown section $sec" ;;
   esac
 done
