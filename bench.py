@@ -151,7 +151,7 @@ def run_reference(args, rank):
         "impl": "reference", "metric": "rm_shell_jacobian_assembly_throughput", "value": val, "unit": "GDOF/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "rm_shell_plate_%dx%d_q2q1" % (n, n), "sample": sample},
+        "config": {"workload": "rm_shell_plate_%dx%d_q2q1_cfg3" % (n, n), "sample": sample},
         "cpu_baseline": {"value": val, "unit": "GDOF/s", "cores": int(threads), "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "GDOF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "dolfinx 0.5.1/PETSc/MUMPS are not installable here; this is the oracle's C/OpenMP restatement"}))
