@@ -136,8 +136,8 @@ k_hex_assemble(int form, double c1, double c2, const double* __restrict__ geo, c
   }
 }
 
-// ---- gradient-record variant (FEMO_HEX_GRAD=1 at femo_hex_setup; NOT YET MEASURED: written after the round-1 GPU budget
-// was spent, its element maths is covered by the CPU harness, its launch by tests/test_gpu_hex.py::test_gradient_records) ----
+// ---- gradient-record variant (FEMO_HEX_GRAD=1 at femo_hex_setup).  Correct on the B200 and bitwise equal to the default
+// kernel, but not faster (0.382 vs 0.354 ms at 48^3, profiles/r01v_hex_grad_worker.log): off by default ----
 __global__ void k_hex_geom2(const double* __restrict__ geo, int64_t n_rec, double* __restrict__ geo2) {
   const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;       // r = cell * 8 + q
   if (r < n_rec) geom2_qp(geo + r * GEO, (int)(r & 7), geo2 + r * GEO2);
