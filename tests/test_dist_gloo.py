@@ -102,3 +102,37 @@ def test_distributed_hexahedral_solid_matches_global_solve(tmp_path, world):
         tot_send += int(d["send"]); tot_recv += int(d["recv"])
     assert (seen == 1).all() and (cells_seen == 1).all()
     assert tot_send == tot_recv and tot_send > 0
+
+
+def test_distributed_two_grid_preconditioner(tmp_path):
+    """NumPy prototype of the N-rank V-cycle (tests/dist_mg_worker.py): nested partition, local prolongation, restriction
+    through a reverse halo exchange.  Same outer iteration count at world sizes 1, 2 and 3, far below Jacobi PCG, and the
+    solution of the oracle's global solve."""
+    from oracle.rm_shell_ref import RMShellOracle
+    from tests.dist_mg_worker import global_keys, problem
+    nodes_c, quads_c, nodes_f, quads_f = problem()
+    o = RMShellOracle(nodes_f, quads_f, False, False)
+    nn = nodes_f.shape[0]
+    o.set_inputs(thickness=np.full(nn, 0.1), E=np.full(nn, 1e8), nu=np.full(nn, 0.3), density=np.full(nn, 10.0),
+                 F_solid=np.tile([0.0, 0.0, 5.0], nn))
+    o.set_strong_bc(lambda x: np.less(x[0], 3e-16))
+    w = o.solve_state().reshape(-1, 3)
+    gk = global_keys(o.topo)
+    order = np.argsort(gk)
+    counts = {}
+    for world in (1, 2, 3):
+        out = tmp_path / ("w%d" % world); out.mkdir()
+        port = _free_port()
+        procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "dist_mg_worker.py"), str(r), str(world),
+                                   str(port), str(out)], cwd=ROOT) for r in range(world)]
+        for pr in procs:
+            assert pr.wait(timeout=900) == 0
+        for r in range(world):
+            d = np.load(os.path.join(out, "mg_rank%d.npz" % r))
+            pos = order[np.searchsorted(gk[order], d["gkey"])]
+            assert np.abs(d["x"].reshape(-1, 3) - w[pos]).max() <= 1e-7 * np.abs(w).max()
+            counts.setdefault(world, (int(d["its"]), int(d["its_jacobi"])))
+            assert counts[world] == (int(d["its"]), int(d["its_jacobi"]))
+    its = [counts[k][0] for k in (1, 2, 3)]
+    assert max(its) - min(its) <= 1, counts                    # the preconditioner is the same operator on any partition
+    assert 0 < its[0] * 10 < counts[1][1], counts              # and an order of magnitude fewer iterations than Jacobi PCG
