@@ -73,6 +73,7 @@ SIGNATURES = {
     "femo_dist_setup": [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, C.c_int64],
     "femo_dist_init": [_P, _P],
     "femo_halo_exchange": [_P, _P, C.c_int],
+    "femo_halo_accumulate": [_P, _P, C.c_int],
     "femo_dist_allreduce": [_P, _D, C.c_int],
     "femo_dist_counts": [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
     "femo_mg_create": [C.c_int, C.POINTER(_P), C.POINTER(_P)],

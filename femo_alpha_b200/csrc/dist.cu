@@ -72,6 +72,14 @@ __global__ void k_halo_unpack(double* __restrict__ x, const int32_t* __restrict_
   x[3 * (int64_t)blocks[b] + k] = buf[i];
 }
 
+__global__ void k_halo_unpack_add(double* __restrict__ x, const int32_t* __restrict__ blocks, int64_t n,
+                                  const double* __restrict__ buf) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= 3 * n) return;
+  int64_t b = i / 3; int k = (int)(i - 3 * b);
+  x[3 * (int64_t)blocks[b] + k] += buf[i];
+}
+
 struct DevGuard2 {
   int prev = 0;
   explicit DevGuard2(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); }
@@ -101,6 +109,36 @@ int halo_exchange(femo_ctx* c, double* x) {
   }
   c->halo_count += 1;
   return check_launch(c, "halo exchange");
+}
+
+// Reverse halo exchange: owners += the values their ghosts hold on the other ranks (restriction of the N-rank V-cycle,
+// DESIGN 15; prototype tests/dist_mg_worker.py).  Same neighbour lists as halo_exchange with the roles of the buffers
+// swapped; an owned block can be a ghost on several neighbours, so the contributions are added neighbour by neighbour
+// (one small launch each, fixed order -> deterministic).  NOT YET RUN ON HARDWARE.
+int halo_accumulate(femo_ctx* c, double* x) {
+  if (c->world <= 1) return 0;
+  if (!c->nccl_comm) return femo_fail("halo_accumulate: communicator not initialised (femo_dist_init)");
+  ncclComm_t comm = (ncclComm_t)c->nccl_comm;
+  if (c->n_recv > 0) {
+    k_halo_pack<<<(unsigned)cdiv(3 * c->n_recv, 256), 256, 0, c->stream>>>(x, c->recv_blocks, c->n_recv, c->recv_buf);
+    c->launches += 1;
+  }
+  NCCL_TRY(g_nccl.GroupStart());
+  for (int i = 0; i < c->n_nbr; ++i) {
+    const int ns = c->send_off[i + 1] - c->send_off[i], nr = c->recv_off[i + 1] - c->recv_off[i];
+    if (nr > 0) NCCL_TRY(g_nccl.Send(c->recv_buf + 3 * (int64_t)c->recv_off[i], 3 * (size_t)nr, ncclDouble, c->nbr_rank[i], comm, c->stream));
+    if (ns > 0) NCCL_TRY(g_nccl.Recv(c->send_buf + 3 * (int64_t)c->send_off[i], 3 * (size_t)ns, ncclDouble, c->nbr_rank[i], comm, c->stream));
+  }
+  NCCL_TRY(g_nccl.GroupEnd());
+  for (int i = 0; i < c->n_nbr; ++i) {
+    const int ns = c->send_off[i + 1] - c->send_off[i];
+    if (ns == 0) continue;
+    k_halo_unpack_add<<<(unsigned)cdiv(3 * (int64_t)ns, 256), 256, 0, c->stream>>>(x, c->send_blocks + c->send_off[i], ns,
+                                                                                 c->send_buf + 3 * (int64_t)c->send_off[i]);
+    c->launches += 1;
+  }
+  c->halo_count += 1;
+  return check_launch(c, "halo accumulate");
 }
 
 int dist_allreduce_sum(femo_ctx* c, double* v, int n) {
@@ -189,6 +227,20 @@ int femo_halo_exchange(femo_ctx* c, double* x, int on_device) {
     CUDA_TRY(cudaMemcpyAsync(xd, x, sizeof(double) * c->ndof, cudaMemcpyHostToDevice, c->stream));
   }
   TRY(halo_exchange(c, xd));
+  if (!on_device) CUDA_TRY(cudaMemcpyAsync(x, xd, sizeof(double) * c->ndof, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int femo_halo_accumulate(femo_ctx* c, double* x, int on_device) {
+  if (!c || !c->setup_done) return femo_fail("femo_halo_accumulate: context not set up");
+  DevGuard2 g(c->device);
+  double* xd = x;
+  if (!on_device) {
+    xd = c->tmp2;
+    CUDA_TRY(cudaMemcpyAsync(xd, x, sizeof(double) * c->ndof, cudaMemcpyHostToDevice, c->stream));
+  }
+  TRY(halo_accumulate(c, xd));
   if (!on_device) CUDA_TRY(cudaMemcpyAsync(x, xd, sizeof(double) * c->ndof, cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   return 0;

@@ -239,6 +239,7 @@ int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out);   // out
 int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out);      // outputs.cu
 int measure_peaks(femo_ctx* c, double* tf, double* gbs);                  // solver.cu
 int halo_exchange(femo_ctx* c, double* x);                                // dist.cu: ghost entries <- owners
+int halo_accumulate(femo_ctx* c, double* x);                              // dist.cu: owners += ghost copies (reverse halo)
 int dist_allreduce_sum(femo_ctx* c, double* dev_vals, int n);             // dist.cu: in-place on the stream
 int dist_allreduce_host(femo_ctx* c, double* host_vals, int n);           // dist.cu
 void dist_free(femo_ctx* c);                                              // dist.cu

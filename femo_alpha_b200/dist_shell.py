@@ -114,6 +114,12 @@ class DistributedShell:
         L.check(self.dev.lib.femo_halo_exchange(self.dev._ctx, L.ptr(x), 0))
         return x
 
+    def halo_accumulate(self, x):
+        """owned entries += the values of their ghost copies on the other ranks (collective); returns x"""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        L.check(self.dev.lib.femo_halo_accumulate(self.dev._ctx, L.ptr(x), 0))
+        return x
+
     def comm_counts(self):
         h = C.c_int64(0); a = C.c_int64(0)
         L.check(self.dev.lib.femo_dist_counts(self.dev._ctx, C.byref(h), C.byref(a)))

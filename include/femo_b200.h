@@ -167,6 +167,10 @@ int femo_dist_setup(femo_ctx* ctx, int rank, int world, int n_nbr, const int32_t
 int femo_dist_init(femo_ctx* ctx, const void* id128);
 /* ghost entries of x (n_dof) <- owners' values; collective */
 int femo_halo_exchange(femo_ctx* ctx, double* x, int on_device);
+/* reverse exchange: owned entries of x += the values their ghost copies hold on the other ranks (ghost entries are
+ * left unchanged); collective.  The restriction step of a distributed V-cycle (no reference counterpart: the
+ * reference is serial). */
+int femo_halo_accumulate(femo_ctx* ctx, double* x, int on_device);
 /* sum n <= 8 host scalars over ranks; collective */
 int femo_dist_allreduce(femo_ctx* ctx, double* vals, int n);
 int femo_dist_counts(femo_ctx* ctx, int64_t* halo_exchanges, int64_t* allreduces);

@@ -52,3 +52,17 @@ def test_multi_gpu_hexahedral_solid_matches_oracle(built_lib, n):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     sys.stdout.write(r.stdout[-4000:]); sys.stderr.write(r.stderr[-4000:])
     assert r.returncode == 0
+
+
+@pytest.mark.xfail(strict=False, reason="femo_halo_accumulate was written after the round-1 GPU budget was spent: not yet run on "
+                                        "hardware (the algorithm it serves is prototyped over gloo in tests/dist_mg_worker.py)")
+@pytest.mark.parametrize("n", [2, 3])
+def test_reverse_halo_exchange(built_lib, n):
+    """owners += ghost copies (tests/dist_gpu_accumulate_worker.py)"""
+    if _ngpu() < n:
+        pytest.skip("needs %d GPUs" % n)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr",
+           "127.0.0.1", "--master-port", "29536", os.path.join(ROOT, "tests", "dist_gpu_accumulate_worker.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    sys.stdout.write(r.stdout[-3000:]); sys.stderr.write(r.stderr[-3000:])
+    assert r.returncode == 0
