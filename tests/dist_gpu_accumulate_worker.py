@@ -23,7 +23,8 @@ def main():
     ds.init_comm()
     lp = ds.lp
     # copies of every block over the ranks, from the partition tables (all-gathered keys)
-    keys = torch.zeros(int(lp.block_gkey.max()) + 1 + 4 * len(p["nodes"]), dtype=torch.int64, device="cuda")
+    n_keys = 2 * lp.n_global_vertices + lp.n_global_edges + lp.n_global_cells          # same on every rank
+    keys = torch.zeros(n_keys, dtype=torch.int64, device="cuda")
     keys[torch.from_numpy(lp.block_gkey).cuda()] += 1
     dist.all_reduce(keys)
     copies = keys.cpu().numpy()[lp.block_gkey].astype(np.float64)
