@@ -75,11 +75,17 @@ def refine_quads(nodes, quads):
     return nodes_f, qf.reshape(4 * nc, 4).astype(np.int32)
 
 
-def prolongation(fine_blocks, coarse_blocks, nb_fine, nb_coarse):
+def prolongation(fine_blocks, coarse_blocks, nb_fine, nb_coarse, parent=None, child=None, allow_missing_rows=False):
     """Block-scalar prolongation between a mesh and its `refine_quads` parent.
     fine_blocks (4 nc, 13), coarse_blocks (nc, 13): femo_get_cell_blocks of the two levels.
-    Returns scipy CSR (nb_fine x nb_coarse)."""
+    Returns scipy CSR (nb_fine x nb_coarse).
+
+    General form (one rank of a partitioned hierarchy, dist_multigrid.py): `parent[i]` = row of `coarse_blocks` that is the
+    parent of fine cell i and `child[i]` = its child index (0..3); fine cells may then come in any number and order, and
+    with `allow_missing_rows` fine block nodes that no listed cell holds get an empty row instead of an error."""
     import scipy.sparse as sp
+    if parent is not None:
+        return _prolongation_general(fine_blocks, coarse_blocks, nb_fine, nb_coarse, parent, child, allow_missing_rows)
     fb = np.asarray(fine_blocks, dtype=np.int64)
     cb = np.asarray(coarse_blocks, dtype=np.int64)
     nc = cb.shape[0]
@@ -110,6 +116,49 @@ def prolongation(fine_blocks, coarse_blocks, nb_fine, nb_coarse):
     head = np.ones(r_sorted.size, dtype=bool); head[1:] = r_sorted[1:] != r_sorted[:-1]
     first[r_sorted[head]] = g_sorted[head]
     if (first < 0).any():
+        raise RuntimeError("prolongation: a fine block node belongs to no fine cell")
+    keep = (grp == first[rows]) & (np.abs(vals) > 1e-14)
+    P = sp.csr_matrix((vals[keep], (rows[keep], cols[keep])), shape=(nb_fine, nb_coarse))
+    P.sum_duplicates(); P.sort_indices()
+    return P
+
+
+def _child_weights():
+    W2 = np.zeros((4, 9, 9)); W1 = np.zeros((4, 4, 4))
+    for k in range(4):
+        ci, cj = k % 2, k // 2
+        for a in range(9):
+            W2[k, a] = _q2((ci + _REF2[a, 0]) / 2.0, (cj + _REF2[a, 1]) / 2.0)
+        for a in range(4):
+            W1[k, a] = _q1((ci + _REF1[a, 0]) / 2.0, (cj + _REF1[a, 1]) / 2.0)
+    return W2, W1
+
+
+def _prolongation_general(fine_blocks, coarse_blocks, nb_fine, nb_coarse, parent, child, allow_missing_rows):
+    import scipy.sparse as sp
+    fb = np.asarray(fine_blocks, dtype=np.int64)
+    cb = np.asarray(coarse_blocks, dtype=np.int64)
+    parent = np.asarray(parent, dtype=np.int64); child = np.asarray(child, dtype=np.int64)
+    nf = fb.shape[0]
+    assert parent.shape == (nf,) and child.shape == (nf,)
+    W2, W1 = _child_weights()
+    rows2 = np.repeat(fb[:, :9, None], 9, axis=2)                           # nf,9,9
+    cols2 = np.broadcast_to(cb[parent][:, None, :9], (nf, 9, 9))
+    vals2 = W2[child]
+    rows1 = np.repeat(fb[:, 9:, None], 4, axis=2)
+    cols1 = np.broadcast_to(cb[parent][:, None, 9:], (nf, 4, 4))
+    vals1 = W1[child]
+    rows = np.concatenate([rows2.ravel(), rows1.ravel()])
+    cols = np.concatenate([cols2.ravel(), cols1.ravel()])
+    vals = np.concatenate([vals2.ravel(), vals1.ravel()])
+    # a fine node shared by several fine cells gets the same row from each of them (conforming spaces): keep one copy
+    grp = np.concatenate([np.repeat(np.arange(nf * 9), 9), nf * 9 + np.repeat(np.arange(nf * 4), 4)])
+    first = np.full(nb_fine, -1, dtype=np.int64)
+    order = np.argsort(rows, kind="stable")
+    r_sorted, g_sorted = rows[order], grp[order]
+    head = np.ones(r_sorted.size, dtype=bool); head[1:] = r_sorted[1:] != r_sorted[:-1]
+    first[r_sorted[head]] = g_sorted[head]
+    if (first < 0).any() and not allow_missing_rows:
         raise RuntimeError("prolongation: a fine block node belongs to no fine cell")
     keep = (grp == first[rows]) & (np.abs(vals) > 1e-14)
     P = sp.csr_matrix((vals[keep], (rows[keep], cols[keep])), shape=(nb_fine, nb_coarse))

@@ -99,7 +99,15 @@ def main(rank, world, port, out_dir):
     assert (inv_c[rows.col[owned_row]] >= 0).all(), "stencil of an owned fine node left the local coarse mesh"
     keep = inv_c[rows.col] >= 0
     Pb = sp.csr_matrix((rows.data[keep], (rows.row[keep], inv_c[rows.col[keep]])), shape=(Lf.topo.nb, Lc.topo.nb))
-    P = sp.kron(Pb, sp.identity(3)).tocsr()
+    # the product's rank-local builder (femo_alpha_b200/dist_multigrid.py) gives the same rows without the global matrix
+    from femo_alpha_b200.dist_multigrid import local_prolongation, nested_parts
+    assert np.array_equal(nested_parts(part_c, 2)[0], part_f) and np.array_equal(nested_parts(part_c, 2)[1], part_c)
+    Pl = local_prolongation(Lf.lp, Lc.lp, Lf.topo.cell_blocks, Lc.topo.cell_blocks)
+    own_rows = np.nonzero(Lf.lp.own_block_mask)[0]
+    assert abs(Pl[own_rows] - Pb[own_rows]).max() < 1e-15
+    filled = np.nonzero(np.diff(Pl.indptr) > 0)[0]
+    assert abs(Pl[filled] - Pb[filled]).max() < 1e-15              # rows of ghost nodes, where present, agree as well
+    P = sp.kron(Pl, sp.identity(3)).tocsr()
 
     def gdot(L, u, v):
         t = torch.tensor([float(np.dot(L.own * u, v))], dtype=torch.float64)
