@@ -66,3 +66,48 @@ def test_prolongation_partition_of_unity_on_skew_and_junction_meshes():
     # nested geometry: coordinates are reproduced at the fine Q1 / vertex nodes (bilinear map)
     xc, xf = tc.block_coords(), tf.block_coords()
     assert np.abs((P @ xc)[tf.nq2:] - xf[tf.nq2:]).max() <= 1e-13
+
+
+def test_nested_partition_and_local_prolongation_three_levels():
+    """dist_multigrid.py (host side of the N-rank V-cycle): on every rank and between every pair of consecutive levels the
+    rank-local prolongation reproduces the rows of the global one for the fine block nodes the rank owns."""
+    import scipy.sparse as sp
+    from femo_alpha_b200.dist_multigrid import local_prolongation, nested_parts
+    from femo_alpha_b200.partition import attach_blocks, build_local_part, partition_cells_rcb
+    rng = np.random.default_rng(5)
+    nodes, quads = plate_mesh(5, 3, 2.0, 1.5)
+    nodes[:, :2] += 0.04 * rng.standard_normal((nodes.shape[0], 2))
+    meshes = [(nodes, quads)]
+    for _ in range(2):
+        meshes.append(refine_quads(*meshes[-1]))
+    meshes = meshes[::-1]                                      # finest first
+    world = 3
+    parts = nested_parts(partition_cells_rcb(meshes[-1][0][meshes[-1][1]].mean(axis=1), world), 3)
+    assert [p.size for p in parts] == [m[1].shape[0] for m in meshes]
+    gtopos = [ShellTopology(*m) for m in meshes]
+
+    def gkeys(t):
+        k = np.empty(t.nb, dtype=np.int64); k[:t.nq2] = np.arange(t.nq2); k[t.nq2:] = t.nn + t.ne + t.nc + np.arange(t.nn)
+        return k
+
+    for lf in range(2):
+        tf, tc = gtopos[lf], gtopos[lf + 1]
+        Pg = prolongation(tf.cell_blocks, tc.cell_blocks, tf.nb, tc.nb).tocsr()
+        kf, kc = gkeys(tf), gkeys(tc)
+        of, oc = np.argsort(kf), np.argsort(kc)
+        for rank in range(world):
+            lps, topos = [], []
+            for lvl in (lf, lf + 1):
+                lp = build_local_part(meshes[lvl][0], meshes[lvl][1], parts[lvl], rank, world)
+                t = ShellTopology(lp.nodes, lp.quads)
+                attach_blocks(lp, t.cell_blocks)
+                lps.append(lp); topos.append(t)
+            Pl = local_prolongation(lps[0], lps[1], topos[0].cell_blocks, topos[1].cell_blocks)
+            f2g = of[np.searchsorted(kf[of], lps[0].block_gkey)]
+            c2g = oc[np.searchsorted(kc[oc], lps[1].block_gkey)]
+            own = np.nonzero(lps[0].own_block_mask)[0]
+            # scatter the local rows to global columns and compare with the global rows
+            Pl = Pl.tocoo()
+            G = sp.csr_matrix((Pl.data, (Pl.row, c2g[Pl.col])), shape=(topos[0].nb, tc.nb))
+            assert abs(G[own] - Pg[f2g[own]]).max() < 1e-15
+            assert np.allclose(np.asarray(G[own].sum(axis=1)).ravel(), 1.0)       # partition of unity on the owned rows
