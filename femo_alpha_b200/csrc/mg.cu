@@ -189,11 +189,13 @@ int mg_smooth(femo_mg* m, int l, bool zero_guess) {
         k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, nullptr, 0.0, 0.0, 1.0 / theta, 1, c->dinv6, c->dinv3, c->nn, c->nq2,
                                                  Lv.r, Lv.d, Lv.x);
       } else {
+        if (c->world > 1) TRY(halo_exchange(c, Lv.x));      // distributed finest level: ghosts of the operand follow their owners
         TRY(bsr_spmv(c, Lv.x, Lv.t, 1));
         k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, Lv.t, 1.0, 0.0, 1.0 / theta, 0, c->dinv6, c->dinv3, c->nn, c->nq2,
                                                  Lv.r, Lv.d, Lv.x);
       }
     } else {
+      if (c->world > 1) TRY(halo_exchange(c, Lv.d));
       TRY(bsr_spmv(c, Lv.d, Lv.t, 1));
       const double rho_new = 1.0 / (2.0 * sigma - rho);
       k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.r, Lv.t, 1.0, rho_new * rho, 2.0 * rho_new / delta, 0, c->dinv6, c->dinv3,
@@ -217,11 +219,15 @@ int mg_vcycle(femo_mg* m, int l) {
   }
   MgLevel& Lc = m->L[l + 1];
   TRY(mg_smooth(m, l, true));
+  if (c->world > 1) TRY(halo_exchange(c, Lv.x));
   TRY(bsr_spmv(c, Lv.x, Lv.t, 1));
   k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, Lv.b, -1.0, Lv.t, Lv.r);
   k_transfer<<<(unsigned)cdiv(3 * Lv.nbc, 256), 256, 0, c->stream>>>(Lv.R_ptr, Lv.R_col, Lv.R_w, Lv.r, Lc.c->bcmask, Lv.nbc, 0, Lc.b);
   TRY(check_launch(c, "mg restrict"));
   c->launches += 2;
+  // distributed level above a replicated one (dist_multigrid.py): R carries zero weights on ghost rows, so every rank
+  // holds the contribution of the fine nodes it owns; the sum over ranks is the coarse residual, on every rank
+  if (c->world > 1) TRY(dist_allreduce_sum(c, Lc.b, (int)Lc.c->ndof));
   TRY(mg_vcycle(m, l + 1));
   k_transfer<<<(unsigned)cdiv(3 * Lv.nbf, 256), 256, 0, c->stream>>>(Lv.P_ptr, Lv.P_col, Lv.P_w, Lc.x, c->bcmask, Lv.nbf, 1, Lv.x);
   TRY(check_launch(c, "mg prolong"));
@@ -244,6 +250,7 @@ int mg_lambda_max(femo_mg* m, int l) {
     if (!(nrm2 > 0)) return femo_fail("multigrid: zero vector in the power iteration");
     if (it > 0) lam = sqrt(nrm2);
     k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0 / sqrt(nrm2), Lv.x, 0.0, Lv.x, Lv.b);
+    if (c->world > 1) TRY(halo_exchange(c, Lv.b));
     TRY(bsr_spmv(c, Lv.b, Lv.t, 1));
     k_cheb_step<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(Lv.t, nullptr, 0.0, 0.0, 1.0, 1, c->dinv6, c->dinv3, c->nn,
                                                                     c->nq2, Lv.r, Lv.d, Lv.x);
@@ -311,6 +318,7 @@ int femo_mg_create(int n_levels, femo_ctx** ctxs, femo_mg** out) {
   for (int l = 0; l < n_levels; ++l) {
     if (!ctxs[l] || !ctxs[l]->setup_done) { delete m; return femo_fail("femo_mg_create: level context not set up"); }
     if (ctxs[l]->kind != 0) { delete m; return femo_fail("femo_mg_create: RM-shell contexts only"); }
+    if (l > 0 && ctxs[l]->world > 1) { delete m; return femo_fail("femo_mg_create: only the finest level may be a multi-GPU context; coarser levels are replicated"); }
     if (ctxs[l]->world > 1) { delete m; return femo_fail("femo_mg_create: multigrid levels are single-GPU contexts"); }
     if (ctxs[l]->device != ctxs[0]->device) { delete m; return femo_fail("femo_mg_create: levels must share one device"); }
     m->L[l].c = ctxs[l];
@@ -441,6 +449,7 @@ int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int m
       if (it == 0) CUDA_TRY(cudaMemcpyAsync(m->pp, L0.x, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
       else k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, L0.x, rz_new / rz, m->pp, m->pp);
       rz = rz_new;
+      if (c->world > 1) TRY(halo_exchange(c, m->pp));
       TRY(bsr_spmv(c, m->pp, m->pAp, 1));
       double pAp = 0;
       TRY(dev_dot(c, m->pp, m->pAp, n, &pAp));
@@ -457,6 +466,7 @@ int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int m
     }
   }
   if (zero_bc) k_mg_mask<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, c->bcmask, m->px);
+  if (c->world > 1) TRY(halo_exchange(c, m->px));          // ghost entries of the solution follow their owners
   cudaEventRecord(c->ev1, c->stream);
   CUDA_TRY(cudaMemcpyAsync(sol, m->px, sizeof(double) * n, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));

@@ -66,3 +66,17 @@ def test_reverse_halo_exchange(built_lib, n):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     sys.stdout.write(r.stdout[-3000:]); sys.stderr.write(r.stderr[-3000:])
     assert r.returncode == 0
+
+
+@pytest.mark.xfail(strict=False, reason="the N-GPU V-cycle (mg.cu world > 1 branches, dist_multigrid.DistributedHierarchy) was written "
+                                        "after the round-1 GPU budget was spent: not yet run on hardware (algorithm prototyped over gloo)")
+@pytest.mark.parametrize("n", [2, 3])
+def test_distributed_vcycle(built_lib, n):
+    """V-cycle preconditioned state solve with a distributed finest level (tests/dist_gpu_mg_worker.py)"""
+    if _ngpu() < n:
+        pytest.skip("needs %d GPUs" % n)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr",
+           "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "tests", "dist_gpu_mg_worker.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(r.stdout[-3000:]); sys.stderr.write(r.stderr[-3000:])
+    assert r.returncode == 0

@@ -111,3 +111,40 @@ def test_nested_partition_and_local_prolongation_three_levels():
             G = sp.csr_matrix((Pl.data, (Pl.row, c2g[Pl.col])), shape=(topos[0].nb, tc.nb))
             assert abs(G[own] - Pg[f2g[own]]).max() < 1e-15
             assert np.allclose(np.asarray(G[own].sum(axis=1)).ravel(), 1.0)       # partition of unity on the owned rows
+
+
+def test_transfer_arrays_of_a_distributed_finest_level():
+    """dist_multigrid.transfer_arrays / replicated_part: P maps the replicated level-1 vector to the local fine blocks, and
+    the ownership-weighted R restricts so that the sum over the ranks is the global restriction."""
+    import scipy.sparse as sp
+    from femo_alpha_b200.dist_multigrid import local_prolongation, nested_parts, replicated_part, transfer_arrays
+    from femo_alpha_b200.partition import attach_blocks, build_local_part, partition_cells_rcb
+    nodes_c, quads_c = plate_mesh(6, 3, 3.0, 1.5)
+    nodes_f, quads_f = refine_quads(nodes_c, quads_c)
+    tf, tc = ShellTopology(nodes_f, quads_f), ShellTopology(nodes_c, quads_c)
+    Pg = prolongation(tf.cell_blocks, tc.cell_blocks, tf.nb, tc.nb).tocsr()
+    rng = np.random.default_rng(0)
+    r_f, e_c = rng.standard_normal((tf.nb, 3)), rng.standard_normal((tc.nb, 3))
+    kf = np.empty(tf.nb, dtype=np.int64); kf[:tf.nq2] = np.arange(tf.nq2); kf[tf.nq2:] = tf.nn + tf.ne + tf.nc + np.arange(tf.nn)
+    of = np.argsort(kf)
+    world = 3
+    parts = nested_parts(partition_cells_rcb(nodes_c[quads_c].mean(axis=1), world), 2)
+    lp_all = replicated_part(nodes_c, quads_c)
+    assert np.array_equal(lp_all.cell_global, np.arange(quads_c.shape[0])) and np.array_equal(lp_all.vertex_global, np.arange(len(nodes_c)))
+    total = np.zeros((tc.nb, 3))
+    for rank in range(world):
+        lp = build_local_part(nodes_f, quads_f, parts[0], rank, world)
+        t = ShellTopology(lp.nodes, lp.quads)
+        attach_blocks(lp, t.cell_blocks)
+        P = local_prolongation(lp, lp_all, t.cell_blocks, tc.cell_blocks)
+        Pp, Pc, Pw, Rp, Rc, Rw = transfer_arrays(P, lp.own_block_mask.astype(np.float64))
+        assert Pp[-1] == Rp[-1] and Pp.dtype == np.int32 and Rw.dtype == np.float64
+        f2g = of[np.searchsorted(kf[of], lp.block_gkey)]
+        own = lp.own_block_mask
+        # prolongation of the replicated coarse vector on the owned rows
+        Pm = sp.csr_matrix((Pw, Pc, Pp), shape=(t.nb, tc.nb))
+        assert np.abs((Pm @ e_c)[own] - (Pg @ e_c)[f2g[own]]).max() < 1e-14
+        # this rank's share of the restriction of a (ghost-consistent) fine vector
+        Rm = sp.csr_matrix((Rw, Rc, Rp), shape=(tc.nb, t.nb))
+        total += Rm @ r_f[f2g]
+    assert np.abs(total - Pg.T @ r_f).max() < 1e-13
