@@ -7,6 +7,7 @@
 #   ncu     launch list of a short bench run and of a short dynamic run (per-launch durations, no clock control)
 #   hex     config-5 solid forms: parity tests + 160^3 assembly / PCG timings (scripts/hex_bench.py)
 #   ncuhex  ncu --set full of one k_hex_assemble launch -> gpurun_out/${TAG}_hex_asm.ncu-rep
+#   pending2 the multi-GPU items of DESIGN 15 (DistributedSolid, reverse halo, N-GPU V-cycle); needs --gpus 2+
 #   pending everything written after the round-1 GPU budget was spent, 1 GPU
 #   hexscale weak scaling of config 5 on NGPU GPUs (scripts/hex_bench_dist.py; first run pending)
 #   disthex N-GPU parity of the hexahedral solids (needs `gpurun --gpus 2` or more; first run pending)
@@ -49,6 +50,9 @@ for sec in "$@"; do
       # everything DESIGN 15 lists as written but not yet run on hardware (1 GPU): the xfail-marked tests report XPASS when green
       timeout 900 python -m pytest tests/test_gpu_hex.py tests/test_gpu_shape.py tests/test_gpu_golden.py -m gpu -q --tb=short -rxX -s -k "gradient_records or penalty_shape or golden_hexahedral" > gpurun_out/${T}_pytest_pending.log 2>&1; echo "pytest pending rc=$?"; grep -E "gradient records:|rel.err|XPASS|XFAIL|passed|failed|xfailed|xpassed" gpurun_out/${T}_pytest_pending.log | tail -n 14
       FEMO_HEX_GRAD=1 timeout 600 python scripts/hex_bench.py --n ${HEX_N:-160} --out gpurun_out/${T}_hex_bench_grad.json > gpurun_out/${T}_hex_bench_grad.log 2>&1; echo "hex bench (gradient records) rc=$?"; tail -n 3 gpurun_out/${T}_hex_bench_grad.log | cut -c1-700 ;;
+    pending2)
+      # the multi-GPU items of DESIGN 15 (needs `gpurun --gpus 2` or more): XPASS = green on hardware
+      timeout 1500 python -m pytest tests/test_gpu_dist.py -m gpu -q --tb=short -rxX -s -k "hexahedral or reverse_halo or distributed_vcycle" > gpurun_out/${T}_pytest_pending2.log 2>&1; echo "pytest pending2 rc=$?"; grep -E "^rank|XPASS|XFAIL|passed|failed|xfailed|xpassed|Error" gpurun_out/${T}_pytest_pending2.log | tail -n 24 ;;
     *) echo "unknown section $sec" ;;
   esac
 done
