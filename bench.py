@@ -104,6 +104,7 @@ def cpu_baseline(n, budget_s=12.0, rows=None):
     sample of the same workload: an n x rows strip of the n x n plate.  Checker / baseline only."""
     from oracle import c_port
     from oracle.rm_shell_ref import ShellTopology
+    c_port.use_all_cores()
     rows = rows or max(8, min(n, 24))
     nodes, quads = plate(n, rows, 0.0, 10.0, 10.0 * rows / n)
     topo = ShellTopology(nodes, quads)
@@ -132,6 +133,7 @@ def run_reference(args, rank):
         return
     from oracle import c_port
     from oracle.rm_shell_ref import ShellTopology
+    c_port.use_all_cores()           # torch.distributed.run exports OMP_NUM_THREADS=1
     n = args.n
     rows = max(8, min(n, 24))
     nodes, quads = plate(n, rows, 0.0, 10.0, 10.0 * rows / n)

@@ -29,7 +29,9 @@ def _stale(target, deps):
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    headers = [os.path.join(CSRC, "femo_internal.cuh"), os.path.join(CSRC, "tile_plan.hpp"), os.path.join(HERE, "..", "include", "femo_b200.h")]
+    # every header of the library: a stale object file is exactly what would ship to the GPU box (*.so is git-ignored but pushed)
+    headers = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".hpp", ".h")))
+    headers.append(os.path.join(HERE, "..", "include", "femo_b200.h"))
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     nvcc = _nvcc()

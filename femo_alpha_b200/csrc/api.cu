@@ -52,18 +52,8 @@ __global__ void k_axpby(double a, const double* x, double b, const double* y, in
 __global__ void k_block_coords(const double* xyz, const int32_t* edges, const int32_t* cv, int64_t nn, int64_t ne,
                                int64_t nc, double* out) {
   int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  int64_t nq2 = nn + ne + nc;
-  if (I >= nq2 + nn) return;
-  V3 p;
-  if (I < nn) p = ldv3(xyz + 3 * I);
-  else if (I < nn + ne) {
-    int64_t e = I - nn;
-    p = 0.5 * (ldv3(xyz + 3 * (int64_t)edges[2 * e]) + ldv3(xyz + 3 * (int64_t)edges[2 * e + 1]));
-  } else if (I < nq2) {
-    int64_t c = I - nn - ne;
-    p = 0.25 * (ldv3(xyz + 3 * (int64_t)cv[4 * c]) + ldv3(xyz + 3 * (int64_t)cv[4 * c + 1]) +
-                ldv3(xyz + 3 * (int64_t)cv[4 * c + 2]) + ldv3(xyz + 3 * (int64_t)cv[4 * c + 3]));
-  } else p = ldv3(xyz + 3 * (I - nq2));
+  if (I >= 2 * nn + ne + nc) return;
+  const V3 p = block_coord(xyz, edges, cv, nn, ne, nc, I);
   out[3 * I] = p.x; out[3 * I + 1] = p.y; out[3 * I + 2] = p.z;
 }
 __global__ void k_bsr_apply_bc(const int32_t* rowptr, const int32_t* colidx, const double* mask, int64_t nb, double* vals) {

@@ -80,6 +80,25 @@ __global__ void k_halo_unpack_add(double* __restrict__ x, const int32_t* __restr
   x[3 * (int64_t)blocks[b] + k] += buf[i];
 }
 
+// one grouped send / receive with every neighbour (3 doubles per listed block).  The group is ALWAYS closed: an error
+// between GroupStart and GroupEnd would otherwise leave later NCCL calls of this thread queued into an open group.
+int neighbour_exchange(femo_ctx* c, ncclComm_t comm, double* out_buf, const std::vector<int>& out_off, double* in_buf,
+                       const std::vector<int>& in_off, cudaStream_t stream = nullptr) {
+  cudaStream_t st = stream ? stream : c->stream;
+  NCCL_TRY(g_nccl.GroupStart());
+  ncclResult_t first = ncclSuccess;
+  for (int i = 0; i < c->n_nbr && first == ncclSuccess; ++i) {
+    const int no = out_off[i + 1] - out_off[i], ni = in_off[i + 1] - in_off[i];
+    if (no > 0) first = g_nccl.Send(out_buf + 3 * (int64_t)out_off[i], 3 * (size_t)no, ncclDouble, c->nbr_rank[i], comm, st);
+    if (ni > 0 && first == ncclSuccess)
+      first = g_nccl.Recv(in_buf + 3 * (int64_t)in_off[i], 3 * (size_t)ni, ncclDouble, c->nbr_rank[i], comm, st);
+  }
+  const ncclResult_t end = g_nccl.GroupEnd();
+  if (first != ncclSuccess) return femo_fail(std::string("halo send / receive: ") + g_nccl.GetErrorString(first));
+  if (end != ncclSuccess) return femo_fail(std::string("ncclGroupEnd: ") + g_nccl.GetErrorString(end));
+  return 0;
+}
+
 struct DevGuard2 {
   int prev = 0;
   explicit DevGuard2(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); }
@@ -96,13 +115,7 @@ int halo_exchange(femo_ctx* c, double* x) {
     k_halo_pack<<<(unsigned)cdiv(3 * c->n_send, 256), 256, 0, c->stream>>>(x, c->send_blocks, c->n_send, c->send_buf);
     c->launches += 1;
   }
-  NCCL_TRY(g_nccl.GroupStart());
-  for (int i = 0; i < c->n_nbr; ++i) {
-    const int ns = c->send_off[i + 1] - c->send_off[i], nr = c->recv_off[i + 1] - c->recv_off[i];
-    if (ns > 0) NCCL_TRY(g_nccl.Send(c->send_buf + 3 * (int64_t)c->send_off[i], 3 * (size_t)ns, ncclDouble, c->nbr_rank[i], comm, c->stream));
-    if (nr > 0) NCCL_TRY(g_nccl.Recv(c->recv_buf + 3 * (int64_t)c->recv_off[i], 3 * (size_t)nr, ncclDouble, c->nbr_rank[i], comm, c->stream));
-  }
-  NCCL_TRY(g_nccl.GroupEnd());
+  TRY(neighbour_exchange(c, comm, c->send_buf, c->send_off, c->recv_buf, c->recv_off));
   if (c->n_recv > 0) {
     k_halo_unpack<<<(unsigned)cdiv(3 * c->n_recv, 256), 256, 0, c->stream>>>(x, c->recv_blocks, c->n_recv, c->recv_buf);
     c->launches += 1;
@@ -114,7 +127,7 @@ int halo_exchange(femo_ctx* c, double* x) {
 // Reverse halo exchange: owners += the values their ghosts hold on the other ranks (restriction of the N-rank V-cycle,
 // DESIGN 15; prototype tests/dist_mg_worker.py).  Same neighbour lists as halo_exchange with the roles of the buffers
 // swapped; an owned block can be a ghost on several neighbours, so the contributions are added neighbour by neighbour
-// (one small launch each, fixed order -> deterministic).  NOT YET RUN ON HARDWARE.
+// (one small launch each, fixed order -> deterministic).
 int halo_accumulate(femo_ctx* c, double* x) {
   if (c->world <= 1) return 0;
   if (!c->nccl_comm) return femo_fail("halo_accumulate: communicator not initialised (femo_dist_init)");
@@ -123,13 +136,7 @@ int halo_accumulate(femo_ctx* c, double* x) {
     k_halo_pack<<<(unsigned)cdiv(3 * c->n_recv, 256), 256, 0, c->stream>>>(x, c->recv_blocks, c->n_recv, c->recv_buf);
     c->launches += 1;
   }
-  NCCL_TRY(g_nccl.GroupStart());
-  for (int i = 0; i < c->n_nbr; ++i) {
-    const int ns = c->send_off[i + 1] - c->send_off[i], nr = c->recv_off[i + 1] - c->recv_off[i];
-    if (nr > 0) NCCL_TRY(g_nccl.Send(c->recv_buf + 3 * (int64_t)c->recv_off[i], 3 * (size_t)nr, ncclDouble, c->nbr_rank[i], comm, c->stream));
-    if (ns > 0) NCCL_TRY(g_nccl.Recv(c->send_buf + 3 * (int64_t)c->send_off[i], 3 * (size_t)ns, ncclDouble, c->nbr_rank[i], comm, c->stream));
-  }
-  NCCL_TRY(g_nccl.GroupEnd());
+  TRY(neighbour_exchange(c, comm, c->recv_buf, c->recv_off, c->send_buf, c->send_off));
   for (int i = 0; i < c->n_nbr; ++i) {
     const int ns = c->send_off[i + 1] - c->send_off[i];
     if (ns == 0) continue;

@@ -283,6 +283,22 @@ FEMO_HD void outer_acc(double* K, V3 a, V3 b) {
   K[6] += a.z * b.x; K[7] += a.z * b.y; K[8] += a.z * b.z;
 }
 
+// position of block node I: Q2 vertices [0,nn), edge mid-points, cell centres, then the Q1 rotation nodes
+FEMO_HD V3 block_coord(const double* xyz, const int32_t* edges, const int32_t* cv, int64_t nn, int64_t ne, int64_t nc, int64_t I) {
+  const int64_t nq2 = nn + ne + nc;
+  if (I < nn) return ldv3(xyz + 3 * I);
+  if (I < nn + ne) {
+    const int64_t e = I - nn;
+    return 0.5 * (ldv3(xyz + 3 * (int64_t)edges[2 * e]) + ldv3(xyz + 3 * (int64_t)edges[2 * e + 1]));
+  }
+  if (I < nq2) {
+    const int64_t c = I - nn - ne;
+    return 0.25 * (ldv3(xyz + 3 * (int64_t)cv[4 * c]) + ldv3(xyz + 3 * (int64_t)cv[4 * c + 1]) +
+                   ldv3(xyz + 3 * (int64_t)cv[4 * c + 2]) + ldv3(xyz + 3 * (int64_t)cv[4 * c + 3]));
+  }
+  return ldv3(xyz + 3 * (I - nq2));
+}
+
 // geometry of one cell at one reference point
 struct QpGeom {
   V3 E0, E1, E2;        // local orthonormal frame           kinematics.py:54-70

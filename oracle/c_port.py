@@ -31,6 +31,15 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def use_all_cores():
+    """Let the OpenMP loops of both ports use every core this process may run on, whatever OMP_NUM_THREADS says
+    (torch.distributed.run exports OMP_NUM_THREADS=1 to its workers).  Returns the thread count."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().rmc_set_threads(C.c_int(n))
+    hexlib().hexc_set_threads(C.c_int(n))
+    return n
+
+
 def element_matrices(topo, h, E, nu, uhat, ewm, m=4):
     cv = np.ascontiguousarray(topo.cv, dtype=np.int32)
     out = np.empty((topo.nc, 39, 39))

@@ -6,6 +6,9 @@
  * element -> CSR position map (MatSetValuesLocal without the per-row search), cells distributed over threads with
  * atomic adds. */
 #include <math.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <stdint.h>
 #include <string.h>
 
@@ -73,4 +76,14 @@ int hexc_assemble_csr(int64_t nc, const double* xyz, const int32_t* cells, const
     }
   }
   return 0;
+}
+
+/* number of OpenMP threads of the following calls (bench.py sets it to the host cores it may use: under
+ * torch.distributed.run the environment carries OMP_NUM_THREADS=1, which would make the CPU arm single-threaded) */
+void hexc_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
 }

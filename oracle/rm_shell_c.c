@@ -197,3 +197,13 @@ void rmc_csr_spmv(int64_t n, const int64_t* indptr, const int32_t* indices, cons
     y[i] = s;
   }
 }
+
+/* number of OpenMP threads of the following calls (bench.py sets it to the host cores it may use: under
+ * torch.distributed.run the environment carries OMP_NUM_THREADS=1, which would make the CPU arm single-threaded) */
+void rmc_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}

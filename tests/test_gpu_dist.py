@@ -39,12 +39,10 @@ def test_two_gpu_time_stepping_matches_oracle(built_lib, name, sw):
     assert r.returncode == 0
 
 
-@pytest.mark.xfail(strict=False, reason="NCCL path of DistributedSolid not yet run on hardware (round-1 GPU budget spent); "
-                                        "its host logic is covered over gloo in tests/test_dist_gloo.py")
 @pytest.mark.parametrize("n", [2, 3])
 def test_multi_gpu_hexahedral_solid_matches_oracle(built_lib, n):
     """SURVEY 8 f4 on N GPUs (DistributedSolid): state, compliance, volume, adjoint density gradient
-    (tests/dist_gpu_hex_worker.py).  Not yet run on hardware in round 1."""
+    (tests/dist_gpu_hex_worker.py)."""
     if _ngpu() < n:
         pytest.skip("needs %d GPUs" % n)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr",
@@ -54,8 +52,6 @@ def test_multi_gpu_hexahedral_solid_matches_oracle(built_lib, n):
     assert r.returncode == 0
 
 
-@pytest.mark.xfail(strict=False, reason="femo_halo_accumulate was written after the round-1 GPU budget was spent: not yet run on "
-                                        "hardware (the algorithm it serves is prototyped over gloo in tests/dist_mg_worker.py)")
 @pytest.mark.parametrize("n", [2, 3])
 def test_reverse_halo_exchange(built_lib, n):
     """owners += ghost copies (tests/dist_gpu_accumulate_worker.py)"""
@@ -68,8 +64,6 @@ def test_reverse_halo_exchange(built_lib, n):
     assert r.returncode == 0
 
 
-@pytest.mark.xfail(strict=False, reason="the N-GPU V-cycle (mg.cu world > 1 branches, dist_multigrid.DistributedHierarchy) was written "
-                                        "after the round-1 GPU budget was spent: not yet run on hardware (algorithm prototyped over gloo)")
 @pytest.mark.parametrize("n", [2, 3])
 def test_distributed_vcycle(built_lib, n):
     """V-cycle preconditioned state solve with a distributed finest level (tests/dist_gpu_mg_worker.py)"""

@@ -56,16 +56,14 @@ def test_total_shape_derivative_of_the_compliance():
     assert np.isclose(total @ du, fd, rtol=1e-5), (total @ du, fd)
 
 
-@pytest.mark.xfail(strict=False, reason="csrc/penalty_shape.cu was written after the round-1 GPU budget was spent: not yet run on "
-                                        "hardware (its maths is covered by tests/test_shape_host.py against the complex-step oracle)")
 def test_penalty_shape(built_lib):
-    """Shape partial of a penalty-BC context, facet terms included (Nanson's factor); own process
-    (tests/penalty_shape_worker.py) so that a fault in the unproven kernels cannot poison the rest of the suite."""
+    """Shape partial of a penalty-BC context, facet terms included (Nanson's factor; on by default), in its own process
+    (tests/penalty_shape_worker.py)."""
     import os
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, os.path.join(root, "tests", "penalty_shape_worker.py")], cwd=root, capture_output=True,
-                       text=True, timeout=900, env=dict(os.environ, FEMO_PENALTY_SHAPE="1"))
+                       text=True, timeout=900)
     sys.stdout.write(r.stdout[-3000:]); sys.stderr.write(r.stderr[-3000:])
     assert r.returncode == 0
