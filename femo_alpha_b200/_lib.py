@@ -72,6 +72,7 @@ SIGNATURES = {
     "femo_nccl_unique_id": [_P],
     "femo_dist_setup": [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, C.c_int64],
     "femo_dist_init": [_P, _P],
+    "femo_dist_share_comm": [_P, _P],
     "femo_halo_exchange": [_P, _P, C.c_int],
     "femo_halo_accumulate": [_P, _P, C.c_int],
     "femo_dist_allreduce": [_P, _D, C.c_int],
@@ -82,6 +83,9 @@ SIGNATURES = {
     "femo_mg_setup": [_P, C.c_int, C.c_int],
     "femo_mg_get_lambda": [_P, C.c_int, _D],
     "femo_mg_solve": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int), _D, C.c_int, C.c_int],
+    "femo_direct_setup": [_P],
+    "femo_direct_solve": [_P, _P, _P, C.c_int, _D, C.c_int, C.c_int],
+    "femo_direct_info": [_P, _D],
     "femo_dyn_create": [_P, C.c_double, C.c_int, C.c_int, C.c_double, C.POINTER(_P)],
     "femo_dyn_destroy": [_P],
     "femo_dyn_set_mg": [_P, _P],

@@ -9,7 +9,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfemo_b200.so")
-SOURCES = ["api.cu", "topology.cu", "assemble.cu", "assemble_tiles.cu", "solver.cu", "outputs.cu", "dist.cu", "mg.cu", "dynamic.cu", "hex.cu", "penalty_shape.cu"]
+SOURCES = ["api.cu", "topology.cu", "assemble.cu", "assemble_tiles.cu", "solver.cu", "outputs.cu", "dist.cu", "mg.cu", "coarse.cu", "dynamic.cu", "hex.cu", "penalty_shape.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fopenmp", "--use_fast_math=false"]
 

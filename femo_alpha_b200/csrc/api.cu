@@ -100,6 +100,21 @@ int copy_out(femo_ctx* c, double* dst, const double* src, int64_t n, int on_devi
   return 0;
 }
 
+}  // namespace
+
+int vec_mul(femo_ctx* c, const double* a, const double* m, int64_t n, double* out) {
+  k_mul<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(a, m, n, out);
+  c->launches += 1;
+  return check_launch(c, "k_mul");
+}
+int vec_axpby(femo_ctx* c, double a, const double* x, double b, const double* y, int64_t n, double* out) {
+  k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(a, x, b, y, n, out);
+  c->launches += 1;
+  return check_launch(c, "k_axpby");
+}
+
+namespace {
+
 #define NEED_SETUP(c, name) \
   if (!(c) || !(c)->setup_done) return femo_fail(std::string(name) + ": context not set up (femo_mesh_set + femo_shell_setup)")
 
@@ -141,6 +156,7 @@ int femo_ctx_destroy(femo_ctx* c) {
   cudaStreamSynchronize(c->stream);
   dist_free(c);
   tile_plan_free(c);
+  coarse_free(c->direct); c->direct = nullptr;
   void* ptrs[] = {c->xyz, c->cv, c->ce, c->edges, c->cell_blocks, c->hE, c->tab, c->h, c->E, c->nu, c->rho, c->f, c->uhat,
                   c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
                   c->nc_adj, c->rec, c->bcmask, c->bcbits, c->colbc, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
@@ -282,6 +298,7 @@ int femo_set_strong_bc(femo_ctx* c, int64_t n, const int32_t* dofs) {
   TRY(check_launch(c, "k_col_bc"));
   c->launches += 2;
   c->prec_valid = false;
+  c->mat_epoch += 1;
   return 0;
 }
 

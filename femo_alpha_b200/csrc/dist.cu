@@ -167,7 +167,7 @@ int dist_allreduce_host(femo_ctx* c, double* hv, int n) {
 }
 
 void dist_free(femo_ctx* c) {
-  if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->nccl_comm);
+  if (c->nccl_comm && c->comm_owner && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->nccl_comm);
   c->nccl_comm = nullptr;
   dev_free(&c->send_blocks); dev_free(&c->recv_blocks); dev_free(&c->send_buf); dev_free(&c->recv_buf); dev_free(&c->own);
 }
@@ -222,6 +222,18 @@ int femo_dist_init(femo_ctx* c, const void* id128) {
   ncclComm_t comm = nullptr;
   NCCL_TRY(g_nccl.CommInitRank(&comm, c->world, id, c->rank));
   c->nccl_comm = comm;
+  c->comm_owner = true;
+  return 0;
+}
+
+// the levels of a distributed multigrid hierarchy live on the same ranks: they use the communicator of the finest level
+int femo_dist_share_comm(femo_ctx* c, femo_ctx* owner) {
+  if (!c || !owner) return femo_fail("femo_dist_share_comm: null argument");
+  if (c->world != owner->world || c->rank != owner->rank) return femo_fail("femo_dist_share_comm: rank / world differ");
+  if (c->world > 1 && !owner->nccl_comm) return femo_fail("femo_dist_share_comm: the owner has no communicator (femo_dist_init)");
+  if (c->nccl_comm && c->comm_owner && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->nccl_comm);
+  c->nccl_comm = owner->nccl_comm;
+  c->comm_owner = false;
   return 0;
 }
 

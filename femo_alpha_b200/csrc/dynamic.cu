@@ -42,7 +42,7 @@ struct femo_dyn {
   bool ready = false, energies_valid = false;
   double* hist = nullptr;                     // levels * ndof, level-major
   double *io1 = nullptr, *io2 = nullptr;      // staging of host-side histories
-  double* Cinv = nullptr; int64_t ncinv = 0;
+  CoarseSolver* cs = nullptr;      // direct solver of the effective operator (coarse.cu)
   double *v = nullptr, *kw = nullptr, *t1 = nullptr, *t2 = nullptr, *rhs = nullptr, *W = nullptr, *mu = nullptr, *lm = nullptr;
   double* dh = nullptr;
   double *fh = nullptr, *en_dev = nullptr;    // load history (levels x n_force) and per-level w.Kw on the device
@@ -202,7 +202,7 @@ int dyn_linear_solve(femo_dyn* d, const double* b, double* x, double rtol, int m
   femo_ctx* c = d->c;
   int it = 0; double rr = 0;
   if (d->solver == 1) {
-    TRY(dense_inverse_apply(c, d->Cinv, b, x));
+    TRY(coarse_apply(c, d->cs, b, x));
     it = 1;
   } else if (d->solver == 3) {
     // warm start (femo_mg_solve starts from zero): solve A delta = b - A x0 to the tolerance rtol |b| / |b - A x0|
@@ -250,6 +250,7 @@ int dyn_energies(femo_dyn* d) {
 
 // assembly entry point of every solver: K, or A while the context is in dynamic mode
 int assemble_jacobian(femo_ctx* c) {
+  c->mat_epoch += 1;
   if (c->kind == 1) return hex_assemble(c);
   if (c->dyn_on) return dyn_assemble(c);
   return assemble_stiffness(c);
@@ -287,9 +288,10 @@ int femo_dyn_destroy(femo_dyn* d) {
   cudaStreamSynchronize(c->stream);
   if (d->mg) { for (int l = 0; l < mg_num_levels(d->mg); ++l) dyn_disable(mg_level_ctx(d->mg, l)); mg_invalidate(d->mg); }
   dyn_disable(c);
-  double** vecs[] = {&d->hist, &d->io1, &d->io2, &d->Cinv, &d->v, &d->kw, &d->t1, &d->t2, &d->rhs, &d->W, &d->mu, &d->lm, &d->dh,
+  double** vecs[] = {&d->hist, &d->io1, &d->io2, &d->v, &d->kw, &d->t1, &d->t2, &d->rhs, &d->W, &d->mu, &d->lm, &d->dh,
                      &d->fh, &d->en_dev};
   for (double** v : vecs) dev_free(v);
+  coarse_free(d->cs); d->cs = nullptr;
   if (d->fwd_graph) cudaGraphExecDestroy(d->fwd_graph);
   if (d->gstream) cudaStreamDestroy(d->gstream);
   if (d->e0) cudaEventDestroy(d->e0);
@@ -329,7 +331,7 @@ int femo_dyn_setup(femo_dyn* d, int solver) {
     TRY(femo_mg_setup(d->mg, 3, 0));          // assembles A on every level through assemble_jacobian()
   } else {
     TRY(dyn_assemble(c));
-    if (s == 1) TRY(dense_inverse_build(c, &d->Cinv, &d->ncinv));
+    if (s == 1) { if (!d->cs) TRY(coarse_analyse(c, &d->cs)); TRY(coarse_factor(c, d->cs)); }
     else TRY(precond_setup(c));
   }
   if (d->self_weight) TRY(self_weight_load(c, d->g_acc, d->W));

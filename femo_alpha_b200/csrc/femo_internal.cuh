@@ -60,6 +60,8 @@ struct Tables {
   double dn1[FEMO_MAX_NQ][4][2];
 };
 
+struct CoarseSolver;   // coarse.cu: block-tridiagonal direct solver
+
 struct femo_ctx {
   int device = 0;
   cudaStream_t stream = 0;
@@ -150,6 +152,7 @@ struct femo_ctx {
   // multi-GPU (one process per GPU): owner mask, halo lists, NCCL communicator (dist.cu)
   int world = 1, rank = 0;
   void* nccl_comm = nullptr;
+  bool comm_owner = false;      // false: borrowed from another context of this rank (femo_dist_share_comm)
   int n_nbr = 0;
   std::vector<int> nbr_rank, send_off, recv_off;   // neighbour ranks and block offsets (n_nbr+1)
   int64_t n_send = 0, n_recv = 0;                 // blocks
@@ -167,6 +170,9 @@ struct femo_ctx {
   double *scal = nullptr;       // device scalars
   double *cellbuf = nullptr;    // nc*39 element vectors
   bool jac_valid = false, prec_valid = false;
+  int64_t mat_epoch = 0;        // bumped whenever c->vals or the BC masks change (consumers cache factorisations against it)
+  CoarseSolver* direct = nullptr;   // femo_direct_* (coarse.cu)
+  int64_t direct_epoch = -1;
   double t_rec = 0, t_asm = 0, t_solve = 0, t_iter = 0;
   double dmma_tf = 0;           // last measured fp64 mma.sync rate (TFLOP/s)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -259,8 +265,17 @@ struct femo_mg;
 int mg_num_levels(femo_mg* m);                                            // mg.cu
 femo_ctx* mg_level_ctx(femo_mg* m, int l);
 void mg_invalidate(femo_mg* m);
-int dense_inverse_build(femo_ctx* c, double** Cinv, int64_t* n_have);     // inverse of the BC-applied c->vals
-int dense_inverse_apply(femo_ctx* c, const double* Cinv, const double* b, double* x);
+// coarse.cu: direct solver (block-tridiagonal factorisation on level sets) of the BC-applied c->vals
+int coarse_analyse(femo_ctx* c, CoarseSolver** out);
+int coarse_factor(femo_ctx* c, CoarseSolver* cs);
+int coarse_apply(femo_ctx* c, CoarseSolver* cs, const double* b, double* x);     // device vectors; kernels only (capturable)
+void coarse_free(CoarseSolver* cs);
+int coarse_num_levels(const CoarseSolver* cs);
+int64_t coarse_max_front(const CoarseSolver* cs);
+double coarse_bytes(const CoarseSolver* cs);
+bool coarse_is_dense(const CoarseSolver* cs);
+int vec_mul(femo_ctx* c, const double* a, const double* m, int64_t n, double* out);                         // api.cu: out = a .* m
+int vec_axpby(femo_ctx* c, double a, const double* x, double b, const double* y, int64_t n, double* out);   // api.cu
 
 // ---- device maths --------------------------------------------------------------
 #ifdef __CUDACC__

@@ -10,8 +10,7 @@
 //                  on [lmax/10, 1.1 lmax], lmax by power iteration: linear and A-self-adjoint -> the V-cycle is SPD
 //   transfer       nested Q2xQ1 spaces: P = coarse basis evaluated at the fine nodes (block-scalar CSR, rows = fine
 //                  block nodes), R = P^T stored as its own CSR so that both directions are gathers (no atomics)
-//   coarsest       dense inverse (cuSOLVER potrf + potri, bound at run time) applied as one GEMV
-#include <dlfcn.h>
+//   coarsest       direct solve: block-tridiagonal factorisation on level sets (coarse.cu; no library)
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -30,8 +29,7 @@ struct MgLevel {
 struct femo_mg {
   std::vector<MgLevel> L;
   int deg = 3;
-  double* Cinv = nullptr;      // dense inverse of the coarsest operator (n x n)
-  int64_t ncoarse = 0;
+  CoarseSolver* cs = nullptr;  // direct solver of the coarsest operator (coarse.cu)
   bool ready = false;
   double *pr = nullptr, *pz = nullptr, *pp = nullptr, *pAp = nullptr, *px = nullptr, *pb = nullptr;   // PCG vectors (level 0)
   int64_t vcycles = 0;
@@ -99,81 +97,9 @@ __global__ void k_transfer(const int32_t* __restrict__ ptr, const int32_t* __res
   y[t] = add ? y[t] + s : s;
 }
 
-// dense copy of the BC-modified operator: rows/cols of clamped dofs replaced by the identity (column-major = row-major)
-__global__ void k_dense_fill(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
-                             const double* __restrict__ vals, const double* __restrict__ bcmask, int64_t nb, int64_t n,
-                             double* __restrict__ A) {
-  const int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (I >= nb) return;
-  for (int32_t k = rowptr[I]; k < rowptr[I + 1]; ++k) {
-    const int64_t J = colidx[k];
-    for (int i = 0; i < 3; ++i)
-      for (int j = 0; j < 3; ++j) {
-        const int64_t r = 3 * I + i, cc = 3 * J + j;
-        double v = vals[(int64_t)k * 9 + 3 * i + j] * bcmask[r] * bcmask[cc];
-        if (r == cc && bcmask[r] == 0.0) v = 1.0;
-        A[r * n + cc] = v;
-      }
-  }
-}
-
-// potri(LOWER, column-major) leaves the inverse in the entries (i >= j) at [j n + i], i.e. the row-major UPPER
-// triangle: mirror it into the row-major lower one
-__global__ void k_dense_mirror(double* A, int64_t n) {
-  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (t >= n * n) return;
-  const int64_t r = t / n, cc = t - r * n;
-  if (cc < r) A[r * n + cc] = A[cc * n + r];
-}
-
 __global__ void k_mg_mask(int64_t n, const double* __restrict__ mask, double* __restrict__ x) {
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) x[i] *= mask[i];
-}
-
-// y = A x, dense row-major symmetric, one warp per row, fixed summation order
-__global__ void k_dense_gemv(const double* __restrict__ A, const double* __restrict__ x, int64_t n, double* __restrict__ y) {
-  const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (row >= n) return;
-  const double* a = A + row * n;
-  double s = 0;
-  for (int64_t j = lane; j < n; j += 32) s += a[j] * x[j];
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if (lane == 0) y[row] = s;
-}
-
-// ---- cuSOLVER (dense Cholesky + inverse of the coarsest operator), bound at run time -----------------------------
-struct CusolverApi {
-  void* handle = nullptr;
-  int (*Create)(void**) = nullptr;
-  int (*Destroy)(void*) = nullptr;
-  int (*SetStream)(void*, cudaStream_t) = nullptr;
-  int (*potrf_bufferSize)(void*, int, int, double*, int, int*) = nullptr;
-  int (*potrf)(void*, int, int, double*, int, double*, int, int*) = nullptr;
-  int (*potri_bufferSize)(void*, int, int, double*, int, int*) = nullptr;
-  int (*potri)(void*, int, int, double*, int, double*, int, int*) = nullptr;
-};
-CusolverApi g_cs;
-
-int cusolver_load() {
-  if (g_cs.handle) return 0;
-  const char* env = getenv("FEMO_CUSOLVER_LIB");
-  void* h = env ? dlopen(env, RTLD_NOW | RTLD_GLOBAL) : nullptr;
-  const char* names[] = {"libcusolver.so.11", "libcusolver.so.12", "libcusolver.so", "/usr/local/cuda/lib64/libcusolver.so.11"};
-  for (const char* nm : names)
-    if (!h) h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
-  if (!h) return femo_fail(std::string("multigrid: cannot load libcusolver (set FEMO_CUSOLVER_LIB): ") + dlerror());
-#define BINDS(field, name)                                                            \
-  *(void**)(&g_cs.field) = dlsym(h, name);                                            \
-  if (!g_cs.field) return femo_fail(std::string("libcusolver: missing symbol ") + name)
-  BINDS(Create, "cusolverDnCreate"); BINDS(Destroy, "cusolverDnDestroy"); BINDS(SetStream, "cusolverDnSetStream");
-  BINDS(potrf_bufferSize, "cusolverDnDpotrf_bufferSize"); BINDS(potrf, "cusolverDnDpotrf");
-  BINDS(potri_bufferSize, "cusolverDnDpotri_bufferSize"); BINDS(potri, "cusolverDnDpotri");
-#undef BINDS
-  g_cs.handle = h;
-  return 0;
 }
 
 int mg_smooth(femo_mg* m, int l, bool zero_guess) {
@@ -213,9 +139,7 @@ int mg_vcycle(femo_mg* m, int l) {
   femo_ctx* c = Lv.c;
   const int64_t n = c->ndof;
   if (l == (int)m->L.size() - 1) {
-    k_dense_gemv<<<(unsigned)cdiv(n * 32, 256), 256, 0, c->stream>>>(m->Cinv, Lv.b, n, Lv.x);
-    c->launches += 1;
-    return check_launch(c, "k_dense_gemv");
+    return coarse_apply(c, m->cs, Lv.b, Lv.x);
   }
   MgLevel& Lc = m->L[l + 1];
   TRY(mg_smooth(m, l, true));
@@ -225,10 +149,14 @@ int mg_vcycle(femo_mg* m, int l) {
   k_transfer<<<(unsigned)cdiv(3 * Lv.nbc, 256), 256, 0, c->stream>>>(Lv.R_ptr, Lv.R_col, Lv.R_w, Lv.r, Lc.c->bcmask, Lv.nbc, 0, Lc.b);
   TRY(check_launch(c, "mg restrict"));
   c->launches += 2;
-  // distributed level above a replicated one (dist_multigrid.py): R carries zero weights on ghost rows, so every rank
-  // holds the contribution of the fine nodes it owns; the sum over ranks is the coarse residual, on every rank
-  if (c->world > 1) TRY(dist_allreduce_sum(c, Lc.b, (int)Lc.c->ndof));
+  // distributed fine level (dist_multigrid.py): R carries zero weights on ghost rows, so every rank holds the
+  // contribution of the fine nodes it owns.  Distributed coarse level (nested partition): those contributions land on
+  // owned AND ghost coarse nodes -> reverse halo exchange (owners += ghost copies).  Replicated coarse level: the sum
+  // over ranks is the coarse residual, on every rank.
+  if (Lc.c->world > 1) TRY(halo_accumulate(Lc.c, Lc.b));
+  else if (c->world > 1) TRY(dist_allreduce_sum(c, Lc.b, (int)Lc.c->ndof));
   TRY(mg_vcycle(m, l + 1));
+  if (Lc.c->world > 1) TRY(halo_exchange(Lc.c, Lc.x));      // the prolongation reads ghost coarse nodes
   k_transfer<<<(unsigned)cdiv(3 * Lv.nbf, 256), 256, 0, c->stream>>>(Lv.P_ptr, Lv.P_col, Lv.P_w, Lc.x, c->bcmask, Lv.nbf, 1, Lv.x);
   TRY(check_launch(c, "mg prolong"));
   c->launches += 1;
@@ -274,55 +202,17 @@ int mg_lambda_max(femo_mg* m, int l) {
   return 0;
 }
 
-int dense_inverse_impl(femo_ctx* c, double** Cinv_p, int64_t* n_have) {
-  const int64_t n = c->ndof;
-  if (n > 46000) return femo_fail("dense inverse: operator too large (" + std::to_string(n) + " dofs); add multigrid levels or use the iterative solver");
-  TRY(cusolver_load());
-  if (*n_have != n || !*Cinv_p) { dev_free(Cinv_p); TRY(dev_alloc(Cinv_p, (size_t)n * n)); *n_have = n; }
-  double* Cinv = *Cinv_p;
-  CUDA_TRY(cudaMemsetAsync(Cinv, 0, sizeof(double) * n * n, c->stream));
-  k_dense_fill<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colidx, c->vals, c->bcmask, c->nb, n, Cinv);
-  TRY(check_launch(c, "k_dense_fill"));
-  void* h = nullptr;
-  if (g_cs.Create(&h) != 0) return femo_fail("cusolverDnCreate failed");
-  g_cs.SetStream(h, c->stream);
-  int lw1 = 0, lw2 = 0;
-  const int LOWER = 0;
-  if (g_cs.potrf_bufferSize(h, LOWER, (int)n, Cinv, (int)n, &lw1) != 0) { g_cs.Destroy(h); return femo_fail("potrf_bufferSize failed"); }
-  if (g_cs.potri_bufferSize(h, LOWER, (int)n, Cinv, (int)n, &lw2) != 0) { g_cs.Destroy(h); return femo_fail("potri_bufferSize failed"); }
-  double* work = nullptr; int* info = nullptr;
-  TRY(dev_alloc(&work, (size_t)std::max(lw1, lw2))); TRY(dev_alloc(&info, 2));
-  int r1 = g_cs.potrf(h, LOWER, (int)n, Cinv, (int)n, work, lw1, info);
-  int r2 = g_cs.potri(h, LOWER, (int)n, Cinv, (int)n, work, lw2, info + 1);
-  int hinfo[2] = {0, 0};
-  cudaMemcpyAsync(hinfo, info, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
-  cudaStreamSynchronize(c->stream);
-  g_cs.Destroy(h);
-  dev_free(&work); dev_free(&info);
-  if (r1 != 0 || r2 != 0 || hinfo[0] != 0 || hinfo[1] != 0)
-    return femo_fail("multigrid: dense Cholesky of the coarsest operator failed (not SPD? status " + std::to_string(r1) + "/" +
-                     std::to_string(r2) + ", info " + std::to_string(hinfo[0]) + "/" + std::to_string(hinfo[1]) + ")");
-  k_dense_mirror<<<(unsigned)cdiv(n * n, 256), 256, 0, c->stream>>>(Cinv, n);
-  TRY(check_launch(c, "k_dense_mirror"));
-  c->launches += 2;
-  return 0;
+int mg_coarse_factor(femo_mg* m) {
+  femo_ctx* c = m->L.back().c;
+  if (!m->cs) TRY(coarse_analyse(c, &m->cs));
+  return coarse_factor(c, m->cs);
 }
-
-int mg_coarse_inverse(femo_mg* m) { return dense_inverse_impl(m->L.back().c, &m->Cinv, &m->ncoarse); }
 
 }  // namespace
 
 int mg_num_levels(femo_mg* m) { return m ? (int)m->L.size() : 0; }
 femo_ctx* mg_level_ctx(femo_mg* m, int l) { return m->L[l].c; }
 void mg_invalidate(femo_mg* m) { if (m) m->ready = false; }
-int dense_inverse_build(femo_ctx* c, double** Cinv, int64_t* n_have) { return dense_inverse_impl(c, Cinv, n_have); }
-int dense_inverse_apply(femo_ctx* c, const double* Cinv, const double* b, double* x) {
-  const int64_t n = c->ndof;
-  k_dense_gemv<<<(unsigned)cdiv(n * 32, 256), 256, 0, c->stream>>>(Cinv, b, n, x);
-  c->launches += 1;
-  return check_launch(c, "k_dense_gemv");
-}
-
 extern "C" {
 
 int femo_mg_create(int n_levels, femo_ctx** ctxs, femo_mg** out) {
@@ -332,7 +222,10 @@ int femo_mg_create(int n_levels, femo_ctx** ctxs, femo_mg** out) {
   for (int l = 0; l < n_levels; ++l) {
     if (!ctxs[l] || !ctxs[l]->setup_done) { delete m; return femo_fail("femo_mg_create: level context not set up"); }
     if (ctxs[l]->kind != 0) { delete m; return femo_fail("femo_mg_create: RM-shell contexts only"); }
-    if (l > 0 && ctxs[l]->world > 1) { delete m; return femo_fail("femo_mg_create: only the finest level may be a multi-GPU context; coarser levels are replicated"); }
+    // multi-GPU hierarchies: the finest k levels are distributed (nested partitions, dist_multigrid.py), the rest is
+    // replicated on every rank; the coarsest level is solved directly and must be replicated
+    if (ctxs[l]->world > 1 && l > 0 && ctxs[l - 1]->world <= 1) { delete m; return femo_fail("femo_mg_create: a distributed level below a replicated one"); }
+    if (ctxs[l]->world > 1 && l == n_levels - 1) { delete m; return femo_fail("femo_mg_create: the coarsest level must be replicated (single-GPU context)"); }
     if (ctxs[l]->device != ctxs[0]->device) { delete m; return femo_fail("femo_mg_create: levels must share one device"); }
     m->L[l].c = ctxs[l];
     ctxs[l]->stream = ctxs[0]->stream;
@@ -350,7 +243,7 @@ int femo_mg_destroy(femo_mg* m) {
   if (!m) return 0;
   cudaSetDevice(m->L[0].c->device);
   for (auto& Lv : m->L) mg_free_level(Lv);
-  dev_free(&m->Cinv); dev_free(&m->pr); dev_free(&m->pz); dev_free(&m->pp); dev_free(&m->pAp); dev_free(&m->px); dev_free(&m->pb);
+  coarse_free(m->cs); m->cs = nullptr; dev_free(&m->pr); dev_free(&m->pz); dev_free(&m->pp); dev_free(&m->pAp); dev_free(&m->px); dev_free(&m->pb);
   delete m;
   return 0;
 }
@@ -377,7 +270,7 @@ int femo_mg_set_transfer(femo_mg* m, int l, const int32_t* P_ptr, const int32_t*
 }
 
 // (re)build the preconditioner from the levels' current inputs: assemble every level, block-Jacobi inverses,
-// spectral bounds, dense inverse of the coarsest operator
+// spectral bounds, factorisation of the coarsest operator
 int femo_mg_setup(femo_mg* m, int cheb_degree, int reuse_coarse_inverse) {
   if (!m) return femo_fail("null multigrid handle");
   cudaSetDevice(m->L[0].c->device);
@@ -407,13 +300,13 @@ int femo_mg_setup(femo_mg* m, int cheb_degree, int reuse_coarse_inverse) {
   }
   cudaEventRecord(e2, st);
   // a lagged coarse inverse (from the previous inputs) is still SPD: a valid, slightly weaker preconditioner
-  if (!(reuse_coarse_inverse && m->Cinv && m->ncoarse == m->L.back().c->ndof)) TRY(mg_coarse_inverse(m));
+  if (!(reuse_coarse_inverse && m->cs)) TRY(mg_coarse_factor(m));
   cudaEventRecord(e3, st);
   cudaEventSynchronize(e3);
   if (verbose) {
     float a = 0, b = 0, d = 0;
     cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2); cudaEventElapsedTime(&d, e2, e3);
-    fprintf(stderr, "[femo] mg setup: assemble + block-Jacobi %.1f ms, spectral bounds %.1f ms, coarse inverse (n = %lld) %.1f ms\n",
+    fprintf(stderr, "[femo] mg setup: assemble + block-Jacobi %.1f ms, spectral bounds %.1f ms, coarse factorisation (n = %lld) %.1f ms\n",
             a, b, (long long)m->L.back().c->ndof, d);
   }
   if (!m->pr) {

@@ -1,7 +1,8 @@
 """Host side of the N-rank V-cycle (open item 2): nested partitions of a `refine_quads` hierarchy and the
-rank-local prolongation between two partitioned levels.  NumPy only; the device side (distributed smoothing with the
-existing halo exchange, restriction through `femo_halo_accumulate`, replicated coarse levels) is the next round's work --
-the algorithm is prototyped on these functions in tests/dist_mg_worker.py.
+rank-local prolongation between two partitioned levels (NumPy), and `DistributedHierarchy`, the handle that drives the
+device side (csrc/mg.cu: distributed smoothing with a halo exchange per operator application, restriction through
+`femo_halo_accumulate`, replicated coarse levels below).  The algorithm was prototyped on these functions over gloo
+(tests/dist_mg_worker.py).
 
 Nested partition: a fine cell belongs to the part of its parent.  Then every fine block node owned by a rank lies in an
 owned fine cell whose parent is an owned coarse cell, so its interpolation stencil (the block nodes of that parent) is
@@ -68,24 +69,36 @@ def transfer_arrays(P, row_weight=None):
             np.ascontiguousarray(R.indices, np.int32), np.ascontiguousarray(R.data, np.float64)]
 
 
-class DistributedHierarchy:
-    """V-cycle preconditioned solves on N GPUs: the finest level is a DistributedShell (nested partition), the coarser
-    levels are replicated on every rank (csrc/mg.cu: halo exchange before every operator application of the finest
-    level, one all-reduce of the level-1 residual per V-cycle).  One process per GPU.
+class _AllCells:
+    """Stand-in for the LocalPart of a replicated level (every rank holds every cell; local = global numbering)."""
 
-    NOT YET RUN ON HARDWARE (written after the round-1 GPU budget was spent); the algorithm is the one of
-    tests/dist_mg_worker.py, the transfer arrays are checked on the CPU in tests/test_multigrid_host.py."""
+    def __init__(self, n_cells):
+        self.cell_global = np.arange(n_cells, dtype=np.int64)
+        self.n_global_cells = int(n_cells)
+
+
+class DistributedHierarchy:
+    """V-cycle preconditioned solves on N GPUs, one process per GPU (csrc/mg.cu).
+
+    The finest `n_dist` levels are DistributedShell contexts over NESTED partitions (a fine cell lives on the rank of its
+    parent); the coarser levels are replicated on every rank and the coarsest is solved directly (csrc/coarse.cu).
+    Communication per V-cycle: one halo exchange per operator application of a distributed level, a reverse halo
+    exchange after a restriction between two distributed levels, one all-reduce of the first replicated residual.
+    The preconditioner is the same linear operator as on one GPU: iteration counts do not depend on the rank count
+    (tests/dist_gpu_mg_worker.py)."""
 
     def __init__(self, coarse_nodes, coarse_quads, levels, rank, world, device=0, quadrature_degree=6, cheb_degree=3,
-                 part_coarse=None):
+                 part_coarse=None, n_dist=1):
         import ctypes as C
         from . import _lib as L
         from .dist_shell import DistributedShell
-        from .multigrid import refine_quads
+        from .multigrid import prolongation, refine_quads
         from .partition import partition_cells_rcb
         from .shell_device import ShellDevice
         if levels < 2:
             raise ValueError("a hierarchy needs at least two levels")
+        n_dist = max(1, min(int(n_dist), levels - 1))          # the coarsest level is always replicated
+        self.n_dist, self.rank, self.world = n_dist, int(rank), int(world)
         meshes = [(np.asarray(coarse_nodes, dtype=np.float64), np.asarray(coarse_quads, dtype=np.int32))]
         for _ in range(levels - 1):
             meshes.append(refine_quads(*meshes[-1]))
@@ -94,59 +107,78 @@ class DistributedHierarchy:
             n, q = self.meshes[-1]
             part_coarse = partition_cells_rcb(n[q].mean(axis=1), world)
         self.parts = nested_parts(part_coarse, levels)
-        self.fine = DistributedShell(self.meshes[0][0], self.meshes[0][1], rank, world, part=self.parts[0], device=device,
-                                     quadrature_degree=quadrature_degree)
-        self.coarse = [ShellDevice(n, q, False, False, quadrature_degree, device) for n, q in self.meshes[1:]]
+        self.dist = [DistributedShell(self.meshes[l][0], self.meshes[l][1], rank, world, part=self.parts[l], device=device,
+                                      quadrature_degree=quadrature_degree) for l in range(n_dist)]
+        self.fine = self.dist[0]
+        self.coarse = [ShellDevice(n, q, False, False, quadrature_degree, device) for n, q in self.meshes[n_dist:]]
+        self.devs = [d.dev for d in self.dist] + self.coarse       # one device handle per level
         self.lib, self._L, self._C = L.load(), L, C
-        ctxs = [self.fine.dev._ctx] + [d._ctx for d in self.coarse]
         self._mg = C.c_void_p()
-        L.check(self.lib.femo_mg_create(levels, (C.c_void_p * levels)(*ctxs), C.byref(self._mg)))
         self._keep = []
-        lp_all = replicated_part(*self.meshes[1])
-        P0 = local_prolongation(self.fine.lp, lp_all, self.fine.dev.cell_blocks(), self.coarse[0].cell_blocks())
-        self._set_transfer(0, P0, self.fine.lp.own_block_mask.astype(np.float64))
-        from .multigrid import prolongation as _prolongation
-        for l in range(1, levels - 1):
-            f, c = self.coarse[l - 1], self.coarse[l]
-            self._set_transfer(l, _prolongation(f.cell_blocks(), c.cell_blocks(), f.nb, c.nb), None)
+        self._transfers = []
+        for l in range(levels - 1):
+            f, c = self.devs[l], self.devs[l + 1]
+            if l < n_dist:
+                lp_c = self.dist[l + 1].lp if l + 1 < n_dist else _AllCells(self.meshes[l + 1][1].shape[0])
+                P = local_prolongation(self.dist[l].lp, lp_c, f.cell_blocks(), c.cell_blocks())
+                self._transfers.append((P, self.dist[l].lp.own_block_mask.astype(np.float64)))
+            else:
+                self._transfers.append((prolongation(f.cell_blocks(), c.cell_blocks(), f.nb, c.nb), None))
         self.cheb_degree = int(cheb_degree)
         self._dirty = True
+        self._comm = False
         self.last_solve = dict(iters=0, relres=0.0)
 
-    def _set_transfer(self, level, P, row_weight):
-        a = transfer_arrays(P, row_weight)
-        self._keep.append(a)
-        self._L.check(self.lib.femo_mg_set_transfer(self._mg, level, *[self._L.ptr(v) for v in a]))
+    def _create(self):
+        L, C = self._L, self._C
+        levels = len(self.devs)
+        ctxs = [d._ctx for d in self.devs]
+        L.check(self.lib.femo_mg_create(levels, (C.c_void_p * levels)(*ctxs), C.byref(self._mg)))
+        for l, (P, w) in enumerate(self._transfers):
+            a = transfer_arrays(P, w)
+            self._keep.append(a)
+            L.check(self.lib.femo_mg_set_transfer(self._mg, l, *[L.ptr(v) for v in a]))
+        self._transfers = None
 
     def init_comm(self, dist=None):
+        """Collective: one NCCL communicator (finest level), shared by the other distributed levels."""
         self.fine.init_comm(dist)
+        for d in self.dist[1:]:
+            self._L.check(self.lib.femo_dist_share_comm(d.dev._ctx, self.fine.dev._ctx))
+        self._comm = True
 
     def set_input(self, name, global_values):
         """global nodal arrays of the FINEST mesh (mesh order); parents keep their vertex numbers under refine_quads, so
         the coarser levels take the leading entries"""
         v = np.asarray(global_values, dtype=np.float64)
-        self.fine.set_input(name, v)
-        for d, (nodes, _) in zip(self.coarse, self.meshes[1:]):
+        for l, (nodes, _) in enumerate(self.meshes):
             if v.size == 1:
-                d.set_input(name, v.ravel())
+                vl = v.ravel()
             else:
                 k = v.size // self.meshes[0][0].shape[0]
-                d.set_input(name, np.ascontiguousarray(v.reshape(-1, k)[:nodes.shape[0]]).ravel())
+                vl = np.ascontiguousarray(v.reshape(-1, k)[:nodes.shape[0]]).ravel()
+            (self.dist[l] if l < self.n_dist else self.coarse[l - self.n_dist]).set_input(name, vl)
         self._dirty = True
 
     def set_strong_bc(self, predicate):
-        self.fine.set_strong_bc(predicate)
+        for d in self.dist:
+            d.set_strong_bc(predicate)
         for d in self.coarse:
             blocks = np.nonzero(np.asarray(predicate(d.block_coords().T)).astype(bool))[0]
             d.set_strong_bc(np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel()))
         self._dirty = True
 
-    def setup(self):
-        self._L.check(self.lib.femo_mg_setup(self._mg, self.cheb_degree, 0))
+    def setup(self, reuse_coarse=False):
+        if self.world > 1 and not self._comm:
+            raise RuntimeError("DistributedHierarchy: call init_comm() first")
+        if not self._mg.value:
+            self._create()
+        self._L.check(self.lib.femo_mg_setup(self._mg, self.cheb_degree, int(bool(reuse_coarse))))
         self._dirty = False
 
     def solve(self, rhs_local, rtol=1e-10, max_it=2000, zero_bc=True):
-        """A x = rhs on the finest level; rhs and x in this rank's local block order (collective)."""
+        """A x = rhs on the finest level; rhs and x in this rank's local block order (collective).  Owned entries of
+        rhs must be complete (assemble_load / output_grad of an owner-computes context are); ghost entries are ignored."""
         if self._dirty:
             self.setup()
         C, L = self._C, self._L
@@ -155,7 +187,7 @@ class DistributedHierarchy:
         it = C.c_int(0); rr = C.c_double(0.0)
         L.check(self.lib.femo_mg_solve(self._mg, L.ptr(rhs), L.ptr(out), float(rtol), int(max_it), C.byref(it), C.byref(rr), 0,
                                        int(bool(zero_bc))))
-        self.last_solve = dict(iters=it.value, relres=rr.value)
+        self.last_solve = dict(iters=it.value, relres=rr.value, device_ms=self.fine.dev.last_timings()["solve_ms"])
         return out
 
     def solve_state(self, rtol=1e-10, max_it=2000):
@@ -163,13 +195,18 @@ class DistributedHierarchy:
         self.fine.dev.set_state(u)
         return self.last_solve["iters"], self.last_solve["relres"]
 
+    def solve_adjoint(self, rhs_local, rtol=1e-10, max_it=2000):
+        """A^T lam = rhs, lam[bc] = 0 (state_operation.py:188-220; A is symmetric)"""
+        return self.solve(rhs_local, rtol, max_it, zero_bc=True)
+
     def close(self):
         if getattr(self, "_mg", None) is not None and self._mg.value:
             self.lib.femo_mg_destroy(self._mg)
             self._mg = self._C.c_void_p()
-        for d in [getattr(self, "fine", None)] + list(getattr(self, "coarse", [])):
+        for d in list(getattr(self, "dist", []))[::-1] + list(getattr(self, "coarse", [])):
             if d is not None:
                 d.close()
+        self.dist, self.coarse = [], []
 
     def __del__(self):
         try:

@@ -36,6 +36,7 @@ class ShellDevice:
         self.n_mat, self.n_f = s.n_material, s.n_force
         self.last_solve = dict(iters=0, relres=0.0)
         self._mg = None                 # ShellHierarchy this device is the finest level of (multigrid.py)
+        self._direct = None             # dict(refine=..) when solves go through the sparse direct solver (csrc/coarse.cu)
         self._children = []             # weak references to handles that borrow this context (DynamicShellDevice)
         self._owner = None              # ShellHierarchy this device is a level of: it tears down in order (handles, mg, levels)
 
@@ -166,9 +167,42 @@ class ShellDevice:
         return sp.bsr_matrix((vals, colidx, rowptr), shape=(self.ndof, self.ndof)).tocsr()
 
     # ---- solves -------------------------------------------------------------------------
+    def enable_direct(self, refine=2):
+        """Route solve_state / solve_adjoint / solve_forward through the sparse direct solver (csrc/coarse.cu: what MUMPS
+        is to the reference, fea/utils_dolfinx.py:465-466,514-531).  Runs the symbolic analysis now and raises if the
+        factor would not fit (FEMO_DIRECT_MAX_GB); `refine` steps of iterative refinement per solve."""
+        self._direct = dict(refine=int(refine))
+        try:
+            L.check(self.lib.femo_direct_setup(self._ctx))
+        except Exception:
+            self._direct = None
+            raise
+        return self.direct_info()
+
+    def disable_direct(self):
+        self._direct = None
+
+    def direct_info(self):
+        v = (C.c_double * 4)()
+        L.check(self.lib.femo_direct_info(self._ctx, v))
+        return dict(level_sets=int(v[0]), max_front_dofs=int(v[1]), factor_bytes=float(v[2]), explicit_inverse=bool(v[3]))
+
+    def solve_direct(self, rhs, refine=2, zero_bc=True):
+        """A x = rhs by the direct solver (factorises first if the inputs or BCs changed)."""
+        rhs = np.ascontiguousarray(rhs, dtype=np.float64)
+        L.check(self.lib.femo_direct_setup(self._ctx))
+        out = np.empty(self.ndof)
+        rr = C.c_double(0.0)
+        L.check(self.lib.femo_direct_solve(self._ctx, L.ptr(rhs), L.ptr(out), int(refine), C.byref(rr), 0, int(bool(zero_bc))))
+        self.last_solve = dict(iters=1 + int(refine), relres=rr.value, solver="direct")
+        return out
+
     def solve_state(self, rtol=1e-12, max_it=200000):
         if self._mg is not None:          # nested mesh hierarchy available: V-cycle preconditioned PCG (csrc/mg.cu)
             return self._mg.solve_state(rtol, min(max_it, 5000))
+        if self._direct is not None:
+            self.set_state(self.solve_direct(self.assemble_load(), self._direct["refine"], zero_bc=True))
+            return self.last_solve["iters"], self.last_solve["relres"]
         it = C.c_int(0); rr = C.c_double(0.0)
         L.check(self.lib.femo_solve_state(self._ctx, float(rtol), int(max_it), C.byref(it), C.byref(rr)))
         self.last_solve = dict(iters=it.value, relres=rr.value)
@@ -180,6 +214,8 @@ class ShellDevice:
             out = self._mg.solve(rhs, rtol, min(max_it, 5000), zero_bc=(fn is self.lib.femo_solve_adjoint))
             self.last_solve = dict(self._mg.last_solve)
             return out
+        if self._direct is not None:
+            return self.solve_direct(rhs, self._direct["refine"], zero_bc=(fn is self.lib.femo_solve_adjoint))
         out = np.empty(self.ndof)
         it = C.c_int(0); rr = C.c_double(0.0)
         L.check(fn(self._ctx, L.ptr(rhs), L.ptr(out), float(rtol), int(max_it), C.byref(it), C.byref(rr), 0))

@@ -165,6 +165,9 @@ int femo_dist_setup(femo_ctx* ctx, int rank, int world, int n_nbr, const int32_t
                     const int32_t* recv_blocks, const uint8_t* own_block, int64_t n_owned_cells);
 /* collective: ncclCommInitRank with the broadcast id */
 int femo_dist_init(femo_ctx* ctx, const void* id128);
+/* use the communicator of `owner` (same rank / world) instead of creating one: the distributed levels of a multigrid
+ * hierarchy share the communicator of the finest level.  `owner` must outlive the solves on ctx. */
+int femo_dist_share_comm(femo_ctx* ctx, femo_ctx* owner);
 /* ghost entries of x (n_dof) <- owners' values; collective */
 int femo_halo_exchange(femo_ctx* ctx, double* x, int on_device);
 /* reverse exchange: owned entries of x += the values their ghost copies hold on the other ranks (ghost entries are
@@ -179,7 +182,10 @@ int femo_dist_counts(femo_ctx* ctx, int64_t* halo_exchanges, int64_t* allreduces
  * Replaces the sparse LU (MUMPS through PETSc `preonly + lu`, femo_alpha/fea/utils_dolfinx.py:438-468 setUpKSP /
  * NewtonSolver and :514-531 setUpKSP_MUMPS; fea_dolfinx.py:159-203 FEA.solve / solveLinearBwd) on meshes that come
  * with a hierarchy of uniformly refined quad meshes: level 0 = the mesh of the analysis, level l+1 = its parent.
- * Every level is an ordinary context (same inputs sampled on its own nodes, same BC predicate). */
+ * Every level is an ordinary context (same inputs sampled on its own nodes, same BC predicate).
+ * N GPUs: the finest k levels may be multi-GPU contexts (femo_dist_setup with NESTED partitions: a fine cell lives on the
+ * rank of its parent), the coarser ones are replicated; smoothing exchanges halos per level, restriction between two
+ * distributed levels ends in a reverse halo exchange, into a replicated level in one all-reduce. */
 typedef struct femo_mg femo_mg;
 int femo_mg_create(int n_levels, femo_ctx** level_ctxs, femo_mg** out);
 int femo_mg_destroy(femo_mg* mg);
@@ -188,8 +194,8 @@ int femo_mg_destroy(femo_mg* mg);
 int femo_mg_set_transfer(femo_mg* mg, int level, const int32_t* P_rowptr, const int32_t* P_col, const double* P_w,
                          const int32_t* R_rowptr, const int32_t* R_col, const double* R_w);
 /* (re)build after the inputs changed: assembles every level, block-Jacobi inverses, spectral bounds of the
- * Chebyshev smoother (degree cheb_degree, default 3), dense inverse of the coarsest operator.
- * reuse_coarse_inverse != 0 keeps the coarse inverse of the previous set-up (lagged: still SPD, cheaper set-up
+ * Chebyshev smoother (degree cheb_degree, default 3), direct factorisation of the coarsest operator (femo_direct_*).
+ * reuse_coarse_inverse != 0 keeps the coarse factor of the previous set-up (lagged: still SPD, cheaper set-up
  * inside an optimisation loop with small steps, a few more iterations) */
 int femo_mg_setup(femo_mg* mg, int cheb_degree, int reuse_coarse_inverse);
 int femo_mg_get_lambda(femo_mg* mg, int level, double* lambda_max);
@@ -197,13 +203,28 @@ int femo_mg_get_lambda(femo_mg* mg, int level, double* lambda_max);
 int femo_mg_solve(femo_mg* mg, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
                   int on_device, int zero_bc);
 
+/* ---- sparse direct solver -----------------------------------------------------------------------------------
+ * The reference solves EVERY system with a sparse LU (MUMPS: fea/utils_dolfinx.py:465-466 NewtonSolver "preonly + lu",
+ * :514-531 setUpKSP_MUMPS).  Here: breadth-first level sets of the block-node graph make A block tridiagonal; block
+ * LDL^T with explicit inverses of the Schur complements (hand-written blocked Cholesky + GEMM kernels, no library), a
+ * solve = two sweeps of small matrix-vector kernels (or one product with the explicit inverse up to 8192 dofs).  Used
+ * for the coarsest multigrid level, for the dense stepper of femo_dyn_*, and directly for meshes without a hierarchy
+ * whose fronts fit in memory (the reference's wing box: 32 226 dofs, 71 fronts of <= 843 dofs, 0.4 GB).
+ * Single-GPU contexts.  femo_direct_setup: symbolic analysis on first use + numeric factorisation of the CURRENT
+ * operator (call again after inputs / BCs change).  femo_direct_solve: A x = rhs (clamped entries of rhs ignored) with
+ * `refine` steps of iterative refinement on the fp64 residual; relres = |rhs - A x| / |rhs| of the returned x.
+ * femo_direct_info: [level sets, largest front (dofs), bytes of the factor, 1 if the explicit inverse is used]. */
+int femo_direct_setup(femo_ctx* ctx);
+int femo_direct_solve(femo_ctx* ctx, const double* rhs, double* sol, int refine, double* relres, int on_device, int zero_bc);
+int femo_direct_info(femo_ctx* ctx, double* info4);
+
 /* ---- dynamic (time-stepped) RM shell: SURVEY 8 f1, BASELINE config 4 ------------------------------------------
  * Replaces femo_alpha/dynamic_rm_shell: PlateSim.solve_dynamic_problem (plate_sim.py:281-361), the residual
  * M wddot + K w_mid - F - W of PlateSim.SVK_residual (:190-215) under the implicit midpoint rule (:135-140), and the
  * forward / reverse sweeps of StateOperation.apply_inverse_jacobian and .compute_jacvec_product
  * (state_operation_dynamic.py:140-432,447-702).  The reference assembles and LU-factorises the (step-invariant)
  * Jacobian in every step and keeps N^2 work vectors in the reverse sweep; here A_eff = (2/dt^2) M + K/2 is assembled
- * once (dense inverse up to 46 000 dofs, else block-Jacobi PCG or V-cycle PCG on the levels of an attached
+ * once (direct factorisation up to 46 000 dofs, else block-Jacobi PCG or V-cycle PCG on the levels of an attached
  * multigrid), every step is one K product, one M product and one solve, the whole state history stays in HBM
  * ((n_steps+1) x n_dof doubles, level-major like utils.py:9-16) and the reverse sweep is the two-field (w, wdot)
  * recurrence with O(1) work vectors.  Mass form: linear_shell_model.py:335-348, 4x4 Gauss rule; density = the
