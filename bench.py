@@ -167,7 +167,7 @@ def mg_solve_metric(n, device):
     while n % (2 ** levels) == 0 and n // (2 ** levels) >= 8:
         levels += 1
     base = n // 2 ** (levels - 1)
-    if levels < 2 or 3 * ((2 * base + 1) ** 2 + (base + 1) ** 2) > 46000:
+    if levels < 2:
         return None
     nodes, quads = plate(base, base, 0.0, 10.0, 10.0)
     t0 = time.perf_counter()
@@ -188,14 +188,75 @@ def mg_solve_metric(n, device):
     t0 = time.perf_counter(); h.setup(reuse_coarse=True); t_setup2 = time.perf_counter() - t0
     t0 = time.perf_counter(); it_l, rr_l = h.solve_state(rtol=1e-10); t_state2 = time.perf_counter() - t0
     out = dict(levels=levels, coarse_cells="%dx%d" % (base, base), n_dof=int(h.fine.ndof), smoother="Chebyshev(3) of block-Jacobi",
-               coarsest="dense inverse (cuSOLVER potrf+potri), %d dof" % h.levels[-1].ndof, rtol=1e-10,
+               coarsest="direct (block-tridiagonal LDL^T on level sets, in-tree kernels), %d dof" % h.levels[-1].ndof, rtol=1e-10,
                state_iters=int(it_s), state_relres=float(rr_s), state_s=t_state, state_device_ms=dev_state_ms,
                adjoint_iters=int(adj["iters"]), adjoint_relres=float(adj["relres"]), adjoint_s=t_adj,
                setup_s=t_setup, hierarchy_build_s=t_build,
                state_plus_adjoint_s_per_opt_iteration=t_setup + t_state + t_adj,
                lagged_coarse=dict(setup_s=t_setup2, state_iters=int(it_l), state_relres=float(rr_l), state_s=t_state2,
-                                  note="thickness changed by 5 %, coarse inverse of the previous iterate reused"),
-               note="setup = assemble all levels + smoother bounds + coarse inverse, redone when the inputs change")
+                                  note="thickness changed by 5 %, coarse factor of the previous iterate reused"),
+               note="setup = assemble all levels + smoother bounds + coarse factorisation, redone when the inputs change")
+    h.close()
+    return out
+
+
+def mg_solve_metric_dist(n, rank, world, local_rank, dist, strong):
+    """Metric 2 on N GPUs: V-cycle PCG state + adjoint solve to relres 1e-10 with the finest levels distributed over
+    nested x-strip partitions and the coarsest level (51 cells across) replicated and solved directly
+    (femo_alpha_b200/dist_multigrid.py, csrc/mg.cu, csrc/coarse.cu).  Weak: (n*world) x n plate; strong: the n x n plate."""
+    import torch
+    from femo_alpha_b200.dist_multigrid import DistributedHierarchy
+    levels = 1
+    while n % (2 ** levels) == 0 and n // (2 ** levels) >= 8:
+        levels += 1
+    base = n // 2 ** (levels - 1)
+    if levels < 2:
+        return None
+    bx = base if strong else base * world
+    nodes, quads = plate(bx, base, 0.0, 10.0 * (1 if strong else world), 10.0)
+    ix = np.arange(quads.shape[0]) // base                      # plate() numbers cells x-major
+    part_c = ((ix * world) // bx).astype(np.int32)               # x-strips of whole coarse columns
+
+    def timed(fn):
+        dist.barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = fn()
+        torch.cuda.synchronize()
+        t = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return out, float(t.item())
+
+    h, t_build = timed(lambda: DistributedHierarchy(nodes, quads, levels, rank, world, device=local_rank, part_coarse=part_c,
+                                                    n_dist=levels - 1))
+    h.init_comm(dist)
+    xf = h.meshes[0][0]
+    nn = xf.shape[0]
+    lx = 10.0
+    h.set_input("thickness", 0.1 * (1 + 0.5 * np.sin(2 * np.pi * xf[:, 0] / lx) * np.cos(2 * np.pi * xf[:, 1] / 10)))
+    h.set_input("E", np.full(nn, 1e8)); h.set_input("nu", np.full(nn, 0.3)); h.set_input("density", np.full(nn, 10.0))
+    h.set_input("F_solid", np.tile([0.0, 0.0, 5.0], nn))
+    h.set_strong_bc(lambda x: x[0] < 3e-16)
+    _, t_setup = timed(h.setup)
+    hx0, ar0 = h.fine.comm_counts()
+    (it_s, rr_s), t_state = timed(lambda: h.solve_state(rtol=1e-10))
+    dev_state_ms = h.last_solve["device_ms"]
+    hx1, ar1 = h.fine.comm_counts()
+    rhs = h.fine.dev.output_grad("compliance", "disp_solid")
+    _, t_adj = timed(lambda: h.solve_adjoint(rhs, rtol=1e-10))
+    adj = dict(h.last_solve)
+    C = h.fine.output("compliance")
+    tt = torch.tensor([h.fine.ndof_owned], device="cuda", dtype=torch.float64)
+    dist.all_reduce(tt)
+    out = dict(levels=levels, distributed_levels=h.n_dist, coarse_cells="%dx%d" % (bx, base), n_dof=int(tt.item()),
+               smoother="Chebyshev(3) of block-Jacobi", coarsest="direct (block-tridiagonal LDL^T on level sets), %d dof, replicated"
+               % h.coarse[-1].ndof, rtol=1e-10, state_iters=int(it_s), state_relres=float(rr_s), state_s=t_state,
+               state_device_ms=dev_state_ms, adjoint_iters=int(adj["iters"]), adjoint_relres=float(adj["relres"]),
+               adjoint_s=t_adj, setup_s=t_setup, hierarchy_build_s=t_build, compliance=float(C),
+               state_plus_adjoint_s_per_opt_iteration=t_setup + t_state + t_adj,
+               ms_per_vcycle_iteration=dev_state_ms / max(int(it_s), 1),
+               finest_level_comm_per_iteration=dict(halo_exchanges=(hx1 - hx0) / max(int(it_s), 1),
+                                                    allreduces=(ar1 - ar0) / max(int(it_s), 1)),
+               partition="nested x-strips; times = max over ranks (host clock around synchronised calls)")
     h.close()
     return out
 
@@ -233,13 +294,15 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n = args.n
+    strong = args.scaling == "strong" and world > 1
     if world > 1:
-        # one global (n*world) x n plate on [0, 10 world] x [0, 10], RCB -> x-strips of n x n cells per GPU
-        # (weak scaling); owner-computes assembly with one ghost-cell layer, NCCL halo + all-reduce in the solves
+        # weak (default): one global (n*world) x n plate on [0, 10 world] x [0, 10] in x-strips of n x n cells per GPU;
+        # strong: the ONE n x n plate of config 3 cut into `world` x-strips.  Owner-computes assembly with one
+        # ghost-cell layer, NCCL halo + all-reduce in the solves
         from femo_alpha_b200.dist_shell import DistributedShell
-        from femo_alpha_b200.partition import partition_cells_rcb
-        nodes, quads = plate(n * world, n, 0.0, 10.0 * world, 10.0)
-        part = (np.arange(quads.shape[0]) // (n * n)).astype(np.int32)     # plate() numbers cells x-major
+        nx = n if strong else n * world
+        nodes, quads = plate(nx, n, 0.0, 10.0 * (nx // n), 10.0)
+        part = (((np.arange(quads.shape[0]) // n) * world) // nx).astype(np.int32)     # plate() numbers cells x-major
         ds = DistributedShell(nodes, quads, rank, world, part=part, device=local_rank)
         ds.init_comm(dist)
         d = ds.dev
@@ -339,10 +402,16 @@ def run_ours(args, rank, world, local_rank):
 
     mg = None
     dyn = solid = None
-    if world == 1 and not args.no_mg:
-        mg = mg_solve_metric(n, local_rank)
-        dyn = dynamic_metric()
-        solid = solid_metric()
+    if not args.no_mg:
+        if world == 1:
+            mg = mg_solve_metric(n, local_rank)
+            dyn = dynamic_metric()
+            solid = solid_metric()
+        else:
+            try:
+                mg = mg_solve_metric_dist(n, rank, world, local_rank, dist, strong)
+            except Exception as e:                  # reported, never hidden (every rank raises or none does: collective calls)
+                mg = {"error": "%s: %s" % (type(e).__name__, e)}
 
     if rank != 0:
         if world > 1:
@@ -366,7 +435,7 @@ def run_ours(args, rank, world, local_rank):
     out = {
         "metric": "rm_shell_jacobian_assembly_throughput", "value": ndof_total / (ms * 1e-3) / 1e9, "unit": "GDOF/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "rm_shell_plate_%dx%d_q2q1_cfg3" % (n, n), "cells_per_gpu": int(d.nc),
                    "dof_per_gpu": int(d.ndof), "dof_total": int(ndof_total), "nnz_per_gpu": int(d.nnzb * 9), "quadrature": "4x4 Gauss",
                    "l2_policy": "working set (%.1f GB written per step) >> 126 MB L2" % (d.nnzb * 72 / 1e9),
@@ -404,6 +473,9 @@ def main():
     ap.add_argument("--n", type=int, default=816, help="cells per side of the (per-GPU) plate")
     ap.add_argument("--no-mg", action="store_true", help="skip the multigrid state+adjoint solve metric")
     ap.add_argument("--krylov-iters", type=int, default=100)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = n x n cells per GPU (default, what the driver's scaling run uses); "
+                         "strong = the one n x n plate split over the GPUs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

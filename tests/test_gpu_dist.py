@@ -64,13 +64,14 @@ def test_reverse_halo_exchange(built_lib, n):
     assert r.returncode == 0
 
 
-@pytest.mark.parametrize("n", [2, 3])
-def test_distributed_vcycle(built_lib, n):
-    """V-cycle preconditioned state solve with a distributed finest level (tests/dist_gpu_mg_worker.py)"""
+@pytest.mark.parametrize("n,n_dist", [(2, 1), (2, 3), (3, 2), (4, 3)])
+def test_distributed_vcycle(built_lib, n, n_dist):
+    """V-cycle preconditioned state + adjoint solves with `n_dist` distributed levels over replicated coarser ones
+    (tests/dist_gpu_mg_worker.py): parity with the oracle, iteration count of the single-GPU hierarchy."""
     if _ngpu() < n:
         pytest.skip("needs %d GPUs" % n)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr",
-           "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "tests", "dist_gpu_mg_worker.py")]
+           "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "tests", "dist_gpu_mg_worker.py"), str(n_dist)]
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     sys.stdout.write(r.stdout[-3000:]); sys.stderr.write(r.stderr[-3000:])
     assert r.returncode == 0
