@@ -470,7 +470,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=816, help="cells per side of the (per-GPU) plate")
+    ap.add_argument("--n", "--cells", dest="n", type=int, default=816,
+                    help="cells per side of the (per-GPU) plate (--cells: the spelling torch.distributed.run passes through)")
     ap.add_argument("--no-mg", action="store_true", help="skip the multigrid state+adjoint solve metric")
     ap.add_argument("--krylov-iters", type=int, default=100)
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],

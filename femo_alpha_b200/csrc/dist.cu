@@ -14,6 +14,8 @@
 #include <nccl.h>
 #include <cstdlib>
 #include <cstring>
+#include <string>
+#include <vector>
 #include "femo_internal.cuh"
 
 namespace {
@@ -72,6 +74,18 @@ __global__ void k_halo_unpack(double* __restrict__ x, const int32_t* __restrict_
   x[3 * (int64_t)blocks[b] + k] = buf[i];
 }
 
+// flag[I] = 2 ghost row, 1 owned row with at least one ghost column (boundary), 0 owned row without (interior)
+__global__ void k_classify_rows(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const double* __restrict__ own,
+                                int64_t nb, uint8_t* __restrict__ flag) {
+  const int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= nb) return;
+  if (own[I] == 0.0) { flag[I] = 2; return; }
+  uint8_t f = 0;
+  for (int32_t k = rowptr[I]; k < rowptr[I + 1]; ++k)
+    if (own[colidx[k]] == 0.0) { f = 1; break; }
+  flag[I] = f;
+}
+
 __global__ void k_halo_unpack_add(double* __restrict__ x, const int32_t* __restrict__ blocks, int64_t n,
                                   const double* __restrict__ buf) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -83,8 +97,7 @@ __global__ void k_halo_unpack_add(double* __restrict__ x, const int32_t* __restr
 // one grouped send / receive with every neighbour (3 doubles per listed block).  The group is ALWAYS closed: an error
 // between GroupStart and GroupEnd would otherwise leave later NCCL calls of this thread queued into an open group.
 int neighbour_exchange(femo_ctx* c, ncclComm_t comm, double* out_buf, const std::vector<int>& out_off, double* in_buf,
-                       const std::vector<int>& in_off, cudaStream_t stream = nullptr) {
-  cudaStream_t st = stream ? stream : c->stream;
+                       const std::vector<int>& in_off, cudaStream_t st) {
   NCCL_TRY(g_nccl.GroupStart());
   ncclResult_t first = ncclSuccess;
   for (int i = 0; i < c->n_nbr && first == ncclSuccess; ++i) {
@@ -107,21 +120,43 @@ struct DevGuard2 {
 
 }  // namespace
 
-int halo_exchange(femo_ctx* c, double* x) {
-  if (c->world <= 1) return 0;
+static int halo_exchange_on(femo_ctx* c, double* x, cudaStream_t st) {
   if (!c->nccl_comm) return femo_fail("halo_exchange: communicator not initialised (femo_dist_init)");
   ncclComm_t comm = (ncclComm_t)c->nccl_comm;
   if (c->n_send > 0) {
-    k_halo_pack<<<(unsigned)cdiv(3 * c->n_send, 256), 256, 0, c->stream>>>(x, c->send_blocks, c->n_send, c->send_buf);
+    k_halo_pack<<<(unsigned)cdiv(3 * c->n_send, 256), 256, 0, st>>>(x, c->send_blocks, c->n_send, c->send_buf);
     c->launches += 1;
   }
-  TRY(neighbour_exchange(c, comm, c->send_buf, c->send_off, c->recv_buf, c->recv_off));
+  TRY(neighbour_exchange(c, comm, c->send_buf, c->send_off, c->recv_buf, c->recv_off, st));
   if (c->n_recv > 0) {
-    k_halo_unpack<<<(unsigned)cdiv(3 * c->n_recv, 256), 256, 0, c->stream>>>(x, c->recv_blocks, c->n_recv, c->recv_buf);
+    k_halo_unpack<<<(unsigned)cdiv(3 * c->n_recv, 256), 256, 0, st>>>(x, c->recv_blocks, c->n_recv, c->recv_buf);
     c->launches += 1;
   }
   c->halo_count += 1;
   return check_launch(c, "halo exchange");
+}
+
+int halo_exchange(femo_ctx* c, double* x) {
+  if (c->world <= 1) return 0;
+  return halo_exchange_on(c, x, c->stream);
+}
+
+// split form: the exchange runs on the communication stream once everything queued on the context's stream so far is
+// done; halo_exchange_end makes the context's stream wait for the unpack.  Work launched in between must not touch the
+// ghost entries of x (interior rows of an SpMV do not).
+int halo_exchange_begin(femo_ctx* c, double* x) {
+  if (c->world <= 1) return 0;
+  if (!c->comm_stream) return femo_fail("halo_exchange_begin: no communication stream (femo_dist_setup)");
+  CUDA_TRY(cudaEventRecord(c->ev_ready, c->stream));
+  CUDA_TRY(cudaStreamWaitEvent(c->comm_stream, c->ev_ready, 0));
+  TRY(halo_exchange_on(c, x, c->comm_stream));
+  CUDA_TRY(cudaEventRecord(c->ev_halo, c->comm_stream));
+  return 0;
+}
+int halo_exchange_end(femo_ctx* c) {
+  if (c->world <= 1) return 0;
+  CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+  return 0;
 }
 
 // Reverse halo exchange: owners += the values their ghosts hold on the other ranks (restriction of the N-rank V-cycle,
@@ -136,7 +171,7 @@ int halo_accumulate(femo_ctx* c, double* x) {
     k_halo_pack<<<(unsigned)cdiv(3 * c->n_recv, 256), 256, 0, c->stream>>>(x, c->recv_blocks, c->n_recv, c->recv_buf);
     c->launches += 1;
   }
-  TRY(neighbour_exchange(c, comm, c->recv_buf, c->recv_off, c->send_buf, c->send_off));
+  TRY(neighbour_exchange(c, comm, c->recv_buf, c->recv_off, c->send_buf, c->send_off, c->stream));
   for (int i = 0; i < c->n_nbr; ++i) {
     const int ns = c->send_off[i + 1] - c->send_off[i];
     if (ns == 0) continue;
@@ -167,6 +202,10 @@ int dist_allreduce_host(femo_ctx* c, double* hv, int n) {
 }
 
 void dist_free(femo_ctx* c) {
+  dev_free(&c->rows_int); dev_free(&c->rows_bnd);
+  if (c->comm_stream) { cudaStreamDestroy(c->comm_stream); c->comm_stream = nullptr; }
+  if (c->ev_ready) { cudaEventDestroy(c->ev_ready); c->ev_ready = nullptr; }
+  if (c->ev_halo) { cudaEventDestroy(c->ev_halo); c->ev_halo = nullptr; }
   if (c->nccl_comm && c->comm_owner && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->nccl_comm);
   c->nccl_comm = nullptr;
   dev_free(&c->send_blocks); dev_free(&c->recv_blocks); dev_free(&c->send_buf); dev_free(&c->recv_buf); dev_free(&c->own);
@@ -209,6 +248,29 @@ int femo_dist_setup(femo_ctx* c, int rank, int world, int n_nbr, const int32_t* 
   TRY(dev_alloc(&c->own, (size_t)c->nb));
   CUDA_TRY(cudaMemcpy(c->own, own.data(), sizeof(double) * c->nb, cudaMemcpyHostToDevice));
   c->prec_valid = false;
+  // interior / boundary row lists and the communication stream of the overlapped SpMV (FEMO_HALO_OVERLAP=0: off)
+  dev_free(&c->rows_int); dev_free(&c->rows_bnd);
+  c->n_rows_int = c->n_rows_bnd = 0;
+  const char* env = getenv("FEMO_HALO_OVERLAP");
+  if (world > 1 && !(env && env[0] == '0')) {
+    uint8_t* flag = nullptr;
+    TRY(dev_alloc(&flag, (size_t)c->nb));
+    k_classify_rows<<<(unsigned)cdiv(c->nb, 256), 256, 0, c->stream>>>(c->rowptr, c->colidx, c->own, c->nb, flag);
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    std::vector<uint8_t> hf((size_t)c->nb);
+    cudaError_t e = cudaMemcpy(hf.data(), flag, (size_t)c->nb, cudaMemcpyDeviceToHost);
+    dev_free(&flag);
+    if (e != cudaSuccess) return femo_fail(std::string("femo_dist_setup: row classification failed: ") + cudaGetErrorString(e));
+    std::vector<int32_t> ri, rb;
+    for (int64_t i = 0; i < c->nb; ++i) { if (hf[i] == 0) ri.push_back((int32_t)i); else if (hf[i] == 1) rb.push_back((int32_t)i); }
+    c->n_rows_int = (int64_t)ri.size(); c->n_rows_bnd = (int64_t)rb.size();
+    TRY(dev_alloc(&c->rows_int, ri.size())); TRY(dev_alloc(&c->rows_bnd, rb.size()));
+    if (!ri.empty()) CUDA_TRY(cudaMemcpy(c->rows_int, ri.data(), sizeof(int32_t) * ri.size(), cudaMemcpyHostToDevice));
+    if (!rb.empty()) CUDA_TRY(cudaMemcpy(c->rows_bnd, rb.data(), sizeof(int32_t) * rb.size(), cudaMemcpyHostToDevice));
+    if (!c->comm_stream) CUDA_TRY(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+    if (!c->ev_ready) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_ready, cudaEventDisableTiming));
+    if (!c->ev_halo) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+  }
   return 0;
 }
 

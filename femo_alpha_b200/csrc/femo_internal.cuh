@@ -161,6 +161,12 @@ struct femo_ctx {
   double* own = nullptr;        // nb: 1 = block node owned by this rank, 0 = ghost (null when world == 1)
   int64_t nc_owned = 0;         // owned cells come first in the local cell order
   int64_t halo_count = 0, allreduce_count = 0;
+  // halo / SpMV overlap: owned block rows without (interior) and with (boundary) a ghost column; the exchange runs on
+  // its own stream between two events
+  int32_t *rows_int = nullptr, *rows_bnd = nullptr;
+  int64_t n_rows_int = 0, n_rows_bnd = 0;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_ready = nullptr, ev_halo = nullptr;
   // solver state
   double *w = nullptr, *b = nullptr, *r = nullptr, *z = nullptr, *p = nullptr, *Ap = nullptr, *tmp = nullptr;
   double *tmp2 = nullptr;
@@ -245,6 +251,9 @@ int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out);   // out
 int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out);      // outputs.cu
 int measure_peaks(femo_ctx* c, double* tf, double* gbs);                  // solver.cu
 int halo_exchange(femo_ctx* c, double* x);                                // dist.cu: ghost entries <- owners
+int halo_exchange_begin(femo_ctx* c, double* x);                          // dist.cu: the same on the communication stream ...
+int halo_exchange_end(femo_ctx* c);                                       // ... the context's stream waits for it here
+int dist_spmv(femo_ctx* c, double* x, double* y, double* dot_int, double* dot_bnd, int* n_int, int* n_bnd);   // solver.cu
 int halo_accumulate(femo_ctx* c, double* x);                              // dist.cu: owners += ghost copies (reverse halo)
 int dist_allreduce_sum(femo_ctx* c, double* dev_vals, int n);             // dist.cu: in-place on the stream
 int dist_allreduce_host(femo_ctx* c, double* host_vals, int n);           // dist.cu

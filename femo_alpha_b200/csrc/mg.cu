@@ -24,6 +24,7 @@ struct MgLevel {
   double *P_w = nullptr, *R_w = nullptr;
   double lmax = 0;
   double *x = nullptr, *b = nullptr, *r = nullptr, *d = nullptr, *t = nullptr;
+  double *ev = nullptr;        // last iterate of the power iteration (warm start of the next set-up)
 };
 
 struct femo_mg {
@@ -92,7 +93,10 @@ __global__ void k_transfer(const int32_t* __restrict__ ptr, const int32_t* __res
   if (t >= 3 * nrows) return;
   const int64_t i = t / 3; const int cmp = (int)(t - 3 * i);
   double s = 0;
-  for (int32_t k = ptr[i]; k < ptr[i + 1]; ++k) s += w[k] * x[3 * (int64_t)col[k] + cmp];
+  for (int32_t k = ptr[i]; k < ptr[i + 1]; ++k) {
+    const double wk = w[k];
+    if (wk != 0.0) s += wk * x[3 * (int64_t)col[k] + cmp];      // zero weights: ghost rows of a distributed fine level
+  }
   s *= mask[t];
   y[t] = add ? y[t] + s : s;
 }
@@ -100,6 +104,12 @@ __global__ void k_transfer(const int32_t* __restrict__ ptr, const int32_t* __res
 __global__ void k_mg_mask(int64_t n, const double* __restrict__ mask, double* __restrict__ x) {
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) x[i] *= mask[i];
+}
+
+// y = A x of a level; on a distributed level the ghosts of x are refreshed first (overlapped with the interior rows)
+int mg_spmv(femo_ctx* c, double* x, double* y) {
+  if (c->world > 1) return dist_spmv(c, x, y, nullptr, nullptr, nullptr, nullptr);
+  return bsr_spmv(c, x, y, 1);
 }
 
 int mg_smooth(femo_mg* m, int l, bool zero_guess) {
@@ -115,14 +125,12 @@ int mg_smooth(femo_mg* m, int l, bool zero_guess) {
         k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, nullptr, 0.0, 0.0, 1.0 / theta, 1, c->dinv6, c->dinv3, c->nn, c->nq2,
                                                  Lv.r, Lv.d, Lv.x);
       } else {
-        if (c->world > 1) TRY(halo_exchange(c, Lv.x));      // distributed finest level: ghosts of the operand follow their owners
-        TRY(bsr_spmv(c, Lv.x, Lv.t, 1));
+        TRY(mg_spmv(c, Lv.x, Lv.t));                        // distributed level: halo exchange hidden behind the interior rows
         k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, Lv.t, 1.0, 0.0, 1.0 / theta, 0, c->dinv6, c->dinv3, c->nn, c->nq2,
                                                  Lv.r, Lv.d, Lv.x);
       }
     } else {
-      if (c->world > 1) TRY(halo_exchange(c, Lv.d));
-      TRY(bsr_spmv(c, Lv.d, Lv.t, 1));
+      TRY(mg_spmv(c, Lv.d, Lv.t));
       const double rho_new = 1.0 / (2.0 * sigma - rho);
       k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.r, Lv.t, 1.0, rho_new * rho, 2.0 * rho_new / delta, 0, c->dinv6, c->dinv3,
                                                c->nn, c->nq2, Lv.r, Lv.d, Lv.x);
@@ -143,8 +151,7 @@ int mg_vcycle(femo_mg* m, int l) {
   }
   MgLevel& Lc = m->L[l + 1];
   TRY(mg_smooth(m, l, true));
-  if (c->world > 1) TRY(halo_exchange(c, Lv.x));
-  TRY(bsr_spmv(c, Lv.x, Lv.t, 1));
+  TRY(mg_spmv(c, Lv.x, Lv.t));
   k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, Lv.b, -1.0, Lv.t, Lv.r);
   k_transfer<<<(unsigned)cdiv(3 * Lv.nbc, 256), 256, 0, c->stream>>>(Lv.R_ptr, Lv.R_col, Lv.R_w, Lv.r, Lc.c->bcmask, Lv.nbc, 0, Lc.b);
   TRY(check_launch(c, "mg restrict"));
@@ -176,28 +183,36 @@ __global__ void k_mg_seed(const double* __restrict__ xyz, const int32_t* __restr
   for (int k = 0; k < 3; ++k) v[3 * I + k] = sin(ph + 1.7 * k + 0.11) + 0.5 * cos(3.1 * ph - 0.9 * k);
 }
 
-// largest eigenvalue of D^-1 A by power iteration: at least 8 steps, until two successive estimates agree to 1 %, at most 60
+// largest eigenvalue of D^-1 A by power iteration.  First set-up: from the position-seeded vector, at least 8 steps, until
+// two successive estimates agree to 1 %, at most 24.  Later set-ups (new inputs, same mesh) restart from the previous
+// iterate kept in Lv.ev and need 2 - 6 steps: the dominant eigenvector hardly moves between optimisation iterates.
 int mg_lambda_max(femo_mg* m, int l) {
   MgLevel& Lv = m->L[l];
   femo_ctx* c = Lv.c;
   const int64_t n = c->ndof;
-  k_mg_seed<<<(unsigned)cdiv(c->nb, 256), 256, 0, c->stream>>>(c->xyz, c->edges, c->cv, c->nn, c->ne, c->nc, Lv.x);
+  const bool warm = Lv.ev != nullptr;
+  if (!warm) {
+    TRY(dev_alloc(&Lv.ev, (size_t)n));
+    k_mg_seed<<<(unsigned)cdiv(c->nb, 256), 256, 0, c->stream>>>(c->xyz, c->edges, c->cv, c->nn, c->ne, c->nc, Lv.ev);
+    TRY(check_launch(c, "k_mg_seed"));
+  }
+  CUDA_TRY(cudaMemcpyAsync(Lv.x, Lv.ev, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
   k_mg_mask<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, c->bcmask, Lv.x);
-  TRY(check_launch(c, "k_mg_seed"));
   double lam = 1.0, lam_prev = 0.0;
-  for (int it = 0; it < 60; ++it) {
+  const int min_it = warm ? 2 : 8, max_it = warm ? 6 : 24;
+  for (int it = 0; it <= max_it; ++it) {
     double nrm2 = 0;
     TRY(dev_dot(c, Lv.x, Lv.x, n, &nrm2));
     if (!(nrm2 > 0)) return femo_fail("multigrid: zero vector in the power iteration");
     if (it > 0) { lam_prev = lam; lam = sqrt(nrm2); }
-    if (it >= 8 && fabs(lam - lam_prev) <= 1e-2 * lam) break;
+    if (it == max_it || (it >= min_it && fabs(lam - lam_prev) <= 1e-2 * lam)) break;
     k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0 / sqrt(nrm2), Lv.x, 0.0, Lv.x, Lv.b);
-    if (c->world > 1) TRY(halo_exchange(c, Lv.b));
-    TRY(bsr_spmv(c, Lv.b, Lv.t, 1));
+    TRY(mg_spmv(c, Lv.b, Lv.t));
     k_cheb_step<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(Lv.t, nullptr, 0.0, 0.0, 1.0, 1, c->dinv6, c->dinv3, c->nn,
                                                                     c->nq2, Lv.r, Lv.d, Lv.x);
     TRY(check_launch(c, "mg power iteration"));
   }
+  CUDA_TRY(cudaMemcpyAsync(Lv.ev, Lv.b, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));   // last normalised iterate
   Lv.lmax = lam;
   return 0;
 }
@@ -236,7 +251,7 @@ int femo_mg_create(int n_levels, femo_ctx** ctxs, femo_mg** out) {
 
 static void mg_free_level(MgLevel& Lv) {
   dev_free(&Lv.P_ptr); dev_free(&Lv.P_col); dev_free(&Lv.P_w); dev_free(&Lv.R_ptr); dev_free(&Lv.R_col); dev_free(&Lv.R_w);
-  dev_free(&Lv.x); dev_free(&Lv.b); dev_free(&Lv.r); dev_free(&Lv.d); dev_free(&Lv.t);
+  dev_free(&Lv.x); dev_free(&Lv.b); dev_free(&Lv.r); dev_free(&Lv.d); dev_free(&Lv.t); dev_free(&Lv.ev);
 }
 
 int femo_mg_destroy(femo_mg* m) {
@@ -295,7 +310,12 @@ int femo_mg_setup(femo_mg* m, int cheb_degree, int reuse_coarse_inverse) {
     femo_ctx* c = Lv.c;
     if (l + 1 < m->L.size() && !Lv.P_ptr) return femo_fail("femo_mg_setup: transfer operators missing");
     const size_t n = (size_t)c->ndof;
-    if (!Lv.x) { TRY(dev_alloc(&Lv.x, n)); TRY(dev_alloc(&Lv.b, n)); TRY(dev_alloc(&Lv.r, n)); TRY(dev_alloc(&Lv.d, n)); TRY(dev_alloc(&Lv.t, n)); }
+    if (!Lv.x) {
+      // zero-initialised: on a distributed level the ghost rows of an operator product are never written (dist_spmv),
+      // and the ownership-weighted restriction multiplies those entries by zero -- they must stay finite
+      double** vs[] = {&Lv.x, &Lv.b, &Lv.r, &Lv.d, &Lv.t};
+      for (double** v : vs) { TRY(dev_alloc(v, n)); CUDA_TRY(cudaMemsetAsync(*v, 0, sizeof(double) * n, c->stream)); }
+    }
     if (l + 1 < m->L.size()) TRY(mg_lambda_max(m, (int)l));
   }
   cudaEventRecord(e2, st);
@@ -311,8 +331,8 @@ int femo_mg_setup(femo_mg* m, int cheb_degree, int reuse_coarse_inverse) {
   }
   if (!m->pr) {
     const size_t n = (size_t)m->L[0].c->ndof;
-    TRY(dev_alloc(&m->pr, n)); TRY(dev_alloc(&m->pz, n)); TRY(dev_alloc(&m->pp, n)); TRY(dev_alloc(&m->pAp, n));
-    TRY(dev_alloc(&m->px, n)); TRY(dev_alloc(&m->pb, n));
+    double** vs[] = {&m->pr, &m->pz, &m->pp, &m->pAp, &m->px, &m->pb};
+    for (double** v : vs) { TRY(dev_alloc(v, n)); CUDA_TRY(cudaMemsetAsync(*v, 0, sizeof(double) * n, m->L[0].c->stream)); }
   }
   m->ready = true;
   return 0;
@@ -358,8 +378,7 @@ int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int m
       if (it == 0) CUDA_TRY(cudaMemcpyAsync(m->pp, L0.x, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
       else k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, L0.x, rz_new / rz, m->pp, m->pp);
       rz = rz_new;
-      if (c->world > 1) TRY(halo_exchange(c, m->pp));
-      TRY(bsr_spmv(c, m->pp, m->pAp, 1));
+      TRY(mg_spmv(c, m->pp, m->pAp));
       double pAp = 0;
       TRY(dev_dot(c, m->pp, m->pAp, n, &pAp));
       if (!(pAp > 0)) return femo_fail("femo_mg_solve: operator is not positive definite");

@@ -7,6 +7,9 @@
 //
 // All reductions are two-stage with fixed grids and fixed summation order -> bitwise
 // reproducible iterations (no floating-point atomics anywhere).
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
 #include "femo_internal.cuh"
 
 #define RED_BLOCKS 1184          /* 148 SMs x 8 */
@@ -67,7 +70,7 @@ template <int LANES, int MINB>
 __global__ void __launch_bounds__(256, MINB)
 k_spmv(const int32_t* __restrict__ rowptr, const uint32_t* __restrict__ colw, const double* __restrict__ vals,
        const double* __restrict__ x, const uint8_t* __restrict__ rbits, int64_t nb, double* __restrict__ y,
-       double* __restrict__ dot_part, const double* __restrict__ own) {
+       double* __restrict__ dot_part, const double* __restrict__ own, const int32_t* __restrict__ rows) {
   const int lane = threadIdx.x % LANES;
   constexpr int GPW = 32 / LANES;                       // row groups per warp
   const int sub = (threadIdx.x & 31) / LANES;
@@ -76,8 +79,9 @@ k_spmv(const int32_t* __restrict__ rowptr, const uint32_t* __restrict__ colw, co
   double dacc = 0.0;
   // warp-uniform trip count: every lane takes part in the full-mask shuffles below
   for (int64_t rb = warp * GPW; rb < nb; rb += nwarp * GPW) {
-    const int64_t row = rb + sub;
-    const bool valid = row < nb;
+    // `rows` (multi-GPU): the nb listed block rows (interior or boundary rows of the owned part); null: rows 0 .. nb-1
+    const bool valid = rb + sub < nb;
+    const int64_t row = rows ? (valid ? (int64_t)rows[rb + sub] : 0) : rb + sub;
     const int32_t s = valid ? rowptr[row] : 0, e = valid ? rowptr[row + 1] : 0;
     double y0 = 0, y1 = 0, y2 = 0;
     for (int32_t k = s + lane; k < e; k += LANES) {
@@ -315,6 +319,63 @@ __global__ void k_sum_partials(const double* __restrict__ part, int n, double* _
   if (threadIdx.x == 0) *out = v;
 }
 
+// ---- single-reduction PCG (Chronopoulos & Gear) for multi-GPU contexts ----------------------------------------------------
+// With u = M^-1 r, w = A u, gamma = (r, u), delta = (w, u):  beta = gamma / gamma_old,
+// alpha = gamma / (delta - beta gamma / alpha_old),  p = u + beta p,  s = w + beta s,  x += alpha p,  r -= alpha s.
+// Both inner products are available right after the SpMV, so ONE all-reduce per iteration carries (gamma, delta, r.r).
+// S = (gamma, delta, rr) all-reduced; Oin = (gamma_old, alpha_old) of the previous iteration, Oout receives this one's.
+__global__ void __launch_bounds__(RED_THREADS)
+k_cg_update(const double* __restrict__ S, const double* __restrict__ Oin, double* __restrict__ Oout, int first,
+            const double* __restrict__ own, const double* __restrict__ w, const double* __restrict__ dinv6,
+            const double* __restrict__ dinv3, int64_t nn, int64_t nq2, double* __restrict__ u, double* __restrict__ p,
+            double* __restrict__ s, double* __restrict__ x, double* __restrict__ r, double* __restrict__ part_ru,
+            double* __restrict__ part_rr) {
+  const double gamma = S[0], delta = S[1];
+  double beta = 0.0, alpha;
+  if (first || Oin[0] == 0.0 || Oin[1] == 0.0) alpha = (delta != 0.0) ? gamma / delta : 0.0;
+  else {
+    beta = gamma / Oin[0];
+    const double den = delta - beta * gamma / Oin[1];
+    alpha = (den != 0.0) ? gamma / den : 0.0;
+  }
+  const bool use_old = beta != 0.0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) { Oout[0] = gamma; Oout[1] = alpha; }
+  double ru = 0, rr = 0, dummy = 0;
+  for (int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; I < nq2; I += gridDim.x * (int64_t)blockDim.x) {
+    const int nd = I < nn ? 6 : 3;
+    const double ow = own ? own[I] : 1.0;
+    double rl[6], zl[6];
+    for (int i = 0; i < nd; ++i) {
+      const int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+      const double pn = use_old ? u[d] + beta * p[d] : u[d];
+      const double sn = use_old ? w[d] + beta * s[d] : w[d];
+      p[d] = pn; s[d] = sn;
+      x[d] += alpha * pn;
+      rl[i] = r[d] - alpha * sn;
+    }
+    precond_node(I, nn, nq2, dinv6, dinv3, rl, zl);
+    for (int i = 0; i < nd; ++i) {
+      const int64_t d = (i < 3) ? 3 * I + i : 3 * (nq2 + I) + (i - 3);
+      r[d] = rl[i]; u[d] = zl[i];
+      ru += ow * rl[i] * zl[i]; rr += ow * rl[i] * rl[i];
+    }
+  }
+  block_sum3(ru, rr, dummy);
+  if (threadIdx.x == 0) { part_ru[blockIdx.x] = ru; part_rr[blockIdx.x] = rr; }
+}
+
+// CTA 0: out[0] = sum part_ru; CTA 1: out[1] = sum dot_int + sum dot_bnd; CTA 2: out[2] = sum part_rr; CTA 3: out[3] = sum part_bb
+__global__ void k_cg_sum(const double* __restrict__ part_ru, const double* __restrict__ part_rr, const double* __restrict__ part_bb,
+                         int n_red, const double* __restrict__ dot_int, int n_int, const double* __restrict__ dot_bnd, int n_bnd,
+                         double* __restrict__ out) {
+  double v;
+  if (blockIdx.x == 0) v = sum_partials(part_ru, n_red);
+  else if (blockIdx.x == 1) { v = sum_partials(dot_int, n_int); if (n_bnd > 0) v += sum_partials(dot_bnd, n_bnd); }
+  else if (blockIdx.x == 2) v = sum_partials(part_rr, n_red);
+  else v = sum_partials(part_bb, n_red);
+  if (threadIdx.x == 0) out[blockIdx.x] = v;
+}
+
 // ---- roofline denominators -------------------------------------------------------------
 __global__ void k_fma_peak(double* out, int iters) {
   double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -352,8 +413,42 @@ static int spmv_grid() { return 148 * 6; }
 static int launch_spmv(femo_ctx* c, const double* x, bool with_bc, double* y, double* dot_part, const double* own) {
   const uint32_t* colw = with_bc ? c->colbc : reinterpret_cast<const uint32_t*>(c->colidx);
   const uint8_t* rbits = with_bc ? c->bcbits : nullptr;
-  k_spmv<8, 6><<<spmv_grid(), 256, 0, c->stream>>>(c->rowptr, colw, c->vals, x, rbits, c->nb, y, dot_part, own);
+  k_spmv<8, 6><<<spmv_grid(), 256, 0, c->stream>>>(c->rowptr, colw, c->vals, x, rbits, c->nb, y, dot_part, own, nullptr);
   return 0;
+}
+// the listed rows only (A with BCs); grid sized to the list (boundary lists are short)
+static int launch_spmv_rows(femo_ctx* c, const double* x, double* y, const int32_t* rows, int64_t nrows, double* dot_part, int* grid_out) {
+  int grid = (int)std::min<int64_t>(spmv_grid(), std::max<int64_t>(1, cdiv(nrows, 32)));     // 32 block rows per CTA and pass
+  if (grid_out) *grid_out = grid;
+  if (nrows > 0 || dot_part)
+    k_spmv<8, 6><<<grid, 256, 0, c->stream>>>(c->rowptr, c->colbc, c->vals, x, c->bcbits, nrows, y, dot_part, c->own, rows);
+  return 0;
+}
+
+// y = A x on a multi-GPU context: the halo exchange of x (pack -> ncclSend/Recv -> unpack on the context's communication
+// stream) runs while the interior rows -- owned rows without a ghost column -- are multiplied; the boundary rows follow
+// once the ghosts have arrived.  Ghost rows are not computed (their y entries are never used: every consumer is
+// owner-masked).  dot_int / dot_bnd (optional): per-CTA partials of the owner-masked x.y of the two launches; the
+// numbers of partials written are returned in n_int / n_bnd.
+int dist_spmv(femo_ctx* c, double* x, double* y, double* dot_int, double* dot_bnd, int* n_int, int* n_bnd) {
+  if (!c->jac_valid) return femo_fail("Jacobian not assembled");
+  if (c->world <= 1 || !c->rows_int) {     // single GPU, or no row split (overlap switched off): exchange, then all rows
+    if (c->world > 1) TRY(halo_exchange(c, x));
+    TRY(launch_spmv(c, x, true, y, dot_int, c->world > 1 ? c->own : nullptr));
+    if (n_int) *n_int = spmv_grid();
+    if (n_bnd) *n_bnd = 0;
+    c->launches += 1;
+    return check_launch(c, "k_spmv");
+  }
+  TRY(halo_exchange_begin(c, x));
+  int g0 = 0, g1 = 0;
+  TRY(launch_spmv_rows(c, x, y, c->rows_int, c->n_rows_int, dot_int, &g0));
+  TRY(halo_exchange_end(c));
+  TRY(launch_spmv_rows(c, x, y, c->rows_bnd, c->n_rows_bnd, dot_bnd, &g1));
+  if (n_int) *n_int = g0;
+  if (n_bnd) *n_bnd = g1;
+  c->launches += 2;
+  return check_launch(c, "k_spmv (interior / boundary rows)");
 }
 int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc) {
   if (!c->jac_valid) return femo_fail("Jacobian not assembled");
@@ -367,7 +462,7 @@ int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc) {
 int bsr_spmv_vals(femo_ctx* c, const double* vals, const double* x, double* y, int with_bc) {
   const uint32_t* colw = with_bc ? c->colbc : reinterpret_cast<const uint32_t*>(c->colidx);
   const uint8_t* rbits = with_bc ? c->bcbits : nullptr;
-  k_spmv<8, 6><<<spmv_grid(), 256, 0, c->stream>>>(c->rowptr, colw, vals, x, rbits, c->nb, y, nullptr, nullptr);
+  k_spmv<8, 6><<<spmv_grid(), 256, 0, c->stream>>>(c->rowptr, colw, vals, x, rbits, c->nb, y, nullptr, nullptr, nullptr);
   TRY(check_launch(c, "k_spmv"));
   c->launches += 1;
   return 0;
@@ -416,6 +511,72 @@ int dev_dot_async(femo_ctx* c, const double* a, const double* b, int64_t n, doub
   return 0;
 }
 
+// Multi-GPU PCG: Chronopoulos-Gear recurrences (one all-reduce of three doubles per iteration) over the overlapped SpMV
+// (halo exchange hidden behind the interior rows).  Per iteration: k_cg_update, [pack, send/recv, unpack || interior
+// rows], boundary rows, k_cg_sum, ncclAllReduce.  FEMO_PCG_CLASSIC=1 selects the two-reduction loop of round 1.
+static int pcg_solve_dist(femo_ctx* c, const double* b, double* x, double rtol, int max_it, int* iters, double* relres,
+                          bool fixed_iters) {
+  double* D_int = c->red;
+  double* D_bnd = c->red + 5 * SPMV_BLOCKS;
+  double* P_ru = c->red + 1 * SPMV_BLOCKS;
+  double* P_rr = c->red + 3 * SPMV_BLOCKS;
+  double* P_bb = c->red + 4 * SPMV_BLOCKS;
+  double* S = c->scal + 0;                       // gamma, delta, rr, bb
+  double* O[2] = {c->scal + 24, c->scal + 26};   // (gamma_old, alpha_old) ping-pong
+  double* u = c->z; double* w = c->Ap; double* p = c->p; double* sv = c->tmp;
+  const int64_t n = c->ndof;
+  cudaEventRecord(c->ev0, c->stream);
+  int nI = 0, nB = 0;
+  TRY(dist_spmv(c, x, c->Ap, nullptr, nullptr, nullptr, nullptr));                 // r0 = b - A x0
+  k_pcg_init<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(b, c->Ap, c->dinv6, c->dinv3, c->nn, c->nq2, c->r, u, p, P_ru, P_rr, P_bb, c->own);
+  TRY(dist_spmv(c, u, w, D_int, D_bnd, &nI, &nB));
+  k_cg_sum<<<4, RED_THREADS, 0, c->stream>>>(P_ru, P_rr, P_bb, RED_BLOCKS, D_int, nI, D_bnd, nB, S);
+  TRY(check_launch(c, "pcg init"));
+  c->launches += 2;
+  TRY(dist_allreduce_sum(c, S, 4));
+  double hs[4];
+  CUDA_TRY(cudaMemcpyAsync(hs, S, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  const double bb = hs[3];
+  double rr = hs[2];
+  const double bnorm = sqrt(bb);
+  int it = 0;
+  double rel = bnorm > 0 ? sqrt(rr) / bnorm : 0.0;
+  if (bnorm == 0.0 && !fixed_iters) {
+    CUDA_TRY(cudaMemsetAsync(x, 0, sizeof(double) * n, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    *iters = 0; *relres = 0.0; c->t_solve = 0; c->t_iter = 0;
+    return 0;
+  }
+  const int check_every = 25;
+  bool done = (!fixed_iters && rel <= rtol);
+  while (!done && it < max_it) {
+    const int nloop = std::min(check_every, max_it - it);
+    for (int k = 0; k < nloop; ++k, ++it) {
+      k_cg_update<<<RED_BLOCKS, RED_THREADS, 0, c->stream>>>(S, O[it & 1], O[(it + 1) & 1], it == 0 ? 1 : 0, c->own, w, c->dinv6,
+                                                             c->dinv3, c->nn, c->nq2, u, p, sv, x, c->r, P_ru, P_rr);
+      TRY(dist_spmv(c, u, w, D_int, D_bnd, &nI, &nB));
+      k_cg_sum<<<3, RED_THREADS, 0, c->stream>>>(P_ru, P_rr, P_bb, RED_BLOCKS, D_int, nI, D_bnd, nB, S);
+      TRY(dist_allreduce_sum(c, S, 3));
+    }
+    c->launches += 2 * (int64_t)nloop;
+    TRY(check_launch(c, "pcg iteration"));
+    CUDA_TRY(cudaMemcpyAsync(&rr, S + 2, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    rel = sqrt(rr) / bnorm;
+    if (!(rel == rel)) return femo_fail("pcg: NaN residual (matrix not SPD?)");
+    if (!fixed_iters && rel <= rtol) done = true;
+  }
+  TRY(halo_exchange(c, x));                  // ghost entries of the solution follow their owners
+  cudaEventRecord(c->ev1, c->stream);
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  c->t_solve = ms; c->t_iter = it > 0 ? ms / it : 0.0;
+  *iters = it; *relres = rel;
+  return 0;
+}
+
 // red layout: [0]=pAp partials (SPMV_BLOCKS) | [1],[2] = rz ping-pong | [3] = rr | [4] = bb | [5] spare | [6] dot
 // scal layout: [0]=bb [1]=rr (host reads) [2]=pAp | [10..11],[12..13] = (rz, rr) ping-pong pairs (multi-GPU)
 //
@@ -428,6 +589,10 @@ int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, 
   if (!c->prec_valid) TRY(precond_setup(c));
   const bool dist = c->world > 1;
   if (dist && !c->nccl_comm) return femo_fail("pcg: multi-GPU context without communicator (femo_dist_init)");
+  if (dist) {
+    const char* env = getenv("FEMO_PCG_CLASSIC");
+    if (!(env && env[0] == '1')) return pcg_solve_dist(c, b, x, rtol, max_it, iters, relres, fixed_iters);
+  }
   double* P_pAp = c->red;
   double* P_rz[2] = {c->red + 1 * SPMV_BLOCKS, c->red + 2 * SPMV_BLOCKS};
   double* P_rr = c->red + 3 * SPMV_BLOCKS;
