@@ -57,6 +57,7 @@ SIGNATURES = {
     "femo_assemble_load": [_P, _P, C.c_int],
     "femo_jacobian_apply": [_P, _P, _P, C.c_int, C.c_int],
     "femo_get_bsr": [_P, _P, _P, _P, C.c_int],
+    "femo_get_blocks": [_P, C.c_int64, _P, _P],
     "femo_solve_state": [_P, C.c_double, C.c_int, C.POINTER(C.c_int), _D],
     "femo_solve_adjoint": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int), _D, C.c_int],
     "femo_solve_forward": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int), _D, C.c_int],

@@ -41,6 +41,10 @@ __global__ void k_col_bc(const int32_t* __restrict__ colidx, const uint8_t* __re
   int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (k < nnzb) { const uint32_t col = (uint32_t)colidx[k]; colbc[k] = col | ((uint32_t)bits[col] << 29); }
 }
+__global__ void k_pick_blocks(const double* __restrict__ vals, const int64_t* __restrict__ pos, int64_t n, double* __restrict__ out) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t < 9 * n) out[t] = vals[pos[t / 9] * 9 + t % 9];
+}
 __global__ void k_mul(const double* a, const double* m, int64_t n, double* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) out[i] = a[i] * m[i];
@@ -414,6 +418,29 @@ int femo_get_bsr(femo_ctx* c, int32_t* rowptr, int32_t* colidx, double* vals, in
     }
   }
   return 0;
+}
+
+// selected 3x3 blocks of dR/du by BSR position (diagnostics at sizes where femo_get_bsr would move gigabytes)
+int femo_get_blocks(femo_ctx* c, int64_t n, const int64_t* positions, double* out) {
+  NEED_SETUP(c, "femo_get_blocks");
+  if (n < 0 || (n > 0 && (!positions || !out))) return femo_fail("femo_get_blocks: bad arguments");
+  for (int64_t i = 0; i < n; ++i)
+    if (positions[i] < 0 || positions[i] >= c->nnzb) return femo_fail("femo_get_blocks: block position out of range");
+  DevGuard g(c->device);
+  if (!c->jac_valid) TRY(assemble_jacobian(c));
+  if (n == 0) return 0;
+  int64_t* dp = nullptr; double* dv = nullptr;
+  int r = dev_alloc(&dp, (size_t)n);
+  if (r == 0) r = dev_alloc(&dv, (size_t)9 * n);
+  if (r == 0 && cudaMemcpyAsync(dp, positions, sizeof(int64_t) * n, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) r = femo_fail("femo_get_blocks: copy failed");
+  if (r == 0) {
+    k_pick_blocks<<<(unsigned)cdiv(9 * n, 256), 256, 0, c->stream>>>(c->vals, dp, n, dv);
+    c->launches += 1;
+    r = check_launch(c, "k_pick_blocks");
+  }
+  if (r == 0) r = copy_out(c, out, dv, 9 * n, 0);
+  dev_free(&dp); dev_free(&dv);
+  return r;
 }
 
 int femo_solve_state(femo_ctx* c, double rtol, int max_it, int* iters, double* relres) {

@@ -11,6 +11,7 @@
 //   transfer       nested Q2xQ1 spaces: P = coarse basis evaluated at the fine nodes (block-scalar CSR, rows = fine
 //                  block nodes), R = P^T stored as its own CSR so that both directions are gathers (no atomics)
 //   coarsest       direct solve: block-tridiagonal factorisation on level sets (coarse.cu; no library)
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -25,6 +26,7 @@ struct MgLevel {
   double lmax = 0;
   double *x = nullptr, *b = nullptr, *r = nullptr, *d = nullptr, *t = nullptr;
   double *ev = nullptr;        // last iterate of the power iteration (warm start of the next set-up)
+  int power_its = 0;
 };
 
 struct femo_mg {
@@ -200,8 +202,10 @@ int mg_lambda_max(femo_mg* m, int l) {
   k_mg_mask<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, c->bcmask, Lv.x);
   double lam = 1.0, lam_prev = 0.0;
   const int min_it = warm ? 2 : 8, max_it = warm ? 6 : 24;
+  int its_done = 0;
   for (int it = 0; it <= max_it; ++it) {
     double nrm2 = 0;
+    its_done = it;
     TRY(dev_dot(c, Lv.x, Lv.x, n, &nrm2));
     if (!(nrm2 > 0)) return femo_fail("multigrid: zero vector in the power iteration");
     if (it > 0) { lam_prev = lam; lam = sqrt(nrm2); }
@@ -214,6 +218,7 @@ int mg_lambda_max(femo_mg* m, int l) {
   }
   CUDA_TRY(cudaMemcpyAsync(Lv.ev, Lv.b, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));   // last normalised iterate
   Lv.lmax = lam;
+  Lv.power_its = its_done;
   return 0;
 }
 
@@ -316,7 +321,16 @@ int femo_mg_setup(femo_mg* m, int cheb_degree, int reuse_coarse_inverse) {
       double** vs[] = {&Lv.x, &Lv.b, &Lv.r, &Lv.d, &Lv.t};
       for (double** v : vs) { TRY(dev_alloc(v, n)); CUDA_TRY(cudaMemsetAsync(*v, 0, sizeof(double) * n, c->stream)); }
     }
-    if (l + 1 < m->L.size()) TRY(mg_lambda_max(m, (int)l));
+    if (l + 1 < m->L.size()) {
+      cudaStreamSynchronize(st);
+      const auto t0 = std::chrono::steady_clock::now();
+      TRY(mg_lambda_max(m, (int)l));
+      cudaStreamSynchronize(st);
+      if (verbose)
+        fprintf(stderr, "[femo] mg level %zu (%lld dofs%s): lambda_max %.4f after %d power iterations, %.1f ms\n", l, (long long)c->ndof,
+                c->world > 1 ? ", distributed" : "", Lv.lmax, Lv.power_its,
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    }
   }
   cudaEventRecord(e2, st);
   // a lagged coarse inverse (from the previous inputs) is still SPD: a valid, slightly weaker preconditioner

@@ -200,7 +200,7 @@ class ShellDevice:
     def solve_state(self, rtol=1e-12, max_it=200000):
         if self._mg is not None:          # nested mesh hierarchy available: V-cycle preconditioned PCG (csrc/mg.cu)
             return self._mg.solve_state(rtol, min(max_it, 5000))
-        if self._direct is not None:
+        if getattr(self, "_direct", None) is not None:
             self.set_state(self.solve_direct(self.assemble_load(), self._direct["refine"], zero_bc=True))
             return self.last_solve["iters"], self.last_solve["relres"]
         it = C.c_int(0); rr = C.c_double(0.0)
@@ -214,7 +214,7 @@ class ShellDevice:
             out = self._mg.solve(rhs, rtol, min(max_it, 5000), zero_bc=(fn is self.lib.femo_solve_adjoint))
             self.last_solve = dict(self._mg.last_solve)
             return out
-        if self._direct is not None:
+        if getattr(self, "_direct", None) is not None:
             return self.solve_direct(rhs, self._direct["refine"], zero_bc=(fn is self.lib.femo_solve_adjoint))
         out = np.empty(self.ndof)
         it = C.c_int(0); rr = C.c_double(0.0)

@@ -110,6 +110,9 @@ int femo_jacobian_apply(femo_ctx* ctx, const double* x, double* y, int with_bc, 
 /* diagnostic/test: copy the BSR structure+values to host.  rowptr (nb+1) int32, colidx (nnzb) int32,
  * vals (nnzb,3,3) fp64; any pointer may be NULL.  with_bc applies the dolfinx BC convention. */
 int femo_get_bsr(femo_ctx* ctx, int32_t* rowptr, int32_t* colidx, double* vals, int with_bc);
+/* selected 3x3 blocks of dR/du (row-major, no BCs) by their BSR positions: out (n, 9).  Diagnostics / tests at sizes where
+ * femo_get_bsr would move gigabytes (the reference's getValuesCSR on a sub-matrix, fea/utils_dolfinx.py:34-50 callers) */
+int femo_get_blocks(femo_ctx* ctx, int64_t n, const int64_t* positions, double* out);
 
 /* ---- solves ---------------------------------------------------------------------- */
 /* replaces FEA.solve -> solveNonlinear -> NewtonSolver (fea/fea_dolfinx.py:159-170,

@@ -230,3 +230,77 @@ def test_tiled_assembly_many_chunks(built_lib, monkeypatch, shape, ws):
         assert abs(Kd - K).max() <= 1e-12 * abs(K).max()
         assert abs(Kd - Kd.T).max() <= 1e-14 * abs(K).max()
         d.close()
+
+
+def test_jacobian_at_benchmark_size_matches_oracle_strip(built_lib):
+    """Parity at the size bench.py runs (config 3: 816 x 816 cells, 10 002 534 dofs, 81.9 M blocks; every persistent CTA of
+    the tiled kernel walks ~281 chunks, int32 positions up to 8.2e7).  The C port of the oracle assembles two 816 x 6-cell
+    strips of the SAME plate and inputs; rows of nodes strictly inside a strip couple to nodes of the strip only, so
+    there  K_full . v  ==  K_strip . v|strip  and the diagonals agree, to 1e-12."""
+    from bench import plate, inputs_for
+    from femo_alpha_b200.shell_device import ShellDevice
+    from oracle import c_port
+    from oracle.rm_shell_ref import ShellTopology
+    n, rows = 816, 6
+    nodes, quads = plate(n, n, 0.0, 10.0, 10.0)
+    inp = inputs_for(nodes)
+    d = ShellDevice(nodes, quads)
+    for k in ("thickness", "E", "nu"):
+        d.set_input(k, inp[k])
+    assert d.ndof == 10002534
+    xb = d.block_coords()
+    rng = np.random.default_rng(11)
+    v = rng.standard_normal(d.ndof)
+    Kv = d.jacobian_apply(v).reshape(-1, 3)
+    diag = _bsr_diagonal(d)
+    hy = 10.0 / n
+
+    def key(x):                      # half-cell grid coordinates are integers; rotation nodes are told apart by `kind`
+        return np.rint(2 * x[:, 0] / hy).astype(np.int64) * 4096 + np.rint(2 * x[:, 1] / hy).astype(np.int64)
+
+    kfull = key(xb)
+    kind_full = (np.arange(d.nb) >= d.nq2).astype(np.int64)
+    order = np.lexsort((kfull, kind_full))
+    skeys = kind_full[order] * (1 << 40) + kfull[order]
+    worst = 0.0
+    for j0 in (0, 405, n - rows):                                 # bottom edge, middle, top edge of the plate
+        ys = j0 * hy
+        sn, sq = plate(n, rows, 0.0, 10.0, rows * hy)
+        sn = sn + np.array([0.0, ys, 0.0])
+        topo = ShellTopology(sn, sq)
+        x, y = sn[:, 0], sn[:, 1]
+        h_s = 0.1 * (1 + 0.5 * np.sin(2 * np.pi * x / 10) * np.cos(2 * np.pi * y / 10))
+        asm = c_port.CsrAssembler(topo)
+        asm.assemble(h_s, np.full(sn.shape[0], 1e8), np.full(sn.shape[0], 0.3))
+        Ks = asm.matrix()
+        xs = topo.block_coords()
+        kind_s = (np.arange(topo.nb) >= topo.nq2).astype(np.int64)
+        pos = np.searchsorted(skeys, kind_s * (1 << 40) + key(xs))
+        full_of = order[pos]                                      # strip block node -> block node of the full plate
+        assert np.array_equal(kfull[full_of], key(xs)) and np.array_equal(kind_full[full_of], kind_s)
+        vs = v.reshape(-1, 3)[full_of].ravel()
+        Ksv = (Ks @ vs).reshape(-1, 3)
+        inside = (xs[:, 1] > ys + 1e-9) & (xs[:, 1] < ys + rows * hy - 1e-9)
+        if j0 == 0:
+            inside |= xs[:, 1] < 1e-9                             # the plate's own edge is not a cut
+        if j0 == n - rows:
+            inside |= xs[:, 1] > 10.0 - 1e-9
+        e1 = np.abs(Kv[full_of][inside] - Ksv[inside]).max() / np.abs(Ksv[inside]).max()
+        ds = Ks.diagonal().reshape(-1, 3)
+        e2 = np.abs(diag[full_of][inside] - ds[inside]).max() / np.abs(ds[inside]).max()
+        print("strip at row %d: %d rows compared, K.v rel.err %.2e, diagonal rel.err %.2e" % (j0, 3 * inside.sum(), e1, e2))
+        worst = max(worst, e1, e2)
+    d.close()
+    assert worst <= 1e-12
+
+
+def _bsr_diagonal(d):
+    """(nb, 3) diagonal of dR/du: the diagonal blocks are fetched by position (femo_get_blocks), not the 5.9 GB of values"""
+    from femo_alpha_b200 import _lib as L
+    rowptr, colidx, _ = d.get_bsr(values=False)
+    rows = np.repeat(np.arange(d.nb, dtype=np.int64), np.diff(rowptr.astype(np.int64)))
+    dpos = np.ascontiguousarray(np.nonzero(colidx == rows)[0], dtype=np.int64)
+    assert dpos.size == d.nb
+    blocks = np.empty((d.nb, 9))
+    L.check(d.lib.femo_get_blocks(d._ctx, d.nb, L.ptr(dpos), L.ptr(blocks)))
+    return np.ascontiguousarray(blocks[:, [0, 4, 8]])

@@ -155,3 +155,30 @@ def test_navier_simply_supported_plate():
     w_navier = 0.00406235 * q * a ** 4 / D
     w_shear = 0.07367 * q * a ** 2 / (0.833 * E / (2 * (1 + nu)) * h)        # Mindlin correction of the SS plate (5e-4 here)
     assert abs(w[3 * centre + 2] / (w_navier + w_shear) - 1.0) < 2e-3, (w[3 * centre + 2], w_navier)
+
+
+def test_sympy_differentiation_of_the_energy_matches_the_hand_derived_element():
+    """K_e, R_e and dR_e/dh of one distorted, WARPED cell with uhat != 0, derived by SymPy from the literal energy
+    density (oracle/sympy_check.py: every derivative is a sympy.diff result, the dE2/dX terms of the bending strain
+    included), against the oracle's hand-derived strain operator and constitutive matrices -- to 1e-13."""
+    from oracle import sympy_check as S
+    from oracle.rm_shell_ref import RMShellOracle
+    rng = np.random.default_rng(4)
+    nodes = np.array([[0, 0, 0], [1.1, 0.1, 0.15], [1.3, 0.9, -0.1], [-0.1, 1.0, 0.2]], dtype=float)      # VTK cyclic order
+    quads = np.array([[0, 1, 2, 3]])
+    o = RMShellOracle(nodes, quads, False, False)
+    h = 0.05 * (1 + 0.5 * rng.random(4)); E = 1e6 * (1 + 0.2 * rng.random(4)); nu = 0.25 + 0.1 * rng.random(4)
+    f = rng.standard_normal((4, 3)); uhat = 0.03 * rng.standard_normal((4, 3))
+    o.set_inputs(thickness=h, E=E, nu=nu, density=np.ones(4), F_solid=f.ravel(), uhat=uhat.ravel())
+    t = o.topo
+    w = rng.standard_normal(t.ndof)
+    cv, we = t.cv[0], w[t.cell_dofs[0]]
+    K, R, dR = S.element_quantities(nodes[cv], uhat[cv], h[cv], E[cv], nu[cv], f[cv], we)
+    Ko = o.element_matrices()[0]
+    Ro = Ko @ we - o.element_loads()[0]
+    dRo = o.element_param_action(w, "dh")[0]
+    rel = lambda a, b: np.abs(a - b).max() / np.abs(b).max()
+    assert rel(K, Ko) <= 1e-13 and rel(R, Ro) <= 1e-13 and rel(dR, dRo) <= 1e-13
+    # the cell is genuinely warped: dropping the dE2/dX terms would change K_e at the 1e-2 level
+    xv = nodes[cv]
+    assert abs(np.dot(np.cross(xv[1] - xv[0], xv[2] - xv[0]), xv[3] - xv[0])) > 1e-2
