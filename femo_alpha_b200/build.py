@@ -56,7 +56,26 @@ def build(force: bool = False, verbose: bool = False) -> str:
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
+    build_metis()
     return LIB
+
+
+METIS_LIB = os.path.join(HERE, "libfemo_metis.so")
+METIS_ARCHIVES = ["/usr/local/cuda/targets/x86_64-linux/lib/libmetis_static.a", "/usr/local/cuda/lib64/libmetis_static.a"]
+
+
+def build_metis(force: bool = False):
+    """libfemo_metis.so: csrc/metis_shim.c + CUDA's libmetis_static.a (host only).  Optional: without the archive the
+    graph partitioner falls back to RCB (femo_alpha_b200/partition.py)."""
+    src = os.path.join(CSRC, "metis_shim.c")
+    arch = next((a for a in METIS_ARCHIVES if os.path.exists(a)), None)
+    if arch is None:
+        return None
+    if force or _stale(METIS_LIB, [src]):
+        r = subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", METIS_LIB, src, arch, "-lm"], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("libfemo_metis.so: link failed:\n%s\n%s" % (r.stdout, r.stderr))
+    return METIS_LIB
 
 
 if __name__ == "__main__":

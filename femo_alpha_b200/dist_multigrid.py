@@ -93,7 +93,7 @@ class DistributedHierarchy:
         from . import _lib as L
         from .dist_shell import DistributedShell
         from .multigrid import prolongation, refine_quads
-        from .partition import partition_cells_rcb
+        from .partition import partition_cells
         from .shell_device import ShellDevice
         if levels < 2:
             raise ValueError("a hierarchy needs at least two levels")
@@ -105,7 +105,7 @@ class DistributedHierarchy:
         self.meshes = meshes[::-1]                                 # level 0 = finest
         if part_coarse is None:
             n, q = self.meshes[-1]
-            part_coarse = partition_cells_rcb(n[q].mean(axis=1), world)
+            part_coarse = partition_cells(n, q, world)
         self.parts = nested_parts(part_coarse, levels)
         self.dist = [DistributedShell(self.meshes[l][0], self.meshes[l][1], rank, world, part=self.parts[l], device=device,
                                       quadrature_degree=quadrature_degree) for l in range(n_dist)]

@@ -18,7 +18,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib as L
-from .partition import attach_blocks, build_local_part, halo_arrays, partition_cells_rcb
+from .partition import attach_blocks, build_local_part, halo_arrays, partition_cells
 from .shell_device import ShellDevice
 
 
@@ -28,8 +28,8 @@ class DistributedShell:
         nodes = np.asarray(nodes, dtype=np.float64)
         quads = np.asarray(quads)
         self.rank, self.world = int(rank), int(world)
-        if part is None:
-            part = partition_cells_rcb(nodes[quads].mean(axis=1), world)
+        if part is None:            # METIS k-way on the dual graph for curved / non-manifold meshes, RCB for flat plates
+            part = partition_cells(nodes, quads, world)
         self.part = np.asarray(part, dtype=np.int32)
         lp = build_local_part(nodes, quads, self.part, self.rank, self.world)
         self.dev = ShellDevice(lp.nodes, lp.quads, element_wise_material, elementwise_pressure, quadrature_degree, device)

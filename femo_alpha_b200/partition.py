@@ -1,7 +1,8 @@
 """Mesh partitioning for the multi-GPU RM-shell path: host-side NumPy only.
 
-One process per GPU.  Cells are split into ``world`` parts by recursive coordinate bisection of
-the cell centroids.  A Q2/Q1 block node (vertex, edge mid-point, cell centre, rotation vertex) is
+One process per GPU.  Cells are split into ``world`` parts by METIS k-way partitioning of the cell-adjacency graph
+(curved / non-manifold meshes such as wing boxes; `partition_cells_graph`) or by recursive coordinate bisection of the
+cell centroids (flat plates; `partition_cells_rcb`); `partition_cells` chooses.  A Q2/Q1 block node (vertex, edge mid-point, cell centre, rotation vertex) is
 *owned* by the lowest part among the cells that contain it.  A rank keeps every cell that contains
 a node it owns -- its own cells plus one layer of ghost cells -- so that the rows of its owned
 nodes are assembled completely from local data (owner-computes: no collective in assembly, and the
@@ -46,6 +47,109 @@ def partition_cells_rcb(centroids: np.ndarray, world: int) -> np.ndarray:
 
     rec(np.arange(n), 0, int(world))
     return part
+
+
+def cell_adjacency(quads: np.ndarray):
+    """Dual graph of a quad surface mesh as CSR (xadj, adjncy), int64: two cells are adjacent when they share an edge.
+    Non-manifold edges (wing-box junctions: 3 or 4 cells on one edge) connect every pair of their cells."""
+    q = np.asarray(quads, dtype=np.int64)
+    nc = q.shape[0]
+    nn = int(q.max()) + 1
+    ev = np.stack([q, np.roll(q, -1, axis=1)], axis=2)                     # (nc, 4, 2): VTK cyclic order -> the 4 edges
+    key = (np.minimum(ev[..., 0], ev[..., 1]) * nn + np.maximum(ev[..., 0], ev[..., 1])).ravel()
+    cell = np.repeat(np.arange(nc, dtype=np.int64), 4)
+    order = np.argsort(key, kind="stable")
+    key, cell = key[order], cell[order]
+    start = np.r_[0, np.nonzero(key[1:] != key[:-1])[0] + 1, key.size]
+    cnt = np.diff(start)
+    rows, cols = [], []
+    for k in np.unique(cnt[cnt > 1]):                                         # all pairs inside every group of k cells
+        g = start[:-1][cnt == k]
+        members = cell[g[:, None] + np.arange(k)[None, :]]                    # (ng, k)
+        i, j = np.nonzero(~np.eye(int(k), dtype=bool))
+        rows.append(members[:, i].ravel()); cols.append(members[:, j].ravel())
+    if not rows:
+        return np.zeros(nc + 1, dtype=np.int64), np.zeros(0, dtype=np.int64)
+    pair = np.unique(np.concatenate(rows) * nc + np.concatenate(cols))       # two cells sharing two edges: one arc
+    r, c = pair // nc, pair % nc
+    xadj = np.zeros(nc + 1, dtype=np.int64)
+    np.add.at(xadj, r + 1, 1)
+    return np.cumsum(xadj), np.ascontiguousarray(c)
+
+
+_METIS = None
+
+
+def _metis_lib():
+    """libfemo_metis.so (csrc/metis_shim.c linked against CUDA's libmetis_static.a by build.py), or None."""
+    global _METIS
+    if _METIS is None:
+        import ctypes as C
+        import os
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libfemo_metis.so")
+        if not os.path.exists(path):
+            _METIS = False
+        else:
+            lib = C.CDLL(path)
+            lib.femo_metis_kway.restype = C.c_int
+            lib.femo_metis_kway.argtypes = [C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
+            _METIS = lib
+    return _METIS or None
+
+
+def partition_cells_graph(quads: np.ndarray, world: int, centroids=None, seed: int = 20261104) -> np.ndarray:
+    """k-way partition of the cell-adjacency graph (METIS, fixed seed: every rank computes the same partition).
+    Parts are renumbered by the position of their centroid along the longest axis of the mesh, so that neighbouring
+    part ids tend to be neighbouring ranks.  Falls back to recursive coordinate bisection (with a warning) when
+    libfemo_metis.so was not built; `centroids` (nc, 3) is then required."""
+    import ctypes as C
+    q = np.asarray(quads)
+    nc = q.shape[0]
+    if world <= 1:
+        return np.zeros(nc, dtype=np.int32)
+    lib = _metis_lib()
+    if lib is None:
+        import warnings
+        warnings.warn("femo_alpha_b200: libfemo_metis.so not built (no libmetis_static.a?) -- falling back to RCB")
+        if centroids is None:
+            raise RuntimeError("partition_cells_graph: RCB fallback needs the cell centroids")
+        return partition_cells_rcb(np.asarray(centroids), world)
+    xadj, adjncy = cell_adjacency(q)
+    part = np.empty(nc, dtype=np.int64)
+    cut = C.c_int64(0)
+    r = lib.femo_metis_kway(nc, xadj.ctypes.data_as(C.c_void_p), adjncy.ctypes.data_as(C.c_void_p), int(world), 0, int(seed),
+                            part.ctypes.data_as(C.c_void_p), C.byref(cut))
+    if r != 0:
+        raise RuntimeError("METIS_PartGraphKway failed (status %d)" % r)
+    if np.unique(part).size != world:
+        raise RuntimeError("METIS returned %d of %d parts" % (np.unique(part).size, world))
+    if centroids is not None:                                                    # order the parts along the longest axis
+        cen = np.asarray(centroids, dtype=np.float64)
+        axis = int(np.argmax(cen.max(0) - cen.min(0)))
+        pos = np.array([cen[part == p, axis].mean() for p in range(world)])
+        rank_of = np.empty(world, dtype=np.int64)
+        rank_of[np.argsort(pos, kind="stable")] = np.arange(world)
+        part = rank_of[part]
+    partition_cells_graph.last_edge_cut = int(cut.value)
+    return part.astype(np.int32)
+
+
+def partition_cells(nodes: np.ndarray, quads: np.ndarray, world: int, method: str = "auto") -> np.ndarray:
+    """'rcb', 'graph' (METIS k-way on the dual graph) or 'auto': graph partitioning for meshes with non-manifold
+    junctions or curvature (wing boxes), coordinate bisection for flat single-sheet meshes (plates), where RCB gives
+    straight cuts."""
+    nodes = np.asarray(nodes, dtype=np.float64)
+    q = np.asarray(quads)
+    cen = nodes[q].mean(axis=1)
+    if method == "rcb":
+        return partition_cells_rcb(cen, world)
+    if method == "graph":
+        return partition_cells_graph(q, world, cen)
+    if method != "auto":
+        raise ValueError("partition method must be 'auto', 'rcb' or 'graph'")
+    ext = np.sort(nodes.max(0) - nodes.min(0))
+    flat = ext[0] <= 1e-9 * max(ext[2], 1e-300)
+    return partition_cells_rcb(cen, world) if (flat or _metis_lib() is None) else partition_cells_graph(q, world, cen)
 
 
 @dataclass
