@@ -557,7 +557,9 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
                const int32_t* __restrict__ hitem_ptr, const uint32_t* __restrict__ hitems,
                const int32_t* __restrict__ hcell_ptr, const int32_t* __restrict__ hcells,
                const double* __restrict__ rec, const double* __restrict__ frame, const Tables* __restrict__ tab, int nq,
-               int hitem_cap, int hcell_cap, int dest_cap, int ref_cap, int64_t nchunks, double* __restrict__ vals) {
+               int hitem_cap, int hcell_cap, int dest_cap, int ref_cap, int64_t nchunks, double* __restrict__ vals, int dbg) {
+  // dbg (FEMO_TILE_DEBUG, timing experiments only -- results are wrong when set): 1 no global stores, 2 no tile arithmetic,
+  // 4 no halo items, 8 no gather / rotation on the writer side
   using Cfg = WsCfg<MODE>;
   constexpr int WS_THREADS = Cfg::NT, CT = Cfg::CT, WT = Cfg::WT, DPT = Cfg::DPT;
   extern __shared__ __align__(16) double smem[];
@@ -605,7 +607,8 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       if (it >= 2) bar_sync(BAR_EMPTY + buf, WS_THREADS);   // writers are done with mom[buf] (chunk it-2)
       const double* rc = smem + L.rec0 + buf * L.rec_stride + slot;
       double* mom = smem + L.mom0 + buf * L.mom_stride + slot * MOM_CELL;
-      if (cw < 3) {
+      if (dbg & 2) {
+      } else if (cw < 3) {
         const int t = 2 * cw + half;                 // tiles (0,0) (0,1) (0,2) (1,1) (1,2) (2,2)
         const int I = t < 3 ? 0 : (t < 5 ? 1 : 2);
         const int J = t < 3 ? t : (t < 5 ? t - 2 : 2);
@@ -617,7 +620,7 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       } else if (cw == 5) {
         tile_ut(rc, R, nq, 2, mom, half, 2, half ? 1 : 2);
       }
-      if (cw >= Cfg::HALO0) {                          // halo items on the lighter warps: one pair per thread
+      if (cw >= Cfg::HALO0 && !(dbg & 4)) {                          // halo items on the lighter warps: one pair per thread
         const int h0 = hitem_ptr[chunk], nh = hitem_ptr[chunk + 1] - h0;
         double* hm = smem + L.hmom0 + buf * L.hmom_stride;
         for (int i = (cw - Cfg::HALO0) * 32 + lane; i < nh; i += (Cfg::NCW - Cfg::HALO0) * 32) {
@@ -699,7 +702,7 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
 #pragma unroll
         for (int u = 0; u < DPT; ++u) {
         const int di = base + u * WT + wtid;
-        if (di < nd) {
+        if (di < nd && !(dbg & 8)) {
           const uint32_t info = sInfo[di];
           const int start = info & 0xFFFFF, n = info >> 20;
           double K[9];
@@ -755,7 +758,7 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
         }
         bar_sync(BAR_WRITER, WT);
         const int cnt = min(DPT * WT, nd - base);
-        if (wtid < (WT / 9) * 9) {                                        // WT/9 blocks x 9 entries per pass, k fixed per thread
+        if (wtid < (WT / 9) * 9 && !(dbg & 1)) {                          // WT/9 blocks x 9 entries per pass, k fixed per thread
           const int k = wtid % 9, kt = (k % 3) * 3 + k / 3;
 #pragma unroll 3
           for (int hh = wtid / 9; hh < cnt; hh += WT / 9) {
@@ -870,16 +873,18 @@ int assemble_jacobian_tiles(femo_ctx* c, const double* uh) {
   cudaEventRecord(c->ev1, c->stream);
   if (c->tl_ws) {
     const unsigned grid = (unsigned)std::min<int64_t>(c->tl_nchunks, c->tl_sms);
+    const char* ed = getenv("FEMO_TILE_DEBUG");
+    const int dbg = ed ? atoi(ed) : 0;
     if (c->tl_ws == 2)
       k_asm_tiles_ws<1><<<grid, WsCfg<1>::NT, c->tl_smem, c->stream>>>(
         c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
         c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap,
-        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals);
+        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals, dbg);
     else
       k_asm_tiles_ws<0><<<grid, WsCfg<0>::NT, c->tl_smem, c->stream>>>(
         c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
         c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap,
-        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals);
+        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals, dbg);
     return check_launch(c, "k_asm_tiles_ws");
   }
   k_asm_tiles<<<(unsigned)c->tl_nchunks, TL_THREADS, c->tl_smem, c->stream>>>(

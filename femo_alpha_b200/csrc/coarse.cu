@@ -248,6 +248,40 @@ k_dense_apply(const double* __restrict__ X, const double* __restrict__ z, int64_
   if (lane == 0) out[perm[row]] = s;
 }
 
+// r = b - A x with every product and sum carried in double-double (error-free TwoProd through fma, TwoSum), one thread per
+// block row.  Iterative refinement needs the residual to more digits than the solution has: in plain fp64 it stalls at
+// eps |A| |x| / |b| (~1e-8 on the wing box, kappa ~ 1e12).  A with the BC convention (clamped rows / columns -> identity).
+__device__ __forceinline__ void dd_add_prod(double a, double b, double& hi, double& lo) {
+  const double p = __dmul_rn(a, b), pe = __fma_rn(a, b, -p);    // a b = p + pe exactly (intrinsics: never contracted)
+  const double s = __dadd_rn(hi, p), bb = s - hi;               // TwoSum(hi, p)
+  const double se = (hi - (s - bb)) + (p - bb);
+  hi = s; lo += se + pe;
+}
+__global__ void k_residual_dd(const int32_t* __restrict__ rowptr, const uint32_t* __restrict__ colw, const double* __restrict__ vals,
+                              const uint8_t* __restrict__ rbits, const double* __restrict__ x, const double* __restrict__ b,
+                              int64_t nb, double* __restrict__ r) {
+  const int64_t I = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (I >= nb) return;
+  double hi[3] = {0, 0, 0}, lo[3] = {0, 0, 0};
+  for (int32_t k = rowptr[I]; k < rowptr[I + 1]; ++k) {
+    const uint32_t w = colw[k];
+    const double* a = vals + (int64_t)k * 9;
+    const double* xp = x + 3 * (int64_t)(w & 0x1fffffffu);
+    const double xc[3] = {(w & 0x20000000u) ? 0.0 : xp[0], (w & 0x40000000u) ? 0.0 : xp[1], (w & 0x80000000u) ? 0.0 : xp[2]};
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) dd_add_prod(a[3 * i + j], xc[j], hi[i], lo[i]);
+  }
+  const unsigned bits = rbits[I];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const double bi = b[3 * I + i];
+    if (bits & (1u << i)) r[3 * I + i] = bi - x[3 * I + i];                 // identity row
+    else r[3 * I + i] = (bi - hi[i]) - lo[i];                               // bi - hi is exact to one rounding when they nearly cancel
+  }
+}
+
 __global__ void k_set_diag(double* A, int64_t n) {
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) A[i * n + i] = 1.0;
@@ -523,7 +557,8 @@ int femo_direct_setup(femo_ctx* c) {
   return r;
 }
 
-// A x = rhs with `refine` steps of iterative refinement on the fp64 residual; relres = |rhs - A x| / |rhs| of the result
+// A x = rhs with `refine` steps of iterative refinement on a residual accumulated in double-double (k_residual_dd);
+// relres = |rhs - A x| / |rhs| of the result
 int femo_direct_solve(femo_ctx* c, const double* rhs, double* sol, int refine, double* relres, int on_device, int zero_bc) {
   if (!c || !c->setup_done) return femo_fail("femo_direct_solve: context not set up");
   if (!c->direct || !c->direct->factored || c->direct_epoch != c->mat_epoch || !c->jac_valid)
@@ -537,8 +572,9 @@ int femo_direct_solve(femo_ctx* c, const double* rhs, double* sol, int refine, d
   double bb = 0, rr = 0;
   TRY(dev_dot(c, c->b, c->b, n, &bb));
   for (int it = 0; it <= refine; ++it) {
-    TRY(bsr_spmv(c, c->tmp2, c->Ap, 1));
-    TRY(vec_axpby(c, 1.0, c->b, -1.0, c->Ap, n, c->r));
+    k_residual_dd<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colbc, c->vals, c->bcbits, c->tmp2, c->b, c->nb, c->r);
+    c->launches += 1;
+    TRY(check_launch(c, "k_residual_dd"));
     TRY(dev_dot(c, c->r, c->r, n, &rr));
     if (it == refine || !(rr > 0)) break;
     TRY(coarse_apply(c, c->direct, c->r, c->z));

@@ -215,7 +215,7 @@ int femo_mg_solve(femo_mg* mg, const double* rhs, double* sol, double rtol, int 
  * whose fronts fit in memory (the reference's wing box: 32 226 dofs, 71 fronts of <= 843 dofs, 0.4 GB).
  * Single-GPU contexts.  femo_direct_setup: symbolic analysis on first use + numeric factorisation of the CURRENT
  * operator (call again after inputs / BCs change).  femo_direct_solve: A x = rhs (clamped entries of rhs ignored) with
- * `refine` steps of iterative refinement on the fp64 residual; relres = |rhs - A x| / |rhs| of the returned x.
+ * `refine` steps of iterative refinement on a residual accumulated in double-double; relres = |rhs - A x| / |rhs| of the returned x.
  * femo_direct_info: [level sets, largest front (dofs), bytes of the factor, 1 if the explicit inverse is used]. */
 int femo_direct_setup(femo_ctx* ctx);
 int femo_direct_solve(femo_ctx* ctx, const double* rhs, double* sol, int refine, double* relres, int on_device, int zero_bc);

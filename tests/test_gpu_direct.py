@@ -26,7 +26,7 @@ def test_direct_solver_small_problems(built_lib, name):
     assert info["explicit_inverse"] and info["level_sets"] >= 3
     w = o.solve_state()
     d.solve_state()
-    # the TRUE fp64 residual cannot go below eps |A| |x| / |b| (~1e-9 on a thin plate): the forward error is the test
+    # refinement on a double-double residual: the reported residual is the true one
     print("%s: %s | relres %.2e | rel. error %.2e" % (name, info, d.last_solve["relres"], rel(d.get_state(), w)))
     assert d.last_solve["relres"] <= 1e-7
     assert rel(d.get_state(), w) <= 1e-8
