@@ -63,6 +63,7 @@ SIGNATURES = {
     "femo_solve_forward": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int), _D, C.c_int],
     "femo_dRdf_T_apply": [_P, C.c_int, _P, _P, C.c_int],
     "femo_dRdf_apply": [_P, C.c_int, _P, _P, C.c_int],
+    "femo_dRdf_T_apply_noalloc": [_P, C.c_int, _P, _P],
     "femo_output": [_P, C.c_int, _D],
     "femo_output_grad": [_P, C.c_int, C.c_int, _P, C.c_int],
     "femo_set_stress_params": [_P, C.c_double, C.c_double],

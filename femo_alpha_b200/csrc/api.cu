@@ -247,6 +247,7 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   TRY(dev_alloc(&c->red, 8 * 1184)); TRY(dev_alloc(&c->scal, 32));
   TRY(dev_alloc(&c->cellbuf, (size_t)c->nc * 39));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
+  noalloc_prepare(c->device);     // femo_dRdf_T_apply_noalloc: resolve its static scratch at set-up (never fails the set-up)
   c->setup_done = true; c->jac_valid = false; c->prec_valid = false;
   return 0;
 }

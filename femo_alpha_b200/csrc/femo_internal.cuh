@@ -249,6 +249,7 @@ int out_scalar(femo_ctx* c, int which, double* val);                      // out
 int out_grad(femo_ctx* c, int which, int arg, double* g_dev);             // outputs.cu
 int dRdf_T_apply(femo_ctx* c, int arg, const double* lam, double* out);   // outputs.cu
 int dRdf_apply(femo_ctx* c, int arg, const double* df, double* out);      // outputs.cu
+void noalloc_prepare(int device);                                         // outputs.cu: address of the static scratch array
 int measure_peaks(femo_ctx* c, double* tf, double* gbs);                  // solver.cu
 int halo_exchange(femo_ctx* c, double* x);                                // dist.cu: ghost entries <- owners
 int halo_exchange_begin(femo_ctx* c, double* x);                          // dist.cu: the same on the communication stream ...

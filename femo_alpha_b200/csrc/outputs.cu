@@ -767,3 +767,70 @@ int stress_field(femo_ctx* c, int surface, double* out) {
   c->launches += 1;
   return check_launch(c, "k_copy_cell4");
 }
+
+// ---- allocation-free variant of the matrix-free (dR/dparam)^T lam product ------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA-graph capture, tight serving loops, harnesses that forbid allocation).
+//
+// The regular path (dRdf_T_apply above) lets k_cell_op<OP_PARAM_T> write one element vector per cell into the context's
+// cudaMalloc'ed `cellbuf` and gathers it per node / per cell.  Here that per-cell scratch is a file-scope device array of
+// FEMO_NOALLOC_MAX_CELLS x 4 doubles (2 MiB; every GPU that loads the library holds it until the process exits).
+// In HOST code the name `g_noalloc_cellbuf` is only a host-side stand-in for the symbol, not a device address: the
+// address the kernels receive comes from cudaGetSymbolAddress, resolved once per device with that device current.
+// All calls share the array and it keeps the previous call's contents: the part a call uses is cleared first, and two
+// calls that overlap on the GPU (different streams, different contexts on one device) race.
+static __device__ __align__(256) double g_noalloc_cellbuf[(size_t)FEMO_NOALLOC_MAX_CELLS * 4];
+
+namespace {
+constexpr int NOALLOC_MAX_DEV = 64;
+double* g_noalloc_ptr[NOALLOC_MAX_DEV] = {};        // device address of the scratch array, per device
+std::string g_noalloc_err[NOALLOC_MAX_DEV];
+
+// the caller has made `device` current
+int noalloc_resolve(int device, double** out) {
+  if (device < 0 || device >= NOALLOC_MAX_DEV) return femo_fail("allocation-free scratch: device index out of range");
+  if (!g_noalloc_ptr[device]) {
+    double* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_cellbuf);
+    if (e != cudaSuccess || !p) {
+      g_noalloc_err[device] = std::string("cudaGetSymbolAddress(g_noalloc_cellbuf) failed: ") + cudaGetErrorString(e);
+      return femo_fail(g_noalloc_err[device]);
+    }
+    g_noalloc_ptr[device] = p;
+  }
+  *out = g_noalloc_ptr[device];
+  return 0;
+}
+}  // namespace
+
+// called by femo_shell_setup (device current): resolves the scratch address at set-up so that the entry point below does
+// nothing but launch.  A failure is kept for the entry point to report; it does not fail the set-up.
+void noalloc_prepare(int device) {
+  double* p = nullptr;
+  (void)noalloc_resolve(device, &p);
+}
+
+extern "C" int femo_dRdf_T_apply_noalloc(femo_ctx* c, int arg, const double* lam_dev, double* out_dev) {
+  if (!c || !c->setup_done) return femo_fail("femo_dRdf_T_apply_noalloc: context not set up (femo_mesh_set + femo_shell_setup)");
+  if (c->kind != 0) return femo_fail("femo_dRdf_T_apply_noalloc: RM-shell contexts only");
+  if (!lam_dev || !out_dev) return femo_fail("femo_dRdf_T_apply_noalloc: null device pointer");
+  const int mode = mode_of(arg);
+  if (mode < 0) return femo_fail("femo_dRdf_T_apply_noalloc: argument not supported (thickness, E, nu)");
+  if (c->nc > FEMO_NOALLOC_MAX_CELLS)
+    return femo_fail("femo_dRdf_T_apply_noalloc: " + std::to_string(c->nc) + " cells exceed the static scratch of " +
+                     std::to_string(FEMO_NOALLOC_MAX_CELLS) + " cells (FEMO_NOALLOC_MAX_CELLS); use femo_dRdf_T_apply");
+  int prev = 0;
+  cudaGetDevice(&prev);
+  if (prev != c->device) cudaSetDevice(c->device);
+  struct Restore { int p, d; ~Restore() { if (p != d) cudaSetDevice(p); } } restore{prev, c->device};
+  double* buf = nullptr;
+  TRY(noalloc_resolve(c->device, &buf));
+  CUDA_TRY(cudaMemsetAsync(buf, 0, sizeof(double) * 4 * (size_t)c->nc, c->stream));     // shared array: start from zero
+  CellArgs A = base_args(c);
+  A.vec_l = lam_dev; A.mode = mode; A.out = buf; A.out_stride = 4;
+  TRY(run_cell_op<OP_PARAM_T>(c, A));
+  if (c->ewm) k_copy_strided<<<(unsigned)cdiv(c->nc, 256), 256, 0, c->stream>>>(buf, 4, c->nc, out_dev);
+  else k_node_gather<<<(unsigned)cdiv(c->nn, 256), 256, 0, c->stream>>>(c->nc_ptr, c->nc_adj, buf, 4, c->nq2, c->nn, 9, 1, out_dev);
+  c->launches += 1;
+  return check_launch(c, "femo_dRdf_T_apply_noalloc");
+}

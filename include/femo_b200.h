@@ -206,6 +206,18 @@ int femo_mg_get_lambda(femo_mg* mg, int level, double* lambda_max);
 int femo_mg_solve(femo_mg* mg, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
                   int on_device, int zero_bc);
 
+/* ---- allocation-free variant of femo_dRdf_T_apply (thickness, E, nu) -----------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid allocation).
+ * out_dev (n_material doubles) = (dR/darg)^T lam_dev (n_dof doubles) at the context's current state and inputs; both
+ * pointers are DEVICE pointers.  The per-cell scratch of the element kernel lives in a static device array of
+ * FEMO_NOALLOC_MAX_CELLS x 4 doubles (2 MiB per GPU that loads the library, held until exit): meshes with more cells are
+ * rejected with an error.  The call allocates and frees nothing and does not synchronise: its launches are queued on
+ * the context's stream (femo_set_stream) and out_dev is valid once that stream has reached them.  Every call on a GPU
+ * shares the one array (cleared at the start of each call): calls that overlap on the GPU race. */
+#define FEMO_NOALLOC_MAX_CELLS 65536
+int femo_dRdf_T_apply_noalloc(femo_ctx* ctx, int arg, const double* lam_dev, double* out_dev);
+
 /* ---- sparse direct solver -----------------------------------------------------------------------------------
  * The reference solves EVERY system with a sparse LU (MUMPS: fea/utils_dolfinx.py:465-466 NewtonSolver "preonly + lu",
  * :514-531 setUpKSP_MUMPS).  Here: breadth-first level sets of the block-node graph make A block tridiagonal; block
