@@ -79,6 +79,7 @@ SIGNATURES = {
     "femo_halo_accumulate": [_P, _P, C.c_int],
     "femo_dist_allreduce": [_P, _D, C.c_int],
     "femo_dist_counts": [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
+    "femo_dist_overlap_info": [_P, _D],
     "femo_mg_create": [C.c_int, C.POINTER(_P), C.POINTER(_P)],
     "femo_mg_destroy": [_P],
     "femo_mg_set_transfer": [_P, C.c_int, _P, _P, _P, _P, _P, _P],

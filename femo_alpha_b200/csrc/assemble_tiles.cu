@@ -30,19 +30,19 @@ using femo_tiles::MOM_TT;
 using femo_tiles::MOM_UT;
 
 #define TL_THREADS 192
-#define TL_NF 12
+// 10 fields per (cell, quadrature point).  Round 1 also stored cm33 +- cd/4; they are one FMA away from cm33 and cd, and
+// dropping them shrinks the record stream by a sixth and makes room in shared memory for double-buffered halo records.
+#define TL_NF 10
 #define TF_K00 0
 #define TF_K01 1
 #define TF_K10 2
 #define TF_K11 3
 #define TF_CM11 4
 #define TF_CM12 5
-#define TF_C3P 6    /* cm33 + cd/4 */
-#define TF_C3M 7    /* cm33 - cd/4 */
+#define TF_CM33 6
+#define TF_CD 7
 #define TF_CS 8
-#define TF_CD 9
-#define TF_CM33 10
-#define TF_HB 11    /* h^2/12 */
+#define TF_HB 9     /* h^2/12 */
 
 struct TileTab {                       // reference tables staged once per CTA (6000 B)
   double dphi2[FEMO_MAX_NQ][9][2];
@@ -107,7 +107,6 @@ __global__ void k_cell_records_tiles(const double* __restrict__ xyz, const int32
     r[TF_K00 * C] = dot(g.Kx0, gc.E0); r[TF_K01 * C] = dot(g.Kx0, gc.E1);
     r[TF_K10 * C] = dot(g.Kx1, gc.E0); r[TF_K11 * C] = dot(g.Kx1, gc.E1);
     r[TF_CM11 * C] = wd * cf.cm11; r[TF_CM12 * C] = wd * cf.cm12;
-    r[TF_C3P * C] = cm33 + 0.25 * cd; r[TF_C3M * C] = cm33 - 0.25 * cd;
     r[TF_CS * C] = wd * cf.cs; r[TF_CD * C] = cd;
     r[TF_CM33 * C] = cm33; r[TF_HB * C] = hq * hq / 12.0;
   }
@@ -131,7 +130,9 @@ __device__ __forceinline__ void tile_uu(const double* __restrict__ rc, const Til
   for (int q = 0; q < nq; ++q) {
     const double* r = rc + q * (TL_NF * C);
     const double k00 = r[TF_K00 * C], k01 = r[TF_K01 * C], k10 = r[TF_K10 * C], k11 = r[TF_K11 * C];
-    const double w11 = r[TF_CM11 * C], w12 = r[TF_CM12 * C], w3p = r[TF_C3P * C], w3m = r[TF_C3M * C], ws = r[TF_CS * C];
+    const double w11 = r[TF_CM11 * C], w12 = r[TF_CM12 * C], ws = r[TF_CS * C];
+    const double w33 = r[TF_CM33 * C], wd4 = r[TF_CD * C];
+    const double w3p = fma(0.25, wd4, w33), w3m = fma(-0.25, wd4, w33);          // cm33 +- cd/4
     double bx[3], by[3];
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
@@ -277,58 +278,67 @@ __device__ __forceinline__ void tile_ut(const double* __restrict__ rc, const Til
 }
 
 
-// one halo contribution (cell of another chunk, local pair lo <= hi): same moments, one pair per thread
-__device__ __forceinline__ void halo_item(const double* __restrict__ rc, const TileTab& R, int nq, int a, int b,
+// one halo contribution (cell of another chunk, local pair lo <= hi): same moments, one pair per thread.  The records come
+// from L2 in 8-byte pieces (one 32-byte sector each): the loop is unrolled so that HALO_UNROLL points' loads are in flight
+// (r02f experiments: the halo items cost 0.69 of 3.69 ms, bound by L2 latency and sector traffic, not by arithmetic)
+// HALO_UNROLL is a template parameter (a constant expression: the unroll pragma does not expand macros): 4 for records read
+// from global memory (8 was slower there: 3.86 against 3.69 ms), 8 for the shared-memory copies
+// rc: the cell's record; point q, field f at rc[q * qs + f * fs] (global [chunk][q][field][lane] layout: qs = TL_NF * C,
+// fs = C; shared-memory copy of a halo cell: qs = TL_NF, fs = 1)
+template <int HALO_UNROLL>
+__device__ __forceinline__ void halo_item(const double* __restrict__ rc, int qs, int fs, const TileTab& R, int nq, int a, int b,
                                           double* __restrict__ o) {
   double m0 = 0, m1 = 0, m2 = 0, m3 = 0, m4 = 0;
   if (b < 9) {
-#pragma unroll 4
+#pragma unroll HALO_UNROLL
     for (int q = 0; q < nq; ++q) {
-      const double* r = rc + q * (TL_NF * C);
-      const double k00 = r[TF_K00 * C], k01 = r[TF_K01 * C], k10 = r[TF_K10 * C], k11 = r[TF_K11 * C];
+      const double* r = rc + q * qs;
+      const double k00 = r[TF_K00 * fs], k01 = r[TF_K01 * fs], k10 = r[TF_K10 * fs], k11 = r[TF_K11 * fs];
       const double2 ga = *reinterpret_cast<const double2*>(&R.dphi2[q][a][0]);
       const double2 gb = *reinterpret_cast<const double2*>(&R.dphi2[q][b][0]);
       double ax, ay, bx, by;
       PHYS(ax, ay, ga); PHYS(bx, by, gb);
-      const double w11 = r[TF_CM11 * C], w12 = r[TF_CM12 * C], w3p = r[TF_C3P * C], w3m = r[TF_C3M * C], ws = r[TF_CS * C];
-      m0 += (w11 * ax) * bx + (w3p * ay) * by;
-      m1 += (w12 * ax) * by + (w3m * ay) * bx;
-      m2 += (w12 * ay) * bx + (w3m * ax) * by;
-      m3 += (w11 * ay) * by + (w3p * ax) * bx;
-      m4 += (ws * ax) * bx + (ws * ay) * by;
+      const double w11 = r[TF_CM11 * fs], w12 = r[TF_CM12 * fs], ws = r[TF_CS * fs];
+      const double w33 = r[TF_CM33 * fs], wd4 = r[TF_CD * fs];
+      const double w3p = fma(0.25, wd4, w33), w3m = fma(-0.25, wd4, w33);
+      m0 = fma(w11 * ax, bx, fma(w3p * ay, by, m0));
+      m1 = fma(w12 * ax, by, fma(w3m * ay, bx, m1));
+      m2 = fma(w12 * ay, bx, fma(w3m * ax, by, m2));
+      m3 = fma(w11 * ay, by, fma(w3p * ax, bx, m3));
+      m4 = fma(ws * ax, bx, fma(ws * ay, by, m4));
     }
   } else if (a >= 9) {
     const int ta = a - 9, tb = b - 9;
-#pragma unroll 4
+#pragma unroll HALO_UNROLL
     for (int q = 0; q < nq; ++q) {
-      const double* r = rc + q * (TL_NF * C);
-      const double k00 = r[TF_K00 * C], k01 = r[TF_K01 * C], k10 = r[TF_K10 * C], k11 = r[TF_K11 * C];
+      const double* r = rc + q * qs;
+      const double k00 = r[TF_K00 * fs], k01 = r[TF_K01 * fs], k10 = r[TF_K10 * fs], k11 = r[TF_K11 * fs];
       const double2 ga = *reinterpret_cast<const double2*>(&R.dn1[q][ta][0]);
       const double2 gb = *reinterpret_cast<const double2*>(&R.dn1[q][tb][0]);
       double ax, ay, bx, by;
       PHYS(ax, ay, ga); PHYS(bx, by, gb);
-      const double hb = r[TF_HB * C], cs = r[TF_CS * C], cd = r[TF_CD * C];
-      const double cb11 = hb * r[TF_CM11 * C], cb12 = hb * r[TF_CM12 * C], cb33 = hb * r[TF_CM33 * C];
+      const double hb = r[TF_HB * fs], cs = r[TF_CS * fs], cd = r[TF_CD * fs];
+      const double cb11 = hb * r[TF_CM11 * fs], cb12 = hb * r[TF_CM12 * fs], cb33 = hb * r[TF_CM33 * fs];
       const double Na = R.n1[q][ta], Nb = R.n1[q][tb];
       const double ns = cs * Na;
-      m0 += (cb11 * ay) * by + (cb33 * ax) * bx + ns * Nb;
-      m1 -= (cb12 * ay) * bx + (cb33 * ax) * by;
-      m2 -= (cb12 * ax) * by + (cb33 * ay) * bx;
-      m3 += (cb11 * ax) * bx + (cb33 * ay) * by + ns * Nb;
-      m4 += (cd * Na) * Nb;
+      m0 = fma(cb11 * ay, by, fma(cb33 * ax, bx, fma(ns, Nb, m0)));
+      m1 = fma(-(cb12 * ay), bx, fma(-(cb33 * ax), by, m1));
+      m2 = fma(-(cb12 * ax), by, fma(-(cb33 * ay), bx, m2));
+      m3 = fma(cb11 * ax, bx, fma(cb33 * ay, by, fma(ns, Nb, m3)));
+      m4 = fma(cd * Na, Nb, m4);
     }
   } else {
     const int tb = b - 9;
-#pragma unroll 4
+#pragma unroll HALO_UNROLL
     for (int q = 0; q < nq; ++q) {
-      const double* r = rc + q * (TL_NF * C);
-      const double k00 = r[TF_K00 * C], k01 = r[TF_K01 * C], k10 = r[TF_K10 * C], k11 = r[TF_K11 * C];
+      const double* r = rc + q * qs;
+      const double k00 = r[TF_K00 * fs], k01 = r[TF_K01 * fs], k10 = r[TF_K10 * fs], k11 = r[TF_K11 * fs];
       const double2 ga = *reinterpret_cast<const double2*>(&R.dphi2[q][a][0]);
       double ax, ay;
       PHYS(ax, ay, ga);
       const double N = R.n1[q][tb];
-      const double csn = r[TF_CS * C] * N, cdn = r[TF_CD * C] * N;
-      m0 += csn * ax; m1 += csn * ay; m2 += cdn * ax; m3 += cdn * ay;
+      const double csn = r[TF_CS * fs] * N, cdn = r[TF_CD * fs] * N;
+      m0 = fma(csn, ax, m0); m1 = fma(csn, ay, m1); m2 = fma(cdn, ax, m2); m3 = fma(cdn, ay, m3);
     }
   }
   o[0] = m0; o[1] = m1; o[2] = m2; o[3] = m3; o[4] = m4;
@@ -337,6 +347,10 @@ __device__ __forceinline__ void halo_item(const double* __restrict__ rc, const T
 __device__ __forceinline__ void cp_async4(void* s, const void* g) {
   const unsigned a = (unsigned)__cvta_generic_to_shared(s);
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(a), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* s, const void* g) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(s);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(a), "l"(g) : "memory");
 }
 __device__ __forceinline__ void cp_async16(void* s, const void* g) {
   const unsigned a = (unsigned)__cvta_generic_to_shared(s);
@@ -446,7 +460,7 @@ k_asm_tiles(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__ de
         const int64_t p = it >> 8;
         const int code = it & 0xff, a = code / 13, b = code - 13 * a;
         const double* rh = rec + (p / C) * ((int64_t)nq * TL_NF * C) + (p % C);
-        halo_item(rh, R, nq, a, b, sMom + MOM_HALO_BASE + MOM_HALO * i);
+        halo_item<4>(rh, TL_NF * C, C, R, nq, a, b, sMom + MOM_HALO_BASE + MOM_HALO * i);
       }
     }
   }
@@ -512,13 +526,17 @@ k_asm_tiles(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__ de
 #define BAR_EMPTY 3     /* +buf */
 #define BAR_COMPUTE 5
 #define BAR_WRITER 6
+#define BAR_HALO 7
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-struct WsSmem { int mom0, mom_stride, hmom0, hmom_stride, frame, rec0, rec_stride, sk, plan, flags, total; };   // offsets in doubles
+struct WsSmem { int mom0, mom_stride, hmom0, hmom_stride, frame, rec0, rec_stride, sk, plan, flags, hrec, total; };   // offsets in doubles
 
-__host__ __device__ inline WsSmem ws_smem_layout(int nq, int hitem_cap, int hcell_cap, int dest_cap, int ref_cap) {
+// sk_rows: 3x3 blocks staged per store round (writer threads x destinations per thread); hrec_cells: halo cells whose
+// records are staged in shared memory (0: the halo items read them from global memory)
+__host__ __device__ inline WsSmem ws_smem_layout(int nq, int hitem_cap, int hcell_cap, int dest_cap, int ref_cap, int sk_rows = 384,
+                                                 int hrec_cells = 0) {
   WsSmem L;
   int o = (int)(sizeof(TileTab) / sizeof(double));
   L.mom0 = o; L.mom_stride = MOM_HALO_BASE + 1; o += 2 * L.mom_stride;
@@ -526,9 +544,13 @@ __host__ __device__ inline WsSmem ws_smem_layout(int nq, int hitem_cap, int hcel
   L.frame = o; o += (C + hcell_cap) * 9;
   o = (o + 1) & ~1;
   L.rec0 = o; L.rec_stride = nq * TL_NF * C; o += 2 * L.rec_stride;
-  L.sk = o; o += 384 * 9;
+  L.sk = o; o += sk_rows * 9;
   L.plan = o; o += (3 * dest_cap + ref_cap + 1) / 2 + 1;
   L.flags = o; o += 8;
+  // records (per-cell stride nq * TL_NF + 1 doubles: an even stride maps every cell to the same banks and serialises the
+  // loads of a warp whose items span several cells -- measured 4.49 ms against 3.76 without staging) + processing indices
+  // two buffers (the records of chunk k+1 are copied while chunk k is processed) + three cell lists (k, k+1, k+2) of ints
+  L.hrec = o; o += 2 * hrec_cells * (nq * TL_NF + 1) + (3 * hrec_cells + 1) / 2;
   L.total = o;
   return L;
 }
@@ -557,13 +579,14 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
                const int32_t* __restrict__ hitem_ptr, const uint32_t* __restrict__ hitems,
                const int32_t* __restrict__ hcell_ptr, const int32_t* __restrict__ hcells,
                const double* __restrict__ rec, const double* __restrict__ frame, const Tables* __restrict__ tab, int nq,
-               int hitem_cap, int hcell_cap, int dest_cap, int ref_cap, int64_t nchunks, double* __restrict__ vals, int dbg) {
+               int hitem_cap, int hcell_cap, int dest_cap, int ref_cap, int64_t nchunks, double* __restrict__ vals, int dbg,
+               int hrec_cells, const int32_t* __restrict__ hfix) {
   // dbg (FEMO_TILE_DEBUG, timing experiments only -- results are wrong when set): 1 no global stores, 2 no tile arithmetic,
   // 4 no halo items, 8 no gather / rotation on the writer side
   using Cfg = WsCfg<MODE>;
   constexpr int WS_THREADS = Cfg::NT, CT = Cfg::CT, WT = Cfg::WT, DPT = Cfg::DPT;
   extern __shared__ __align__(16) double smem[];
-  const WsSmem L = ws_smem_layout(nq, hitem_cap, hcell_cap, dest_cap, ref_cap);
+  const WsSmem L = ws_smem_layout(nq, hitem_cap, hcell_cap, dest_cap, ref_cap, WT * DPT, hrec_cells);
   TileTab& R = *reinterpret_cast<TileTab*>(smem);
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int slot = lane & (C - 1), half = lane >> 4;
@@ -591,6 +614,21 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       const double2* g = reinterpret_cast<const double2*>(rec + first * rec_chunk);
       double2* sr = reinterpret_cast<double2*>(smem + L.rec0);
       for (int i = ctid; i < n2; i += CT) cp_async16(sr + i, g + i);
+      if (hrec_cells > 0 && cw >= Cfg::HALO0) {        // halo pipeline prologue: lists of chunks 0 and 1, records of chunk 0
+        double* hr = smem + L.hrec;
+        int32_t* hpb = reinterpret_cast<int32_t*>(hr + 2 * hrec_cells * (nq * TL_NF + 1));
+        const int htid = (cw - Cfg::HALO0) * 32 + lane, HT = (Cfg::NCW - Cfg::HALO0) * 32;
+        const int per = nq * TL_NF;
+        for (int i = htid; i < hrec_cells; i += HT) {
+          cp_async4(hpb + i, hfix + first * hrec_cells + i);
+          if (n_it > 1) cp_async4(hpb + hrec_cells + i, hfix + (first + G) * hrec_cells + i);
+        }
+        for (int i = htid; i < hrec_cells * per; i += HT) {
+          const int sc = i / per, idx = i - sc * per;
+          const int64_t pc = hfix[first * hrec_cells + sc];          // fixed-width rows, -1 padded
+          if (pc >= 0) cp_async8(hr + sc * (per + 1) + idx, rec + (pc / C) * rec_chunk + (pc % C) + (int64_t)idx * C);
+        }
+      }
     }
     cp_async_commit();
     for (int it = 0; it < n_it; ++it) {
@@ -598,6 +636,31 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       const int buf = it & 1;
       cp_async_wait<0>();
       bar_sync(BAR_COMPUTE, CT);               // rec[buf] complete; everybody left rec[buf ^ 1] (iteration it-1)
+      // halo warps: the records of a chunk's (few) halo cells are staged in shared memory -- a chunk's ~115 halo items come
+      // from ~9 cells, and read from global memory per item they cost 13x the L2 sectors (r02f: 0.69 of 3.69 ms).  The
+      // copies of chunk it+1 are issued now and land during this iteration (two record buffers); the cell lists run two
+      // chunks ahead (three small buffers), so no global load sits between the barrier and the copies.
+      int nhc_s = 0;
+      if (hrec_cells > 0 && cw >= Cfg::HALO0) {
+        double* hr = smem + L.hrec;
+        const int per = nq * TL_NF;
+        int32_t* hpb = reinterpret_cast<int32_t*>(hr + 2 * hrec_cells * (per + 1));
+        const int32_t* hp = hpb + (it % 3) * hrec_cells;
+        while (nhc_s < hrec_cells && hp[nhc_s] >= 0) ++nhc_s;
+        const int htid = (cw - Cfg::HALO0) * 32 + lane, HT = (Cfg::NCW - Cfg::HALO0) * 32;
+        if (it + 1 < n_it) {
+          const int32_t* hpn = hpb + ((it + 1) % 3) * hrec_cells;
+          double* hrn = hr + (buf ^ 1) * hrec_cells * (per + 1);
+          for (int i = htid; i < hrec_cells * per; i += HT) {
+            const int sc = i / per, idx = i - sc * per;
+            const int64_t pc = hpn[sc];
+            if (pc >= 0) cp_async8(hrn + sc * (per + 1) + idx, rec + (pc / C) * rec_chunk + (pc % C) + (int64_t)idx * C);
+          }
+        }
+        if (it + 2 < n_it)
+          for (int i = htid; i < hrec_cells; i += HT) cp_async4(hpb + ((it + 2) % 3) * hrec_cells + i, hfix + (chunk + 2 * G) * hrec_cells + i);
+        cp_async_commit();
+      }
       if (it + 1 < n_it) {
         const double2* g = reinterpret_cast<const double2*>(rec + (chunk + G) * rec_chunk);
         double2* sr = reinterpret_cast<double2*>(smem + L.rec0 + (buf ^ 1) * L.rec_stride);
@@ -623,12 +686,21 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       if (cw >= Cfg::HALO0 && !(dbg & 4)) {                          // halo items on the lighter warps: one pair per thread
         const int h0 = hitem_ptr[chunk], nh = hitem_ptr[chunk + 1] - h0;
         double* hm = smem + L.hmom0 + buf * L.hmom_stride;
+        // records of this chunk's halo cells: copied during the previous iteration, complete since the loop-top wait + barrier
+        const double* hr = smem + L.hrec + buf * hrec_cells * (nq * TL_NF + 1);
+        const int32_t* hp = reinterpret_cast<const int32_t*>(smem + L.hrec + 2 * hrec_cells * (nq * TL_NF + 1)) + (it % 3) * hrec_cells;
         for (int i = (cw - Cfg::HALO0) * 32 + lane; i < nh; i += (Cfg::NCW - Cfg::HALO0) * 32) {
           const uint32_t item = hitems[h0 + i];
           const int64_t p = item >> 8;
           const int code = item & 0xff, a = code / 13, b = code - 13 * a;
-          const double* rh = rec + (p / C) * rec_chunk + (p % C);
-          halo_item(rh, R, nq, a, b, hm + MOM_HALO * i);
+          if (hrec_cells > 0) {
+            int sc = 0;
+            while (sc < nhc_s - 1 && hp[sc] != (int32_t)p) ++sc;     // <= hrec_cells entries; p is always among them
+            halo_item<8>(hr + sc * (nq * TL_NF + 1), TL_NF, 1, R, nq, a, b, hm + MOM_HALO * i);
+          } else {
+            const double* rh = rec + (p / C) * rec_chunk + (p % C);
+            halo_item<4>(rh, TL_NF * C, C, R, nq, a, b, hm + MOM_HALO * i);
+          }
         }
       }
       __threadfence_block();
@@ -799,7 +871,7 @@ void tile_plan_free(femo_ctx* c) {
   dev_free(&c->tl_cell_order); dev_free(&c->tl_dest_ptr); dev_free(&c->tl_dest_pos); dev_free(&c->tl_dest_tpos);
   dev_free(&c->tl_dest_info); dev_free(&c->tl_refs); dev_free(&c->tl_hitems); dev_free(&c->tl_ref_ptr);
   dev_free(&c->tl_hitem_ptr); dev_free(&c->tl_hcell_ptr); dev_free(&c->tl_hcells); dev_free(&c->tl_rec);
-  dev_free(&c->tl_frame);
+  dev_free(&c->tl_frame); dev_free(&c->tl_hfix);
 }
 
 // FEMO_TILE=0 disables the tiled kernel; FEMO_TILE_ORDER=identity keeps the caller's cell order (default: Morton)
@@ -833,10 +905,27 @@ int tile_plan_setup(femo_ctx* c) {
   const int dest_cap = P.max_dests, ref_cap = P.max_refs;
   size_t smem = sizeof(double) * (size_t)tile_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap).total;
   if (smem > 227 * 1024) return 0;                      // halo too large for one CTA: older kernels take over
-  const size_t smem_ws = sizeof(double) * (size_t)ws_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap).total;
   const char* ews = getenv("FEMO_TILE_WS");             // FEMO_TILE_WS=0: two independent CTAs per SM instead of warp roles
-  c->tl_ws = smem_ws <= 227 * 1024 ? (ews ? atoi(ews) : 2) : 0;   // 1: 6+6 warps, 2: 8+8 warps with setmaxnreg
-  if (c->tl_ws) smem = smem_ws;
+  const int ws_req = ews ? atoi(ews) : 2;                 // 1: 6+6 warps, 2: 8+8 warps with setmaxnreg
+  const int sk_rows = ws_req == 2 ? WsCfg<1>::WT * WsCfg<1>::DPT : WsCfg<0>::WT * WsCfg<0>::DPT;
+  size_t smem_ws = sizeof(double) * (size_t)ws_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap, sk_rows, 0).total;
+  c->tl_ws = smem_ws <= 227 * 1024 ? ws_req : 0;
+  c->tl_hrec = 0;
+  if (c->tl_ws) {
+    // FEMO_TILE_HREC=1: stage the halo cells' records in shared memory (when they fit) instead of reading them from global
+    // memory per halo item.  OFF by default: measured at cfg 3 (profiles/r02l_asm_experiments*.log) the items get 2.7x
+    // cheaper, but the ~1 400 scattered 8-byte cp.async per chunk cost more LSU time than they save (3.55 against 3.39 ms).
+    const char* eh = getenv("FEMO_TILE_HREC");
+    const size_t with_h = sizeof(double) * (size_t)ws_smem_layout(c->nq, hitem_cap, hcell_cap, dest_cap, ref_cap, sk_rows, hcell_cap).total;
+    if (eh && atoi(eh) == 1 && hcell_cap > 0 && with_h <= 227 * 1024) { c->tl_hrec = hcell_cap; smem_ws = with_h; }
+    smem = smem_ws;
+  }
+  if (c->tl_hrec) {                                      // fixed-width halo-cell lists: row `chunk`, -1 padded
+    std::vector<int32_t> fixed((size_t)P.nchunks * hcell_cap, -1);
+    for (int64_t ch = 0; ch < P.nchunks; ++ch)
+      for (int32_t k = P.hcell_ptr[ch]; k < P.hcell_ptr[ch + 1]; ++k) fixed[(size_t)ch * hcell_cap + (k - P.hcell_ptr[ch])] = P.hcells[k];
+    TRY(upload(&c->tl_hfix, fixed));
+  }
   TRY(upload(&c->tl_cell_order, P.cell_order)); TRY(upload(&c->tl_dest_ptr, P.dest_ptr));
   TRY(upload(&c->tl_dest_pos, P.dest_pos)); TRY(upload(&c->tl_dest_tpos, P.dest_tpos));
   TRY(upload(&c->tl_dest_info, P.dest_info)); TRY(upload(&c->tl_ref_ptr, P.ref_ptr)); TRY(upload(&c->tl_refs, P.refs));
@@ -857,8 +946,9 @@ int tile_plan_setup(femo_ctx* c) {
     c->tl_sms = prop.multiProcessorCount;
   }
   if (getenv("FEMO_VERBOSE"))
-    fprintf(stderr, "[femo] tile plan: %lld chunks of %d cells, %lld dests, %lld refs, %lld halo items (max/chunk %d), smem %zu B\n",
-            (long long)P.nchunks, C, (long long)c->tl_ndest, (long long)c->tl_nref, (long long)c->tl_nhitem, P.max_hitems, smem);
+    fprintf(stderr, "[femo] tile plan: %lld chunks of %d cells, %lld dests, %lld refs, %lld halo items (max/chunk %d) from <= %d halo cells (%s), smem %zu B\n",
+            (long long)P.nchunks, C, (long long)c->tl_ndest, (long long)c->tl_nref, (long long)c->tl_nhitem, P.max_hitems, P.max_hcells,
+            c->tl_hrec ? "records staged in shared memory" : "records read from global memory", smem);
   c->tile_ok = true;
   return 0;
 }
@@ -879,12 +969,12 @@ int assemble_jacobian_tiles(femo_ctx* c, const double* uh) {
       k_asm_tiles_ws<1><<<grid, WsCfg<1>::NT, c->tl_smem, c->stream>>>(
         c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
         c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap,
-        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals, dbg);
+        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals, dbg, c->tl_hrec, c->tl_hfix);
     else
       k_asm_tiles_ws<0><<<grid, WsCfg<0>::NT, c->tl_smem, c->stream>>>(
         c->tl_dest_ptr, c->tl_dest_pos, c->tl_dest_tpos, c->tl_dest_info, c->tl_ref_ptr, c->tl_refs, c->tl_hitem_ptr,
         c->tl_hitems, c->tl_hcell_ptr, c->tl_hcells, c->tl_rec, c->tl_frame, c->tab, c->nq, c->tl_hitem_cap,
-        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals, dbg);
+        c->tl_hcell_cap, c->tl_dest_cap, c->tl_ref_cap, c->tl_nchunks, c->vals, dbg, c->tl_hrec, c->tl_hfix);
     return check_launch(c, "k_asm_tiles_ws");
   }
   k_asm_tiles<<<(unsigned)c->tl_nchunks, TL_THREADS, c->tl_smem, c->stream>>>(

@@ -206,6 +206,7 @@ void dist_free(femo_ctx* c) {
   if (c->comm_stream) { cudaStreamDestroy(c->comm_stream); c->comm_stream = nullptr; }
   if (c->ev_ready) { cudaEventDestroy(c->ev_ready); c->ev_ready = nullptr; }
   if (c->ev_halo) { cudaEventDestroy(c->ev_halo); c->ev_halo = nullptr; }
+  for (auto& e : c->ev_trace) if (e) { cudaEventDestroy(e); e = nullptr; }
   if (c->nccl_comm && c->comm_owner && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->nccl_comm);
   c->nccl_comm = nullptr;
   dev_free(&c->send_blocks); dev_free(&c->recv_blocks); dev_free(&c->send_buf); dev_free(&c->recv_buf); dev_free(&c->own);
@@ -270,6 +271,10 @@ int femo_dist_setup(femo_ctx* c, int rank, int world, int n_nbr, const int32_t* 
     if (!c->comm_stream) CUDA_TRY(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
     if (!c->ev_ready) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_ready, cudaEventDisableTiming));
     if (!c->ev_halo) CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+    const char* et = getenv("FEMO_TRACE_OVERLAP");
+    c->trace_overlap = (et && et[0] == '1') ? 1 : 0;
+    if (c->trace_overlap)
+      for (auto& e : c->ev_trace) if (!e) CUDA_TRY(cudaEventCreate(&e));
   }
   return 0;
 }
@@ -331,6 +336,23 @@ int femo_dist_allreduce(femo_ctx* c, double* vals, int n) {
   if (!c) return femo_fail("null context");
   DevGuard2 g(c->device);
   return dist_allreduce_host(c, vals, n);
+}
+
+// FEMO_TRACE_OVERLAP=1 at femo_dist_setup: times of the LAST overlapped operator application, in ms after its start:
+// ms[0] halo exchange complete (pack + ncclSend/Recv + unpack, communication stream), ms[1] interior rows complete,
+// ms[2] boundary rows complete (context's stream).  ms[0] <= ms[1] means the exchange was hidden behind the interior rows.
+int femo_dist_overlap_info(femo_ctx* c, double* ms3) {
+  if (!c || !ms3) return femo_fail("femo_dist_overlap_info: null argument");
+  if (!c->trace_overlap || !c->ev_trace[0]) return femo_fail("femo_dist_overlap_info: set FEMO_TRACE_OVERLAP=1 before femo_dist_setup");
+  DevGuard2 g(c->device);
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->comm_stream));
+  for (int i = 0; i < 3; ++i) {
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, c->ev_trace[0], c->ev_trace[i + 1]));
+    ms3[i] = ms;
+  }
+  return 0;
 }
 
 int femo_dist_counts(femo_ctx* c, int64_t* halo_exchanges, int64_t* allreduces) {

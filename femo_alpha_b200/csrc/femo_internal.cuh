@@ -112,6 +112,7 @@ struct femo_ctx {
   // tiled planar assembly (assemble_tiles.cu, tile_plan.hpp): chunks of 32 cells in processing order
   bool tile_ok = false;
   int tl_ws = 0;
+  int tl_hrec = 0;              // halo cells whose records the tiled kernel stages in shared memory (0: read from global)
   int tl_sms = 148;
   int64_t tl_nchunks = 0, tl_ndest = 0, tl_nref = 0, tl_nhitem = 0;
   int tl_hitem_cap = 0, tl_hcell_cap = 0, tl_dest_cap = 0, tl_ref_cap = 0;
@@ -119,6 +120,7 @@ struct femo_ctx {
   int32_t *tl_cell_order = nullptr, *tl_dest_ptr = nullptr, *tl_dest_pos = nullptr, *tl_dest_tpos = nullptr;
   uint32_t *tl_dest_info = nullptr, *tl_refs = nullptr, *tl_hitems = nullptr;
   int32_t *tl_ref_ptr = nullptr, *tl_hitem_ptr = nullptr, *tl_hcell_ptr = nullptr, *tl_hcells = nullptr;
+  int32_t *tl_hfix = nullptr;   // [chunk][tl_hrec] halo cells of a chunk, -1 padded (staged halo records)
   double *tl_rec = nullptr, *tl_frame = nullptr;  // [chunk][q][12 fields][32 lanes], [slot][9]
   // block node -> (cell, local index) adjacency, cell-ascending
   int32_t *nc_ptr = nullptr;    // nb+1
@@ -167,6 +169,8 @@ struct femo_ctx {
   int64_t n_rows_int = 0, n_rows_bnd = 0;
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_ready = nullptr, ev_halo = nullptr;
+  cudaEvent_t ev_trace[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // FEMO_TRACE_OVERLAP=1: timed events of the last dist_spmv
+  int trace_overlap = 0;
   // solver state
   double *w = nullptr, *b = nullptr, *r = nullptr, *z = nullptr, *p = nullptr, *Ap = nullptr, *tmp = nullptr;
   double *tmp2 = nullptr;

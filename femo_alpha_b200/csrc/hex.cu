@@ -63,7 +63,8 @@ static_assert(HEX_PASS == 64, "k_hex_assemble stages one item pair per lane");
 constexpr int HEX_WARPS = 4;
 constexpr int HEX_GSTRIDE = 8 * GEO + 2;                 // 16-byte aligned rows, 4 banks apart
 constexpr int HEX_REGION = 8 * HEX_GSTRIDE;              // >= 9 * HEX_PASS
-__global__ void __launch_bounds__(32 * HEX_WARPS, 5)
+template <int MINB>     // resident CTAs per SM the compiler plans for (5: 96 registers, 11.9 ms at 160^3; 7: 72 registers, spills, 21.2 ms -- r02h)
+__global__ void __launch_bounds__(32 * HEX_WARPS, MINB)
 k_hex_assemble(int form, double c1, double c2, const double* __restrict__ geo, const int32_t* __restrict__ cells,
                const double* __restrict__ scale, const int32_t* __restrict__ nc_ptr, const int32_t* __restrict__ nc_adj,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int64_t nb,
@@ -290,8 +291,12 @@ int hex_assemble(femo_ctx* c) {
     k_hex_assemble_g<<<(unsigned)cdiv(c->nb, HEXG_WARPS), 32 * HEXG_WARPS, 0, c->stream>>>(
         c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo2, c->hx_cells, c->hx_scale, c->nc_ptr, c->nc_adj, c->rowptr, c->colidx, c->nb,
         c->vals);
+  else if (getenv("FEMO_HEX_MINB") && atoi(getenv("FEMO_HEX_MINB")) == 7)      // occupancy experiment
+    k_hex_assemble<7><<<(unsigned)cdiv(c->nb, HEX_WARPS), 32 * HEX_WARPS, 0, c->stream>>>(
+        c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo, c->hx_cells, c->hx_scale, c->nc_ptr, c->nc_adj, c->rowptr, c->colidx, c->nb,
+        c->vals);
   else
-    k_hex_assemble<<<(unsigned)cdiv(c->nb, HEX_WARPS), 32 * HEX_WARPS, 0, c->stream>>>(
+    k_hex_assemble<5><<<(unsigned)cdiv(c->nb, HEX_WARPS), 32 * HEX_WARPS, 0, c->stream>>>(
         c->hx_form, c->hx_c1, c->hx_c2, c->hx_geo, c->hx_cells, c->hx_scale, c->nc_ptr, c->nc_adj, c->rowptr, c->colidx, c->nb,
         c->vals);
   TRY(check_launch(c, "k_hex_assemble"));

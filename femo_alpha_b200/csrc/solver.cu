@@ -440,11 +440,18 @@ int dist_spmv(femo_ctx* c, double* x, double* y, double* dot_int, double* dot_bn
     c->launches += 1;
     return check_launch(c, "k_spmv");
   }
+  // trace (FEMO_TRACE_OVERLAP=1): [0] start, [1] halo done (communication stream), [2] interior rows done, [3] boundary rows
+  // done (context's stream); read back by femo_dist_overlap_info
+  const bool tr = c->trace_overlap != 0;
+  if (tr) cudaEventRecord(c->ev_trace[0], c->stream);
   TRY(halo_exchange_begin(c, x));
+  if (tr) cudaEventRecord(c->ev_trace[1], c->comm_stream);
   int g0 = 0, g1 = 0;
   TRY(launch_spmv_rows(c, x, y, c->rows_int, c->n_rows_int, dot_int, &g0));
+  if (tr) cudaEventRecord(c->ev_trace[2], c->stream);
   TRY(halo_exchange_end(c));
   TRY(launch_spmv_rows(c, x, y, c->rows_bnd, c->n_rows_bnd, dot_bnd, &g1));
+  if (tr) cudaEventRecord(c->ev_trace[3], c->stream);
   if (n_int) *n_int = g0;
   if (n_bnd) *n_bnd = g1;
   c->launches += 2;

@@ -60,6 +60,10 @@ class DistributedShell:
         dist.broadcast(t, src=0)
         buf = t.cpu().numpy().copy()
         L.check(self.dev.lib.femo_dist_init(self.dev._ctx, L.ptr(buf)))
+        # NCCL establishes its peer-to-peer connections lazily, at the first send / receive and the first all-reduce of
+        # a communicator (~1.5 s at 4 GPUs): pay that here, once, not inside the first solver set-up
+        self.halo_exchange(np.zeros(self.dev.ndof))
+        L.check(self.dev.lib.femo_dist_allreduce(self.dev._ctx, (C.c_double * 1)(0.0), 1))
 
     # ---- inputs: global arrays in external (mesh) order ------------------------------------------
     def _slice(self, name, values):
@@ -119,6 +123,13 @@ class DistributedShell:
         x = np.ascontiguousarray(x, dtype=np.float64)
         L.check(self.dev.lib.femo_halo_accumulate(self.dev._ctx, L.ptr(x), 0))
         return x
+
+    def overlap_info(self):
+        """(halo done, interior rows done, boundary rows done) in ms after the start of the last operator application;
+        needs FEMO_TRACE_OVERLAP=1 in the environment when the object was built"""
+        v = (C.c_double * 3)()
+        L.check(self.dev.lib.femo_dist_overlap_info(self.dev._ctx, v))
+        return float(v[0]), float(v[1]), float(v[2])
 
     def comm_counts(self):
         h = C.c_int64(0); a = C.c_int64(0)

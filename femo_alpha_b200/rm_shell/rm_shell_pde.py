@@ -42,11 +42,15 @@ class RMShellPDE:
         chain = getattr(mesh, "mg_meshes", None)
         if chain and len(chain) >= 2 and os.environ.get("FEMO_MG", "1") != "0":
             n_coarse = 3 * (2 * chain[0][0].shape[0] + 3 * chain[0][1].shape[0])      # upper bound of the coarsest dof count
-            if n_coarse <= 46000:
+            if n_coarse <= 400000:       # the coarsest level is factorised by the sparse direct solver (csrc/coarse.cu)
                 from ..multigrid import ShellHierarchy
                 self.hierarchy = ShellHierarchy.for_device(dev, chain, quadrature_degree, device,
                                                            element_wise_material=element_wise_material,
                                                            elementwise_pressure=elementwise_pressure)
+        # no hierarchy (a mesh read from a file, e.g. the reference's wing box): sparse direct solves like the reference's
+        # MUMPS, as long as the factor fits; decided at the first solve, Krylov fallback otherwise (FEMO_DIRECT=0: off)
+        if self.hierarchy is None and dev.ndof <= 600000 and os.environ.get("FEMO_DIRECT", "1") != "0":
+            dev.enable_direct(refine=2, lazy=True)
         nn, nc = dev.nn, dev.nc
         self.W = FunctionSpace(mesh, "W", dev.ndof, dev, "CG2CG1")
         self.VT = FunctionSpace(mesh, "VT", nc if element_wise_material else nn, dev,

@@ -167,17 +167,33 @@ class ShellDevice:
         return sp.bsr_matrix((vals, colidx, rowptr), shape=(self.ndof, self.ndof)).tocsr()
 
     # ---- solves -------------------------------------------------------------------------
-    def enable_direct(self, refine=2):
+    def enable_direct(self, refine=2, lazy=False):
         """Route solve_state / solve_adjoint / solve_forward through the sparse direct solver (csrc/coarse.cu: what MUMPS
-        is to the reference, fea/utils_dolfinx.py:465-466,514-531).  Runs the symbolic analysis now and raises if the
-        factor would not fit (FEMO_DIRECT_MAX_GB); `refine` steps of iterative refinement per solve."""
-        self._direct = dict(refine=int(refine))
+        is to the reference, fea/utils_dolfinx.py:465-466,514-531).  By default the symbolic analysis and a first
+        factorisation run now and raise if the factor would not fit (FEMO_DIRECT_MAX_GB); `refine` steps of iterative
+        refinement per solve.  lazy=True (what RMShellPDE uses for meshes without a hierarchy) defers that to the first
+        solve -- BCs and inputs are not known yet -- and falls back to the Krylov solver, with a warning, if it fails."""
+        self._direct = dict(refine=int(refine), auto=bool(lazy))
+        if lazy:
+            return None
         try:
             L.check(self.lib.femo_direct_setup(self._ctx))
         except Exception:
             self._direct = None
             raise
         return self.direct_info()
+
+    def _direct_or_none(self, rhs, zero_bc):
+        """direct solve, or None after switching an auto-enabled direct solver off because it cannot serve this problem"""
+        try:
+            return self.solve_direct(rhs, self._direct["refine"], zero_bc=zero_bc)
+        except RuntimeError as e:
+            if not self._direct.get("auto"):
+                raise
+            import warnings
+            warnings.warn("femo_alpha_b200: direct solver unavailable for this problem (%s); using the Krylov solver" % e)
+            self._direct = None
+            return None
 
     def disable_direct(self):
         self._direct = None
@@ -201,8 +217,10 @@ class ShellDevice:
         if self._mg is not None:          # nested mesh hierarchy available: V-cycle preconditioned PCG (csrc/mg.cu)
             return self._mg.solve_state(rtol, min(max_it, 5000))
         if getattr(self, "_direct", None) is not None:
-            self.set_state(self.solve_direct(self.assemble_load(), self._direct["refine"], zero_bc=True))
-            return self.last_solve["iters"], self.last_solve["relres"]
+            u = self._direct_or_none(self.assemble_load(), True)
+            if u is not None:
+                self.set_state(u)
+                return self.last_solve["iters"], self.last_solve["relres"]
         it = C.c_int(0); rr = C.c_double(0.0)
         L.check(self.lib.femo_solve_state(self._ctx, float(rtol), int(max_it), C.byref(it), C.byref(rr)))
         self.last_solve = dict(iters=it.value, relres=rr.value)
@@ -215,7 +233,9 @@ class ShellDevice:
             self.last_solve = dict(self._mg.last_solve)
             return out
         if getattr(self, "_direct", None) is not None:
-            return self.solve_direct(rhs, self._direct["refine"], zero_bc=(fn is self.lib.femo_solve_adjoint))
+            out = self._direct_or_none(rhs, fn is self.lib.femo_solve_adjoint)
+            if out is not None:
+                return out
         out = np.empty(self.ndof)
         it = C.c_int(0); rr = C.c_double(0.0)
         L.check(fn(self._ctx, L.ptr(rhs), L.ptr(out), float(rtol), int(max_it), C.byref(it), C.byref(rr), 0))

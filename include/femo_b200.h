@@ -180,6 +180,10 @@ int femo_halo_accumulate(femo_ctx* ctx, double* x, int on_device);
 /* sum n <= 8 host scalars over ranks; collective */
 int femo_dist_allreduce(femo_ctx* ctx, double* vals, int n);
 int femo_dist_counts(femo_ctx* ctx, int64_t* halo_exchanges, int64_t* allreduces);
+/* diagnostics (set FEMO_TRACE_OVERLAP=1 before femo_dist_setup): CUDA-event times of the last overlapped operator
+ * application in ms after its start: [0] halo exchange complete (communication stream), [1] interior rows complete,
+ * [2] boundary rows complete.  [0] <= [1]: the exchange was hidden behind the interior rows. */
+int femo_dist_overlap_info(femo_ctx* ctx, double* ms3);
 
 /* ---- geometric multigrid preconditioner for the state / adjoint solves --------------------------------
  * Replaces the sparse LU (MUMPS through PETSc `preonly + lu`, femo_alpha/fea/utils_dolfinx.py:438-468 setUpKSP /

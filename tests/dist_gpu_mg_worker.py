@@ -12,6 +12,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+# relres 1e-11 leaves a forward error of ~1e-8 on this plate (kappa ~ 1e9): converge further so that the 1e-8 comparison
+# with the oracle has a margin
+RTOL = 1e-13
+
+
 def main():
     import torch
     import torch.distributed as dist
@@ -35,10 +40,10 @@ def main():
         h.set_input(k, v)
     clamp = lambda xx: np.less(xx[0], 3e-16)
     h.set_strong_bc(clamp)
-    its, rr = h.solve_state(rtol=1e-11, max_it=300)
+    its, rr = h.solve_state(rtol=RTOL, max_it=400)
     w_loc = h.fine.dev.get_state().reshape(-1, 3)
     # adjoint of the compliance: A lam = dC/du (local right-hand side; owned entries are complete)
-    lam_loc = h.solve_adjoint(h.fine.dev.output_grad("compliance", "disp_solid"), rtol=1e-11, max_it=300).reshape(-1, 3)
+    lam_loc = h.solve_adjoint(h.fine.dev.output_grad("compliance", "disp_solid"), rtol=RTOL, max_it=400).reshape(-1, 3)
     its_a = h.last_solve["iters"]
     o = RMShellOracle(nodes_f, quads_f, False, False)
     o.set_inputs(**inputs)
@@ -58,13 +63,13 @@ def main():
     for k, v in inputs.items():
         s.set_input(k, v)
     s.set_strong_bc(clamp)
-    its1, _ = s.solve_state(rtol=1e-11, max_it=300)
+    its1, _ = s.solve_state(rtol=RTOL, max_it=400)
     s.close()
     hx, ar = h.fine.comm_counts()
     print("rank %d/%d distributed V-cycle PCG (%d distributed levels of %d): state %d / adjoint %d iterations (single GPU: %d), "
           "relres %.1e | u err %.2e | lam err %.2e | %d halo exchanges, %d all-reduces on the finest level"
           % (rank, world, n_dist, levels, its, its_a, its1, rr, err, err_a, hx, ar), flush=True)
-    ok = err <= 1e-8 and err_a <= 1e-8 and 0 < its <= its1 + 2 and rr <= 1e-11
+    ok = err <= 1e-8 and err_a <= 1e-8 and 0 < its <= its1 + 2 and rr <= RTOL
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     h.close()

@@ -232,6 +232,32 @@ def test_tiled_assembly_many_chunks(built_lib, monkeypatch, shape, ws):
         d.close()
 
 
+@pytest.mark.parametrize("ws", ["2", "1"])
+def test_halo_records_staged_in_shared_memory_change_nothing(built_lib, monkeypatch, ws):
+    """The tiled kernel reads the records of a chunk's halo cells from global memory per halo item (default) or stages them
+    in shared memory (FEMO_TILE_HREC=1, double-buffered cp.async): same numbers in the same order, so the
+    matrices are bitwise equal -- on a distorted plate with ~90 chunks, tilted out of the xy plane."""
+    from oracle.rm_shell_ref import plate_mesh
+    from femo_alpha_b200.shell_device import ShellDevice
+    monkeypatch.setenv("FEMO_TILE_WS", ws)
+    rng = np.random.default_rng(9)
+    nodes, quads = plate_mesh(48, 30, 4.0, 3.0)
+    nn = nodes.shape[0]
+    nodes[:, :2] += 0.1 * (4.0 / 48) * rng.standard_normal((nn, 2))
+    nodes[:, 2] = 0.3 * nodes[:, 0]
+    inp = dict(thickness=0.05 * (1 + 0.5 * rng.random(nn)), E=1e6 * (1 + 0.2 * rng.random(nn)), nu=0.25 + 0.1 * rng.random(nn))
+    vals = []
+    for hrec in ("1", "0"):
+        monkeypatch.setenv("FEMO_TILE_HREC", hrec)
+        d = ShellDevice(nodes, quads)
+        assert d.sizes.all_planar == 1
+        for k, v in inp.items():
+            d.set_input(k, v)
+        vals.append(d.get_bsr()[2].copy())
+        d.close()
+    assert np.array_equal(vals[0], vals[1])
+
+
 def test_jacobian_at_benchmark_size_matches_oracle_strip(built_lib):
     """Parity at the size bench.py runs (config 3: 816 x 816 cells, 10 002 534 dofs, 81.9 M blocks; every persistent CTA of
     the tiled kernel walks ~281 chunks, int32 positions up to 8.2e7).  The C port of the oracle assembles two 816 x 6-cell
