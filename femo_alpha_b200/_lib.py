@@ -54,6 +54,7 @@ SIGNATURES = {
     "femo_get_state": [_P, _P, C.c_int],
     "femo_assemble_jacobian": [_P],
     "femo_assemble_residual": [_P, _P, _P, C.c_int],
+    "femo_evaluate_residual": [_P, C.c_int, _P, _P, _P, _P, _P],
     "femo_assemble_load": [_P, _P, C.c_int],
     "femo_jacobian_apply": [_P, _P, _P, C.c_int, C.c_int],
     "femo_get_bsr": [_P, _P, _P, _P, C.c_int],

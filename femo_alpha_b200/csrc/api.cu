@@ -172,6 +172,8 @@ int femo_ctx_destroy(femo_ctx* c) {
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  for (auto& e : c->ev_copy) if (e) cudaEventDestroy(e);
   delete c;
   return 0;
 }
@@ -387,6 +389,75 @@ int femo_assemble_residual(femo_ctx* c, const double* w, double* R, int on_devic
   TRY(check_launch(c, "k_axpby"));
   c->launches += 1;
   return copy_out(c, R, c->tmp, c->ndof, on_device);
+}
+
+// One evaluation of the residual through host buffers with the copies overlapped (bench.py's end-to-end figure; what
+// StateOperation.compute_residual does per call: update every input, then assembleVector(R), state_operation.py:86-131):
+//   * inputs the Jacobian depends on (thickness, E, nu, uhat) go up first on the context's stream, dR/du is assembled;
+//   * the other inputs (F_solid, density) and the state go up on a second stream WHILE the assembly runs;
+//   * R = K w - F is produced in row ranges and every range starts its way back to the host as soon as it is complete,
+//     while the SpMV still works on the next one.
+// which[i] / data[i] / sizes[i]: input ids and HOST arrays (pinned memory makes the copies asynchronous; pageable memory
+// works, serialised by the driver); w_host: state (n_dof) or null for the resident one; R_host: n_dof doubles.
+int femo_evaluate_residual(femo_ctx* c, int n_in, const int* which, const double* const* data, const int64_t* sizes,
+                           const double* w_host, double* R_host) {
+  NEED_SHELL(c, "femo_evaluate_residual");
+  if (n_in < 0 || (n_in > 0 && (!which || !data || !sizes)) || !R_host) return femo_fail("femo_evaluate_residual: bad arguments");
+  if (c->world > 1) return femo_fail("femo_evaluate_residual: single-GPU contexts (multi-GPU ranks use femo_set_input + femo_assemble_residual)");
+  DevGuard g(c->device);
+  if (!c->copy_stream) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (auto& e : c->ev_copy) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  const int64_t n = c->ndof;
+  bool matrix_changed = false, uhat_given = false;
+  for (int pass = 0; pass < 2; ++pass)                     // pass 0: Jacobian inputs on the main stream; pass 1: the rest on the copy stream
+    for (int i = 0; i < n_in; ++i) {
+      int64_t want = 0;
+      double** slot = input_slot(c, which[i], &want);
+      if (!slot) return femo_fail("femo_evaluate_residual: unknown input id");
+      if (sizes[i] != want && sizes[i] != 1) return femo_fail("femo_evaluate_residual: size mismatch for input " + std::to_string(which[i]));
+      const bool for_matrix = which[i] != FEMO_F_SOLID && (which[i] != FEMO_DENSITY || c->dyn_on);
+      if (for_matrix != (pass == 0)) continue;
+      cudaStream_t st = pass == 0 ? c->stream : c->copy_stream;
+      if (sizes[i] == 1) {                                  // utils_dolfinx.update: a single value fills the function
+        cudaStream_t keep = c->stream; c->stream = st;
+        const int r = fill(c, *slot, want, data[i][0]);
+        c->stream = keep;
+        TRY(r);
+        if (which[i] == FEMO_UHAT) c->uhat_zero = (data[i][0] == 0.0);
+      } else {
+        CUDA_TRY(cudaMemcpyAsync(*slot, data[i], sizeof(double) * want, cudaMemcpyHostToDevice, st));
+        if (which[i] == FEMO_UHAT) uhat_given = true;
+      }
+      if (for_matrix) matrix_changed = true;
+    }
+  if (w_host) CUDA_TRY(cudaMemcpyAsync(c->tmp2, w_host, sizeof(double) * n, cudaMemcpyHostToDevice, c->copy_stream));
+  CUDA_TRY(cudaEventRecord(c->ev_copy[0], c->copy_stream));
+  if (uhat_given) {                                         // which kernels run depends on uhat == 0 (as in femo_set_input)
+    double nrm = 0;
+    TRY(dev_dot(c, c->uhat, c->uhat, 3 * c->nn, &nrm));
+    c->uhat_zero = (nrm == 0.0);
+  }
+  if (matrix_changed) { c->jac_valid = false; c->prec_valid = false; }
+  if (!c->jac_valid) TRY(assemble_jacobian(c));             // runs while F_solid / density / w are still on their way up
+  CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_copy[0], 0));
+  TRY(assemble_load(c, c->b));
+  const double* wd = w_host ? c->tmp2 : c->w;
+  const int NR = 4;                                         // row ranges; the last ones hide the first ones' way back
+  for (int j = 0; j < NR; ++j) {
+    const int64_t r0 = c->nb * j / NR, r1 = c->nb * (j + 1) / NR;
+    TRY(bsr_spmv_range(c, wd, c->tmp, r0, r1));
+    k_axpby<<<(unsigned)cdiv(3 * (r1 - r0), 256), 256, 0, c->stream>>>(1.0, c->tmp + 3 * r0, -1.0, c->b + 3 * r0, 3 * (r1 - r0), c->tmp + 3 * r0);
+    c->launches += 1;
+    CUDA_TRY(cudaEventRecord(c->ev_copy[1 + j], c->stream));
+    CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_copy[1 + j], 0));
+    CUDA_TRY(cudaMemcpyAsync(R_host + 3 * r0, c->tmp + 3 * r0, sizeof(double) * 3 * (r1 - r0), cudaMemcpyDeviceToHost, c->copy_stream));
+  }
+  TRY(check_launch(c, "femo_evaluate_residual"));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->copy_stream));
+  return 0;
 }
 
 int femo_jacobian_apply(femo_ctx* c, const double* x, double* y, int with_bc, int on_device) {

@@ -43,6 +43,11 @@ struct CoarseSolver {
   int *flag = nullptr;                // device: set when a Cholesky pivot is not positive
   double bytes = 0;
   bool factored = false;
+  // the sweeps are 2 small kernels per level set (hundreds of launches, launch-bound): captured once per (b, x) pointer
+  // pair into a CUDA graph and replayed; the factor arrays never move, so a re-factorisation keeps the graphs valid
+  struct SweepGraph { const double* b = nullptr; double* x = nullptr; cudaGraphExec_t exec = nullptr; };
+  SweepGraph graphs[4];
+  cudaStream_t gstream = nullptr;     // capture needs a non-legacy stream
 };
 
 namespace {
@@ -380,6 +385,8 @@ int spd_inverse_dev(femo_ctx* c, CoarseSolver* cs, double* S, double* L, double*
 
 void coarse_free(CoarseSolver* cs) {
   if (!cs) return;
+  for (auto& g : cs->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (cs->gstream) cudaStreamDestroy(cs->gstream);
   dev_free(&cs->perm); dev_free(&cs->order); dev_free(&cs->node_lev); dev_free(&cs->node_pos);
   dev_free(&cs->Sinv); dev_free(&cs->G); dev_free(&cs->GT); dev_free(&cs->z); dev_free(&cs->xp); dev_free(&cs->dense);
   dev_free(&cs->flag);
@@ -509,16 +516,7 @@ int coarse_factor(femo_ctx* c, CoarseSolver* cs) {
   return 0;
 }
 
-// x = A^-1 b (device vectors, caller's ordering; b and x may alias).  Kernels only: capturable in a CUDA graph.
-int coarse_apply(femo_ctx* c, CoarseSolver* cs, const double* b, double* x) {
-  if (!cs || !cs->factored) return femo_fail("direct solver: not factorised");
-  const int64_t n = cs->n;
-  if (cs->dense) {
-    k_gather_perm<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(b, cs->perm, n, cs->z);
-    k_dense_apply<<<(unsigned)cdiv(n * 32, 256), 256, 0, c->stream>>>(cs->dense, cs->z, n, cs->perm, x);
-    c->launches += 2;
-    return check_launch(c, "coarse: dense apply");
-  }
+static int coarse_sweeps(femo_ctx* c, CoarseSolver* cs, const double* b, double* x) {
   for (int l = 0; l < cs->nl; ++l) {
     const int64_t m = cs->lp[l + 1] - cs->lp[l], mp = l ? cs->lp[l] - cs->lp[l - 1] : 0;
     k_sweep_fwd<<<(unsigned)cdiv(m * 32, 256), 256, 0, c->stream>>>(cs->G + cs->oG[l], (int)m, (int)mp, l ? cs->z + cs->lp[l - 1] : nullptr, b,
@@ -533,6 +531,50 @@ int coarse_apply(femo_ctx* c, CoarseSolver* cs, const double* b, double* x) {
   }
   c->launches += 2 * (int64_t)cs->nl;
   return check_launch(c, "coarse: sweeps");
+}
+
+// x = A^-1 b (device vectors, caller's ordering; b and x may alias).  Kernels only: capturable in a CUDA graph.
+int coarse_apply(femo_ctx* c, CoarseSolver* cs, const double* b, double* x) {
+  if (!cs || !cs->factored) return femo_fail("direct solver: not factorised");
+  const int64_t n = cs->n;
+  if (cs->dense) {
+    k_gather_perm<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(b, cs->perm, n, cs->z);
+    k_dense_apply<<<(unsigned)cdiv(n * 32, 256), 256, 0, c->stream>>>(cs->dense, cs->z, n, cs->perm, x);
+    c->launches += 2;
+    return check_launch(c, "coarse: dense apply");
+  }
+  // graph replay of the sweeps (FEMO_COARSE_GRAPH=0: plain launches).  Not while the caller itself is capturing.
+  static const bool use_graph = !(getenv("FEMO_COARSE_GRAPH") && getenv("FEMO_COARSE_GRAPH")[0] == '0');
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (use_graph) cudaStreamIsCapturing(c->stream, &st);
+  if (!use_graph || st != cudaStreamCaptureStatusNone || cs->nl < 8) return coarse_sweeps(c, cs, b, x);
+  CoarseSolver::SweepGraph* g = nullptr;
+  for (auto& e : cs->graphs) if (e.exec && e.b == b && e.x == x) g = &e;
+  if (!g) {
+    for (auto& e : cs->graphs) if (!e.exec) { g = &e; break; }
+    if (!g) return coarse_sweeps(c, cs, b, x);                       // more pointer pairs than slots: plain launches
+    if (!cs->gstream) CUDA_TRY(cudaStreamCreateWithFlags(&cs->gstream, cudaStreamNonBlocking));
+    cudaStream_t keep = c->stream;
+    const int64_t keep_launches = c->launches;
+    c->stream = cs->gstream;
+    cudaGraph_t graph = nullptr;
+    int r = 0;
+    if (cudaStreamBeginCapture(cs->gstream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) r = 1;
+    if (r == 0) r = coarse_sweeps(c, cs, b, x);
+    const cudaError_t ee = cudaStreamEndCapture(cs->gstream, &graph);
+    c->stream = keep; c->launches = keep_launches;
+    if (r != 0 || ee != cudaSuccess || !graph || cudaGraphInstantiate(&g->exec, graph, 0) != cudaSuccess) {
+      if (graph) cudaGraphDestroy(graph);
+      g->exec = nullptr;
+      cudaGetLastError();
+      return coarse_sweeps(c, cs, b, x);                             // capture unavailable: plain launches
+    }
+    cudaGraphDestroy(graph);
+    g->b = b; g->x = x;
+  }
+  CUDA_TRY(cudaGraphLaunch(g->exec, c->stream));
+  c->launches += 2 * (int64_t)cs->nl;
+  return 0;
 }
 
 int coarse_num_levels(const CoarseSolver* cs) { return cs ? cs->nl : 0; }

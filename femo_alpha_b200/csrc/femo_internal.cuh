@@ -186,6 +186,8 @@ struct femo_ctx {
   double t_rec = 0, t_asm = 0, t_solve = 0, t_iter = 0;
   double dmma_tf = 0;           // last measured fp64 mma.sync rate (TFLOP/s)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t copy_stream = nullptr;   // femo_evaluate_residual: host <-> device copies overlapped with the kernels
+  cudaEvent_t ev_copy[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   // dynamic (time-stepped) operator, dynamic.cu: while dyn_on, `vals` holds A_eff = (2/dt^2) M + K/2 (the matrix every
   // solver / preconditioner / multigrid level works on) and `vals_K` the stiffness K; `mvals` one scalar per BSR block
   // (the mass matrix is block-scalar: rho h int phi_a phi_b on u-u blocks, rho h hE^2 int N_a N_b on theta-theta blocks)
@@ -243,6 +245,7 @@ int assemble_jacobian(femo_ctx* c);                                       // dyn
 int assemble_load(femo_ctx* c, double* F_dev);                            // assemble.cu
 int bsr_spmv(femo_ctx* c, const double* x, double* y, int with_bc);       // solver.cu
 int bsr_spmv_vals(femo_ctx* c, const double* vals, const double* x, double* y, int with_bc);   // solver.cu
+int bsr_spmv_range(femo_ctx* c, const double* x, double* y, int64_t r0, int64_t r1);           // solver.cu: block rows [r0, r1) of K x
 int penalty_apply(femo_ctx* c, const double* x, double* y, double sign);  // solver.cu  y += sign * P x
 int precond_setup(femo_ctx* c);                                           // solver.cu
 int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, int* iters,
@@ -259,6 +262,8 @@ int halo_exchange(femo_ctx* c, double* x);                                // dis
 int halo_exchange_begin(femo_ctx* c, double* x);                          // dist.cu: the same on the communication stream ...
 int halo_exchange_end(femo_ctx* c);                                       // ... the context's stream waits for it here
 int dist_spmv(femo_ctx* c, double* x, double* y, double* dot_int, double* dot_bnd, int* n_int, int* n_bnd);   // solver.cu
+int vals_to_float(femo_ctx* c, float* out);                               // solver.cu: fp32 copy of c->vals (nnzb * 9)
+int bsr_spmv_f32(femo_ctx* c, const float* vals32, double* x, double* y); // solver.cu: y = A32 x (BCs; halo overlapped when distributed)
 int halo_accumulate(femo_ctx* c, double* x);                              // dist.cu: owners += ghost copies (reverse halo)
 int dist_allreduce_sum(femo_ctx* c, double* dev_vals, int n);             // dist.cu: in-place on the stream
 int dist_allreduce_host(femo_ctx* c, double* host_vals, int n);           // dist.cu

@@ -25,6 +25,7 @@ struct MgLevel {
   double *P_w = nullptr, *R_w = nullptr;
   double lmax = 0;
   double *x = nullptr, *b = nullptr, *r = nullptr, *d = nullptr, *t = nullptr;
+  float* vals32 = nullptr;     // fp32 copy of the level's block values for the smoother / residual inside the V-cycle
   double *ev = nullptr;        // last iterate of the power iteration (warm start of the next set-up)
   int power_its = 0;
 };
@@ -108,8 +109,11 @@ __global__ void k_mg_mask(int64_t n, const double* __restrict__ mask, double* __
   if (i < n) x[i] *= mask[i];
 }
 
-// y = A x of a level; on a distributed level the ghosts of x are refreshed first (overlapped with the interior rows)
-int mg_spmv(femo_ctx* c, double* x, double* y) {
+// y = A x of a level; on a distributed level the ghosts of x are refreshed first (overlapped with the interior rows).
+// v32: the level's fp32 copy -- used inside the preconditioner only (smoothing, residual before restriction, spectral
+// bound), never for the operator of the outer PCG
+int mg_spmv(femo_ctx* c, double* x, double* y, const float* v32 = nullptr) {
+  if (v32) return bsr_spmv_f32(c, v32, x, y);
   if (c->world > 1) return dist_spmv(c, x, y, nullptr, nullptr, nullptr, nullptr);
   return bsr_spmv(c, x, y, 1);
 }
@@ -127,12 +131,12 @@ int mg_smooth(femo_mg* m, int l, bool zero_guess) {
         k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, nullptr, 0.0, 0.0, 1.0 / theta, 1, c->dinv6, c->dinv3, c->nn, c->nq2,
                                                  Lv.r, Lv.d, Lv.x);
       } else {
-        TRY(mg_spmv(c, Lv.x, Lv.t));                        // distributed level: halo exchange hidden behind the interior rows
+        TRY(mg_spmv(c, Lv.x, Lv.t, Lv.vals32));             // distributed level: halo exchange hidden behind the interior rows
         k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.b, Lv.t, 1.0, 0.0, 1.0 / theta, 0, c->dinv6, c->dinv3, c->nn, c->nq2,
                                                  Lv.r, Lv.d, Lv.x);
       }
     } else {
-      TRY(mg_spmv(c, Lv.d, Lv.t));
+      TRY(mg_spmv(c, Lv.d, Lv.t, Lv.vals32));
       const double rho_new = 1.0 / (2.0 * sigma - rho);
       k_cheb_step<<<grid, 128, 0, c->stream>>>(Lv.r, Lv.t, 1.0, rho_new * rho, 2.0 * rho_new / delta, 0, c->dinv6, c->dinv3,
                                                c->nn, c->nq2, Lv.r, Lv.d, Lv.x);
@@ -153,7 +157,7 @@ int mg_vcycle(femo_mg* m, int l) {
   }
   MgLevel& Lc = m->L[l + 1];
   TRY(mg_smooth(m, l, true));
-  TRY(mg_spmv(c, Lv.x, Lv.t));
+  TRY(mg_spmv(c, Lv.x, Lv.t, Lv.vals32));
   k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, Lv.b, -1.0, Lv.t, Lv.r);
   k_transfer<<<(unsigned)cdiv(3 * Lv.nbc, 256), 256, 0, c->stream>>>(Lv.R_ptr, Lv.R_col, Lv.R_w, Lv.r, Lc.c->bcmask, Lv.nbc, 0, Lc.b);
   TRY(check_launch(c, "mg restrict"));
@@ -211,7 +215,7 @@ int mg_lambda_max(femo_mg* m, int l) {
     if (it > 0) { lam_prev = lam; lam = sqrt(nrm2); }
     if (it == max_it || (it >= min_it && fabs(lam - lam_prev) <= 1e-2 * lam)) break;
     k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0 / sqrt(nrm2), Lv.x, 0.0, Lv.x, Lv.b);
-    TRY(mg_spmv(c, Lv.b, Lv.t));
+    TRY(mg_spmv(c, Lv.b, Lv.t, Lv.vals32));
     k_cheb_step<<<(unsigned)cdiv(c->nq2, 128), 128, 0, c->stream>>>(Lv.t, nullptr, 0.0, 0.0, 1.0, 1, c->dinv6, c->dinv3, c->nn,
                                                                     c->nq2, Lv.r, Lv.d, Lv.x);
     TRY(check_launch(c, "mg power iteration"));
@@ -256,7 +260,7 @@ int femo_mg_create(int n_levels, femo_ctx** ctxs, femo_mg** out) {
 
 static void mg_free_level(MgLevel& Lv) {
   dev_free(&Lv.P_ptr); dev_free(&Lv.P_col); dev_free(&Lv.P_w); dev_free(&Lv.R_ptr); dev_free(&Lv.R_col); dev_free(&Lv.R_w);
-  dev_free(&Lv.x); dev_free(&Lv.b); dev_free(&Lv.r); dev_free(&Lv.d); dev_free(&Lv.t); dev_free(&Lv.ev);
+  dev_free(&Lv.x); dev_free(&Lv.b); dev_free(&Lv.r); dev_free(&Lv.d); dev_free(&Lv.t); dev_free(&Lv.ev); dev_free(&Lv.vals32);
 }
 
 int femo_mg_destroy(femo_mg* m) {
@@ -308,6 +312,13 @@ int femo_mg_setup(femo_mg* m, int cheb_degree, int reuse_coarse_inverse) {
     femo_ctx* c = m->L[l].c;
     if (!c->jac_valid) TRY(assemble_jacobian(c));
     TRY(precond_setup(c));
+    // fp32 copy for the smoothers of every level but the coarsest (FEMO_MG_FP32=0: smooth with the fp64 values)
+    const char* e32 = getenv("FEMO_MG_FP32");
+    const bool want32 = !(e32 && e32[0] == '0') && l + 1 < m->L.size();
+    if (want32) {
+      if (!m->L[l].vals32) TRY(dev_alloc(&m->L[l].vals32, (size_t)c->nnzb * 9));
+      TRY(vals_to_float(c, m->L[l].vals32));
+    } else dev_free(&m->L[l].vals32);
   }
   cudaEventRecord(e1, st);
   for (size_t l = 0; l < m->L.size(); ++l) {

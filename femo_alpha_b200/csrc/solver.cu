@@ -66,11 +66,13 @@ __device__ __forceinline__ double sum_partials(const double* __restrict__ part, 
 
 // y = K x or y = A x.  LANES lanes cooperate on one block row, one block per lane and pass.
 // Optionally accumulates the partial dot x.y per CTA (deterministic) into dot_part[blockIdx.x].
-template <int LANES, int MINB>
+// VT: storage type of the block values -- double (the operator) or float (the copy the multigrid smoothers use: half the
+// bytes of a bandwidth-bound kernel; products and sums are fp64 either way)
+template <int LANES, int MINB, typename VT = double>
 __global__ void __launch_bounds__(256, MINB)
-k_spmv(const int32_t* __restrict__ rowptr, const uint32_t* __restrict__ colw, const double* __restrict__ vals,
+k_spmv(const int32_t* __restrict__ rowptr, const uint32_t* __restrict__ colw, const VT* __restrict__ vals,
        const double* __restrict__ x, const uint8_t* __restrict__ rbits, int64_t nb, double* __restrict__ y,
-       double* __restrict__ dot_part, const double* __restrict__ own, const int32_t* __restrict__ rows) {
+       double* __restrict__ dot_part, const double* __restrict__ own, const int32_t* __restrict__ rows, int64_t row_base = 0) {
   const int lane = threadIdx.x % LANES;
   constexpr int GPW = 32 / LANES;                       // row groups per warp
   const int sub = (threadIdx.x & 31) / LANES;
@@ -81,15 +83,16 @@ k_spmv(const int32_t* __restrict__ rowptr, const uint32_t* __restrict__ colw, co
   for (int64_t rb = warp * GPW; rb < nb; rb += nwarp * GPW) {
     // `rows` (multi-GPU): the nb listed block rows (interior or boundary rows of the owned part); null: rows 0 .. nb-1
     const bool valid = rb + sub < nb;
-    const int64_t row = rows ? (valid ? (int64_t)rows[rb + sub] : 0) : rb + sub;
+    // row_base (rows == null): the nb rows row_base .. row_base + nb - 1 (row ranges of the pipelined residual, api.cu)
+    const int64_t row = rows ? (valid ? (int64_t)rows[rb + sub] : 0) : row_base + rb + sub;
     const int32_t s = valid ? rowptr[row] : 0, e = valid ? rowptr[row + 1] : 0;
     double y0 = 0, y1 = 0, y2 = 0;
     for (int32_t k = s + lane; k < e; k += LANES) {
       const uint32_t w = colw[k];
-      const double* ap = vals + (int64_t)k * 9;
+      const VT* ap = vals + (int64_t)k * 9;
       double a[9];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) a[i] = ap[i];
+      for (int i = 0; i < 9; ++i) a[i] = (double)ap[i];
       const double* xp = x + 3 * COL_OF(w);
       const double x0 = (w & 0x20000000u) ? 0.0 : xp[0], x1 = (w & 0x40000000u) ? 0.0 : xp[1], x2 = (w & 0x80000000u) ? 0.0 : xp[2];
       y0 += a[0] * x0 + a[1] * x1 + a[2] * x2;
@@ -473,6 +476,47 @@ int bsr_spmv_vals(femo_ctx* c, const double* vals, const double* x, double* y, i
   TRY(check_launch(c, "k_spmv"));
   c->launches += 1;
   return 0;
+}
+
+// ---- fp32 copy of the block values (multigrid smoothers, mg.cu) ---------------------------------------------------------------
+__global__ void k_vals_to_float(const double* __restrict__ v, int64_t n, float* __restrict__ o) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (int64_t)blockDim.x) o[i] = (float)v[i];
+}
+int vals_to_float(femo_ctx* c, float* out) {
+  k_vals_to_float<<<148 * 8, 256, 0, c->stream>>>(c->vals, c->nnzb * 9, out);
+  c->launches += 1;
+  return check_launch(c, "k_vals_to_float");
+}
+// y = A32 x (BCs applied) with the context's pattern; multi-GPU contexts: halo exchange overlapped with the interior rows
+// exactly like dist_spmv
+int bsr_spmv_f32(femo_ctx* c, const float* vals32, double* x, double* y) {
+  if (c->world <= 1 || !c->rows_int) {
+    if (c->world > 1) TRY(halo_exchange(c, x));
+    k_spmv<8, 6, float><<<spmv_grid(), 256, 0, c->stream>>>(c->rowptr, c->colbc, vals32, x, c->bcbits, c->nb, y, nullptr, nullptr, nullptr);
+    c->launches += 1;
+    return check_launch(c, "k_spmv<float>");
+  }
+  TRY(halo_exchange_begin(c, x));
+  const int gi = (int)std::min<int64_t>(spmv_grid(), std::max<int64_t>(1, cdiv(c->n_rows_int, 32)));
+  const int gb = (int)std::min<int64_t>(spmv_grid(), std::max<int64_t>(1, cdiv(c->n_rows_bnd, 32)));
+  if (c->n_rows_int > 0)
+    k_spmv<8, 6, float><<<gi, 256, 0, c->stream>>>(c->rowptr, c->colbc, vals32, x, c->bcbits, c->n_rows_int, y, nullptr, c->own, c->rows_int);
+  TRY(halo_exchange_end(c));
+  if (c->n_rows_bnd > 0)
+    k_spmv<8, 6, float><<<gb, 256, 0, c->stream>>>(c->rowptr, c->colbc, vals32, x, c->bcbits, c->n_rows_bnd, y, nullptr, c->own, c->rows_bnd);
+  c->launches += 2;
+  return check_launch(c, "k_spmv<float> (interior / boundary rows)");
+}
+
+// y[rows r0 .. r1) = K x (no BCs), the other rows of y untouched: row ranges of the pipelined residual (femo_evaluate_residual)
+int bsr_spmv_range(femo_ctx* c, const double* x, double* y, int64_t r0, int64_t r1) {
+  if (!c->jac_valid) return femo_fail("Jacobian not assembled");
+  if (r1 <= r0) return 0;
+  const int grid = (int)std::min<int64_t>(spmv_grid(), std::max<int64_t>(1, cdiv(r1 - r0, 32)));
+  k_spmv<8, 6><<<grid, 256, 0, c->stream>>>(c->rowptr, reinterpret_cast<const uint32_t*>(c->colidx), c->vals, x, nullptr, r1 - r0, y, nullptr,
+                                            nullptr, nullptr, r0);
+  c->launches += 1;
+  return check_launch(c, "k_spmv (row range)");
 }
 
 int penalty_apply(femo_ctx* c, const double* x, double* y, double sign) {

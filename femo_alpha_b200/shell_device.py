@@ -142,6 +142,26 @@ class ShellDevice:
         L.check(self.lib.femo_assemble_residual(self._ctx, L.ptr(w), L.ptr(out), L.on_device(out)))
         return out
 
+    def evaluate_residual(self, inputs, w=None, out=None):
+        """R(w; inputs) through host buffers in one call with the copies overlapped (femo_evaluate_residual): `inputs`
+        maps input names to host arrays (pinned memory makes the overlap real), `w` the state or None for the resident
+        one.  Equivalent to set_input for every entry followed by assemble_residual(w, out)."""
+        if self._mg is not None:                    # the coarser levels of a hierarchy follow through set_input
+            for k, v in inputs.items():
+                self.set_input(k, v)
+            return self.assemble_residual(w, out)
+        if out is None:
+            out = np.empty(self.ndof)
+        names = list(inputs)
+        arrs = [np.ascontiguousarray(np.asarray(inputs[k], dtype=np.float64).ravel()) for k in names]
+        ids = (C.c_int * len(names))(*[self._arg_id(k) for k in names])
+        ptrs = (C.c_void_p * len(names))(*[a.ctypes.data for a in arrs])
+        sizes = (C.c_int64 * len(names))(*[a.size for a in arrs])
+        if w is not None:
+            w = np.ascontiguousarray(w, dtype=np.float64)
+        L.check(self.lib.femo_evaluate_residual(self._ctx, len(names), ids, ptrs, sizes, L.ptr(w), L.ptr(out)))
+        return out
+
     def assemble_load(self):
         out = np.empty(self.ndof)
         L.check(self.lib.femo_assemble_load(self._ctx, L.ptr(out), 0))

@@ -103,6 +103,15 @@ int femo_assemble_jacobian(femo_ctx* ctx);
 /* replaces assembleVector(residual_form) (fea/utils_dolfinx.py:194-198):
  * R = dR/du * w - load(F_solid); w = NULL uses the stored state. */
 int femo_assemble_residual(femo_ctx* ctx, const double* w, double* R, int on_device);
+/* One residual evaluation through HOST buffers with the copies overlapped -- what StateOperation does per call (update
+ * every input, then assembleVector(R): csdl_alpha_opt/state_operation.py:86-131, fea/utils_dolfinx.py:174-198) as ONE
+ * call: the inputs dR/du depends on go up first and the Jacobian is assembled while F_solid / density / the state are
+ * still on their way up on a second stream; R = K w - F comes back in row ranges while the SpMV still works on the next
+ * one.  which / data / sizes: n_in input ids with their host arrays (size 1 = fill, like femo_set_input); w_host: the
+ * state (n_dof) or NULL for the resident one; R_host: n_dof doubles.  Pinned host memory makes the overlap real.
+ * Single-GPU contexts. */
+int femo_evaluate_residual(femo_ctx* ctx, int n_in, const int* which, const double* const* data, const int64_t* sizes,
+                           const double* w_host, double* R_host);
 /* load vector int f . du J dx only */
 int femo_assemble_load(femo_ctx* ctx, double* F, int on_device);
 /* y = dR/du x (no BCs) / y = A x (with BCs); replaces computeMatVecProductFwd (utils_dolfinx.py:275-283) */

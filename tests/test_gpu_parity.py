@@ -232,6 +232,31 @@ def test_tiled_assembly_many_chunks(built_lib, monkeypatch, shape, ws):
         d.close()
 
 
+@pytest.mark.parametrize("name", ["plate_varh", "plate_dg0", "warped"])
+def test_evaluate_residual_equals_separate_calls(built_lib, name):
+    """femo_evaluate_residual (inputs up, assembly, residual back in row ranges, copies on a second stream) against
+    set_input + assemble_residual and against the oracle; twice, with changed inputs, resident and explicit state."""
+    p = make_problem(name)
+    o, d = oracle_for(p), device_for(p)
+    rng = np.random.default_rng(5)
+    w = rng.standard_normal(d.ndof)
+    for scale in (1.0, 1.2):
+        inputs = {k: scale * np.asarray(p[k]) if k == "thickness" else np.asarray(p[k]) for k in ("thickness", "E", "nu", "F_solid")}
+        if p["uhat"] is not None:
+            inputs["uhat"] = np.asarray(p["uhat"])
+        got = d.evaluate_residual(inputs, w)
+        for k, v in inputs.items():
+            d.set_input(k, v)
+        ref = d.assemble_residual(w)
+        assert np.array_equal(got, ref)
+        o.set_inputs(thickness=inputs["thickness"])
+        R = o.assemble_residual(w)
+        assert np.abs(got - R).max() <= 1e-12 * np.abs(R).max()
+    d.set_state(w)
+    assert np.array_equal(d.evaluate_residual({"thickness": inputs["thickness"]}), ref)      # resident state, one input
+    d.close()
+
+
 @pytest.mark.parametrize("ws", ["2", "1"])
 def test_halo_records_staged_in_shared_memory_change_nothing(built_lib, monkeypatch, ws):
     """The tiled kernel reads the records of a chunk's halo cells from global memory per halo item (default) or stages them
