@@ -10,6 +10,7 @@
 //                    precomputed cell->nnz permutation); contributions to the same BSR block
 //                    are summed in a fixed order through shared memory, each block of the
 //                    matrix is written exactly once -> bitwise reproducible, no atomics.
+//   k_warped_elem + k_warped_gather   warped meshes: element matrices per group of 32 cells, then one thread per block
 #include "femo_internal.cuh"
 
 namespace {
@@ -19,7 +20,7 @@ __global__ void k_cell_records(const double* __restrict__ xyz, const int32_t* __
                                const double* __restrict__ uhat, const double* __restrict__ h,
                                const double* __restrict__ E, const double* __restrict__ nu,
                                const double* __restrict__ hE, const Tables* __restrict__ tab, int64_t nc, int nq,
-                               int ewm, int nqf, int stride, double* __restrict__ rec) {
+                               int ewm, int nqf, int stride, int grouped, double* __restrict__ rec) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= nc * nq) return;
   int64_t cell = i / nq; int q = (int)(i - cell * nq);
@@ -42,7 +43,10 @@ __global__ void k_cell_records(const double* __restrict__ xyz, const int32_t* __
   }
   Coefs cf = clt_coefs(hq, Eq, nuq, hE[cell], g.Ju, 0);
   double wd = tab->W[q] * g.detJ;
-  double* r = rec + cell * stride + REC_HEADER + q * nqf;
+  // grouped != 0 (warped path of k_warped_elem): [group of 32 cells][q][field][lane] without the per-cell header, so that a
+  // CTA stages its group with one contiguous copy and lane = cell reads are conflict-free
+  double loc[REC_NQF_WARPED];
+  double* r = grouped ? loc : rec + cell * stride + REC_HEADER + q * nqf;
   V3 E0 = g.E0, E1 = g.E1;
   if (nqf == REC_NQF_PLANAR) {
     // planar cell: any in-plane orthonormal frame gives the same energy (isotropic CLT), so one
@@ -70,6 +74,10 @@ __global__ void k_cell_records(const double* __restrict__ xyz, const int32_t* __
     V3 g0 = k00 * g.dE2_0 + k10 * g.dE2_1, g1 = k01 * g.dE2_0 + k11 * g.dE2_1;
     double* gg = r + REC_G0;
     gg[0] = g0.x; gg[1] = g0.y; gg[2] = g0.z; gg[3] = g1.x; gg[4] = g1.y; gg[5] = g1.z;
+  }
+  if (grouped) {
+    double* o = rec + (((cell >> 5) * (int64_t)nq + q) * nqf * 32 + (cell & 31));
+    for (int f = 0; f < nqf; ++f) o[f * 32] = loc[f];
   }
 }
 
@@ -152,8 +160,8 @@ __device__ __forceinline__ void block_planar(const double* __restrict__ rc, cons
   }
 }
 
-// general (warped / per-point frame) version
-__device__ __forceinline__ void block_general(const double* __restrict__ rc, const SmemTab& T, int nq, int a, int b,
+// general (warped / per-point frame) version (host + device: scripts/probes/warped_tile_host.cu checks warped_tile against it)
+__host__ __device__ __forceinline__ void block_general(const double* __restrict__ rc, const SmemTab& T, int nq, int a, int b,
                                               double* K) {
   const double* r = rc + REC_HEADER;
 #pragma unroll
@@ -260,6 +268,190 @@ k_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ cdest, 
   for (int k = 0; k < 9; ++k) o[k] = K[k];
 }
 
+// ------------------------------------------------------------------------------------------
+// Warped (non-planar) cells, cell-centric ("warped cells").  k_gather<false> re-reads the 3.2 KB
+// record of a cell once per contribution (169 times): L2-bound.  Here
+//   k_warped_elem    one CTA per group of 32 cells: the group's records are staged in shared memory once, lane = cell,
+//                    a warp takes one task = node a with WP_NB consecutive nodes b >= a of the same kind at a time
+//                    (the rows of a, scaled by the CLT coefficients, are shared by the tile); the 91 blocks a <= b of the
+//                    symmetric element matrix go to a scratch array  elem[group][pair][lane][9];
+//   k_warped_gather  one thread per BSR block: sums its contributions (block or transposed block) from the scratch in
+//                    list order and the CTA writes 256 blocks as one contiguous run.
+// Every block of the matrix is written once, the summation order is fixed: bitwise reproducible, no atomics.
+#define WP_PAIRS 91
+#define WP_THREADS 256
+#define WP_MAX_TASKS 91
+
+struct WpTasks { int n; unsigned char a[WP_MAX_TASKS], b0[WP_MAX_TASKS], nb[WP_MAX_TASKS]; };
+
+__host__ __device__ __forceinline__ int wp_pair(int a, int b) { return a * 13 - a * (a - 1) / 2 + (b - a); }   // a <= b
+
+#define WP_RF(f) r[(f) * 32]
+template <int NB>
+__host__ __device__ __forceinline__ void warped_tile(const double* __restrict__ rs, const SmemTab& T, int nq, int a, int b0, int nb,
+                                            double (*K)[9]) {
+#pragma unroll
+  for (int j = 0; j < NB; ++j)
+#pragma unroll
+    for (int i = 0; i < 9; ++i) K[j][i] = 0.0;
+  if (a < 9 && b0 < 9) {                                  // displacement - displacement
+    for (int q = 0; q < nq; ++q) {
+      const double* r = rs + q * (REC_NQF_WARPED * 32);
+      const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);
+      const V3 E0 = v3(WP_RF(REC_E0), WP_RF(REC_E0 + 1), WP_RF(REC_E0 + 2)), E1 = v3(WP_RF(REC_E0 + 3), WP_RF(REC_E0 + 4), WP_RF(REC_E0 + 5)),
+               E2 = v3(WP_RF(REC_E0 + 6), WP_RF(REC_E0 + 7), WP_RF(REC_E0 + 8));
+      const double cm11 = WP_RF(REC_CM11), cm12 = WP_RF(REC_CM12), cm33 = WP_RF(REC_CM33), cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
+      const double r0 = T.dphi2[q][a][0], r1 = T.dphi2[q][a][1];
+      const URows A = u_rows(r0 * k00 + r1 * k10, r0 * k01 + r1 * k11, E0, E1, E2);
+      const V3 c0 = cm11 * A.e0 + cm12 * A.e1, c1 = cm12 * A.e0 + cm11 * A.e1, c2 = cm33 * A.e2, c3 = cs * A.g0, c4 = cs * A.g1,
+               c5 = cd * A.dr;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        if (j < nb) {
+          const double s0 = T.dphi2[q][b0 + j][0], s1 = T.dphi2[q][b0 + j][1];
+          const URows B = u_rows(s0 * k00 + s1 * k10, s0 * k01 + s1 * k11, E0, E1, E2);
+          outer_acc(K[j], c0, B.e0); outer_acc(K[j], c1, B.e1); outer_acc(K[j], c2, B.e2);
+          outer_acc(K[j], c3, B.g0); outer_acc(K[j], c4, B.g1); outer_acc(K[j], c5, B.dr);
+        }
+      }
+    }
+  } else if (a < 9) {                                     // displacement (rows) - rotation (columns): shear and drilling only
+    for (int q = 0; q < nq; ++q) {
+      const double* r = rs + q * (REC_NQF_WARPED * 32);
+      const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);
+      const V3 E0 = v3(WP_RF(REC_E0), WP_RF(REC_E0 + 1), WP_RF(REC_E0 + 2)), E1 = v3(WP_RF(REC_E0 + 3), WP_RF(REC_E0 + 4), WP_RF(REC_E0 + 5)),
+               E2 = v3(WP_RF(REC_E0 + 6), WP_RF(REC_E0 + 7), WP_RF(REC_E0 + 8));
+      const double cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
+      const double r0 = T.dphi2[q][a][0], r1 = T.dphi2[q][a][1];
+      const URows A = u_rows(r0 * k00 + r1 * k10, r0 * k01 + r1 * k11, E0, E1, E2);
+      const V3 c3 = cs * A.g0, c4 = cs * A.g1, c5 = cd * A.dr;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        if (j < nb) {
+          const double N = T.n1[q][b0 + j - 9];
+          outer_acc(K[j], c3, N * E1); outer_acc(K[j], c4, (-N) * E0); outer_acc(K[j], c5, N * E2);
+        }
+      }
+    }
+  } else {                                                // rotation - rotation
+    const int ta = a - 9;
+    for (int q = 0; q < nq; ++q) {
+      const double* r = rs + q * (REC_NQF_WARPED * 32);
+      const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);
+      const V3 E0 = v3(WP_RF(REC_E0), WP_RF(REC_E0 + 1), WP_RF(REC_E0 + 2)), E1 = v3(WP_RF(REC_E0 + 3), WP_RF(REC_E0 + 4), WP_RF(REC_E0 + 5)),
+               E2 = v3(WP_RF(REC_E0 + 6), WP_RF(REC_E0 + 7), WP_RF(REC_E0 + 8));
+      const V3 g0 = v3(WP_RF(REC_G0), WP_RF(REC_G0 + 1), WP_RF(REC_G0 + 2)), g1 = v3(WP_RF(REC_G0 + 3), WP_RF(REC_G0 + 4), WP_RF(REC_G0 + 5));
+      const double hb = WP_RF(REC_HB), cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
+      const double cb11 = hb * WP_RF(REC_CM11), cb12 = hb * WP_RF(REC_CM12), cb33 = hb * WP_RF(REC_CM33);
+      const double r0 = T.dn1[q][ta][0], r1 = T.dn1[q][ta][1];
+      const TRows A = t_rows(T.n1[q][ta], r0 * k00 + r1 * k10, r0 * k01 + r1 * k11, E0, E1, E2, g0, g1);
+      const V3 c0 = cb11 * A.k0 + cb12 * A.k1, c1 = cb12 * A.k0 + cb11 * A.k1, c2 = cb33 * A.k2, c3 = cs * A.g0, c4 = cs * A.g1,
+               c5 = cd * A.dr;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        if (j < nb) {
+          const int tb = b0 + j - 9;
+          const double s0 = T.dn1[q][tb][0], s1 = T.dn1[q][tb][1];
+          const TRows B = t_rows(T.n1[q][tb], s0 * k00 + s1 * k10, s0 * k01 + s1 * k11, E0, E1, E2, g0, g1);
+          outer_acc(K[j], c0, B.k0); outer_acc(K[j], c1, B.k1); outer_acc(K[j], c2, B.k2);
+          outer_acc(K[j], c3, B.g0); outer_acc(K[j], c4, B.g1); outer_acc(K[j], c5, B.dr);
+        }
+      }
+    }
+  }
+}
+#undef WP_RF
+
+template <int NB>
+__global__ void __launch_bounds__(WP_THREADS, 2)
+k_warped_elem(const double* __restrict__ rec, const Tables* __restrict__ tab, int nq, WpTasks tasks, double* __restrict__ elem) {
+  extern __shared__ __align__(16) double wp_rec[];          // [nq][25][32]
+  __shared__ SmemTab T;
+  __shared__ int next_task;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int nf = nq * REC_NQF_WARPED;
+  {
+    double* d = (double*)&T;
+    const double* s0 = &tab->dphi2[0][0][0];
+    for (int i = tid; i < FEMO_MAX_NQ * 18; i += WP_THREADS) d[i] = s0[i];
+    double* d1 = &T.n1[0][0]; const double* s1 = &tab->n1[0][0];
+    for (int i = tid; i < FEMO_MAX_NQ * 4; i += WP_THREADS) d1[i] = s1[i];
+    double* d2 = &T.dn1[0][0][0]; const double* s2 = &tab->dn1[0][0][0];
+    for (int i = tid; i < FEMO_MAX_NQ * 8; i += WP_THREADS) d2[i] = s2[i];
+    const double2* src = reinterpret_cast<const double2*>(rec + (int64_t)blockIdx.x * nf * 32);
+    double2* dst = reinterpret_cast<double2*>(wp_rec);
+    for (int i = tid; i < nf * 16; i += WP_THREADS) dst[i] = src[i];
+    if (tid == 0) next_task = 0;
+  }
+  __syncthreads();
+  double* out = elem + (int64_t)blockIdx.x * (WP_PAIRS * 32 * 9) + lane * 9;
+  for (;;) {
+    int t = 0;
+    if (lane == 0) t = atomicAdd(&next_task, 1);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t >= tasks.n) break;
+    const int a = tasks.a[t], b0 = tasks.b0[t], nb = tasks.nb[t];
+    double K[NB][9];
+    warped_tile<NB>(wp_rec + lane, T, nq, a, b0, nb, K);
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+      if (j < nb) {
+        double* o = out + (int64_t)wp_pair(a, b0 + j) * (32 * 9);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) o[k] = K[j][k];
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_warped_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ cptr, const double* __restrict__ elem,
+                int64_t ndest, double* __restrict__ vals) {
+  __shared__ double sK[256 * 9];
+  const int64_t d = blockIdx.x * (int64_t)256 + threadIdx.x;
+  double K[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (d < ndest) {
+    const int32_t i1 = cptr[d + 1];
+    for (int32_t i = cptr[d]; i < i1; ++i) {            // fixed (cell-ascending) summation order
+      const int32_t e = centry[i];
+      const int32_t cell = e / 169; const int pair = e - cell * 169;
+      const int a = pair / 13, b = pair - a * 13;
+      const bool tr = a > b;
+      const int p = tr ? wp_pair(b, a) : wp_pair(a, b);
+      const double* s = elem + (((int64_t)(cell >> 5) * WP_PAIRS + p) * 32 + (cell & 31)) * 9;
+      if (!tr) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) K[k] += s[k];
+      } else {
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int q = 0; q < 3; ++q) K[3 * r + q] += s[3 * q + r];
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 9; ++k) sK[threadIdx.x * 9 + k] = K[k];
+  __syncthreads();
+  const int64_t base = blockIdx.x * (int64_t)(256 * 9);
+  const int64_t n = ndest * 9 - base;
+  for (int j = threadIdx.x; j < 256 * 9 && j < n; j += 256) vals[base + j] = sK[j];
+}
+
+static WpTasks wp_make_tasks(int nb_max) {
+  WpTasks t; t.n = 0;
+  for (int a = 0; a < 13; ++a) {
+    const int ends[2] = {9, 13};
+    for (int kind = (a < 9 ? 0 : 1); kind < 2; ++kind) {
+      const int lo = (kind == 0 || a >= 9) ? a : 9, hi = ends[kind];
+      for (int b = lo; b < hi; b += nb_max) {
+        t.a[t.n] = (unsigned char)a; t.b0[t.n] = (unsigned char)b;
+        t.nb[t.n] = (unsigned char)((hi - b) < nb_max ? (hi - b) : nb_max); ++t.n;
+      }
+    }
+  }
+  return t;
+}
 
 // ------------------------------------------------------------------------------------------
 // Chunked symmetric assembly for planar cells.
@@ -609,7 +801,7 @@ __global__ void k_load_gather(const int32_t* __restrict__ nc_ptr, const int32_t*
 // older kernels: warped (non-planar) meshes, FEMO_TILE=0, or a tile plan that does not fit shared memory
 static int assemble_jacobian_legacy(femo_ctx* c, const double* uh) {
   k_cell_records<<<(unsigned)cdiv(c->nc * c->nq, 128), 128, 0, c->stream>>>(
-      c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->nc, c->nq, c->ewm, c->rec_nqf, c->rec_stride, c->rec);
+      c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->nc, c->nq, c->ewm, c->rec_nqf, c->rec_stride, c->warped_ok, c->rec);
   TRY(check_launch(c, "k_cell_records"));
   cudaEventRecord(c->ev1, c->stream);
   unsigned grid = (unsigned)cdiv(c->ncontrib, GATHER_THREADS);
@@ -621,6 +813,20 @@ static int assemble_jacobian_legacy(femo_ctx* c, const double* uh) {
       case 4: TRY(launch_asm_planar<4>(c)); break;
       default: TRY(launch_asm_planar<0>(c)); break;
     }
+  } else if (c->warped_ok) {
+    const size_t smem = sizeof(double) * c->nq * REC_NQF_WARPED * 32;
+    const unsigned groups = (unsigned)cdiv(c->nc, 32);
+    const WpTasks tasks = wp_make_tasks(c->warped_nb);
+#define WP_LAUNCH(NB)                                                                                            \
+    {                                                                                                             \
+      CUDA_TRY(cudaFuncSetAttribute(k_warped_elem<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  \
+      k_warped_elem<NB><<<groups, WP_THREADS, smem, c->stream>>>(c->rec, c->tab, c->nq, tasks, c->elem);        \
+    }
+    if (c->warped_nb == 1) WP_LAUNCH(1) else if (c->warped_nb == 3) WP_LAUNCH(3) else WP_LAUNCH(2)
+#undef WP_LAUNCH
+    TRY(check_launch(c, "k_warped_elem"));
+    k_warped_gather<<<(unsigned)cdiv(c->nnzb, 256), 256, 0, c->stream>>>(c->centry, c->cptr, c->elem, c->nnzb, c->vals);
+    c->launches += 1;
   } else if (c->all_planar)
     k_gather<true><<<grid, GATHER_THREADS, 0, c->stream>>>(c->centry, c->cdest, c->cptr, c->rec, c->rec_stride, c->tab,
                                                            c->nq, c->ncontrib, c->vals);

@@ -128,6 +128,10 @@ struct femo_ctx {
   // quadrature records
   double* rec = nullptr;
   int rec_nqf = 0, rec_stride = 0;
+  // warped meshes (assemble.cu: k_warped_elem + k_warped_gather): records grouped by 32 cells, scratch for the 91 blocks
+  // a <= b of every element matrix
+  int warped_ok = 0, warped_nb = 1;
+  double* elem = nullptr;
   // boundary conditions
   double* bcmask = nullptr;     // ndof: 1 free, 0 clamped
   uint8_t* bcbits = nullptr;    // nb: bit d set = dof 3 b + d clamped (same information, 1 byte per block node)

@@ -355,3 +355,39 @@ def _bsr_diagonal(d):
     blocks = np.empty((d.nb, 9))
     L.check(d.lib.femo_get_blocks(d._ctx, d.nb, L.ptr(dpos), L.ptr(blocks)))
     return np.ascontiguousarray(blocks[:, [0, 4, 8]])
+
+
+@pytest.mark.parametrize("nb", ["1", "2", "3", "legacy"])
+def test_warped_cells_cell_centric_assembly(built_lib, monkeypatch, nb):
+    """Non-planar cells (assemble.cu: k_warped_elem + k_warped_gather): element matrices per group of 32 cells with 1, 2 or
+    3 node pairs per task, and the round-1 contribution-gather kernel (FEMO_WARPED=0), against the oracle on a doubly
+    curved, distorted plate (437 cells: 14 groups, the last one partly filled) with mesh motion; symmetric and
+    identical from run to run."""
+    from oracle.rm_shell_ref import plate_mesh, RMShellOracle
+    from femo_alpha_b200.shell_device import ShellDevice
+    if nb == "legacy":
+        monkeypatch.setenv("FEMO_WARPED", "0")
+    else:
+        monkeypatch.setenv("FEMO_WARPED_NB", nb)
+    rng = np.random.default_rng(13)
+    nodes, quads = plate_mesh(23, 19, 4.0, 3.0)
+    nn = nodes.shape[0]
+    nodes[:, :2] += 0.1 * (3.0 / 19) * rng.standard_normal((nn, 2))
+    nodes[:, 2] = 0.3 * np.sin(nodes[:, 0]) * np.cos(1.3 * nodes[:, 1])
+    inp = dict(thickness=0.05 * (1 + 0.5 * rng.random(nn)), E=1e6 * (1 + 0.2 * rng.random(nn)), nu=0.25 + 0.1 * rng.random(nn),
+               uhat=0.01 * rng.standard_normal(3 * nn))
+    for deg in (6, 4):
+        o = RMShellOracle(nodes, quads, False, False, deg)
+        o.set_inputs(**inp)
+        d = ShellDevice(nodes, quads, False, False, deg)
+        assert d.sizes.all_planar == 0
+        for k, v in inp.items():
+            d.set_input(k, v)
+        Kd = d.get_csr()
+        K = o.assemble_dRdu(with_penalty=False).tocsr()
+        assert abs(Kd - K).max() <= 1e-12 * abs(K).max()
+        if nb != "legacy":
+            _sym_check(Kd)
+        d.assemble_jacobian()
+        assert np.array_equal(d.get_csr().data, Kd.data)
+        d.close()
