@@ -163,7 +163,7 @@ int femo_ctx_destroy(femo_ctx* c) {
   coarse_free(c->direct); c->direct = nullptr;
   void* ptrs[] = {c->xyz, c->cv, c->ce, c->edges, c->cell_blocks, c->hE, c->tab, c->h, c->E, c->nu, c->rho, c->f, c->uhat,
                   c->rowptr, c->colidx, c->vals, c->centry, c->cdest, c->cptr, c->diag_pos, c->ut_pos, c->tu_pos, c->nc_ptr,
-                  c->nc_adj, c->rec, c->elem, c->bcmask, c->bcbits, c->colbc, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
+                  c->nc_adj, c->rec, c->elem, c->wp_order, c->bcmask, c->bcbits, c->colbc, c->pen_cell, c->pen_dest_pos, c->pen_dest_ptr, c->pen_src, c->pen_me,
                   c->pen_val, c->pen_dest_col, c->tab4, c->cell_tags, c->pen_row, c->pen_row_ptr, c->w, c->b, c->r, c->z, c->p, c->Ap, c->tmp,
                   c->tmp2, c->dinv6, c->dinv3, c->red, c->scal, c->cellbuf, c->it_pack, c->it_dest, c->chunk_ptr, c->halo_ptr,
                   c->halo_cells, c->tpos, c->tabm, c->vals_K, c->mvals, c->mass_me, c->hx_cells, c->hx_geo, c->hx_geo2, c->hx_rho, c->pen_vkey, c->pen_vptr, c->pen_vadj, c->pen_bkey, c->pen_bptr,
@@ -236,19 +236,19 @@ int femo_shell_setup(femo_ctx* c, const femo_shell_opts* o) {
   c->rec_stride = REC_HEADER + c->nq * c->rec_nqf;
   c->warped_ok = 0;
   if (!c->all_planar) {
-    // cell-centric kernels for warped cells (FEMO_WARPED=0: the round-1 contribution-gather kernel); the group's records
-    // (nq * 25 * 32 doubles) must fit a CTA's shared memory
+    // cell-centric kernels for warped cells (FEMO_WARPED=0: the round-1 contribution-gather kernel); the records of a
+    // group of 32 cells (nq * 25 * 32 doubles) must fit a CTA's shared memory.  FEMO_WARPED_NB: node pairs per task (1..4)
     const char* ev = getenv("FEMO_WARPED");
     const char* en = getenv("FEMO_WARPED_NB");
-    c->warped_nb = en ? atoi(en) : 2;
-    if (c->warped_nb < 1 || c->warped_nb > 3) c->warped_nb = 2;
+    c->warped_nb = en ? atoi(en) : 3;
+    if (c->warped_nb < 1 || c->warped_nb > 4) c->warped_nb = 3;
+    const char* et = getenv("FEMO_WARPED_NBT");      // columns per rotation-rotation task (1..4)
+    c->warped_nbt = et ? atoi(et) : 2;
+    if (c->warped_nbt < 1 || c->warped_nbt > 4) c->warped_nbt = 2;
     if (!(ev && atoi(ev) == 0) && (size_t)c->nq * REC_NQF_WARPED * 32 * sizeof(double) <= 200 * 1024) c->warped_ok = 1;
   }
   if (c->warped_ok) {
-    const size_t groups = (size_t)cdiv(c->nc, 32);
-    TRY(dev_alloc(&c->rec, groups * 32 * c->nq * REC_NQF_WARPED));
-    CUDA_TRY(cudaMemsetAsync(c->rec, 0, sizeof(double) * groups * 32 * c->nq * REC_NQF_WARPED, c->stream));   // lanes past the last cell
-    TRY(dev_alloc(&c->elem, groups * 91 * 32 * 9));
+    TRY(warped_setup(c));
   } else if (!c->tile_ok) TRY(dev_alloc(&c->rec, (size_t)c->nc * c->rec_stride));
   const int64_t n = c->ndof;
   TRY(dev_alloc(&c->bcmask, n)); TRY(fill(c, c->bcmask, n, 1.0));

@@ -11,6 +11,8 @@
 //                    are summed in a fixed order through shared memory, each block of the
 //                    matrix is written exactly once -> bitwise reproducible, no atomics.
 //   k_warped_elem + k_warped_gather   warped meshes: element matrices per group of 32 cells, then one thread per block
+#include <algorithm>
+#include <vector>
 #include "femo_internal.cuh"
 
 namespace {
@@ -20,7 +22,7 @@ __global__ void k_cell_records(const double* __restrict__ xyz, const int32_t* __
                                const double* __restrict__ uhat, const double* __restrict__ h,
                                const double* __restrict__ E, const double* __restrict__ nu,
                                const double* __restrict__ hE, const Tables* __restrict__ tab, int64_t nc, int nq,
-                               int ewm, int nqf, int stride, int grouped, double* __restrict__ rec) {
+                               int ewm, int nqf, int stride, double* __restrict__ rec) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= nc * nq) return;
   int64_t cell = i / nq; int q = (int)(i - cell * nq);
@@ -43,10 +45,7 @@ __global__ void k_cell_records(const double* __restrict__ xyz, const int32_t* __
   }
   Coefs cf = clt_coefs(hq, Eq, nuq, hE[cell], g.Ju, 0);
   double wd = tab->W[q] * g.detJ;
-  // grouped != 0 (warped path of k_warped_elem): [group of 32 cells][q][field][lane] without the per-cell header, so that a
-  // CTA stages its group with one contiguous copy and lane = cell reads are conflict-free
-  double loc[REC_NQF_WARPED];
-  double* r = grouped ? loc : rec + cell * stride + REC_HEADER + q * nqf;
+  double* r = rec + cell * stride + REC_HEADER + q * nqf;
   V3 E0 = g.E0, E1 = g.E1;
   if (nqf == REC_NQF_PLANAR) {
     // planar cell: any in-plane orthonormal frame gives the same energy (isotropic CLT), so one
@@ -74,10 +73,6 @@ __global__ void k_cell_records(const double* __restrict__ xyz, const int32_t* __
     V3 g0 = k00 * g.dE2_0 + k10 * g.dE2_1, g1 = k01 * g.dE2_0 + k11 * g.dE2_1;
     double* gg = r + REC_G0;
     gg[0] = g0.x; gg[1] = g0.y; gg[2] = g0.z; gg[3] = g1.x; gg[4] = g1.y; gg[5] = g1.z;
-  }
-  if (grouped) {
-    double* o = rec + (((cell >> 5) * (int64_t)nq + q) * nqf * 32 + (cell & 31));
-    for (int f = 0; f < nqf; ++f) o[f * 32] = loc[f];
   }
 }
 
@@ -160,7 +155,7 @@ __device__ __forceinline__ void block_planar(const double* __restrict__ rc, cons
   }
 }
 
-// general (warped / per-point frame) version (host + device: scripts/probes/warped_tile_host.cu checks warped_tile against it)
+// general (warped / per-point frame) version (host + device: scripts/probes/warped_tile_host.cu checks warped_uu / warped_ut / warped_tt against it)
 __host__ __device__ __forceinline__ void block_general(const double* __restrict__ rc, const SmemTab& T, int nq, int a, int b,
                                               double* K) {
   const double* r = rc + REC_HEADER;
@@ -274,102 +269,229 @@ k_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ cdest, 
 //   k_warped_elem    one CTA per group of 32 cells: the group's records are staged in shared memory once, lane = cell,
 //                    a warp takes one task = node a with WP_NB consecutive nodes b >= a of the same kind at a time
 //                    (the rows of a, scaled by the CLT coefficients, are shared by the tile); the 91 blocks a <= b of the
-//                    symmetric element matrix go to a scratch array  elem[group][pair][lane][9];
+//                    symmetric element matrix go to a scratch array  elem[group][pair][lane][10] (9 + 1 pad);
 //   k_warped_gather  one thread per BSR block: sums its contributions (block or transposed block) from the scratch in
 //                    list order and the CTA writes 256 blocks as one contiguous run.
 // Every block of the matrix is written once, the summation order is fixed: bitwise reproducible, no atomics.
 #define WP_PAIRS 91
+#define WP_BS 10                      /* doubles per block in the scratch: 9 + 1 pad, so that a block is five 16-byte loads */
 #define WP_THREADS 256
 #define WP_MAX_TASKS 91
 
-struct WpTasks { int n; unsigned char a[WP_MAX_TASKS], b0[WP_MAX_TASKS], nb[WP_MAX_TASKS]; };
+struct WpTasks { int n, n_uu; unsigned char a[WP_MAX_TASKS], b0[WP_MAX_TASKS], nb[WP_MAX_TASKS]; };
 
 __host__ __device__ __forceinline__ int wp_pair(int a, int b) { return a * 13 - a * (a - 1) / 2 + (b - a); }   // a <= b
 
 #define WP_RF(f) r[(f) * 32]
+#define WP_LOAD_FRAME                                                                                                        \
+  const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);                       \
+  const V3 E0 = v3(WP_RF(REC_E0), WP_RF(REC_E0 + 1), WP_RF(REC_E0 + 2)),                                                     \
+           E1 = v3(WP_RF(REC_E0 + 3), WP_RF(REC_E0 + 4), WP_RF(REC_E0 + 5)),                                                 \
+           E2 = v3(WP_RF(REC_E0 + 6), WP_RF(REC_E0 + 7), WP_RF(REC_E0 + 8));
+
+// Displacement - displacement blocks.  With d = the two physical gradient components of a node in the local frame,
+//   K_ab = sum_q  da0 db0 M00 + da1 db0 M10 + da0 db1 M10^T + da1 db1 M11
+// where the 3x3 matrices depend on the point only (weighted CLT coefficients, c3p/m = cm33 +- cd/4):
+//   M00 = cm11 E0 E0^T + c3p E1 E1^T + cs E2 E2^T,  M11 = cm11 E1 E1^T + c3p E0 E0^T + cs E2 E2^T,  M10 = cm12 E1 E0^T + c3m E0 E1^T
+// (u_rows: e0 = d0 E0, e1 = d1 E1, e2 = d1 E0 + d0 E1, g0 = d0 E2, g1 = d1 E2, dr = (d1 E0 - d0 E1)/2, expanded).
+// The "U" records hold k (4) and M00 (6), M11 (6), M10 (9): 25 fields like the frame records.
+#define REC_U_M00 4
+#define REC_U_M11 10
+#define REC_U_M10 16
+__host__ __device__ __forceinline__ void wp_m_tensors(V3 E0, V3 E1, V3 E2, double cm11, double cm12, double cm33, double cs,
+                                                      double cd, double* m /* 21 */) {
+  const double c3p = cm33 + 0.25 * cd, c3m = cm33 - 0.25 * cd;
+  const double a0[3] = {E0.x, E0.y, E0.z}, a1[3] = {E1.x, E1.y, E1.z}, a2[3] = {E2.x, E2.y, E2.z};
+  int n = 0;
+  for (int i = 0; i < 3; ++i)
+    for (int j = i; j < 3; ++j) {
+      m[n] = cm11 * a0[i] * a0[j] + c3p * a1[i] * a1[j] + cs * a2[i] * a2[j];
+      m[6 + n] = cm11 * a1[i] * a1[j] + c3p * a0[i] * a0[j] + cs * a2[i] * a2[j];
+      ++n;
+    }
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) m[12 + 3 * i + j] = cm12 * a1[i] * a0[j] + c3m * a0[i] * a1[j];
+}
+
+// node a (rows) against nb <= NB nodes b0.. (columns): W0 = da0 M00 + da1 M10, W1 = da0 M10^T + da1 M11 once per point,
+// then K_ab += db0 W0 + db1 W1 (18 FMAs per pair and point)
 template <int NB>
-__host__ __device__ __forceinline__ void warped_tile(const double* __restrict__ rs, const SmemTab& T, int nq, int a, int b0, int nb,
-                                            double (*K)[9]) {
+__host__ __device__ __forceinline__ void warped_uu(const double* __restrict__ rs, const SmemTab& T, int nq, int a, int b0, int nb,
+                                                   double (*K)[9]) {
 #pragma unroll
   for (int j = 0; j < NB; ++j)
 #pragma unroll
     for (int i = 0; i < 9; ++i) K[j][i] = 0.0;
-  if (a < 9 && b0 < 9) {                                  // displacement - displacement
-    for (int q = 0; q < nq; ++q) {
-      const double* r = rs + q * (REC_NQF_WARPED * 32);
-      const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);
-      const V3 E0 = v3(WP_RF(REC_E0), WP_RF(REC_E0 + 1), WP_RF(REC_E0 + 2)), E1 = v3(WP_RF(REC_E0 + 3), WP_RF(REC_E0 + 4), WP_RF(REC_E0 + 5)),
-               E2 = v3(WP_RF(REC_E0 + 6), WP_RF(REC_E0 + 7), WP_RF(REC_E0 + 8));
-      const double cm11 = WP_RF(REC_CM11), cm12 = WP_RF(REC_CM12), cm33 = WP_RF(REC_CM33), cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
-      const double r0 = T.dphi2[q][a][0], r1 = T.dphi2[q][a][1];
-      const URows A = u_rows(r0 * k00 + r1 * k10, r0 * k01 + r1 * k11, E0, E1, E2);
-      const V3 c0 = cm11 * A.e0 + cm12 * A.e1, c1 = cm12 * A.e0 + cm11 * A.e1, c2 = cm33 * A.e2, c3 = cs * A.g0, c4 = cs * A.g1,
-               c5 = cd * A.dr;
-#pragma unroll
-      for (int j = 0; j < NB; ++j) {
-        if (j < nb) {
-          const double s0 = T.dphi2[q][b0 + j][0], s1 = T.dphi2[q][b0 + j][1];
-          const URows B = u_rows(s0 * k00 + s1 * k10, s0 * k01 + s1 * k11, E0, E1, E2);
-          outer_acc(K[j], c0, B.e0); outer_acc(K[j], c1, B.e1); outer_acc(K[j], c2, B.e2);
-          outer_acc(K[j], c3, B.g0); outer_acc(K[j], c4, B.g1); outer_acc(K[j], c5, B.dr);
-        }
-      }
+  for (int q = 0; q < nq; ++q) {
+    const double* r = rs + q * (REC_NQF_WARPED * 32);
+    const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);
+    const double r0 = T.dphi2[q][a][0], r1 = T.dphi2[q][a][1];
+    const double da0 = r0 * k00 + r1 * k10, da1 = r0 * k01 + r1 * k11;
+    double W0[9], W1[9];
+    {
+      const double xx = WP_RF(REC_U_M00), xy = WP_RF(REC_U_M00 + 1), xz = WP_RF(REC_U_M00 + 2), yy = WP_RF(REC_U_M00 + 3),
+                   yz = WP_RF(REC_U_M00 + 4), zz = WP_RF(REC_U_M00 + 5);
+      W0[0] = da0 * xx; W0[1] = da0 * xy; W0[2] = da0 * xz; W0[3] = da0 * xy; W0[4] = da0 * yy; W0[5] = da0 * yz;
+      W0[6] = da0 * xz; W0[7] = da0 * yz; W0[8] = da0 * zz;
     }
-  } else if (a < 9) {                                     // displacement (rows) - rotation (columns): shear and drilling only
-    for (int q = 0; q < nq; ++q) {
-      const double* r = rs + q * (REC_NQF_WARPED * 32);
-      const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);
-      const V3 E0 = v3(WP_RF(REC_E0), WP_RF(REC_E0 + 1), WP_RF(REC_E0 + 2)), E1 = v3(WP_RF(REC_E0 + 3), WP_RF(REC_E0 + 4), WP_RF(REC_E0 + 5)),
-               E2 = v3(WP_RF(REC_E0 + 6), WP_RF(REC_E0 + 7), WP_RF(REC_E0 + 8));
-      const double cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
-      const double r0 = T.dphi2[q][a][0], r1 = T.dphi2[q][a][1];
-      const URows A = u_rows(r0 * k00 + r1 * k10, r0 * k01 + r1 * k11, E0, E1, E2);
-      const V3 c3 = cs * A.g0, c4 = cs * A.g1, c5 = cd * A.dr;
-#pragma unroll
-      for (int j = 0; j < NB; ++j) {
-        if (j < nb) {
-          const double N = T.n1[q][b0 + j - 9];
-          outer_acc(K[j], c3, N * E1); outer_acc(K[j], c4, (-N) * E0); outer_acc(K[j], c5, N * E2);
-        }
-      }
+    {
+      const double xx = WP_RF(REC_U_M11), xy = WP_RF(REC_U_M11 + 1), xz = WP_RF(REC_U_M11 + 2), yy = WP_RF(REC_U_M11 + 3),
+                   yz = WP_RF(REC_U_M11 + 4), zz = WP_RF(REC_U_M11 + 5);
+      W1[0] = da1 * xx; W1[1] = da1 * xy; W1[2] = da1 * xz; W1[3] = da1 * xy; W1[4] = da1 * yy; W1[5] = da1 * yz;
+      W1[6] = da1 * xz; W1[7] = da1 * yz; W1[8] = da1 * zz;
     }
-  } else {                                                // rotation - rotation
-    const int ta = a - 9;
-    for (int q = 0; q < nq; ++q) {
-      const double* r = rs + q * (REC_NQF_WARPED * 32);
-      const double k00 = WP_RF(REC_K00), k01 = WP_RF(REC_K01), k10 = WP_RF(REC_K10), k11 = WP_RF(REC_K11);
-      const V3 E0 = v3(WP_RF(REC_E0), WP_RF(REC_E0 + 1), WP_RF(REC_E0 + 2)), E1 = v3(WP_RF(REC_E0 + 3), WP_RF(REC_E0 + 4), WP_RF(REC_E0 + 5)),
-               E2 = v3(WP_RF(REC_E0 + 6), WP_RF(REC_E0 + 7), WP_RF(REC_E0 + 8));
-      const V3 g0 = v3(WP_RF(REC_G0), WP_RF(REC_G0 + 1), WP_RF(REC_G0 + 2)), g1 = v3(WP_RF(REC_G0 + 3), WP_RF(REC_G0 + 4), WP_RF(REC_G0 + 5));
-      const double hb = WP_RF(REC_HB), cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
-      const double cb11 = hb * WP_RF(REC_CM11), cb12 = hb * WP_RF(REC_CM12), cb33 = hb * WP_RF(REC_CM33);
-      const double r0 = T.dn1[q][ta][0], r1 = T.dn1[q][ta][1];
-      const TRows A = t_rows(T.n1[q][ta], r0 * k00 + r1 * k10, r0 * k01 + r1 * k11, E0, E1, E2, g0, g1);
-      const V3 c0 = cb11 * A.k0 + cb12 * A.k1, c1 = cb12 * A.k0 + cb11 * A.k1, c2 = cb33 * A.k2, c3 = cs * A.g0, c4 = cs * A.g1,
-               c5 = cd * A.dr;
 #pragma unroll
-      for (int j = 0; j < NB; ++j) {
-        if (j < nb) {
-          const int tb = b0 + j - 9;
-          const double s0 = T.dn1[q][tb][0], s1 = T.dn1[q][tb][1];
-          const TRows B = t_rows(T.n1[q][tb], s0 * k00 + s1 * k10, s0 * k01 + s1 * k11, E0, E1, E2, g0, g1);
-          outer_acc(K[j], c0, B.k0); outer_acc(K[j], c1, B.k1); outer_acc(K[j], c2, B.k2);
-          outer_acc(K[j], c3, B.g0); outer_acc(K[j], c4, B.g1); outer_acc(K[j], c5, B.dr);
-        }
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const double m = WP_RF(REC_U_M10 + 3 * i + j);
+        W0[3 * i + j] += da1 * m;
+        W1[3 * j + i] += da0 * m;
+      }
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+      if (j < nb) {
+        const double s0 = T.dphi2[q][b0 + j][0], s1 = T.dphi2[q][b0 + j][1];
+        const double db0 = s0 * k00 + s1 * k10, db1 = s0 * k01 + s1 * k11;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) K[j][i] += db0 * W0[i] + db1 * W1[i];
       }
     }
   }
 }
+
+// Displacement node a (rows) against the four rotation nodes (columns): only shear and drilling couple, and the column
+// rows are N times a vector of the frame (t_rows: g0 = N E1, g1 = -N E0, dr = N E2):  K_ab = N_b (c3 E1^T - c4 E0^T + c5 E2^T)
+__host__ __device__ __forceinline__ void warped_ut(const double* __restrict__ rs, const SmemTab& T, int nq, int a, double (*K)[9]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int i = 0; i < 9; ++i) K[j][i] = 0.0;
+  for (int q = 0; q < nq; ++q) {
+    const double* r = rs + q * (REC_NQF_WARPED * 32);
+    WP_LOAD_FRAME
+    const double cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
+    const double r0 = T.dphi2[q][a][0], r1 = T.dphi2[q][a][1];
+    const URows A = u_rows(r0 * k00 + r1 * k10, r0 * k01 + r1 * k11, E0, E1, E2);
+    double W[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    outer_acc(W, cs * A.g0, E1); outer_acc(W, (-cs) * A.g1, E0); outer_acc(W, cd * A.dr, E2);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const double N = T.n1[q][j];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) K[j][i] += N * W[i];
+    }
+  }
+}
+
+// Rotation node a (rows) against nb <= 4 rotation nodes b0.. (columns).  The rows of a column node are linear in its value
+// and its two gradient components (t_rows):  k0 = N X0 - d0 E1,  k1 = N X1 + d1 E0,  k2 = N X2 + d0 E0 - d1 E1,
+// g0 = N E1, g1 = -N E0, dr = N E2  with  X0 = E0 x g_0, X1 = E1 x g_1, X2 = E0 x g_1 + E1 x g_0  (the dE2/dX terms), so
+//   K_ab = N_b WN + d0_b W0 + d1_b W1,   WN = c0 X0^T + c1 X1^T + c2 X2^T + c3 E1^T - c4 E0^T + c5 E2^T,
+//   W0 = c2 E0^T - c0 E1^T,   W1 = c1 E0^T - c2 E1^T     (c: the rows of a scaled by the bending / shear / drilling coefficients)
+__host__ __device__ __forceinline__ void warped_tt(const double* __restrict__ rs, const SmemTab& T, int nq, int a, int b0, int nb,
+                                                   double (*K)[9]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int i = 0; i < 9; ++i) K[j][i] = 0.0;
+  const int ta = a - 9;
+  for (int q = 0; q < nq; ++q) {
+    const double* r = rs + q * (REC_NQF_WARPED * 32);
+    WP_LOAD_FRAME
+    const V3 g0 = v3(WP_RF(REC_G0), WP_RF(REC_G0 + 1), WP_RF(REC_G0 + 2)), g1 = v3(WP_RF(REC_G0 + 3), WP_RF(REC_G0 + 4), WP_RF(REC_G0 + 5));
+    const double hb = WP_RF(REC_HB), cs = WP_RF(REC_CS), cd = WP_RF(REC_CD);
+    const double cb11 = hb * WP_RF(REC_CM11), cb12 = hb * WP_RF(REC_CM12), cb33 = hb * WP_RF(REC_CM33);
+    const V3 X0 = cross(E0, g0), X1 = cross(E1, g1), X2 = cross(E0, g1) + cross(E1, g0);
+    const double Na = T.n1[q][ta], r0 = T.dn1[q][ta][0], r1 = T.dn1[q][ta][1];
+    const double d0 = r0 * k00 + r1 * k10, d1 = r0 * k01 + r1 * k11;
+    const V3 ak0 = Na * X0 - d0 * E1, ak1 = Na * X1 + d1 * E0, ak2 = Na * X2 + d0 * E0 - d1 * E1;
+    const V3 c0 = cb11 * ak0 + cb12 * ak1, c1 = cb12 * ak0 + cb11 * ak1, c2 = cb33 * ak2;
+    const V3 c3 = (cs * Na) * E1, c4 = (-cs * Na) * E0, c5 = (cd * Na) * E2;
+    double WN[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, W0[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, W1[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    outer_acc(WN, c0, X0); outer_acc(WN, c1, X1); outer_acc(WN, c2, X2);
+    outer_acc(WN, c3, E1); outer_acc(WN, (-1.0) * c4, E0); outer_acc(WN, c5, E2);
+    outer_acc(W0, c2, E0); outer_acc(W0, (-1.0) * c0, E1);
+    outer_acc(W1, c1, E0); outer_acc(W1, (-1.0) * c2, E1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (j < nb) {
+        const int tb = b0 - 9 + j;
+        const double s0 = T.dn1[q][tb][0], s1 = T.dn1[q][tb][1], Nb = T.n1[q][tb];
+        const double e0 = s0 * k00 + s1 * k10, e1 = s0 * k01 + s1 * k11;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) K[j][i] += Nb * WN[i] + e0 * W0[i] + e1 * W1[i];
+      }
+    }
+  }
+}
+#undef WP_LOAD_FRAME
 #undef WP_RF
 
+__device__ __forceinline__ void wp_store_block(double* __restrict__ o, const double* K) {      // o is 16-byte aligned
+  double2* o2 = reinterpret_cast<double2*>(o);
+  o2[0] = make_double2(K[0], K[1]); o2[1] = make_double2(K[2], K[3]); o2[2] = make_double2(K[4], K[5]);
+  o2[3] = make_double2(K[6], K[7]); o2[4] = make_double2(K[8], 0.0);
+}
+
+// quadrature record of (cell, q) in the group layout [q][field][lane]: role 0 the fields of k_cell_records' warped branch
+// (frames, dE2/dX terms, coefficients), role 1 the "U" record (k and the three M matrices)
+__device__ __noinline__ void warped_record(const double* __restrict__ xyz, const int32_t* __restrict__ cv,
+                                           const double* __restrict__ uhat, const double* __restrict__ h,
+                                           const double* __restrict__ E, const double* __restrict__ nu,
+                                           const double* __restrict__ hE, const Tables* __restrict__ tab, int ewm, int role,
+                                           int64_t cell, int q, double* __restrict__ o) {
+  V3 xv[4], uh[4];
+  int32_t vid[4];
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    vid[v] = cv[cell * 4 + v];
+    xv[v] = ldv3(xyz + 3 * (int64_t)vid[v]);
+    if (uhat) uh[v] = ldv3(uhat + 3 * (int64_t)vid[v]);
+  }
+  QpGeom g;
+  qp_geometry(xv, uhat ? uh : nullptr, tab->X0[q], tab->X1[q], g);
+  double hq, Eq, nuq;
+  if (ewm) { hq = h[cell]; Eq = E[cell]; nuq = nu[cell]; }
+  else {
+    hq = Eq = nuq = 0;
+#pragma unroll
+    for (int v = 0; v < 4; ++v) { double N = tab->n1[q][v]; hq += N * h[vid[v]]; Eq += N * E[vid[v]]; nuq += N * nu[vid[v]]; }
+  }
+  const Coefs cf = clt_coefs(hq, Eq, nuq, hE[cell], g.Ju, 0);
+  const double wd = tab->W[q] * g.detJ;
+  const double k00 = dot(g.Kx0, g.E0), k01 = dot(g.Kx0, g.E1), k10 = dot(g.Kx1, g.E0), k11 = dot(g.Kx1, g.E1);
+  o[REC_K00 * 32] = k00; o[REC_K01 * 32] = k01; o[REC_K10 * 32] = k10; o[REC_K11 * 32] = k11;
+  if (role == 1) {
+    double m[21];
+    wp_m_tensors(g.E0, g.E1, g.E2, wd * cf.cm11, wd * cf.cm12, wd * cf.cm33, wd * cf.cs, wd * cf.cd, m);
+#pragma unroll
+    for (int i = 0; i < 21; ++i) o[(REC_U_M00 + i) * 32] = m[i];
+    return;
+  }
+  o[REC_CM11 * 32] = wd * cf.cm11; o[REC_CM12 * 32] = wd * cf.cm12; o[REC_CM33 * 32] = wd * cf.cm33;
+  o[REC_HB * 32] = hq * hq / 12.0;
+  o[REC_CS * 32] = wd * cf.cs; o[REC_CD * 32] = wd * cf.cd;
+  const V3 g0 = k00 * g.dE2_0 + k10 * g.dE2_1, g1 = k01 * g.dE2_0 + k11 * g.dE2_1;
+  const double fr[15] = {g.E0.x, g.E0.y, g.E0.z, g.E1.x, g.E1.y, g.E1.z, g.E2.x, g.E2.y, g.E2.z, g0.x, g0.y, g0.z, g1.x, g1.y, g1.z};
+#pragma unroll
+  for (int i = 0; i < 15; ++i) o[(REC_E0 + i) * 32] = fr[i];
+}
+
+// Two CTAs per group of 32 cells: role 1 (odd blockIdx) the displacement-displacement tasks over the U records, role 0
+// the displacement-rotation and rotation-rotation tasks over the frame records; each CTA builds its own records.
 template <int NB>
 __global__ void __launch_bounds__(WP_THREADS, 2)
-k_warped_elem(const double* __restrict__ rec, const Tables* __restrict__ tab, int nq, WpTasks tasks, double* __restrict__ elem) {
+k_warped_elem(const double* __restrict__ xyz, const int32_t* __restrict__ cv, const double* __restrict__ uhat,
+              const double* __restrict__ h, const double* __restrict__ E, const double* __restrict__ nu,
+              const double* __restrict__ hE, const Tables* __restrict__ tab, int ewm, int64_t nc, int nq, WpTasks tasks,
+              double* __restrict__ elem) {
   extern __shared__ __align__(16) double wp_rec[];          // [nq][25][32]
   __shared__ SmemTab T;
   __shared__ int next_task;
   const int tid = threadIdx.x, lane = tid & 31;
-  const int nf = nq * REC_NQF_WARPED;
+  const int role = blockIdx.x & 1;
+  const int64_t group = blockIdx.x >> 1;
   {
     double* d = (double*)&T;
     const double* s0 = &tab->dphi2[0][0][0];
@@ -378,37 +500,55 @@ k_warped_elem(const double* __restrict__ rec, const Tables* __restrict__ tab, in
     for (int i = tid; i < FEMO_MAX_NQ * 4; i += WP_THREADS) d1[i] = s1[i];
     double* d2 = &T.dn1[0][0][0]; const double* s2 = &tab->dn1[0][0][0];
     for (int i = tid; i < FEMO_MAX_NQ * 8; i += WP_THREADS) d2[i] = s2[i];
-    const double2* src = reinterpret_cast<const double2*>(rec + (int64_t)blockIdx.x * nf * 32);
-    double2* dst = reinterpret_cast<double2*>(wp_rec);
-    for (int i = tid; i < nf * 16; i += WP_THREADS) dst[i] = src[i];
-    if (tid == 0) next_task = 0;
+    if (tid == 0) next_task = role ? 0 : tasks.n_uu;
+    // the group's records, one (cell, point) per thread and pass: lane = cell, warp = point
+    const int64_t cell = group * 32 + lane;
+    for (int q = tid >> 5; q < nq; q += WP_THREADS / 32) {
+      double* o = wp_rec + (size_t)q * (REC_NQF_WARPED * 32) + lane;
+      if (cell < nc) warped_record(xyz, cv, uhat, h, E, nu, hE, tab, ewm, role, cell, q, o);
+      else
+        for (int f = 0; f < REC_NQF_WARPED; ++f) o[f * 32] = 0.0;
+    }
   }
   __syncthreads();
-  double* out = elem + (int64_t)blockIdx.x * (WP_PAIRS * 32 * 9) + lane * 9;
+  const int t_end = role ? tasks.n_uu : tasks.n;
+  double* out = elem + group * (WP_PAIRS * 32 * WP_BS) + lane * WP_BS;
   for (;;) {
     int t = 0;
     if (lane == 0) t = atomicAdd(&next_task, 1);
     t = __shfl_sync(0xffffffffu, t, 0);
-    if (t >= tasks.n) break;
+    if (t >= t_end) break;
     const int a = tasks.a[t], b0 = tasks.b0[t], nb = tasks.nb[t];
-    double K[NB][9];
-    warped_tile<NB>(wp_rec + lane, T, nq, a, b0, nb, K);
+    if (role) {
+      double K[NB][9];
+      warped_uu<NB>(wp_rec + lane, T, nq, a, b0, nb, K);
 #pragma unroll
-    for (int j = 0; j < NB; ++j) {
-      if (j < nb) {
-        double* o = out + (int64_t)wp_pair(a, b0 + j) * (32 * 9);
+      for (int j = 0; j < NB; ++j)
+        if (j < nb) wp_store_block(out + (int64_t)wp_pair(a, b0 + j) * (32 * WP_BS), K[j]);
+    } else {
+      double K[4][9];
+      if (a < 9) warped_ut(wp_rec + lane, T, nq, a, K);
+      else warped_tt(wp_rec + lane, T, nq, a, b0, nb, K);
 #pragma unroll
-        for (int k = 0; k < 9; ++k) o[k] = K[j][k];
-      }
+      for (int j = 0; j < 4; ++j)
+        if (j < nb) wp_store_block(out + (int64_t)wp_pair(a, b0 + j) * (32 * WP_BS), K[j]);
     }
   }
 }
 
+// One thread per BSR block: sums the contributions (block a <= b of the element matrix, or its transpose) in list order
+// with five 16-byte loads each; the CTA writes its 256 blocks as one contiguous run.  Every block of the matrix is written
+// exactly once.  (Summing only the upper triangle and writing the mirror blocks 72 bytes at a time halves the scratch
+// reads but measured slower: 4.5 against 3.6 ms at config-3 size, profiles/r02s_warped_bench.json.)
+// The runs of 256 blocks are taken in the order of the first cell contributing to them (`order`, built once): block (A, B)
+// and its mirror (B, A) read the same element-matrix block, rows A and B are far apart in the matrix (vertex, edge, centre
+// and rotation nodes are numbered one after the other) but close in this order, so the second read hits L2.
 __global__ void __launch_bounds__(256)
-k_warped_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ cptr, const double* __restrict__ elem,
-                int64_t ndest, double* __restrict__ vals) {
+k_warped_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ cptr, const int32_t* __restrict__ order,
+                const double* __restrict__ elem, int64_t ndest, double* __restrict__ vals) {
   __shared__ double sK[256 * 9];
-  const int64_t d = blockIdx.x * (int64_t)256 + threadIdx.x;
+  const int64_t run = order ? order[blockIdx.x] : blockIdx.x;
+  const int64_t d = run * 256 + threadIdx.x;
   double K[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   if (d < ndest) {
     const int32_t i1 = cptr[d + 1];
@@ -418,38 +558,49 @@ k_warped_gather(const int32_t* __restrict__ centry, const int32_t* __restrict__ 
       const int a = pair / 13, b = pair - a * 13;
       const bool tr = a > b;
       const int p = tr ? wp_pair(b, a) : wp_pair(a, b);
-      const double* s = elem + (((int64_t)(cell >> 5) * WP_PAIRS + p) * 32 + (cell & 31)) * 9;
+      const double2* s2 = reinterpret_cast<const double2*>(elem + (((int64_t)(cell >> 5) * WP_PAIRS + p) * 32 + (cell & 31)) * WP_BS);
+      const double2 v0 = s2[0], v1 = s2[1], v2 = s2[2], v3 = s2[3], v4 = s2[4];
       if (!tr) {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) K[k] += s[k];
+        K[0] += v0.x; K[1] += v0.y; K[2] += v1.x; K[3] += v1.y; K[4] += v2.x; K[5] += v2.y; K[6] += v3.x; K[7] += v3.y; K[8] += v4.x;
       } else {
-#pragma unroll
-        for (int r = 0; r < 3; ++r)
-#pragma unroll
-          for (int q = 0; q < 3; ++q) K[3 * r + q] += s[3 * q + r];
+        K[0] += v0.x; K[3] += v0.y; K[6] += v1.x; K[1] += v1.y; K[4] += v2.x; K[7] += v2.y; K[2] += v3.x; K[5] += v3.y; K[8] += v4.x;
       }
     }
   }
 #pragma unroll
   for (int k = 0; k < 9; ++k) sK[threadIdx.x * 9 + k] = K[k];
   __syncthreads();
-  const int64_t base = blockIdx.x * (int64_t)(256 * 9);
+  const int64_t base = run * (256 * 9);
   const int64_t n = ndest * 9 - base;
   for (int j = threadIdx.x; j < 256 * 9 && j < n; j += 256) vals[base + j] = sK[j];
 }
 
-static WpTasks wp_make_tasks(int nb_max) {
+__global__ void k_warped_run_keys(const int32_t* __restrict__ centry, const int32_t* __restrict__ cptr, int64_t ndest,
+                                  int64_t nruns, int32_t* __restrict__ key) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (r >= nruns) return;
+  int32_t cell = 0x7fffffff;                      // first cell contributing to the run's first non-empty block
+  for (int64_t d = r * 256; d < ndest && d < (r + 1) * 256; ++d)
+    if (cptr[d + 1] > cptr[d]) { cell = centry[cptr[d]] / 169; break; }
+  key[r] = cell;
+}
+
+// tasks [0, n_uu): displacement node a against up to nb_max displacement nodes b >= a, largest first (the CTA's warps draw
+// tasks from a counter: longest-processing-time order keeps the tail short); then the rotation-rotation tasks (at most
+// nbt columns each) and one task per displacement node against the four rotation nodes
+static WpTasks wp_make_tasks(int nb_max, int nbt = 2) {
   WpTasks t; t.n = 0;
-  for (int a = 0; a < 13; ++a) {
-    const int ends[2] = {9, 13};
-    for (int kind = (a < 9 ? 0 : 1); kind < 2; ++kind) {
-      const int lo = (kind == 0 || a >= 9) ? a : 9, hi = ends[kind];
-      for (int b = lo; b < hi; b += nb_max) {
-        t.a[t.n] = (unsigned char)a; t.b0[t.n] = (unsigned char)b;
-        t.nb[t.n] = (unsigned char)((hi - b) < nb_max ? (hi - b) : nb_max); ++t.n;
-      }
-    }
-  }
+  auto add = [&](int a, int b, int nb) { t.a[t.n] = (unsigned char)a; t.b0[t.n] = (unsigned char)b; t.nb[t.n] = (unsigned char)nb; ++t.n; };
+  for (int size = nb_max; size >= 1; --size)
+    for (int a = 0; a < 9; ++a)
+      for (int b = a; b < 9; b += nb_max)
+        if (((9 - b) < nb_max ? (9 - b) : nb_max) == size) add(a, b, size);
+  t.n_uu = t.n;
+  for (int size = nbt; size >= 1; --size)
+    for (int a = 9; a < 13; ++a)
+      for (int b = a; b < 13; b += nbt)
+        if (((13 - b) < nbt ? (13 - b) : nbt) == size) add(a, b, size);
+  for (int a = 0; a < 9; ++a) add(a, 9, 4);
   return t;
 }
 
@@ -798,10 +949,52 @@ __global__ void k_load_gather(const int32_t* __restrict__ nc_ptr, const int32_t*
 
 }  // namespace
 
-// older kernels: warped (non-planar) meshes, FEMO_TILE=0, or a tile plan that does not fit shared memory
+// warped meshes: records + element matrices in one kernel (events: ev1 between the two kernels, so that last_timings
+// reports element matrices / gather)
+static int assemble_jacobian_warped(femo_ctx* c, const double* uh) {
+  const size_t smem = sizeof(double) * c->nq * REC_NQF_WARPED * 32;
+  const unsigned groups = (unsigned)cdiv(c->nc, 32);
+  const WpTasks tasks = wp_make_tasks(c->warped_nb, c->warped_nbt);
+#define WP_LAUNCH(NB)                                                                                            \
+  {                                                                                                             \
+    CUDA_TRY(cudaFuncSetAttribute(k_warped_elem<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  \
+    k_warped_elem<NB><<<2 * groups, WP_THREADS, smem, c->stream>>>(c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->ewm, \
+                                                               c->nc, c->nq, tasks, c->elem);                   \
+  }
+  if (c->warped_nb == 1) WP_LAUNCH(1) else if (c->warped_nb == 2) WP_LAUNCH(2) else if (c->warped_nb == 4) WP_LAUNCH(4) else WP_LAUNCH(3)
+#undef WP_LAUNCH
+  TRY(check_launch(c, "k_warped_elem"));
+  cudaEventRecord(c->ev1, c->stream);
+  k_warped_gather<<<(unsigned)cdiv(c->nnzb, 256), 256, 0, c->stream>>>(c->centry, c->cptr, c->wp_order, c->elem, c->nnzb, c->vals);
+  TRY(check_launch(c, "k_warped_gather"));
+  return 0;
+}
+
+// scratch of the warped path: 91 padded blocks per cell, and the order in which k_warped_gather takes its runs of 256
+// blocks (FEMO_WARPED_ORDER=0: matrix order).  Called once from femo_shell_setup.
+int warped_setup(femo_ctx* c) {
+  TRY(dev_alloc(&c->elem, (size_t)cdiv(c->nc, 32) * WP_PAIRS * 32 * WP_BS));
+  dev_free(&c->wp_order);
+  const char* eo = getenv("FEMO_WARPED_ORDER");
+  if (eo && atoi(eo) == 0) return 0;
+  const int64_t nruns = cdiv(c->nnzb, 256);
+  TRY(dev_alloc(&c->wp_order, (size_t)nruns));
+  k_warped_run_keys<<<(unsigned)cdiv(nruns, 128), 128, 0, c->stream>>>(c->centry, c->cptr, c->nnzb, nruns, c->wp_order);
+  TRY(check_launch(c, "k_warped_run_keys"));
+  std::vector<int32_t> key((size_t)nruns), ord((size_t)nruns);
+  CUDA_TRY(cudaMemcpyAsync(key.data(), c->wp_order, sizeof(int32_t) * nruns, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  for (int64_t i = 0; i < nruns; ++i) ord[i] = (int32_t)i;
+  std::stable_sort(ord.begin(), ord.end(), [&](int32_t x, int32_t y) { return key[x] < key[y]; });
+  CUDA_TRY(cudaMemcpyAsync(c->wp_order, ord.data(), sizeof(int32_t) * nruns, cudaMemcpyHostToDevice, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// older kernels: FEMO_TILE=0, FEMO_WARPED=0, or a plan that does not fit shared memory
 static int assemble_jacobian_legacy(femo_ctx* c, const double* uh) {
   k_cell_records<<<(unsigned)cdiv(c->nc * c->nq, 128), 128, 0, c->stream>>>(
-      c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->nc, c->nq, c->ewm, c->rec_nqf, c->rec_stride, c->warped_ok, c->rec);
+      c->xyz, c->cv, uh, c->h, c->E, c->nu, c->hE, c->tab, c->nc, c->nq, c->ewm, c->rec_nqf, c->rec_stride, c->rec);
   TRY(check_launch(c, "k_cell_records"));
   cudaEventRecord(c->ev1, c->stream);
   unsigned grid = (unsigned)cdiv(c->ncontrib, GATHER_THREADS);
@@ -813,20 +1006,6 @@ static int assemble_jacobian_legacy(femo_ctx* c, const double* uh) {
       case 4: TRY(launch_asm_planar<4>(c)); break;
       default: TRY(launch_asm_planar<0>(c)); break;
     }
-  } else if (c->warped_ok) {
-    const size_t smem = sizeof(double) * c->nq * REC_NQF_WARPED * 32;
-    const unsigned groups = (unsigned)cdiv(c->nc, 32);
-    const WpTasks tasks = wp_make_tasks(c->warped_nb);
-#define WP_LAUNCH(NB)                                                                                            \
-    {                                                                                                             \
-      CUDA_TRY(cudaFuncSetAttribute(k_warped_elem<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  \
-      k_warped_elem<NB><<<groups, WP_THREADS, smem, c->stream>>>(c->rec, c->tab, c->nq, tasks, c->elem);        \
-    }
-    if (c->warped_nb == 1) WP_LAUNCH(1) else if (c->warped_nb == 3) WP_LAUNCH(3) else WP_LAUNCH(2)
-#undef WP_LAUNCH
-    TRY(check_launch(c, "k_warped_elem"));
-    k_warped_gather<<<(unsigned)cdiv(c->nnzb, 256), 256, 0, c->stream>>>(c->centry, c->cptr, c->elem, c->nnzb, c->vals);
-    c->launches += 1;
   } else if (c->all_planar)
     k_gather<true><<<grid, GATHER_THREADS, 0, c->stream>>>(c->centry, c->cdest, c->cptr, c->rec, c->rec_stride, c->tab,
                                                            c->nq, c->ncontrib, c->vals);
@@ -843,6 +1022,8 @@ int assemble_stiffness(femo_ctx* c) {
   cudaEventRecord(c->ev0, c->stream);
   if (c->tile_ok) {
     TRY(assemble_jacobian_tiles(c, uh));
+  } else if (c->warped_ok) {
+    TRY(assemble_jacobian_warped(c, uh));
   } else {
     TRY(assemble_jacobian_legacy(c, uh));
   }

@@ -130,8 +130,9 @@ struct femo_ctx {
   int rec_nqf = 0, rec_stride = 0;
   // warped meshes (assemble.cu: k_warped_elem + k_warped_gather): records grouped by 32 cells, scratch for the 91 blocks
   // a <= b of every element matrix
-  int warped_ok = 0, warped_nb = 1;
+  int warped_ok = 0, warped_nb = 1, warped_nbt = 2;
   double* elem = nullptr;
+  int32_t* wp_order = nullptr;  // runs of 256 blocks in the order of their first contributing cell (k_warped_gather)
   // boundary conditions
   double* bcmask = nullptr;     // ndof: 1 free, 0 clamped
   uint8_t* bcbits = nullptr;    // nb: bit d set = dof 3 b + d clamped (same information, 1 byte per block node)
@@ -237,6 +238,7 @@ int topo_build(femo_ctx* c, const int32_t* conn_vtk_host);                // top
 int pattern_build(femo_ctx* c);                                           // topology.cu
 int penalty_build(femo_ctx* c, const uint8_t* vertex_on_host);            // topology.cu
 int asm_plan_build(femo_ctx* c);                                          // topology.cu
+int warped_setup(femo_ctx* c);                                            // assemble.cu
 int tile_plan_setup(femo_ctx* c);                                         // assemble_tiles.cu
 void tile_plan_free(femo_ctx* c);                                         // assemble_tiles.cu
 int assemble_jacobian_tiles(femo_ctx* c, const double* uhat);             // assemble_tiles.cu (records + assembly)

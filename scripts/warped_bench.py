@@ -1,6 +1,6 @@
 """Warped-cell Jacobian assembly at config-3 size (doubly curved plate, 816 x 816 cells): the cell-centric kernels
-(k_warped_elem<NB> + k_warped_gather, NB = 1, 2, 3 node pairs per task) against the round-1 contribution-gather kernel
-(FEMO_WARPED=0).  Times are CUDA events inside the library (records kernel / assembly kernels).
+(k_warped_elem<NB> + k_warped_gather, NB = 1 .. 4 displacement-node pairs per task) against the round-1 contribution-gather kernel
+(FEMO_WARPED=0).  Times are CUDA events inside the library (element-matrix kernel / gather kernel; records + gather for the legacy path).
     python scripts/warped_bench.py [n] > gpurun_out/warped_bench.json"""
 import json
 import os
@@ -22,9 +22,13 @@ def main():
     inp = inputs_for(nodes)
     out = {"workload": "doubly curved plate %dx%d, Jacobian assembly" % (n, n)}
     ref = None
-    for tag, env in (("nb1", {"FEMO_WARPED_NB": "1"}), ("nb2", {"FEMO_WARPED_NB": "2"}), ("nb3", {"FEMO_WARPED_NB": "3"}),
+    only = sys.argv[2] if len(sys.argv) > 2 else None          # e.g. 'default': one variant (ncu captures)
+    for tag, env in (("default", {}), ("nb2", {"FEMO_WARPED_NB": "2"}), ("nb3_t4", {"FEMO_WARPED_NB": "3", "FEMO_WARPED_NBT": "4"}),
+                     ("nb3_t1", {"FEMO_WARPED_NB": "3", "FEMO_WARPED_NBT": "1"}), ("nb4", {"FEMO_WARPED_NB": "4"}),
                      ("legacy", {"FEMO_WARPED": "0"})):
-        for k in ("FEMO_WARPED", "FEMO_WARPED_NB"):
+        if only and tag != only:
+            continue
+        for k in ("FEMO_WARPED", "FEMO_WARPED_NB", "FEMO_WARPED_NBT", "FEMO_WARPED_ORDER"):
             os.environ.pop(k, None)
         os.environ.update(env)
         d = ShellDevice(nodes, quads)
@@ -44,9 +48,9 @@ def main():
         if ref is None:
             ref = Kv
         t_ms = float(np.mean(rec) + np.mean(ker))
-        out[tag] = dict(n_dof=int(d.ndof), records_ms=float(np.mean(rec)), kernels_ms=float(np.mean(ker)), ms=t_ms,
+        out[tag] = dict(n_dof=int(d.ndof), first_kernel_ms=float(np.mean(rec)), second_kernel_ms=float(np.mean(ker)), ms=t_ms,
                         gdof_s=d.ndof / (t_ms * 1e-3) / 1e9, roofline_frac=CELL_BYTES * d.nc / (t_ms * 1e-3) / 1e9 / peak,
-                        Kv_rel_diff_to_nb1=float(np.abs(Kv - ref).max() / np.abs(ref).max()))
+                        Kv_rel_diff_to_first=float(np.abs(Kv - ref).max() / np.abs(ref).max()))
         print(tag, out[tag], file=sys.stderr, flush=True)
         d.close()
     print(json.dumps(out))

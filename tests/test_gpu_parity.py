@@ -357,7 +357,7 @@ def _bsr_diagonal(d):
     return np.ascontiguousarray(blocks[:, [0, 4, 8]])
 
 
-@pytest.mark.parametrize("nb", ["1", "2", "3", "legacy"])
+@pytest.mark.parametrize("nb", ["1", "2", "3", "4", "legacy"])
 def test_warped_cells_cell_centric_assembly(built_lib, monkeypatch, nb):
     """Non-planar cells (assemble.cu: k_warped_elem + k_warped_gather): element matrices per group of 32 cells with 1, 2 or
     3 node pairs per task, and the round-1 contribution-gather kernel (FEMO_WARPED=0), against the oracle on a doubly
