@@ -86,6 +86,7 @@ SIGNATURES = {
     "femo_mg_set_transfer": [_P, C.c_int, _P, _P, _P, _P, _P, _P],
     "femo_mg_setup": [_P, C.c_int, C.c_int],
     "femo_mg_get_lambda": [_P, C.c_int, _D],
+    "femo_mg_set_refine": [_P, C.c_int, C.c_double],
     "femo_mg_solve": [_P, _P, _P, C.c_double, C.c_int, C.POINTER(C.c_int), _D, C.c_int, C.c_int],
     "femo_direct_setup": [_P],
     "femo_direct_solve": [_P, _P, _P, C.c_int, _D, C.c_int, C.c_int],

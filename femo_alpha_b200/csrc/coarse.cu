@@ -599,6 +599,18 @@ int femo_direct_setup(femo_ctx* c) {
   return r;
 }
 
+}  // extern "C"
+
+// r = b - A x over all local block rows, accumulated in double-double (A with the BC rows / columns replaced by identity, as
+// every SpMV of the library); multi-GPU callers exchange the halo of x before and of r after
+int residual_dd(femo_ctx* c, const double* x, const double* b, double* r) {
+  k_residual_dd<<<(unsigned)cdiv(c->nb, 128), 128, 0, c->stream>>>(c->rowptr, c->colbc, c->vals, c->bcbits, x, b, c->nb, r);
+  c->launches += 1;
+  return check_launch(c, "k_residual_dd");
+}
+
+extern "C" {
+
 // A x = rhs with `refine` steps of iterative refinement on a residual accumulated in double-double (k_residual_dd);
 // relres = |rhs - A x| / |rhs| of the result
 int femo_direct_solve(femo_ctx* c, const double* rhs, double* sol, int refine, double* relres, int on_device, int zero_bc) {

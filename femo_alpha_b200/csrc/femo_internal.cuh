@@ -257,6 +257,7 @@ int precond_setup(femo_ctx* c);                                           // sol
 int pcg_solve(femo_ctx* c, const double* b, double* x, double rtol, int max_it, int* iters,
               double* relres, bool fixed_iters);                          // solver.cu
 int dev_dot(femo_ctx* c, const double* a, const double* b, int64_t n, double* out_host);   // solver.cu
+int residual_dd(femo_ctx* c, const double* x, const double* b, double* r);   // coarse.cu: b - A x in double-double
 int dev_dot_async(femo_ctx* c, const double* a, const double* b, int64_t n, double* out_dev);   // solver.cu (no sync)
 int out_scalar(femo_ctx* c, int which, double* val);                      // outputs.cu
 int out_grad(femo_ctx* c, int which, int arg, double* g_dev);             // outputs.cu

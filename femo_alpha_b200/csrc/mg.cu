@@ -36,6 +36,10 @@ struct femo_mg {
   CoarseSolver* cs = nullptr;  // direct solver of the coarsest operator (coarse.cu)
   bool ready = false;
   double *pr = nullptr, *pz = nullptr, *pp = nullptr, *pAp = nullptr, *px = nullptr, *pb = nullptr;   // PCG vectors (level 0)
+  // iterative refinement around the PCG (femo_mg_set_refine): x += PCG(b - A x), the residual accumulated in double-double
+  int refine = 0;
+  double refine_rtol = 1e-6;
+  double *pxa = nullptr, *pb0 = nullptr;   // accumulated solution, right-hand side of the outer problem
   int64_t vcycles = 0;
 };
 
@@ -267,7 +271,7 @@ int femo_mg_destroy(femo_mg* m) {
   if (!m) return 0;
   cudaSetDevice(m->L[0].c->device);
   for (auto& Lv : m->L) mg_free_level(Lv);
-  coarse_free(m->cs); m->cs = nullptr; dev_free(&m->pr); dev_free(&m->pz); dev_free(&m->pp); dev_free(&m->pAp); dev_free(&m->px); dev_free(&m->pb);
+  coarse_free(m->cs); m->cs = nullptr; dev_free(&m->pr); dev_free(&m->pz); dev_free(&m->pp); dev_free(&m->pAp); dev_free(&m->px); dev_free(&m->pb); dev_free(&m->pxa); dev_free(&m->pb0);
   delete m;
   return 0;
 }
@@ -372,6 +376,17 @@ int femo_mg_get_lambda(femo_mg* m, int l, double* lam) {
 // PCG on the finest level with one V-cycle as preconditioner.  rhs / sol: n_dof doubles (host or device);
 // clamped entries of rhs are ignored (homogeneous Dirichlet), x0 = 0; zero_bc zeroes the clamped entries of sol
 // (state_operation.py:217-218).
+// Iterative refinement around femo_mg_solve's PCG: `steps` > 0 adds that many corrections  x += PCG(b - A x)  with the
+// residual accumulated in double-double, each solved to inner_rtol relative to its own right-hand side.  relres of
+// femo_mg_solve is then the TRUE residual of the result (CG's recurrence residual drifts from it by ~eps |A| |x|, and the
+// true one cannot go below that either: x is stored in fp64).
+int femo_mg_set_refine(femo_mg* m, int steps, double inner_rtol) {
+  if (!m) return femo_fail("femo_mg_set_refine: null hierarchy");
+  if (steps < 0 || steps > 8 || !(inner_rtol > 0 && inner_rtol < 1)) return femo_fail("femo_mg_set_refine: steps in [0, 8], 0 < inner_rtol < 1");
+  m->refine = steps; m->refine_rtol = inner_rtol;
+  return 0;
+}
+
 int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
                   int on_device, int zero_bc) {
   if (!m || !m->ready) return femo_fail("femo_mg_solve: call femo_mg_setup first (and again after the inputs change)");
@@ -381,18 +396,23 @@ int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int m
   const int64_t n = c->ndof;
   MgLevel& L0 = m->L[0];
   CUDA_TRY(cudaMemcpyAsync(m->pb, rhs, sizeof(double) * n, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-  // b <- mask * b, x = 0, r = b
+  // b <- mask * b
   k_mg_mask<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, c->bcmask, m->pb);
-  CUDA_TRY(cudaMemsetAsync(m->px, 0, sizeof(double) * n, c->stream));
-  CUDA_TRY(cudaMemcpyAsync(m->pr, m->pb, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
   cudaEventRecord(c->ev0, c->stream);
-  double bb = 0, rz = 0, rr = 0;
+  double bb = 0;
   TRY(dev_dot(c, m->pb, m->pb, n, &bb));
-  const double bnorm = sqrt(bb);
+  const double bnorm0 = sqrt(bb);
   int it = 0;
   double rel = 0;
-  if (bnorm > 0) {
-    rr = bb; rel = 1.0;
+  // PCG on A x = pb from x = 0 until |r| <= stop (recurrence residual); returns |r| / |pb|
+  auto pcg = [&](double stop, double* rel_out) -> int {
+    CUDA_TRY(cudaMemsetAsync(m->px, 0, sizeof(double) * n, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(m->pr, m->pb, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+    double pbb = 0, rz = 0, rr = 0;
+    TRY(dev_dot(c, m->pb, m->pb, n, &pbb));
+    *rel_out = 0;
+    if (!(pbb > 0) || sqrt(pbb) <= stop) return 0;
+    bool first = true;
     while (it < max_it) {
       CUDA_TRY(cudaMemcpyAsync(L0.b, m->pr, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
       TRY(mg_vcycle(m, 0));
@@ -400,8 +420,9 @@ int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int m
       double rz_new = 0;
       TRY(dev_dot(c, m->pr, L0.x, n, &rz_new));
       if (!(rz_new > 0)) return femo_fail("femo_mg_solve: preconditioner is not positive definite (r.z = " + std::to_string(rz_new) + ")");
-      if (it == 0) CUDA_TRY(cudaMemcpyAsync(m->pp, L0.x, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+      if (first) CUDA_TRY(cudaMemcpyAsync(m->pp, L0.x, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
       else k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, L0.x, rz_new / rz, m->pp, m->pp);
+      first = false;
       rz = rz_new;
       TRY(mg_spmv(c, m->pp, m->pAp));
       double pAp = 0;
@@ -413,10 +434,35 @@ int femo_mg_solve(femo_mg* m, const double* rhs, double* sol, double rtol, int m
       c->launches += 3;
       ++it;
       TRY(dev_dot(c, m->pr, m->pr, n, &rr));
-      rel = sqrt(rr) / bnorm;
-      if (!(rel == rel)) return femo_fail("femo_mg_solve: NaN residual");
-      if (rel <= rtol) break;
+      *rel_out = sqrt(rr / pbb);
+      if (!(*rel_out == *rel_out)) return femo_fail("femo_mg_solve: NaN residual");
+      if (sqrt(rr) <= stop) break;
     }
+    return 0;
+  };
+  if (bnorm0 > 0) {
+    TRY(pcg(rtol * bnorm0, &rel));
+    if (m->refine > 0) {
+      if (!m->pxa) { TRY(dev_alloc(&m->pxa, (size_t)n)); TRY(dev_alloc(&m->pb0, (size_t)n)); }
+      CUDA_TRY(cudaMemcpyAsync(m->pb0, m->pb, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+      CUDA_TRY(cudaMemcpyAsync(m->pxa, m->px, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+      for (int s = 0; s <= m->refine; ++s) {
+        if (c->world > 1) TRY(halo_exchange(c, m->pxa));
+        TRY(residual_dd(c, m->pxa, m->pb0, m->pb));          // the correction's right-hand side
+        if (c->world > 1) TRY(halo_exchange(c, m->pb));
+        double rr = 0;
+        TRY(dev_dot(c, m->pb, m->pb, n, &rr));
+        rel = sqrt(rr) / bnorm0;                               // true residual of the accumulated solution
+        if (s == m->refine || !(rr > 0) || it >= max_it) break;
+        double rel_in = 0;
+        TRY(pcg(m->refine_rtol * sqrt(rr), &rel_in));
+        k_axpby<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, 1.0, m->pxa, 1.0, m->px, m->pxa);
+        c->launches += 1;
+      }
+      CUDA_TRY(cudaMemcpyAsync(m->px, m->pxa, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+    }
+  } else {
+    CUDA_TRY(cudaMemsetAsync(m->px, 0, sizeof(double) * n, c->stream));
   }
   if (zero_bc) k_mg_mask<<<(unsigned)cdiv(n, 256), 256, 0, c->stream>>>(n, c->bcmask, m->px);
   if (c->world > 1) TRY(halo_exchange(c, m->px));          // ghost entries of the solution follow their owners

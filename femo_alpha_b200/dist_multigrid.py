@@ -139,6 +139,14 @@ class DistributedHierarchy:
             self._keep.append(a)
             L.check(self.lib.femo_mg_set_transfer(self._mg, l, *[L.ptr(v) for v in a]))
         self._transfers = None
+        if getattr(self, "_refine", None):
+            L.check(self.lib.femo_mg_set_refine(self._mg, *self._refine))
+
+    def set_refine(self, steps, inner_rtol=1e-6):
+        """Iterative refinement around the distributed V-cycle PCG (see ShellHierarchy.set_refine); kept until close()."""
+        self._refine = (int(steps), float(inner_rtol))
+        if self._mg.value:
+            self._L.check(self.lib.femo_mg_set_refine(self._mg, *self._refine))
 
     def init_comm(self, dist=None):
         """Collective: one NCCL communicator (finest level), shared by the other distributed levels."""

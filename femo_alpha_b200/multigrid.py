@@ -280,6 +280,13 @@ class ShellHierarchy:
         self._n_setups += 1
         self._dirty = False
 
+    def set_refine(self, steps, inner_rtol=1e-6):
+        """Iterative refinement around the V-cycle PCG (femo_mg_set_refine): `steps` corrections x += PCG(b - A x) with the
+        residual accumulated in double-double; solve() then reports the TRUE relative residual (bounded below by
+        eps |A| |x| / |b|, x being stored in fp64) instead of CG's recurrence residual.  Stands in for the direct solve
+        behind the reference's KSP (femo_alpha/fea/utils_dolfinx.py:514-531)."""
+        L.check(self.lib.femo_mg_set_refine(self._mg, int(steps), float(inner_rtol)))
+
     def lambda_max(self, level):
         v = C.c_double(0.0)
         L.check(self.lib.femo_mg_get_lambda(self._mg, int(level), C.byref(v)))

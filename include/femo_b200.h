@@ -215,6 +215,13 @@ int femo_mg_set_transfer(femo_mg* mg, int level, const int32_t* P_rowptr, const 
  * inside an optimisation loop with small steps, a few more iterations) */
 int femo_mg_setup(femo_mg* mg, int cheb_degree, int reuse_coarse_inverse);
 int femo_mg_get_lambda(femo_mg* mg, int level, double* lambda_max);
+/* iterative refinement around femo_mg_solve's PCG: `steps` (0..8, default 0) corrections x += PCG(b - A x) with the residual
+ * accumulated in double-double, each solved to inner_rtol relative to its own right-hand side; femo_mg_solve then reports
+ * the TRUE relative residual of its result (bounded below by eps |A| |x| / |b|: x is stored in fp64) instead of CG's
+ * recurrence residual.  Stands in for the direct solve behind the reference's KSP (femo_alpha/fea/utils_dolfinx.py:514-531,
+ * MUMPS).  On a shell with kappa ~ 1e9 it removes the solver's share of the forward error; what remains against another
+ * implementation (~1e-8) is the sensitivity of x to last-bit differences of the matrix entries. */
+int femo_mg_set_refine(femo_mg* mg, int steps, double inner_rtol);
 /* PCG with one V-cycle per iteration on A x = rhs (A = dR/du with BCs, x0 = 0); zero_bc as femo_solve_adjoint */
 int femo_mg_solve(femo_mg* mg, const double* rhs, double* sol, double rtol, int max_it, int* iters, double* relres,
                   int on_device, int zero_bc);

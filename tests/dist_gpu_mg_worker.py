@@ -12,9 +12,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-# relres 1e-11 leaves a forward error of ~1e-8 on this plate (kappa ~ 1e9): converge further so that the 1e-8 comparison
-# with the oracle has a margin
-RTOL = 1e-13
+# Plate 10 x 2 with h ~ 0.3.  (With h ~ 0.1, kappa ~ 1e9, device and oracle differ by 0.8e-8 / 1.6e-8 in u / lambda whatever
+# the solver does -- rtol 1e-11 or 1e-13, with or without refinement: the solution is that sensitive to last-bit
+# differences between the two assembled matrices; tests/test_gpu_multigrid.py documents it.)  One refinement step on a
+# double-double residual (femo_mg_set_refine) exercises the halo exchanges of that path.
+RTOL = 1e-11
 
 
 def main():
@@ -31,10 +33,11 @@ def main():
     levels = 4
     h = DistributedHierarchy(nodes_c, quads_c, levels, rank, world, device=local, n_dist=n_dist)
     h.init_comm()
+    h.set_refine(1)
     nodes_f, quads_f = h.meshes[0]
     nn = nodes_f.shape[0]
     x = nodes_f[:, 0]
-    inputs = dict(thickness=0.1 * (1 + 0.3 * np.sin(2 * np.pi * x / 10)), E=np.full(nn, 1e8), nu=np.full(nn, 0.3),
+    inputs = dict(thickness=0.3 * (1 + 0.3 * np.sin(2 * np.pi * x / 10)), E=np.full(nn, 1e8), nu=np.full(nn, 0.3),
                   density=np.full(nn, 10.0), F_solid=np.tile([0.0, 0.0, 5.0], nn))
     for k, v in inputs.items():
         h.set_input(k, v)
@@ -63,13 +66,14 @@ def main():
     for k, v in inputs.items():
         s.set_input(k, v)
     s.set_strong_bc(clamp)
+    s.set_refine(1)
     its1, _ = s.solve_state(rtol=RTOL, max_it=400)
     s.close()
     hx, ar = h.fine.comm_counts()
     print("rank %d/%d distributed V-cycle PCG (%d distributed levels of %d): state %d / adjoint %d iterations (single GPU: %d), "
           "relres %.1e | u err %.2e | lam err %.2e | %d halo exchanges, %d all-reduces on the finest level"
           % (rank, world, n_dist, levels, its, its_a, its1, rr, err, err_a, hx, ar), flush=True)
-    ok = err <= 1e-8 and err_a <= 1e-8 and 0 < its <= its1 + 2 and rr <= RTOL
+    ok = err <= 1e-8 and err_a <= 1e-8 and 0 < its <= its1 + 2 and rr <= 1e-8      # rr: true residual after refinement (2e-9: eps |A| |x| / |b|)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     h.close()
