@@ -83,47 +83,17 @@ def prolongation(fine_blocks, coarse_blocks, nb_fine, nb_coarse, parent=None, ch
     General form (one rank of a partitioned hierarchy, dist_multigrid.py): `parent[i]` = row of `coarse_blocks` that is the
     parent of fine cell i and `child[i]` = its child index (0..3); fine cells may then come in any number and order, and
     with `allow_missing_rows` fine block nodes that no listed cell holds get an empty row instead of an error."""
-    import scipy.sparse as sp
-    if parent is not None:
-        return _prolongation_general(fine_blocks, coarse_blocks, nb_fine, nb_coarse, parent, child, allow_missing_rows)
     fb = np.asarray(fine_blocks, dtype=np.int64)
     cb = np.asarray(coarse_blocks, dtype=np.int64)
-    nc = cb.shape[0]
-    assert fb.shape[0] == 4 * nc
-    # weight tables per (child, local fine node): 9 Q2 nodes -> 9 coarse Q2 weights, 4 Q1 nodes -> 4 coarse Q1 weights
-    W2 = np.zeros((4, 9, 9)); W1 = np.zeros((4, 4, 4))
-    for k in range(4):
-        ci, cj = k % 2, k // 2
-        for a in range(9):
-            W2[k, a] = _q2((ci + _REF2[a, 0]) / 2.0, (cj + _REF2[a, 1]) / 2.0)
-        for a in range(4):
-            W1[k, a] = _q1((ci + _REF1[a, 0]) / 2.0, (cj + _REF1[a, 1]) / 2.0)
-    fbk = fb.reshape(nc, 4, 13)
-    rows2 = np.repeat(fbk[:, :, :9, None], 9, axis=3)                       # nc,4,9,9
-    cols2 = np.broadcast_to(cb[:, None, None, :9], (nc, 4, 9, 9))
-    vals2 = np.broadcast_to(W2[None], (nc, 4, 9, 9))
-    rows1 = np.repeat(fbk[:, :, 9:, None], 4, axis=3)
-    cols1 = np.broadcast_to(cb[:, None, None, 9:], (nc, 4, 4, 4))
-    vals1 = np.broadcast_to(W1[None], (nc, 4, 4, 4))
-    rows = np.concatenate([rows2.ravel(), rows1.ravel()])
-    cols = np.concatenate([cols2.ravel(), cols1.ravel()])
-    vals = np.concatenate([vals2.ravel(), vals1.ravel()])
-    # a fine node shared by several fine cells gets the same row from each of them (conforming spaces): keep one copy
-    grp = np.concatenate([np.repeat(np.arange(nc * 4 * 9), 9), nc * 4 * 9 + np.repeat(np.arange(nc * 4 * 4), 4)])
-    first = np.full(nb_fine, -1, dtype=np.int64)
-    order = np.argsort(rows, kind="stable")
-    r_sorted, g_sorted = rows[order], grp[order]
-    head = np.ones(r_sorted.size, dtype=bool); head[1:] = r_sorted[1:] != r_sorted[:-1]
-    first[r_sorted[head]] = g_sorted[head]
-    if (first < 0).any():
-        raise RuntimeError("prolongation: a fine block node belongs to no fine cell")
-    keep = (grp == first[rows]) & (np.abs(vals) > 1e-14)
-    P = sp.csr_matrix((vals[keep], (rows[keep], cols[keep])), shape=(nb_fine, nb_coarse))
-    P.sum_duplicates(); P.sort_indices()
-    return P
+    if parent is None:
+        assert fb.shape[0] == 4 * cb.shape[0]
+        parent = np.arange(fb.shape[0], dtype=np.int64) // 4          # refine_quads order: children of a cell are adjacent
+        child = np.arange(fb.shape[0], dtype=np.int64) % 4
+    return _prolongation_general(fb, cb, nb_fine, nb_coarse, parent, child, allow_missing_rows)
 
 
 def _child_weights():
+    """weight tables per (child, local fine node): 9 Q2 nodes -> 9 coarse Q2 weights, 4 Q1 nodes -> 4 coarse Q1 weights"""
     W2 = np.zeros((4, 9, 9)); W1 = np.zeros((4, 4, 4))
     for k in range(4):
         ci, cj = k % 2, k // 2
@@ -142,25 +112,22 @@ def _prolongation_general(fine_blocks, coarse_blocks, nb_fine, nb_coarse, parent
     nf = fb.shape[0]
     assert parent.shape == (nf,) and child.shape == (nf,)
     W2, W1 = _child_weights()
-    rows2 = np.repeat(fb[:, :9, None], 9, axis=2)                           # nf,9,9
-    cols2 = np.broadcast_to(cb[parent][:, None, :9], (nf, 9, 9))
-    vals2 = W2[child]
-    rows1 = np.repeat(fb[:, 9:, None], 4, axis=2)
-    cols1 = np.broadcast_to(cb[parent][:, None, 9:], (nf, 4, 4))
-    vals1 = W1[child]
-    rows = np.concatenate([rows2.ravel(), rows1.ravel()])
-    cols = np.concatenate([cols2.ravel(), cols1.ravel()])
-    vals = np.concatenate([vals2.ravel(), vals1.ravel()])
-    # a fine node shared by several fine cells gets the same row from each of them (conforming spaces): keep one copy
-    grp = np.concatenate([np.repeat(np.arange(nf * 9), 9), nf * 9 + np.repeat(np.arange(nf * 4), 4)])
+    # a fine node shared by several fine cells gets the same row from each of them (conforming spaces): the (fine cell,
+    # local node) pair with the lowest index writes it.  Decided per pair (13 per cell), before the rows are expanded.
+    flat = fb.ravel()
+    gid = np.arange(flat.size, dtype=np.int64)
     first = np.full(nb_fine, -1, dtype=np.int64)
-    order = np.argsort(rows, kind="stable")
-    r_sorted, g_sorted = rows[order], grp[order]
-    head = np.ones(r_sorted.size, dtype=bool); head[1:] = r_sorted[1:] != r_sorted[:-1]
-    first[r_sorted[head]] = g_sorted[head]
+    first[flat[::-1]] = gid[::-1]                        # repeated indices: the last write (lowest pair index) stays
     if (first < 0).any() and not allow_missing_rows:
         raise RuntimeError("prolongation: a fine block node belongs to no fine cell")
-    keep = (grp == first[rows]) & (np.abs(vals) > 1e-14)
+    own = (first[flat] == gid).reshape(nf, 13)
+    cbp = cb[parent]
+    c2, a2 = np.nonzero(own[:, :9])
+    c1, a1 = np.nonzero(own[:, 9:])
+    rows = np.concatenate([np.repeat(fb[c2, a2], 9), np.repeat(fb[c1, 9 + a1], 4)])
+    cols = np.concatenate([cbp[c2, :9].ravel(), cbp[c1, 9:].ravel()])
+    vals = np.concatenate([W2[child[c2], a2].ravel(), W1[child[c1], a1].ravel()])
+    keep = np.abs(vals) > 1e-14
     P = sp.csr_matrix((vals[keep], (rows[keep], cols[keep])), shape=(nb_fine, nb_coarse))
     P.sum_duplicates(); P.sort_indices()
     return P
