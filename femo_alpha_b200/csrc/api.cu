@@ -414,11 +414,12 @@ int femo_assemble_residual(femo_ctx* c, const double* w, double* R, int on_devic
 //     while the SpMV still works on the next one.
 // which[i] / data[i] / sizes[i]: input ids and HOST arrays (pinned memory makes the copies asynchronous; pageable memory
 // works, serialised by the driver); w_host: state (n_dof) or null for the resident one; R_host: n_dof doubles.
+// On a rank of a multi-GPU context everything is local (local inputs, local state with its ghost entries, rows of the
+// rank's blocks; owned rows are complete) exactly as in femo_set_input + femo_assemble_residual: no collective.
 int femo_evaluate_residual(femo_ctx* c, int n_in, const int* which, const double* const* data, const int64_t* sizes,
                            const double* w_host, double* R_host) {
   NEED_SHELL(c, "femo_evaluate_residual");
   if (n_in < 0 || (n_in > 0 && (!which || !data || !sizes)) || !R_host) return femo_fail("femo_evaluate_residual: bad arguments");
-  if (c->world > 1) return femo_fail("femo_evaluate_residual: single-GPU contexts (multi-GPU ranks use femo_set_input + femo_assemble_residual)");
   DevGuard g(c->device);
   if (!c->copy_stream) {
     CUDA_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));

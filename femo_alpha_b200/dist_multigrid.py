@@ -176,6 +176,12 @@ class DistributedHierarchy:
             d.set_strong_bc(np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel()))
         self._dirty = True
 
+    def prepare(self):
+        """Create the device-side hierarchy (femo_mg_create + upload of the transfer operators) ahead of the first setup();
+        setup() does it on demand otherwise.  One-time work, not part of the per-design set-up."""
+        if not self._mg.value:
+            self._create()
+
     def setup(self, reuse_coarse=False):
         if self.world > 1 and not self._comm:
             raise RuntimeError("DistributedHierarchy: call init_comm() first")

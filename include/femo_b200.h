@@ -109,7 +109,8 @@ int femo_assemble_residual(femo_ctx* ctx, const double* w, double* R, int on_dev
  * still on their way up on a second stream; R = K w - F comes back in row ranges while the SpMV still works on the next
  * one.  which / data / sizes: n_in input ids with their host arrays (size 1 = fill, like femo_set_input); w_host: the
  * state (n_dof) or NULL for the resident one; R_host: n_dof doubles.  Pinned host memory makes the overlap real.
- * Single-GPU contexts. */
+ * On a rank of a multi-GPU context the arrays are the rank's local ones (as for femo_set_input / femo_assemble_residual:
+ * owned rows of R are complete, no collective). */
 int femo_evaluate_residual(femo_ctx* ctx, int n_in, const int* which, const double* const* data, const int64_t* sizes,
                            const double* w_host, double* R_host);
 /* load vector int f . du J dx only */

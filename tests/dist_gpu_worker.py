@@ -54,11 +54,15 @@ def main(name):
         idx = ds.lp.vertex_global[own_v]
         g_own = g[own_v]
     err_g = np.abs(g_own - g_ref[idx]).max() / np.abs(g_ref).max()
+    # the one-call residual evaluation on a rank: local arrays, bitwise the separate calls
+    R_sep = ds.dev.assemble_residual(w_loc)
+    R_one = ds.dev.evaluate_residual({}, w_loc)
+    same_R = bool(np.array_equal(R_sep, R_one))
     h, a = ds.comm_counts()
     print("rank %d/%d %s: PCG %d its relres %.1e | u err %.2e | C %.12g vs %.12g | mass %.12g vs %.12g | dC/dh err %.2e | "
           "%d halo exchanges, %d all-reduces" % (rank, world, name, it, rr, err_w, C, Cref, M, Mref, err_g, h, a), flush=True)
     ok = err_w <= 1e-8 and abs(C - Cref) <= 1e-8 * abs(Cref) and abs(M - Mref) <= 1e-11 * abs(Mref) and err_g <= 1e-8 \
-        and h > 0 and a > 0
+        and h > 0 and a > 0 and same_R
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
