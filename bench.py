@@ -344,6 +344,8 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # torchrun exports OMP_NUM_THREADS=1: give the library's host-side plan construction this rank's share of the cores
+        os.environ.setdefault("FEMO_HOST_THREADS", str(max(1, (os.cpu_count() or 1) // world)))
     n = args.n
     strong = args.scaling == "strong" and world > 1
     if world > 1:

@@ -15,9 +15,26 @@
 //                      one pair at a time by the owner (the cell's own chunk never needs to talk)
 #pragma once
 #include <stdint.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <string>
 #include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+// threads of the host-side plan construction: FEMO_HOST_THREADS if set (launchers such as torchrun export
+// OMP_NUM_THREADS=1 for every rank), else OpenMP's default
+inline int femo_host_threads() {
+  const char* e = getenv("FEMO_HOST_THREADS");
+  int n = e ? atoi(e) : 0;
+#ifdef _OPENMP
+  if (n <= 0) n = omp_get_max_threads();
+#else
+  n = 1;
+#endif
+  return n < 1 ? 1 : n;
+}
 
 namespace femo_tiles {
 
@@ -103,7 +120,7 @@ inline std::string build(int64_t nc, int64_t nb, const int32_t* rowptr, const in
   std::vector<int32_t> owner((size_t)nnzb, -1);
   std::vector<int32_t> row_of((size_t)nnzb);
   int bad = 0;
-#pragma omp parallel for schedule(static) reduction(| : bad)
+#pragma omp parallel for schedule(static) reduction(| : bad) num_threads(femo_host_threads())
   for (int64_t I = 0; I < nb; ++I) {
     Match m[CAP];
     for (int32_t k = rowptr[I]; k < rowptr[I + 1]; ++k) {
@@ -139,7 +156,7 @@ inline std::string build(int64_t nc, int64_t nb, const int32_t* rowptr, const in
   P.hcell_ptr.assign((size_t)nchunks + 1, 0);
   for (int fill = 0; fill < 2; ++fill) {
     int err = 0;
-#pragma omp parallel for schedule(dynamic, 64) reduction(| : err)
+#pragma omp parallel for schedule(dynamic, 64) reduction(| : err) num_threads(femo_host_threads())
     for (int64_t c = 0; c < nchunks; ++c) {
       Match m[CAP];
       int32_t hc[512]; int nhc = 0;
@@ -252,7 +269,7 @@ inline void morton_order(int64_t nc, const double* xyz, const int32_t* cv /* nc 
     }
   const double inv = cell_size > 0 ? 1.0 / cell_size : 1.0;
   std::vector<std::pair<uint64_t, int32_t>> key((size_t)nc);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(femo_host_threads())
   for (int64_t c = 0; c < nc; ++c) {
     uint64_t q[3];
     for (int d = 0; d < 3; ++d) {
