@@ -155,7 +155,7 @@ __device__ __forceinline__ void block_planar(const double* __restrict__ rc, cons
   }
 }
 
-// general (warped / per-point frame) version (host + device: scripts/probes/warped_tile_host.cu checks warped_uu / warped_ut / warped_tt against it)
+// general (warped / per-point frame) version (host + device: tests/warped_host.cu checks warped_uu / warped_ut / warped_tt against it)
 __host__ __device__ __forceinline__ void block_general(const double* __restrict__ rc, const SmemTab& T, int nq, int a, int b,
                                               double* K) {
   const double* r = rc + REC_HEADER;

@@ -2,8 +2,9 @@
 // block_general (the round-1 formulation the GPU parity tests pinned to the oracle): random records of one group of 32
 // cells in the three layouts (per-cell records, grouped frame records, grouped "U" records with the M matrices), all 91
 // pairs a <= b, NB = 1 .. 4, plus the task list covering every pair exactly once.
-//   nvcc -std=c++17 -O1 -gencode arch=compute_100a,code=sm_100a -I femo_alpha_b200/csrc scripts/probes/warped_tile_host.cu \
-//        -L femo_alpha_b200 -lfemo_b200 -o /tmp/wt && LD_LIBRARY_PATH=femo_alpha_b200 /tmp/wt
+// Compiled and run by tests/test_warped_host.py (CPU suite; the same __host__ __device__ functions the kernel calls):
+//   nvcc -std=c++17 -O1 -gencode arch=compute_100a,code=sm_100a -I femo_alpha_b200/csrc tests/warped_host.cu \
+//        -L femo_alpha_b200 -lfemo_b200 -o tests/_build/warped_host
 #include <cstdio>
 #include <cstdlib>
 #include <cmath>
