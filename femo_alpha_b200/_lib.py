@@ -12,6 +12,8 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfemo_b200.so")
+if os.environ.get("FEMO_LIB_PATH"):          # experiments: another build of the same library (scripts/asm_experiments.py)
+    LIB_PATH = os.environ["FEMO_LIB_PATH"]
 
 THICKNESS, F_SOLID, E, NU, DENSITY, UHAT = range(6)
 COMPLIANCE, MASS, ELASTIC_ENERGY, PNORM_STRESS, VOLUME = range(5)

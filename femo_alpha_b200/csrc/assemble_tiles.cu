@@ -770,16 +770,19 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
       const V3 F0 = ldv3(sFrame), F1 = ldv3(sFrame + 3), F2 = ldv3(sFrame + 6);
       const double* sMom = smem + L.mom0 + buf * L.mom_stride;
       const double* sHm = smem + L.hmom0 + buf * L.hmom_stride;
-      for (int base = 0; base < nd; base += DPT * WT) {
+      // Rounds of 32 destinations per WARP: gather + rotate into the warp's own slice of sK, then the same warp stores its
+      // 32 blocks and their mirror images (lane j of pass i holds value 32 i + j of the slice: 3.6 blocks of 72 contiguous
+      // bytes per store instruction, as before) -- no CTA-wide barrier inside a chunk (round 2; the two barriers per round
+      // of 256 destinations cost the writer warps 17 % of their time, profiles/r02n_ncu_full_k_asm_tiles_ws_details.csv)
+      double* myK = sK + ww * (32 * 9);
+      for (int base = ww * 32; base < nd; base += WT) {
+        const int di = base + lane;
+        double K[9];
 #pragma unroll
-        for (int u = 0; u < DPT; ++u) {
-        const int di = base + u * WT + wtid;
+        for (int k = 0; k < 9; ++k) K[k] = 0.0;
         if (di < nd && !(dbg & 8)) {
           const uint32_t info = sInfo[di];
           const int start = info & 0xFFFFF, n = info >> 20;
-          double K[9];
-#pragma unroll
-          for (int k = 0; k < 9; ++k) K[k] = 0.0;
           if (uniform) {
             // flat patch: add the local-frame moments of all contributions first (fixed order), rotate once
             double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
@@ -824,23 +827,26 @@ k_asm_tiles_ws(const int32_t* __restrict__ dest_ptr, const int32_t* __restrict__
               }
             }
           }
+        }
+        __syncwarp();                                  // the previous round's stores have read the slice
 #pragma unroll
-          for (int k = 0; k < 9; ++k) sK[(u * WT + wtid) * 9 + k] = K[k];
-        }
-        }
-        bar_sync(BAR_WRITER, WT);
-        const int cnt = min(DPT * WT, nd - base);
-        if (wtid < (WT / 9) * 9 && !(dbg & 1)) {                          // WT/9 blocks x 9 entries per pass, k fixed per thread
-          const int k = wtid % 9, kt = (k % 3) * 3 + k / 3;
-#pragma unroll 3
-          for (int hh = wtid / 9; hh < cnt; hh += WT / 9) {
-            const double v = sK[hh * 9 + k];
-            vals[(int64_t)sPos[base + hh] * 9 + k] = v;
-            const int tp = sTpos[base + hh];
-            if (tp >= 0) vals[(int64_t)tp * 9 + kt] = v;
+        for (int k = 0; k < 9; ++k) myK[lane * 9 + k] = K[k];
+        __syncwarp();
+        const int cnt = min(32, nd - base);
+        if (!(dbg & 1)) {
+          int k = lane % 9, hh = lane / 9;
+#pragma unroll 1
+          for (int i = 0; i < 9; ++i) {
+            if (hh < cnt) {
+              const double v = myK[32 * i + lane];
+              vals[(int64_t)sPos[base + hh] * 9 + k] = v;
+              const int tp = sTpos[base + hh];
+              if (tp >= 0) vals[(int64_t)tp * 9 + (k % 3) * 3 + k / 3] = v;
+            }
+            k += 5; hh += 3;                           // value index + 32 = 3 blocks + 5 entries
+            if (k >= 9) { k -= 9; hh += 1; }
           }
         }
-        bar_sync(BAR_WRITER, WT);
       }
       if (it + 2 < n_it) {
         __threadfence_block();
