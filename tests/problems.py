@@ -77,3 +77,31 @@ def device_for(p, penalty=False, quadrature_degree=6):
         blocks = np.nonzero(on)[0]
         d.set_strong_bc(np.sort((3 * blocks[:, None] + np.arange(3)[None, :]).ravel()))
     return d
+
+
+def scordelis_lo_roof(n, skew=0.12):
+    """Scordelis-Lo roof (MacNeal & Harder 1985): cylindrical shell R = 25, L = 50, 80 degrees, t = 0.25, E = 4.32e8, nu = 0,
+    gravity 90 per unit area, rigid diaphragms at the curved ends (u_x = u_z = 0); reference vertical displacement at the
+    middle of the free edge 0.3024.  The FULL roof with n x n quads; `skew` (radians) bends the axial mesh lines sideways by
+    skew * (1 - (phi/phi0)^2) * sin(2 pi y / L): the four vertices of a quad then lie on four different generators of the
+    cylinder and the quad is out of plane (warped cells: per-point frames, dE2/dX terms), while the boundary, the crown
+    mid-point and the free-edge mid-point stay where they are.  (Shifting nodes ALONG the axis would not do: two pairs of
+    vertices on two parallel generators are always coplanar.)  Returns a dict like make_problem plus
+    `bc_dofs(block_coords, nq2)` and the sampling point."""
+    from oracle.rm_shell_ref import plate_mesh
+    R, L, phi0 = 25.0, 50.0, np.deg2rad(40.0)
+    P, quads = plate_mesh(n, n, 2.0 * phi0, L)              # parameter space (phi + phi0, y)
+    phi, y = P[:, 0] - phi0, P[:, 1]
+    phi = phi + skew * (1.0 - (phi / phi0) ** 2) * np.sin(2.0 * np.pi * y / L)
+    nodes = np.stack([R * np.sin(phi), y, R * np.cos(phi)], 1)
+    nn = nodes.shape[0]
+
+    def bc_dofs(xb, nq2):
+        ends = np.nonzero((np.abs(xb[:nq2, 1]) < 1e-9) | (np.abs(xb[:nq2, 1] - L) < 1e-9))[0]
+        crown = int(np.argmin(np.abs(xb[:nq2, 0]) + np.abs(xb[:nq2, 1] - 0.5 * L)))
+        # diaphragms: u_x = u_z = 0; one u_y at the crown mid-point takes out the rigid translation along the axis
+        return np.unique(np.concatenate([3 * ends, 3 * ends + 2, [3 * crown + 1]]).astype(np.int64))
+
+    return dict(nodes=nodes, quads=quads, thickness=np.full(nn, 0.25), E=np.full(nn, 4.32e8), nu=np.zeros(nn),
+                density=np.ones(nn), F_solid=np.tile([0.0, 0.0, -90.0], nn), bc_dofs=bc_dofs,
+                free_edge_mid=np.array([R * np.sin(phi0), 0.5 * L, R * np.cos(phi0)]), reference=0.3024)

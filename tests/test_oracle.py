@@ -157,6 +157,33 @@ def test_navier_simply_supported_plate():
     assert abs(w[3 * centre + 2] / (w_navier + w_shear) - 1.0) < 2e-3, (w[3 * centre + 2], w_navier)
 
 
+def test_scordelis_lo_roof_on_warped_cells():
+    """Third physical pin, the one for CURVED geometry (the reference's own use case, kinematics.py:54-82): the Scordelis-Lo
+    roof, vertical displacement 0.3024 at the middle of the free edge (MacNeal & Harder 1985).  The mesh lines are skewed
+    so that every quad is genuinely non-planar -- per-point frames and the dE2/dX bending terms take part -- and the
+    answer must not care: 8 x 8 quads give 0.249, 16 x 16 give 0.297 (1.9 % below, converging from below like every
+    faceted displacement model of this roof; 24 x 24: 0.300)."""
+    from oracle.rm_shell_ref import RMShellOracle
+    from tests.problems import scordelis_lo_roof
+    got = {}
+    for n in (8, 16):
+        p = scordelis_lo_roof(n)
+        x = p["nodes"][p["quads"]]
+        nrm = np.cross(x[:, 1] - x[:, 0], x[:, 3] - x[:, 0])
+        off = np.abs(np.einsum("ci,ci->c", x[:, 2] - x[:, 0], nrm)) / np.linalg.norm(nrm, axis=1)
+        assert (off > 1e-4).mean() > 0.9                          # (nearly) every cell is out of plane
+        o = RMShellOracle(p["nodes"], p["quads"], False, False)
+        o.set_inputs(**{k: p[k] for k in ("thickness", "E", "nu", "density", "F_solid")})
+        xb = o.topo.block_coords()
+        o.bc_dofs = p["bc_dofs"](xb, o.topo.nq2)
+        w = o.solve_state()
+        node = int(np.argmin(np.linalg.norm(xb[:o.topo.nq2] - p["free_edge_mid"], axis=1)))
+        got[n] = -w[3 * node + 2]
+    ref = 0.3024
+    assert abs(got[16] / ref - 1.0) < 0.025, got
+    assert abs(got[16] - ref) < 0.25 * abs(got[8] - ref), got     # second-order convergence towards the reference
+
+
 def test_sympy_differentiation_of_the_energy_matches_the_hand_derived_element():
     """K_e, R_e and dR_e/dh of one distorted, WARPED cell with uhat != 0, derived by SymPy from the literal energy
     density (oracle/sympy_check.py: every derivative is a sympy.diff result, the dE2/dX terms of the bending strain
