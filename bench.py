@@ -277,7 +277,9 @@ def warped_metric(n, device, steps=5):
       ruled          z = 0.05 sin(pi x / 10), SURVEY's variant: a ruled surface -- every cell is planar but has its own
                      frame, so the tiled kernel runs with per-contribution rotations;
       doubly_curved  z = 0.05 sin(pi x / 10) sin(pi y / 10): every cell is genuinely warped (per-point frames and the
-                     dE2/dX bending terms of kinematics.py:54-82) -- the general kernel."""
+                     dE2/dX bending terms of kinematics.py:54-82) -- the cell-centric warped kernels;
+      wingbox_x16 / wingbox_x64   the reference's wing-box mesh of config 2 (tests/golden/wingbox_mesh.npz: warped cells,
+                     T-junctions) subdivided twice / three times, element-wise material."""
     import torch
     from femo_alpha_b200.shell_device import ShellDevice
     peak, _ = measured_peaks()
@@ -309,6 +311,37 @@ def warped_metric(n, device, steps=5):
             d.close()
         except Exception as e:                      # reported, never hidden
             out[name] = {"error": "%s: %s" % (type(e).__name__, e)}
+    # the reference's own wing-box mesh (config 2: every cell warped, T-junctions), subdivided x16 and x64
+    try:
+        from femo_alpha_b200.multigrid import refine_quads
+        m = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "wingbox_mesh.npz"))
+        mesh = (m["nodes"], m["quads"].astype(np.int32))
+        for level in (1, 2, 3):
+            mesh = refine_quads(*mesh)
+            if level < 2:
+                continue
+            nodes, quads = mesh
+            nc = quads.shape[0]
+            d = ShellDevice(nodes, quads, True, False, device=device)
+            hh = 0.05 * 0.0254
+            d.set_input("E", np.full(nc, 73.1e9)); d.set_input("nu", np.full(nc, 0.33))
+            ts = []
+            for i in range(3 + steps):
+                d.set_input("thickness", np.full(nc, hh * (1.0 + 1e-3 * (i % 2))))
+                d.assemble_jacobian()
+                t = d.last_timings()
+                if i >= 3:
+                    ts.append(t["records_ms"] + t["gather_ms"])
+            t_ms = float(np.mean(ts))
+            ach = CELL_BYTES * d.nc / (t_ms * 1e-3) / 1e9
+            out["wingbox_x%d" % 4 ** level] = dict(
+                all_planar=int(d.sizes.all_planar), kernel="k_warped_elem + k_warped_gather", n_cells=int(nc), n_dof=int(d.ndof),
+                ms_per_assembly=t_ms, value=d.ndof / (t_ms * 1e-3) / 1e9, unit="GDOF/s",
+                roofline=dict(bound="hbm", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak,
+                              algorithmic_bytes_per_launch=CELL_BYTES * d.nc))
+            d.close()
+    except Exception as e:
+        out["wingbox"] = {"error": "%s: %s" % (type(e).__name__, e)}
     return out
 
 
