@@ -45,7 +45,7 @@ for sec in "$@"; do
       timeout 600 python -m pytest tests/test_gpu_dist.py -m gpu -q --tb=short -s -k hexahedral > gpurun_out/${T}_pytest_gpu_disthex.log 2>&1; echo "pytest disthex rc=$?"; grep -E "^rank|passed|failed|xfailed|xpassed|Error|error" gpurun_out/${T}_pytest_gpu_disthex.log | tail -n 12 ;;
     hexscale)
       # weak scaling of config 5 (needs `gpurun --gpus N`, N = NGPU)
-      timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node ${NGPU:-2} --master-addr 127.0.0.1 --master-port 29561 scripts/hex_bench_dist.py --n ${HEX_N:-128} --out gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.json > gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.log 2>&1; echo "hex scale rc=$?"; tail -n 4 gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.log ;;
+      timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node ${NGPU:-2} --master-addr 127.0.0.1 --master-port 29561 scripts/hex_bench_dist.py --cells ${HEX_N:-128} --out gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.json > gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.log 2>&1; echo "hex scale rc=$?"; tail -n 4 gpurun_out/${T}_hex_bench_${NGPU:-2}gpu.log ;;
     pending)
       # everything DESIGN 15 lists as written but not yet run on hardware (1 GPU): the xfail-marked tests report XPASS when green
       timeout 900 python -m pytest tests/test_gpu_hex.py tests/test_gpu_shape.py tests/test_gpu_golden.py -m gpu -q --tb=short -rxX -s -k "gradient_records or penalty_shape or golden_hexahedral" > gpurun_out/${T}_pytest_pending.log 2>&1; echo "pytest pending rc=$?"; grep -E "gradient records:|rel.err|XPASS|XFAIL|passed|failed|xfailed|xpassed" gpurun_out/${T}_pytest_pending.log | tail -n 14

@@ -2,11 +2,13 @@
 elasticity.  Launch with torchrun, one process per GPU:
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29561 \\
-        scripts/hex_bench_dist.py --n 128 [--reps 5] [--krylov-iters 50] [--out FILE]
+        scripts/hex_bench_dist.py --cells 128 [--reps 5] [--krylov-iters 50] [--out FILE]
 
 Assembly is owner-computes (no collective); the PCG iteration exchanges one halo plane per neighbour and all-reduces two
 scalar pairs (NCCL inside libfemo_b200).  Times are CUDA-event times inside the library, maximum over the ranks; rank 0
-prints one JSON line.  NOT YET RUN ON HARDWARE."""
+prints one JSON line.  The N-GPU parity of the same path is tests/test_gpu_dist.py::test_multi_gpu_hexahedral_solid_matches_oracle
+(green at 2 and 3 GPUs); this timing script itself has not had its hardware run (the round's GPU budget ended on a
+command-line mistake: torchrun rejects `--n`)."""
 import argparse
 import json
 import os
@@ -19,7 +21,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=128)
+    ap.add_argument("--cells", "--n", dest="n", type=int, default=128,
+                    help="cells per edge and rank (use --cells under torchrun: Python 3.12 argparse takes --n for an abbreviation of its own options)")
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--krylov-iters", type=int, default=50)
     ap.add_argument("--out", default=None)
